@@ -1,0 +1,84 @@
+// C-ABI entry points that are not tied to the PFPN engine handle: library bookkeeping and the
+// stand-alone convolution call (used by the parity tests and by layer-level callers).
+#include "../../include/pyrapose_b200.h"
+#include "conv_igemm.h"
+#include "errors.h"
+#include "launch_count.h"
+
+#include <atomic>
+
+namespace ppb {
+
+char* last_error_buffer() {
+  static thread_local char buf[kLastErrorSize] = {0};
+  return buf;
+}
+
+std::atomic<long long> g_launches{0};
+
+// Fills the segment/tap tables for a stride-1 ksize x ksize 'same' convolution over one padded-flat plane set.
+void conv_fill_single_seg(ConvParams& p, int batch, int h, int w, int ksize) {
+  p.n_segs = 1;
+  ConvSeg& s = p.seg[0];
+  s.row_begin = 0;
+  s.hp = h + 2;
+  s.wp = w + 2;
+  s.pad = 1;
+  s.rows = batch * s.hp * s.wp;
+  s.tile_begin = 0;
+  s.loc_base = 0;
+  p.n_taps = ksize * ksize;
+  const int half = ksize / 2;
+  for (int r = 0; r < ksize; ++r)
+    for (int c = 0; c < ksize; ++c) s.tap_off[r * ksize + c] = (r - half) * s.wp + (c - half);
+  p.n_mtiles = (s.rows + kConvBlockM - 1) / kConvBlockM;
+}
+
+int conv_pick_block_n(int cout_pad) {
+  if (cout_pad <= kConvMaxBlockN) return cout_pad;
+  if (cout_pad % 256 == 0) return 256;
+  if (cout_pad % 128 == 0) return 128;
+  return 64;
+}
+
+}  // namespace ppb
+
+using namespace ppb;
+
+extern "C" {
+
+int ppb_version(void) { return 100; }
+
+const char* ppb_last_error(void) { return last_error_buffer(); }
+
+long long ppb_launch_count(void) { return g_launches.load(); }
+
+int ppb_conv2d_bf16(const void* x, const void* weight, const float* bias, const void* residual, void* y, int batch,
+                    int h, int w, int cin, int cout, int ksize, int relu, void* stream) {
+  PPB_REQUIRE(x != nullptr && weight != nullptr && y != nullptr, "ppb_conv2d_bf16: null buffer");
+  PPB_REQUIRE(batch > 0 && h > 0 && w > 0, "ppb_conv2d_bf16: bad shape batch=%d h=%d w=%d", batch, h, w);
+  PPB_REQUIRE(ksize == 1 || ksize == 3, "ppb_conv2d_bf16: ksize must be 1 or 3, got %d", ksize);
+  PPB_REQUIRE(cin > 0 && cin % kConvBlockK == 0, "ppb_conv2d_bf16: cin must be a multiple of 64, got %d", cin);
+  PPB_REQUIRE(cout > 0 && cout % 16 == 0, "ppb_conv2d_bf16: cout must be a multiple of 16, got %d", cout);
+  ConvParams p = {};
+  conv_fill_single_seg(p, batch, h, w, ksize);
+  p.cin_blocks = cin / kConvBlockK;
+  p.n_valid = cout;
+  p.block_n = conv_pick_block_n(cout);
+  p.n_ntiles = (cout + p.block_n - 1) / p.block_n;
+  p.epi = kEpiBf16;
+  p.relu = relu;
+  p.bias = bias;
+  p.residual = static_cast<const __nv_bfloat16*>(residual);
+  p.res_ld = cout;
+  p.out = static_cast<__nv_bfloat16*>(y);
+  p.out_ld = cout;
+  CUtensorMap ta, tb;
+  const int rc = conv_encode_tmaps(&ta, &tb, x, p.seg[0].rows, cin, cin, weight, cout, ksize * ksize * cin, p.block_n);
+  if (rc != 0) return fail(kErrCuda, "ppb_conv2d_bf16: cuTensorMapEncodeTiled failed (%d)", rc);
+  PPB_CUDA(conv_launch(ta, tb, p, 0, static_cast<cudaStream_t>(stream)));
+  count_launch();
+  return kOk;
+}
+
+}  // extern "C"

@@ -1,0 +1,81 @@
+// Internal interface of the tcgen05 implicit-GEMM convolution (shared by api.cu and engine.cu).
+//
+// Data layout ("padded-flat"): an NHWC bf16 activation at resolution HxW is stored as a 2-D matrix
+// [B*(H+2)*(W+2), C] whose one-pixel border is kept at zero. A 3x3 stride-1 'same' convolution then
+// is nine shifted GEMMs over the SAME matrix: tap (r,s) reads rows m + (r-1)*(W+2) + (s-1). Every A
+// tile is therefore one plain 2-D TMA box {64 channels x 128 rows}; rows that fall outside the
+// matrix are zero-filled by TMA. Outputs computed at border positions are written as zeros, which
+// re-establishes the invariant for the next layer. Stride-2 convolutions run on four parity planes
+// (space-to-depth) stored back to back in one matrix, so their taps are row offsets as well.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ppb {
+
+constexpr int kConvBlockM = 128;
+constexpr int kConvBlockK = 64;
+constexpr int kConvMaxBlockN = 256;
+constexpr int kConvMaxTaps = 9;
+constexpr int kConvMaxSegs = 3;
+
+enum ConvEpilogue : int {
+  kEpiBf16 = 0,     // bias (+residual) (+ReLU) -> bf16, same row geometry as the input matrix
+  kEpiHeadRaw = 1,  // bias -> fp32 [B, locs, vals]            (training-model '3Dbox' output)
+  kEpiHeadSigmoid = 2,  // bias, sigmoid -> fp32 [B, locs, vals]   ('cls' and 'mask' outputs)
+  kEpiHeadDecode = 3,   // bias, box3D_transform_inv against in-kernel anchors -> fp32 [B, locs*A, 16]
+};
+
+// One pyramid level (or the only plane) of the row space the M tiles walk over.
+struct ConvSeg {
+  int row_begin;   // first row in the A / output matrix; multiple of 128
+  int rows;        // valid rows = B*hp*wp
+  int hp, wp;      // plane geometry including the border
+  int pad;         // border width: 1 (padded-flat) or 0 (plain rows, every row is an output)
+  int tile_begin;  // index of this segment's first M tile
+  int loc_base;    // head epilogues: first location index of this level inside one image
+  int tap_off[kConvMaxTaps];  // signed row offset of each filter tap
+};
+
+struct ConvParams {
+  int n_segs;
+  ConvSeg seg[kConvMaxSegs];
+  int n_taps;
+  int cin_blocks;   // Cin / 64
+  int n_valid;      // Cout (columns beyond it are padding)
+  int block_n;      // UMMA N of one tile: multiple of 16, <= 256
+  int n_ntiles;
+  int n_mtiles;     // over all segments
+  int epi;          // ConvEpilogue
+  int relu;
+  const float* bias;              // [n_valid] fp32, BatchNorm folded in; may be null
+  const __nv_bfloat16* residual;  // kEpiBf16: added before ReLU; row stride res_ld; may be null
+  int res_ld;
+  __nv_bfloat16* out;             // kEpiBf16
+  int out_ld;
+  float* out_f32;                 // head epilogues
+  float* out_hull;                // kEpiHeadDecode: optional [B, locs*A, 4] axis-aligned hull of the 8 corners
+  int locs_per_image;             // sum over levels of H*W
+  int vals_per_loc;               // A*16, A*C or C
+  float anchor[kConvMaxSegs][9][4];  // kEpiHeadDecode: fp32 base anchors per level (Anchors layer)
+  float stride[kConvMaxSegs];
+  float dec_mean[16], dec_std[16];
+};
+
+// Encodes the two TMA descriptors for one convolution. a_rows x a_cols is the activation matrix
+// (bf16, row stride a_ld elements); w is [w_rows, w_cols] bf16 row-major (Cout_pad x taps*Cin).
+int conv_encode_tmaps(CUtensorMap* tmap_a, CUtensorMap* tmap_b, const void* a, long a_rows, int a_cols, int a_ld,
+                      const void* w, int w_rows, int w_cols, int block_n);
+
+// Launches the persistent kernel on `stream` with at most `max_ctas` CTAs (0 = one per SM).
+cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const ConvParams& p, int max_ctas,
+                        cudaStream_t stream);
+
+// Reads (and clears) the fault record a kernel leaves before trapping on a barrier timeout.
+void conv_read_fault(unsigned int out[4]);
+
+int conv_num_sms();
+
+}  // namespace ppb
