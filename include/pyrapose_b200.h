@@ -53,6 +53,88 @@ PPB_API long long ppb_launch_count(void);
 PPB_API int ppb_conv2d_bf16(const void* x, const void* weight, const float* bias, const void* residual, void* y,
                             int batch, int h, int w, int cin, int cout, int ksize, int relu, void* stream);
 
+/* ------------------------------------------------------------------ anchor <-> ground-truth IoU (float64, bit-exact)
+ * ppb_compute_overlap_f64 replaces compute_overlap(boxes, query_boxes) -> overlaps
+ * (PyraPose/utils/compute_overlap.pyx:13-53; call sites PyraPose/utils/anchors.py:310, utils/eval.py:201).
+ *   boxes    : f64 [n,4] (boxes_shared=1: one set for every batch item) or [batch,n,4]
+ *   query    : f64 [batch,k,4]
+ *   overlaps : f64 [batch,n,k], fully written
+ */
+PPB_API int ppb_compute_overlap_f64(const double* boxes, const double* query, double* overlaps, long long n, int k,
+                                    int batch, int boxes_shared, void* stream);
+
+/* Fused compute_gt_annotations (PyraPose/utils/anchors.py:290-318) without materialising the matrix.
+ *   query       : f64 [batch,k_max,4]; query_count: i32 [batch] valid boxes per image, or NULL (= k_max)
+ *   argmax      : i64 [batch,n]   (numpy.argmax: first maximum)
+ *   positive    : u8  [batch,n]   max >= positive_overlap
+ *   ignore      : u8  [batch,n]   max >  negative_overlap && !positive
+ *   max_overlap : f64 [batch,n] or NULL
+ */
+PPB_API int ppb_gt_assign_f64(const double* boxes, const double* query, const int* query_count, int n, int k_max,
+                              int batch, int boxes_shared, double negative_overlap, double positive_overlap,
+                              long long* argmax, unsigned char* positive, unsigned char* ignore,
+                              double* max_overlap, void* stream);
+
+/* ------------------------------------------------------------------ anchors
+ * One pyramid level: out[(y*fw + x)*num_base + a] = base[a] + ((x|y)+0.5)*stride.
+ * f64: PyraPose/utils/anchors.py:415-444 (shift), level loop :402-412.
+ * f32: PyraPose/backend/common.py:93-116 as used by the Anchors layer (PyraPose/layers/_misc.py:24-93).
+ * base: [num_base,4] DEVICE (the nine generate_anchors() boxes, computed by the host as anchors.py:447-478 does).
+ */
+PPB_API int ppb_anchors_shift_f64(const double* base, int num_base, int fh, int fw, double stride, double* out,
+                                  void* stream);
+PPB_API int ppb_anchors_shift_f32(const float* base, int num_base, int fh, int fw, float stride, float* out,
+                                  void* stream);
+
+/* ------------------------------------------------------------------ per-anchor decode (layer API)
+ * RegressBoxes3D / DenormBoxes3D -> box3D_transform_inv / box3D_denormalization
+ * (PyraPose/layers/_misc.py:165-256, PyraPose/backend/common.py:25-90).
+ *   anchors : f32 [anchors_per_image,4] (anchors_batched=0) or [batch,anchors_per_image,4]
+ *   deltas  : f32 [batch,anchors_per_image,16];  out: same shape
+ *   hull    : optional f32 [batch,anchors_per_image,4] axis-aligned hull of the 8 decoded corners (or NULL)
+ *   mean_host / std_host : 16 floats on the HOST, or NULL for the defaults 0 / 0.2
+ */
+PPB_API int ppb_box3d_transform_inv_f32(const float* anchors, const float* deltas, float* out, float* hull, int batch,
+                                        long long anchors_per_image, int anchors_batched, const float* mean_host,
+                                        const float* std_host, int denormalize, void* stream);
+/* RegressBoxes -> bbox_transform_inv (PyraPose/layers/_misc.py:118-162, backend/common.py:6-22); 4 values. */
+PPB_API int ppb_bbox_transform_inv_f32(const float* anchors, const float* deltas, float* out, int batch,
+                                       long long anchors_per_image, int anchors_batched, const float* mean_host,
+                                       const float* std_host, void* stream);
+/* ClipBoxes (PyraPose/layers/_misc.py:259-280): x to [0,width], y to [0,height]. boxes f32 [total_boxes,4]. */
+PPB_API int ppb_clip_boxes_f32(const float* boxes, float* out, long long total_boxes, float width, float height,
+                               void* stream);
+
+/* ------------------------------------------------------------------ FilterDetections
+ * Replaces FilterDetections.call / filter_detections (PyraPose/layers/filter_detections.py:21-118, 153-191).
+ *   boxes [batch,n,4], boxes3D [batch,n,16], classification [batch,n,classes]   f32 (boxes*: 16-byte aligned)
+ *   out_boxes [batch,D,4], out_boxes3D [batch,D,16], out_scores [batch,D] f32, out_labels [batch,D] i32,
+ *   out_indices [batch,D] i32 or NULL (selected anchor index, for gathering `other` tensors); all -1 padded.
+ *   workspace: >= ppb_filter_workspace_bytes(...) bytes of device memory. D = max_detections <= 1024.
+ */
+PPB_API size_t ppb_filter_workspace_bytes(int batch, int n, int num_classes, int class_specific, int max_detections);
+PPB_API int ppb_filter_detections(const float* boxes, const float* boxes3D, const float* classification, int batch,
+                                  int n, int num_classes, int class_specific, int nms, float score_threshold,
+                                  float nms_threshold, int max_detections, float* out_boxes, float* out_boxes3D,
+                                  float* out_scores, int* out_labels, int* out_indices, void* workspace,
+                                  size_t workspace_bytes, void* stream);
+/* dst[b,d,:] = indices[b,d] >= 0 ? src[b, indices[b,d], :] : -1   (filter_detections.py:97,108 for `other`). */
+PPB_API int ppb_gather_rows_f32(const float* src, const int* indices, float* dst, int batch, int n,
+                                int max_detections, int row_elems, void* stream);
+
+/* ------------------------------------------------------------------ evaluator vote filter
+ * Replaces `np.where(scores[0,:,c] > thr)` + `boxes3D[0, idx, :]` (PyraPose/utils/linemod_eval.py:317-319, 427-430;
+ * PyraPose_ROS_wrapper/scripts/pyrapose_node.py:584-586, 638, 648).
+ * Step 1: mask u32 [batch,classes,ceil(n/32)] and counts i32 [batch,classes] (counts may be NULL).
+ * Step 2: offsets i64 [batch*classes+1] = exclusive prefix sum of counts (caller computes it);
+ *         indices i64 [total] ascending per (image,class); votes f32 [total,16]; confidence f32 [batch,classes]|NULL.
+ */
+PPB_API int ppb_score_mask(const float* scores, int batch, int n, int num_classes, float threshold, uint32_t* mask,
+                           int* counts, void* stream);
+PPB_API int ppb_vote_gather(const uint32_t* mask, const float* scores, const float* boxes3D, int batch, int n,
+                            int num_classes, const long long* offsets, long long* indices, float* votes,
+                            float* confidence, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,186 @@
+"""fp32 CPU restatement (torch-CPU convolutions) of the reference's PFPN graph — TEST INFRASTRUCTURE ONLY.
+
+PARITY UNPINNED: TensorFlow 2.1.1 / Keras 2.3.1 / keras-resnet 0.1.0 are not installable here and the
+reference has no tests; this follows the model-building code line by line instead:
+  backbone : keras_resnet.models.ResNet50(include_top=False, freeze_bn=True) as called at
+             /root/reference/PyraPose/models/resnet.py:87,110 (architecture restated from keras-resnet 0.1.0
+             models/_2d.py::ResNet50 + blocks/_2d.py::bottleneck_2d: ZeroPad(3)+7x7/2 VALID, BN(eps=1e-5), ReLU,
+             MaxPool 3x3/2 'same'; bottlenecks [3,4,6,3], stride on the first 1x1, ZeroPad(1)+3x3 VALID, no bias)
+  PFPN     : /root/reference/PyraPose/models/retinanet.py:180-214  (__create_sparceFPN)
+  heads    : retinanet.py:9-54 (cls), 57-98 (mask), 101-131 (3D regression); pyramid concat :224-225
+  inference: retinanet.py:302-335 (retinanet_bbox): Anchors + RegressBoxes3D
+Weights come in as a dict keyed "<keras layer name>/<param>" with HWIO kernels (pyrapose_b200.models.spec
+names); this file never creates weights.
+"""
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from . import anchors as oanchors
+from . import decode as odecode
+
+BN_EPS = 1e-5  # keras-resnet BatchNormalization(epsilon=1e-5)
+
+
+def _t(a):
+    return torch.from_numpy(np.ascontiguousarray(a))
+
+
+def _kernel(w, name):
+    return _t(w[name + "/kernel"]).permute(3, 2, 0, 1).contiguous()  # HWIO -> OIHW
+
+
+def tf_same_pad(size, k, stride):
+    """TensorFlow 'SAME': out = ceil(in/stride); total = max((out-1)*stride + k - in, 0); the extra pixel goes
+    to the bottom/right."""
+    out = -(-size // stride)
+    total = max((out - 1) * stride + k - size, 0)
+    return total // 2, total - total // 2
+
+
+def conv_same(x, w, name, stride=1):
+    """keras.layers.Conv2D(padding='same') with bias, NCHW tensors."""
+    k = _kernel(w, name)
+    kh, kw = k.shape[2], k.shape[3]
+    pt, pb = tf_same_pad(x.shape[2], kh, stride)
+    pl, pr = tf_same_pad(x.shape[3], kw, stride)
+    x = F.pad(x, (pl, pr, pt, pb))
+    b = _t(w[name + "/bias"]) if (name + "/bias") in w else None
+    return F.conv2d(x, k, b, stride=stride)
+
+
+def conv_valid_nobias(x, w, name, stride=1, pad=0):
+    """keras-resnet: explicit ZeroPadding2D(pad) then Conv2D(padding='valid', use_bias=False)."""
+    if pad:
+        x = F.pad(x, (pad, pad, pad, pad))
+    return F.conv2d(x, _kernel(w, name), None, stride=stride)
+
+
+def frozen_bn(x, w, name):
+    g = _t(w[name + "/gamma"]).view(1, -1, 1, 1)
+    b = _t(w[name + "/beta"]).view(1, -1, 1, 1)
+    m = _t(w[name + "/moving_mean"]).view(1, -1, 1, 1)
+    v = _t(w[name + "/moving_variance"]).view(1, -1, 1, 1)
+    return (x - m) / torch.sqrt(v + BN_EPS) * g + b
+
+
+def maxpool_same_3x3_s2(x):
+    pt, pb = tf_same_pad(x.shape[2], 3, 2)
+    pl, pr = tf_same_pad(x.shape[3], 3, 2)
+    x = F.pad(x, (pl, pr, pt, pb), value=float("-inf"))
+    return F.max_pool2d(x, 3, 2)
+
+
+def upsample_like(src, target):
+    """UpsampleLike (layers/_misc.py:96-115) -> tf.image.resize(..., NEAREST) in TF 2.1 (half_pixel_centers):
+    src index = min(floor((dst + 0.5) * in / out), in - 1)."""
+    ih, iw = src.shape[2], src.shape[3]
+    oh, ow = target.shape[2], target.shape[3]
+    ys = torch.clamp(torch.floor((torch.arange(oh, dtype=torch.float32) + 0.5) * (ih / oh)).long(), max=ih - 1)
+    xs = torch.clamp(torch.floor((torch.arange(ow, dtype=torch.float32) + 0.5) * (iw / ow)).long(), max=iw - 1)
+    return src[:, :, ys][:, :, :, xs]
+
+
+def resnet50(x, w, taps=None):
+    """Returns [C2, C3, C4, C5] (NCHW)."""
+    x = conv_valid_nobias(x, w, "conv1", stride=2, pad=3)
+    x = torch.relu(frozen_bn(x, w, "bn_conv1"))
+    if taps is not None:
+        taps["conv1_relu"] = x
+    x = maxpool_same_3x3_s2(x)
+    if taps is not None:
+        taps["pool1"] = x
+    outs = []
+    for stage, blocks in enumerate([3, 4, 6, 3]):
+        for block in range(blocks):
+            tag = "%d%s" % (stage + 2, chr(ord("a") + block))
+            stride = 2 if (block == 0 and stage > 0) else 1
+            y = conv_valid_nobias(x, w, "res%s_branch2a" % tag, stride=stride)
+            y = torch.relu(frozen_bn(y, w, "bn%s_branch2a" % tag))
+            y = conv_valid_nobias(y, w, "res%s_branch2b" % tag, pad=1)
+            y = torch.relu(frozen_bn(y, w, "bn%s_branch2b" % tag))
+            y = conv_valid_nobias(y, w, "res%s_branch2c" % tag)
+            y = frozen_bn(y, w, "bn%s_branch2c" % tag)
+            if block == 0:
+                sc = conv_valid_nobias(x, w, "res%s_branch1" % tag, stride=stride)
+                sc = frozen_bn(sc, w, "bn%s_branch1" % tag)
+            else:
+                sc = x
+            x = torch.relu(y + sc)
+            if taps is not None:
+                taps["res%s_relu" % tag] = x
+        outs.append(x)
+    return outs
+
+
+def sparce_fpn(C3, C4, C5, w, taps=None):
+    """retinanet.py:180-214."""
+    P3 = conv_same(C3, w, "P3_lateral")                       # :192
+    P4 = conv_same(C4, w, "P4_lateral")                       # :193
+    P5 = conv_same(C5, w, "P5_lateral")                       # :194
+    P5_up = upsample_like(P5, P4)                             # :196
+    P4_up = upsample_like(P4, P3)                             # :197
+    P4_mid = conv_same(P5_up + P4, w, "P4_mid")               # :198-199
+    P3_mid = conv_same(P4_up + P3, w, "P3_mid")               # :200-201
+    P3_down = conv_same(P3_mid, w, "P3_down", stride=2)       # :202
+    P3_out = conv_same(P3_mid + P3, w, "P3")                  # :203-204
+    P4_fin = P3_down + P4_mid                                 # :206
+    P4_down = conv_same(P4_mid, w, "P4_down", stride=2)       # :207
+    P4_out = conv_same(P4_fin + P4, w, "P4")                  # :208-209
+    P5_out = conv_same(P4_down + P5, w, "P5")                 # :211-212
+    if taps is not None:
+        taps.update({"P3_lateral": P3, "P4_lateral": P4, "P5_lateral": P5, "P4_mid": P4_mid, "P3_mid": P3_mid,
+                     "P3_down": P3_down, "P4_down": P4_down, "P3": P3_out, "P4": P4_out, "P5": P5_out})
+    return [P3_out, P4_out, P5_out]
+
+
+def _tower(x, w, prefix, out_name):
+    for i in range(4):
+        x = torch.relu(conv_same(x, w, "%s_%d" % (prefix, i)))
+    return conv_same(x, w, out_name)
+
+
+def regression_head(feat, w):
+    """retinanet.py:101-131: NHWC Reshape((-1, 16))."""
+    y = _tower(feat, w, "pyramid_regression3D", "pyramid_regression3D")
+    return y.permute(0, 2, 3, 1).reshape(y.shape[0], -1, 16)
+
+
+def classification_head(feat, w, num_classes):
+    """retinanet.py:9-54: Reshape((-1, C)) then sigmoid."""
+    y = _tower(feat, w, "pyramid_classification", "pyramid_classification")
+    return torch.sigmoid(y.permute(0, 2, 3, 1).reshape(y.shape[0], -1, num_classes))
+
+
+def mask_head(feat, w, num_classes):
+    """retinanet.py:57-98."""
+    y = _tower(feat, w, "mask", "mask_out")
+    return torch.sigmoid(y.permute(0, 2, 3, 1).reshape(y.shape[0], -1, num_classes))
+
+
+def forward_training(images_nhwc, w, num_classes, taps=None, num_threads=None):
+    """retinanet() (retinanet.py:260-299): returns numpy [3Dbox (B,N,16), cls (B,N,C), mask (B,HW/64,C)]."""
+    if num_threads:
+        torch.set_num_threads(num_threads)
+    with torch.no_grad():
+        x = _t(np.asarray(images_nhwc, np.float32)).permute(0, 3, 1, 2).contiguous()
+        _, C3, C4, C5 = resnet50(x, w, taps)
+        feats = sparce_fpn(C3, C4, C5, w, taps)
+        reg = torch.cat([regression_head(f, w) for f in feats], dim=1)                     # :224-225
+        cls = torch.cat([classification_head(f, w, num_classes) for f in feats], dim=1)
+        msk = mask_head(feats[0], w, num_classes)                                           # :296-297
+        shapes = [(int(f.shape[2]), int(f.shape[3])) for f in feats]
+    return reg.numpy(), cls.numpy(), msk.numpy(), shapes
+
+
+def forward_inference(images_nhwc, w, num_classes, anchor_params=None, taps=None, num_threads=None):
+    """retinanet_bbox() (retinanet.py:302-335): [boxes3D (B,N,16), classification (B,N,C), mask]."""
+    reg, cls, msk, shapes = forward_training(images_nhwc, w, num_classes, taps, num_threads)
+    anchors = oanchors.anchors_layer_f32(shapes, anchor_params)
+    anchors = np.broadcast_to(anchors[None], (reg.shape[0],) + anchors.shape)
+    boxes3D = odecode.box3D_transform_inv(anchors, reg)
+    return boxes3D, cls, msk
+
+
+def taps_to_nhwc(taps):
+    return {k: v.permute(0, 2, 3, 1).contiguous().numpy() for k, v in taps.items()}

@@ -1,0 +1,142 @@
+// Per-anchor decode kernels (stand-alone layer API). The engine fuses the same arithmetic into the
+// regression head's epilogue (conv_igemm.cu); these entry points serve RegressBoxes3D / RegressBoxes /
+// DenormBoxes3D / ClipBoxes when they are called as layers on caller-supplied tensors.
+//
+// Reference: PyraPose/backend/common.py:6-22 (bbox_transform_inv), :25-56 (box3D_transform_inv),
+// :59-90 (box3D_denormalization); PyraPose/layers/_misc.py:259-280 (ClipBoxes).
+// Bandwidth-bound: 16 B of anchor + 64 B of deltas read, 64 B written per anchor. Four threads share
+// one anchor, each owning one float4 (x1-,y1-,x2-,y2-based values), so every global access is a fully
+// coalesced 128-bit transaction. Compiled with -fmad=false (TF evaluates mul and add as separate ops).
+#include "../../include/pyrapose_b200.h"
+#include "errors.h"
+#include "launch_count.h"
+
+namespace ppb {
+namespace {
+
+struct Vec16 {
+  float v[16];
+};
+
+// groups = values per anchor / 4 (4 for the 16 corner values, 1 for plain boxes).
+template <int GROUPS, bool DENORM>
+__global__ void __launch_bounds__(256) transform_inv_kernel(const float4* __restrict__ anchors,
+                                                            const float4* __restrict__ deltas,
+                                                            float4* __restrict__ out, float4* __restrict__ hull,
+                                                            long long total_anchors, long long anchors_per_image,
+                                                            int anchors_batched, Vec16 mean, Vec16 stdv) {
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long a = t / GROUPS;
+  const int g = static_cast<int>(t - a * GROUPS);
+  const bool valid = a < total_anchors;  // no early return: the hull reduction below shuffles across lanes
+  const long long a_src = anchors_batched ? a : (a % anchors_per_image);
+  const float4 box = valid ? __ldg(anchors + a_src) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const float4 d = valid ? __ldg(deltas + t) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const float w = box.z - box.x;   // common.py:33
+  const float h = box.w - box.y;   // common.py:34
+  float4 r;
+  r.x = box.x + (d.x * stdv.v[g * 4 + 0] + mean.v[g * 4 + 0]) * w;
+  r.y = box.y + (d.y * stdv.v[g * 4 + 1] + mean.v[g * 4 + 1]) * h;
+  r.z = box.z + (d.z * stdv.v[g * 4 + 2] + mean.v[g * 4 + 2]) * w;
+  r.w = box.w + (d.w * stdv.v[g * 4 + 3] + mean.v[g * 4 + 3]) * h;
+  if (DENORM) {  // common.py:69-84
+    r.x = r.x / 320.0f;
+    r.y = r.y / 240.0f;
+    r.z = r.z / 320.0f;
+    r.w = r.w / 240.0f;
+  }
+  if (valid) out[t] = r;
+  if (GROUPS == 4 && hull != nullptr) {
+    // axis-aligned hull of the 8 corners: min/max over the four threads of this anchor
+    float xmin = fminf(r.x, r.z), xmax = fmaxf(r.x, r.z), ymin = fminf(r.y, r.w), ymax = fmaxf(r.y, r.w);
+#pragma unroll
+    for (int off = 1; off < 4; off <<= 1) {
+      xmin = fminf(xmin, __shfl_xor_sync(0xffffffffu, xmin, off));
+      xmax = fmaxf(xmax, __shfl_xor_sync(0xffffffffu, xmax, off));
+      ymin = fminf(ymin, __shfl_xor_sync(0xffffffffu, ymin, off));
+      ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, off));
+    }
+    if (valid && g == 0) hull[a] = make_float4(xmin, ymin, xmax, ymax);
+  }
+}
+
+__global__ void __launch_bounds__(256) clip_boxes_kernel(const float4* __restrict__ boxes, float4* __restrict__ out,
+                                                         long long total, float width, float height) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  float4 b = __ldg(boxes + i);
+  b.x = fminf(fmaxf(b.x, 0.0f), width);
+  b.y = fminf(fmaxf(b.y, 0.0f), height);
+  b.z = fminf(fmaxf(b.z, 0.0f), width);
+  b.w = fminf(fmaxf(b.w, 0.0f), height);
+  out[i] = b;
+}
+
+Vec16 load16(const float* p, float fill, int n) {
+  Vec16 v;
+  for (int i = 0; i < 16; ++i) v.v[i] = (p != nullptr && i < n) ? p[i] : fill;
+  return v;
+}
+
+}  // namespace
+}  // namespace ppb
+
+using namespace ppb;
+
+extern "C" {
+
+int ppb_box3d_transform_inv_f32(const float* anchors, const float* deltas, float* out, float* hull, int batch,
+                                long long anchors_per_image, int anchors_batched, const float* mean_host,
+                                const float* std_host, int denormalize, void* stream) {
+  PPB_REQUIRE(batch >= 0 && anchors_per_image >= 0, "ppb_box3d_transform_inv_f32: bad sizes");
+  const long long total = static_cast<long long>(batch) * anchors_per_image;
+  if (total == 0) return kOk;
+  PPB_REQUIRE(anchors != nullptr && deltas != nullptr && out != nullptr, "ppb_box3d_transform_inv_f32: null buffer");
+  const Vec16 mean = load16(mean_host, 0.0f, 16), stdv = load16(std_host, 0.2f, 16);
+  const unsigned blocks = static_cast<unsigned>((total * 4 + 255) / 256);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (denormalize)
+    transform_inv_kernel<4, true><<<blocks, 256, 0, st>>>(
+        reinterpret_cast<const float4*>(anchors), reinterpret_cast<const float4*>(deltas),
+        reinterpret_cast<float4*>(out), reinterpret_cast<float4*>(hull), total, anchors_per_image, anchors_batched,
+        mean, stdv);
+  else
+    transform_inv_kernel<4, false><<<blocks, 256, 0, st>>>(
+        reinterpret_cast<const float4*>(anchors), reinterpret_cast<const float4*>(deltas),
+        reinterpret_cast<float4*>(out), reinterpret_cast<float4*>(hull), total, anchors_per_image, anchors_batched,
+        mean, stdv);
+  PPB_CUDA(cudaGetLastError());
+  count_launch();
+  return kOk;
+}
+
+int ppb_bbox_transform_inv_f32(const float* anchors, const float* deltas, float* out, int batch,
+                               long long anchors_per_image, int anchors_batched, const float* mean_host,
+                               const float* std_host, void* stream) {
+  PPB_REQUIRE(batch >= 0 && anchors_per_image >= 0, "ppb_bbox_transform_inv_f32: bad sizes");
+  const long long total = static_cast<long long>(batch) * anchors_per_image;
+  if (total == 0) return kOk;
+  PPB_REQUIRE(anchors != nullptr && deltas != nullptr && out != nullptr, "ppb_bbox_transform_inv_f32: null buffer");
+  const Vec16 mean = load16(mean_host, 0.0f, 4), stdv = load16(std_host, 0.2f, 4);
+  transform_inv_kernel<1, false><<<static_cast<unsigned>((total + 255) / 256), 256, 0,
+                                   static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const float4*>(anchors), reinterpret_cast<const float4*>(deltas),
+      reinterpret_cast<float4*>(out), nullptr, total, anchors_per_image, anchors_batched, mean, stdv);
+  PPB_CUDA(cudaGetLastError());
+  count_launch();
+  return kOk;
+}
+
+int ppb_clip_boxes_f32(const float* boxes, float* out, long long total_boxes, float width, float height,
+                       void* stream) {
+  PPB_REQUIRE(total_boxes >= 0, "ppb_clip_boxes_f32: bad size");
+  if (total_boxes == 0) return kOk;
+  PPB_REQUIRE(boxes != nullptr && out != nullptr, "ppb_clip_boxes_f32: null buffer");
+  clip_boxes_kernel<<<static_cast<unsigned>((total_boxes + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const float4*>(boxes), reinterpret_cast<float4*>(out), total_boxes, width, height);
+  PPB_CUDA(cudaGetLastError());
+  count_launch();
+  return kOk;
+}
+
+}  // extern "C"

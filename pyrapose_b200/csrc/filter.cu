@@ -1,0 +1,622 @@
+// Score thresholding, per-class NMS, top-k and -1 padding on the GPU.
+//
+// Replaces (a) FilterDetections / filter_detections (PyraPose/layers/filter_detections.py:21-118, 121-234:
+// tf.where -> tf.image.non_max_suppression -> concat -> tf.nn.top_k -> gather -> tf.pad(-1)) and (b) the
+// evaluators' host-side vote filter (PyraPose/utils/linemod_eval.py:307-334, 427-430).
+//
+// Pipeline (all device-resident, no host round trip for the FilterDetections path):
+//   class_max_kernel   (class_specific_filter=False only) max / argmax over classes
+//   score_mask_kernel  the only bandwidth-relevant pass: reads the (B, N, C) scores once, coalesced through
+//                      shared memory, and emits one bit per score (warp ballot) -> mask[B][C][ceil(N/32)]
+//   compact_keys_kernel  per (image, class): popc scan over the mask words -> ascending candidate list,
+//                      emitted directly as 64-bit sort keys  (~orderable(score) << 32 | anchor index)
+//   sort_keys_kernel   per (image, class) bitonic sort (shared memory up to 4096 keys, global beyond)
+//   nms_kernel         greedy NMS in score order, TensorFlow semantics (IoU > thr suppresses, no "+1",
+//                      min/max-normalised corners, area <= 0 -> 0, stop at max_detections), float32, no FMA
+//   topk_pad_kernel    per image: merge the per-class survivors, top-k by score (ties -> lower position),
+//                      gather boxes / boxes3D / labels, pad with -1
+// Compiled with -fmad=false so the IoU arithmetic rounds exactly like the reference's.
+#include "../../include/pyrapose_b200.h"
+#include "errors.h"
+#include "launch_count.h"
+
+#include <stdint.h>
+
+namespace ppb {
+namespace {
+
+constexpr int kSortSmemKeys = 4096;
+constexpr int kTopkSmemKeys = 16384;
+constexpr int kMaxDetCap = 1024;
+constexpr int kNmsChunk = 256;
+
+// Monotone map float -> uint32 (ascending order preserved, -0 < +0 irrelevant here).
+__device__ __forceinline__ uint32_t orderable(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+// Key whose ASCENDING order is (score descending, index ascending).
+__device__ __forceinline__ uint64_t make_key(float score, uint32_t idx) {
+  return (static_cast<uint64_t>(~orderable(score)) << 32) | idx;
+}
+
+__host__ __device__ inline int next_pow2(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+// Exclusive block scan of one int per thread (blockDim.x <= 1024); returns the block total in `total`.
+__device__ __forceinline__ int block_exclusive_scan(int v, int* warp_sums, int& total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int incl = v;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const int n = __shfl_up_sync(0xffffffffu, incl, off);
+    if (lane >= off) incl += n;
+  }
+  if (lane == 31) warp_sums[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    const int nw = (blockDim.x + 31) >> 5;
+    int s = lane < nw ? warp_sums[lane] : 0;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, s, off);
+      if (lane >= off) s += n;
+    }
+    warp_sums[lane] = s;  // inclusive warp totals
+  }
+  __syncthreads();
+  const int nw = (blockDim.x + 31) >> 5;
+  total = warp_sums[nw - 1];
+  const int warp_off = warp == 0 ? 0 : warp_sums[warp - 1];
+  const int res = warp_off + incl - v;
+  __syncthreads();  // warp_sums may be reused by the caller's next scan
+  return res;
+}
+
+// ------------------------------------------------------------------ class max / argmax
+// filter_detections.py:83-84 (keras.backend.max / argmax over axis 1; first maximum wins).
+__global__ void __launch_bounds__(256) class_max_kernel(const float* __restrict__ cls, long long total, int C,
+                                                        float* __restrict__ smax, int* __restrict__ sarg) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const float* p = cls + i * C;
+  float best = p[0];
+  int arg = 0;
+  for (int c = 1; c < C; ++c) {
+    const float v = p[c];
+    if (v > best) {
+      best = v;
+      arg = c;
+    }
+  }
+  smax[i] = best;
+  sarg[i] = arg;
+}
+
+// ------------------------------------------------------------------ score -> bit mask
+// grid (ceil(N/TILE), B), 256 threads. mask[(b*C + c)*W + n/32] bit (n%32) = scores[b, n, c] > thr.
+template <int TILE>
+__global__ void __launch_bounds__(256) score_mask_kernel(const float* __restrict__ scores, int N, int C, float thr,
+                                                         uint32_t* __restrict__ mask, int W) {
+  extern __shared__ float tile[];  // [TILE][C]
+  const int b = blockIdx.y;
+  const int n0 = blockIdx.x * TILE;
+  const int rows = min(TILE, N - n0);
+  const long long base = (static_cast<long long>(b) * N + n0) * C;
+  const int elems = rows * C;
+  const float* src = scores + base;
+  if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+    const int vec = elems >> 2;
+    const float4* s4 = reinterpret_cast<const float4*>(src);
+    for (int i = threadIdx.x; i < vec; i += 256) reinterpret_cast<float4*>(tile)[i] = __ldg(s4 + i);
+    for (int i = (vec << 2) + threadIdx.x; i < elems; i += 256) tile[i] = __ldg(src + i);
+  } else {
+    for (int i = threadIdx.x; i < elems; i += 256) tile[i] = __ldg(src + i);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int kGroups = TILE / 32;
+  const int items = kGroups * C;
+  for (int it = warp; it < items; it += 8) {
+    const int g = it / C;
+    const int c = it - g * C;
+    const int r = g * 32 + lane;
+    const bool pass = r < rows && tile[r * C + c] > thr;
+    const uint32_t word = __ballot_sync(0xffffffffu, pass);
+    const int widx = (n0 >> 5) + g;
+    if (lane == 0 && widx < W) mask[(static_cast<long long>(b) * C + c) * W + widx] = word;
+  }
+}
+
+// ------------------------------------------------------------------ mask -> counts (vote path)
+__global__ void __launch_bounds__(256) mask_count_kernel(const uint32_t* __restrict__ mask, int W,
+                                                         int* __restrict__ counts) {
+  __shared__ int warp_sums[32];
+  const uint32_t* words = mask + static_cast<long long>(blockIdx.x) * W;
+  int c = 0;
+  for (int i = threadIdx.x; i < W; i += 256) c += __popc(words[i]);
+  int total;
+  block_exclusive_scan(c, warp_sums, total);
+  if (threadIdx.x == 0) counts[blockIdx.x] = total;
+}
+
+// ------------------------------------------------------------------ mask -> sorted-key candidates
+// grid (C, B). keys segment of (b,c) starts at (b*C+c)*cap. scores index: (b*N + n)*score_stride + c*class_step.
+__global__ void __launch_bounds__(256) compact_keys_kernel(const uint32_t* __restrict__ mask,
+                                                           const float* __restrict__ scores, int N, int C, int W,
+                                                           int score_stride, int cap, uint64_t* __restrict__ keys,
+                                                           int* __restrict__ counts) {
+  __shared__ int warp_sums[32];
+  const int c = blockIdx.x, b = blockIdx.y;
+  const long long bc = static_cast<long long>(b) * C + c;
+  const uint32_t* words = mask + bc * W;
+  uint64_t* seg = keys + bc * cap;
+  int running = 0;
+  for (int base = 0; base < W; base += 256) {
+    const int wi = base + threadIdx.x;
+    uint32_t w = wi < W ? words[wi] : 0u;
+    int total;
+    int pos = running + block_exclusive_scan(__popc(w), warp_sums, total);
+    while (w) {
+      const int bit = __ffs(w) - 1;
+      w &= w - 1;
+      const uint32_t n = static_cast<uint32_t>(wi) * 32u + bit;
+      const float s = __ldg(scores + (static_cast<long long>(b) * N + n) * score_stride + c);
+      seg[pos++] = make_key(s, n);
+    }
+    running += total;
+  }
+  if (threadIdx.x == 0) counts[bc] = running;
+}
+
+// ------------------------------------------------------------------ vote gather (evaluator path)
+// grid (C, B). Output is CSR: offsets[b*C+c] .. offsets[b*C+c+1] in indices / votes.
+__global__ void __launch_bounds__(256) vote_gather_kernel(const uint32_t* __restrict__ mask,
+                                                          const float* __restrict__ scores,
+                                                          const float* __restrict__ boxes3D, int N, int C, int W,
+                                                          const long long* __restrict__ offsets,
+                                                          long long* __restrict__ indices, float* __restrict__ votes,
+                                                          float* __restrict__ conf) {
+  __shared__ int warp_sums[32];
+  __shared__ float conf_sum[8];
+  const int c = blockIdx.x, b = blockIdx.y;
+  const long long bc = static_cast<long long>(b) * C + c;
+  const uint32_t* words = mask + bc * W;
+  const long long out0 = offsets[bc];
+  int running = 0;
+  float csum = 0.0f;
+  for (int base = 0; base < W; base += 256) {
+    const int wi = base + threadIdx.x;
+    uint32_t w = wi < W ? words[wi] : 0u;
+    int total;
+    int pos = running + block_exclusive_scan(__popc(w), warp_sums, total);
+    while (w) {
+      const int bit = __ffs(w) - 1;
+      w &= w - 1;
+      const long long n = static_cast<long long>(wi) * 32 + bit;
+      const long long row = static_cast<long long>(b) * N + n;
+      csum += __ldg(scores + row * C + c);
+      indices[out0 + pos] = n;
+      const float4* src = reinterpret_cast<const float4*>(boxes3D + row * 16);
+      float4* dst = reinterpret_cast<float4*>(votes + (out0 + pos) * 16);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) dst[q] = __ldg(src + q);
+      ++pos;
+    }
+    running += total;
+  }
+  // confidence = sum of the hit scores (PyraPose_ROS_wrapper/scripts/pyrapose_node.py:638); summation order is
+  // not specified by numpy either, so this value carries a tolerance, not bit-exactness.
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) csum += __shfl_xor_sync(0xffffffffu, csum, off);
+  if ((threadIdx.x & 31) == 0) conf_sum[threadIdx.x >> 5] = csum;
+  __syncthreads();
+  if (threadIdx.x == 0 && conf != nullptr) {
+    float t = 0.0f;
+    for (int i = 0; i < 8; ++i) t += conf_sum[i];
+    conf[bc] = t;
+  }
+}
+
+// ------------------------------------------------------------------ per-segment bitonic sort (ascending)
+__device__ __forceinline__ void bitonic_sort_block(uint64_t* a, int n_pow2) {
+  for (int k = 2; k <= n_pow2; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < n_pow2; i += blockDim.x) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const uint64_t x = a[i], y = a[ixj];
+          const bool up = (i & k) == 0;
+          if ((x > y) == up) {
+            a[i] = y;
+            a[ixj] = x;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// grid (segments), 1024 threads, dynamic smem kSortSmemKeys * 8. Segment s holds counts[s] keys at keys + s*cap;
+// cap is a power of two, so the global fallback can pad in place.
+__global__ void __launch_bounds__(1024) sort_keys_kernel(uint64_t* __restrict__ keys, const int* __restrict__ counts,
+                                                         int cap) {
+  extern __shared__ uint64_t skeys[];
+  const int n = counts[blockIdx.x];
+  if (n <= 1) return;
+  uint64_t* seg = keys + static_cast<long long>(blockIdx.x) * cap;
+  const int np2 = next_pow2(n);
+  if (np2 <= kSortSmemKeys) {
+    for (int i = threadIdx.x; i < np2; i += blockDim.x) skeys[i] = i < n ? seg[i] : ~0ull;
+    __syncthreads();
+    bitonic_sort_block(skeys, np2);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) seg[i] = skeys[i];
+  } else {
+    for (int i = n + threadIdx.x; i < np2; i += blockDim.x) seg[i] = ~0ull;
+    __syncthreads();
+    bitonic_sort_block(seg, np2);
+  }
+}
+
+// ------------------------------------------------------------------ greedy NMS
+struct NBox {
+  float a0, a1, a2, a3, area;  // min/max-normalised corners (TF treats them as y1,x1,y2,x2; symmetric)
+};
+
+__device__ __forceinline__ NBox normalise(const float4 b) {
+  NBox r;
+  r.a0 = fminf(b.x, b.z);
+  r.a1 = fminf(b.y, b.w);
+  r.a2 = fmaxf(b.x, b.z);
+  r.a3 = fmaxf(b.y, b.w);
+  r.area = (r.a2 - r.a0) * (r.a3 - r.a1);
+  return r;
+}
+
+// tensorflow/core/kernels/non_max_suppression_op.cc: IOU(); float32, division last.
+__device__ __forceinline__ bool iou_exceeds(const NBox& i, const NBox& j, float thr) {
+  if (i.area <= 0.0f || j.area <= 0.0f) return 0.0f > thr;
+  const float y0 = fmaxf(i.a0, j.a0), x0 = fmaxf(i.a1, j.a1);
+  const float y1 = fminf(i.a2, j.a2), x1 = fminf(i.a3, j.a3);
+  const float inter = fmaxf(y1 - y0, 0.0f) * fmaxf(x1 - x0, 0.0f);
+  return inter / (i.area + j.area - inter) > thr;
+}
+
+// grid (C, B), 256 threads. Reads the sorted keys of (b,c); writes up to max_det anchor indices in selection
+// order to sel_idx[(b*C+c)*max_det ...] and their number to sel_cnt.
+__global__ void __launch_bounds__(kNmsChunk) nms_kernel(const uint64_t* __restrict__ keys,
+                                                        const int* __restrict__ counts, int cap,
+                                                        const float* __restrict__ boxes, int N, int C, int do_nms,
+                                                        float thr, int max_det, int* __restrict__ sel_idx,
+                                                        int* __restrict__ sel_cnt) {
+  __shared__ NBox sel_box[kMaxDetCap];
+  __shared__ NBox chunk_box[kNmsChunk];
+  __shared__ uint32_t chunk_idx[kNmsChunk];
+  __shared__ uint32_t supp[kNmsChunk][kNmsChunk / 32];
+  __shared__ unsigned char alive_s[kNmsChunk];
+  __shared__ int n_sel_s;
+  const int c = blockIdx.x, b = blockIdx.y;
+  const long long bc = static_cast<long long>(b) * C + c;
+  const uint64_t* seg = keys + bc * cap;
+  int* out = sel_idx + bc * max_det;
+  const int n = counts[bc];
+  const int tid = threadIdx.x;
+  if (!do_nms) {  // filter_detections.py:56: without NMS every thresholded candidate goes to top-k
+    const int m = min(n, max_det);
+    for (int r = tid; r < m; r += blockDim.x) out[r] = static_cast<int>(seg[r] & 0xffffffffu);
+    if (tid == 0) sel_cnt[bc] = m;
+    return;
+  }
+  if (tid == 0) n_sel_s = 0;
+  __syncthreads();
+  for (int cs = 0; cs < n; cs += kNmsChunk) {
+    const int n_sel = n_sel_s;
+    if (n_sel >= max_det) break;
+    const int i = cs + tid;
+    const bool valid = i < n;
+    NBox me = {0.f, 0.f, 0.f, 0.f, 0.f};
+    uint32_t idx = 0;
+    if (valid) {
+      idx = static_cast<uint32_t>(seg[i] & 0xffffffffu);
+      me = normalise(__ldg(reinterpret_cast<const float4*>(boxes) + static_cast<long long>(b) * N + idx));
+    }
+    // phase 1: against boxes selected in earlier chunks
+    bool alive = valid;
+    for (int s = 0; s < n_sel && alive; ++s)
+      if (iou_exceeds(me, sel_box[s], thr)) alive = false;
+    chunk_box[tid] = me;
+    chunk_idx[tid] = idx;
+    alive_s[tid] = alive;
+    __syncthreads();
+    // phase 2: which earlier (higher-scored) members of this chunk would suppress me
+    uint32_t m[kNmsChunk / 32];
+#pragma unroll
+    for (int w = 0; w < kNmsChunk / 32; ++w) m[w] = 0u;
+    if (alive) {
+      for (int j = 0; j < tid; ++j)
+        if (alive_s[j] && iou_exceeds(me, chunk_box[j], thr)) m[j >> 5] |= 1u << (j & 31);
+    }
+#pragma unroll
+    for (int w = 0; w < kNmsChunk / 32; ++w) supp[tid][w] = m[w];
+    __syncthreads();
+    // phase 3: serial greedy resolution inside the chunk
+    if (tid == 0) {
+      uint32_t kept[kNmsChunk / 32];
+#pragma unroll
+      for (int w = 0; w < kNmsChunk / 32; ++w) kept[w] = 0u;
+      int ns = n_sel;
+      const int lim = min(kNmsChunk, n - cs);
+      for (int j = 0; j < lim && ns < max_det; ++j) {
+        if (!alive_s[j]) continue;
+        bool ok = true;
+#pragma unroll
+        for (int w = 0; w < kNmsChunk / 32; ++w) ok = ok && ((supp[j][w] & kept[w]) == 0u);
+        if (ok) {
+          kept[j >> 5] |= 1u << (j & 31);
+          sel_box[ns] = chunk_box[j];
+          out[ns] = static_cast<int>(chunk_idx[j]);
+          ++ns;
+        }
+      }
+      n_sel_s = ns;
+    }
+    __syncthreads();
+  }
+  if (tid == 0) sel_cnt[bc] = n_sel_s;
+}
+
+// ------------------------------------------------------------------ top-k over classes, gather, pad
+// grid (B), 1024 threads, dynamic smem np2*8 (or global scratch when np2 > kTopkSmemKeys).
+// Position p = c*max_det + rank preserves the order of the concatenated per-class lists
+// (filter_detections.py:81), so "ties -> lower position" equals tf.nn.top_k's lower-index rule.
+__global__ void __launch_bounds__(1024) topk_pad_kernel(const int* __restrict__ sel_idx, const int* __restrict__ sel_cnt,
+                                                        int Ceff, int max_det, const float* __restrict__ cls,
+                                                        const int* __restrict__ sarg, int N, int C,
+                                                        const float* __restrict__ boxes,
+                                                        const float* __restrict__ boxes3D, float* __restrict__ out_boxes,
+                                                        float* __restrict__ out_boxes3D, float* __restrict__ out_scores,
+                                                        int* __restrict__ out_labels, int* __restrict__ out_indices,
+                                                        uint64_t* __restrict__ scratch, int np2) {
+  extern __shared__ uint64_t skeys[];
+  __shared__ int total_s;
+  const int b = blockIdx.x;
+  uint64_t* a = np2 <= kTopkSmemKeys ? skeys : scratch + static_cast<long long>(b) * np2;
+  const int slots = Ceff * max_det;
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int c = 0; c < Ceff; ++c) t += sel_cnt[b * Ceff + c];
+    total_s = t;
+  }
+  for (int p = threadIdx.x; p < np2; p += blockDim.x) {
+    uint64_t key = ~0ull;
+    if (p < slots) {
+      const int c = p / max_det;
+      const int r = p - c * max_det;
+      if (r < sel_cnt[b * Ceff + c]) {
+        const int idx = sel_idx[(static_cast<long long>(b) * Ceff + c) * max_det + r];
+        const long long row = static_cast<long long>(b) * N + idx;
+        const int label = sarg != nullptr ? sarg[row] : c;
+        key = make_key(__ldg(cls + row * C + label), static_cast<uint32_t>(p));  // filter_detections.py:88
+      }
+    }
+    a[p] = key;
+  }
+  __syncthreads();
+  bitonic_sort_block(a, np2);
+  const int k = min(max_det, total_s);  // filter_detections.py:90
+  for (int t = threadIdx.x; t < max_det * 16; t += blockDim.x) {
+    const int r = t >> 4, j = t & 15;
+    float v3 = -1.0f;
+    if (r < k) {
+      const int p = static_cast<int>(a[r] & 0xffffffffu);
+      const int c = p / max_det;
+      const int idx = sel_idx[(static_cast<long long>(b) * Ceff + c) * max_det + (p - c * max_det)];
+      const long long row = static_cast<long long>(b) * N + idx;
+      v3 = __ldg(boxes3D + row * 16 + j);
+      if (j < 4) out_boxes[(static_cast<long long>(b) * max_det + r) * 4 + j] = __ldg(boxes + row * 4 + j);
+      if (j == 4) {
+        const int label = sarg != nullptr ? sarg[row] : c;
+        out_scores[static_cast<long long>(b) * max_det + r] = __ldg(cls + row * C + label);
+        out_labels[static_cast<long long>(b) * max_det + r] = label;
+        if (out_indices != nullptr) out_indices[static_cast<long long>(b) * max_det + r] = idx;
+      }
+    } else {  // filter_detections.py:100-107: pad with -1
+      if (j < 4) out_boxes[(static_cast<long long>(b) * max_det + r) * 4 + j] = -1.0f;
+      if (j == 4) {
+        out_scores[static_cast<long long>(b) * max_det + r] = -1.0f;
+        out_labels[static_cast<long long>(b) * max_det + r] = -1;
+        if (out_indices != nullptr) out_indices[static_cast<long long>(b) * max_det + r] = -1;
+      }
+    }
+    out_boxes3D[(static_cast<long long>(b) * max_det + r) * 16 + j] = v3;
+  }
+}
+
+// ------------------------------------------------------------------ generic row gather (FilterDetections `other`)
+__global__ void __launch_bounds__(256) gather_rows_kernel(const float* __restrict__ src, const int* __restrict__ indices,
+                                                          float* __restrict__ dst, int B, int N, int D, int row_elems) {
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long total = static_cast<long long>(B) * D * row_elems;
+  if (t >= total) return;
+  const int e = static_cast<int>(t % row_elems);
+  const long long bd = t / row_elems;
+  const int b = static_cast<int>(bd / D);
+  const int idx = indices[bd];
+  dst[t] = idx >= 0 ? __ldg(src + (static_cast<long long>(b) * N + idx) * row_elems + e) : -1.0f;
+}
+
+struct FilterWorkspace {
+  uint32_t* mask;
+  int* counts;
+  uint64_t* keys;
+  int* sel_idx;
+  int* sel_cnt;
+  float* smax;
+  int* sarg;
+  uint64_t* topk_scratch;
+  size_t bytes;
+};
+
+size_t align256(size_t v) { return (v + 255) & ~static_cast<size_t>(255); }
+
+FilterWorkspace carve(void* base, int B, int N, int C, int class_specific, int max_det) {
+  FilterWorkspace w;
+  const int Ceff = class_specific ? C : 1;
+  const int W = (N + 31) / 32;
+  const size_t cap = next_pow2(N > 0 ? N : 1);
+  size_t off = 0;
+  char* p = static_cast<char*>(base);
+  auto take = [&](size_t bytes) {
+    char* r = p != nullptr ? p + off : nullptr;
+    off += align256(bytes);
+    return r;
+  };
+  w.mask = reinterpret_cast<uint32_t*>(take(static_cast<size_t>(B) * Ceff * W * 4));
+  w.counts = reinterpret_cast<int*>(take(static_cast<size_t>(B) * Ceff * 4));
+  w.keys = reinterpret_cast<uint64_t*>(take(static_cast<size_t>(B) * Ceff * cap * 8));
+  w.sel_idx = reinterpret_cast<int*>(take(static_cast<size_t>(B) * Ceff * max_det * 4));
+  w.sel_cnt = reinterpret_cast<int*>(take(static_cast<size_t>(B) * Ceff * 4));
+  w.smax = reinterpret_cast<float*>(take(class_specific ? 0 : static_cast<size_t>(B) * N * 4));
+  w.sarg = reinterpret_cast<int*>(take(class_specific ? 0 : static_cast<size_t>(B) * N * 4));
+  const int np2 = next_pow2(Ceff * max_det);
+  w.topk_scratch = reinterpret_cast<uint64_t*>(take(np2 > kTopkSmemKeys ? static_cast<size_t>(B) * np2 * 8 : 0));
+  w.bytes = off;
+  return w;
+}
+
+int launch_score_mask(const float* scores, int B, int N, int C, float thr, uint32_t* mask, cudaStream_t st) {
+  const int W = (N + 31) / 32;
+  if (C <= 44) {
+    score_mask_kernel<256><<<dim3((N + 255) / 256, B), 256, 256 * C * 4, st>>>(scores, N, C, thr, mask, W);
+  } else {
+    PPB_REQUIRE(C <= 352, "score mask: at most 352 classes are supported, got %d", C);
+    score_mask_kernel<32><<<dim3((N + 31) / 32, B), 256, 32 * C * 4, st>>>(scores, N, C, thr, mask, W);
+  }
+  PPB_CUDA(cudaGetLastError());
+  count_launch();
+  return kOk;
+}
+
+}  // namespace
+}  // namespace ppb
+
+using namespace ppb;
+
+extern "C" {
+
+size_t ppb_filter_workspace_bytes(int batch, int n, int num_classes, int class_specific, int max_detections) {
+  if (batch <= 0 || n <= 0 || num_classes <= 0 || max_detections <= 0) return 256;
+  return carve(nullptr, batch, n, num_classes, class_specific, max_detections).bytes + 256;
+}
+
+int ppb_filter_detections(const float* boxes, const float* boxes3D, const float* classification, int batch, int n,
+                          int num_classes, int class_specific, int nms, float score_threshold, float nms_threshold,
+                          int max_detections, float* out_boxes, float* out_boxes3D, float* out_scores,
+                          int* out_labels, int* out_indices, void* workspace, size_t workspace_bytes, void* stream) {
+  PPB_REQUIRE(batch >= 0 && n > 0 && num_classes > 0, "ppb_filter_detections: bad shape batch=%d n=%d classes=%d",
+              batch, n, num_classes);
+  PPB_REQUIRE(max_detections > 0 && max_detections <= kMaxDetCap,
+              "ppb_filter_detections: max_detections must be in [1, %d], got %d", kMaxDetCap, max_detections);
+  if (batch == 0) return kOk;
+  PPB_REQUIRE(boxes != nullptr && boxes3D != nullptr && classification != nullptr, "ppb_filter_detections: null input");
+  PPB_REQUIRE(out_boxes != nullptr && out_boxes3D != nullptr && out_scores != nullptr && out_labels != nullptr,
+              "ppb_filter_detections: null output");
+  PPB_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15) == 0 && (reinterpret_cast<uintptr_t>(boxes3D) & 15) == 0,
+              "ppb_filter_detections: boxes / boxes3D must be 16-byte aligned");
+  const size_t need = ppb_filter_workspace_bytes(batch, n, num_classes, class_specific, max_detections);
+  PPB_REQUIRE(workspace != nullptr && workspace_bytes >= need,
+              "ppb_filter_detections: workspace too small (%zu < %zu bytes)", workspace_bytes, need);
+  void* ws_base = reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
+  const FilterWorkspace w = carve(ws_base, batch, n, num_classes, class_specific, max_detections);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int Ceff = class_specific ? num_classes : 1;
+  const int W = (n + 31) / 32;
+  const int cap = next_pow2(n);
+  const float* score_src = classification;
+  int score_stride = num_classes;
+  if (!class_specific) {
+    const long long total = static_cast<long long>(batch) * n;
+    class_max_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(classification, total, num_classes,
+                                                                                  w.smax, w.sarg);
+    PPB_CUDA(cudaGetLastError());
+    count_launch();
+    score_src = w.smax;
+    score_stride = 1;
+  }
+  int rc = launch_score_mask(score_src, batch, n, Ceff, score_threshold, w.mask, st);
+  if (rc != kOk) return rc;
+  compact_keys_kernel<<<dim3(Ceff, batch), 256, 0, st>>>(w.mask, score_src, n, Ceff, W, score_stride, cap, w.keys,
+                                                         w.counts);
+  PPB_CUDA(cudaGetLastError());
+  sort_keys_kernel<<<Ceff * batch, 1024, kSortSmemKeys * 8, st>>>(w.keys, w.counts, cap);
+  PPB_CUDA(cudaGetLastError());
+  nms_kernel<<<dim3(Ceff, batch), kNmsChunk, 0, st>>>(w.keys, w.counts, cap, boxes, n, Ceff, nms, nms_threshold,
+                                                      max_detections, w.sel_idx, w.sel_cnt);
+  PPB_CUDA(cudaGetLastError());
+  const int np2 = next_pow2(Ceff * max_detections);
+  const size_t topk_smem = np2 <= kTopkSmemKeys ? static_cast<size_t>(np2) * 8 : 0;
+  static bool attr_set = false;
+  if (!attr_set) {
+    PPB_CUDA(cudaFuncSetAttribute(topk_pad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTopkSmemKeys * 8));
+    attr_set = true;
+  }
+  topk_pad_kernel<<<batch, 1024, topk_smem, st>>>(w.sel_idx, w.sel_cnt, Ceff, max_detections, classification,
+                                                  class_specific ? nullptr : w.sarg, n, num_classes, boxes, boxes3D,
+                                                  out_boxes, out_boxes3D, out_scores, out_labels, out_indices,
+                                                  w.topk_scratch, np2);
+  PPB_CUDA(cudaGetLastError());
+  count_launch(4);
+  return kOk;
+}
+
+int ppb_gather_rows_f32(const float* src, const int* indices, float* dst, int batch, int n, int max_detections,
+                        int row_elems, void* stream) {
+  PPB_REQUIRE(batch >= 0 && n > 0 && max_detections > 0 && row_elems > 0, "ppb_gather_rows_f32: bad shape");
+  const long long total = static_cast<long long>(batch) * max_detections * row_elems;
+  if (total == 0) return kOk;
+  PPB_REQUIRE(src != nullptr && indices != nullptr && dst != nullptr, "ppb_gather_rows_f32: null buffer");
+  gather_rows_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, indices, dst, batch, n, max_detections, row_elems);
+  PPB_CUDA(cudaGetLastError());
+  count_launch();
+  return kOk;
+}
+
+/* Vote filter, step 1: mask + per-(image, class) hit counts. mask: uint32 [batch, classes, ceil(n/32)]. */
+int ppb_score_mask(const float* scores, int batch, int n, int num_classes, float threshold, uint32_t* mask,
+                   int* counts, void* stream) {
+  PPB_REQUIRE(batch >= 0 && n > 0 && num_classes > 0, "ppb_score_mask: bad shape");
+  if (batch == 0) return kOk;
+  PPB_REQUIRE(scores != nullptr && mask != nullptr, "ppb_score_mask: null buffer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = launch_score_mask(scores, batch, n, num_classes, threshold, mask, st);
+  if (rc != kOk) return rc;
+  if (counts != nullptr) {
+    mask_count_kernel<<<batch * num_classes, 256, 0, st>>>(mask, (n + 31) / 32, counts);
+    PPB_CUDA(cudaGetLastError());
+    count_launch();
+  }
+  return kOk;
+}
+
+/* Vote filter, step 2: ascending hit indices and their 16-vectors in CSR order given by `offsets`
+ * (int64 [batch*classes + 1], exclusive prefix sum of the counts from step 1). */
+int ppb_vote_gather(const uint32_t* mask, const float* scores, const float* boxes3D, int batch, int n,
+                    int num_classes, const long long* offsets, long long* indices, float* votes, float* confidence,
+                    void* stream) {
+  PPB_REQUIRE(batch >= 0 && n > 0 && num_classes > 0, "ppb_vote_gather: bad shape");
+  if (batch == 0) return kOk;
+  PPB_REQUIRE(mask != nullptr && scores != nullptr && boxes3D != nullptr && offsets != nullptr,
+              "ppb_vote_gather: null input");
+  vote_gather_kernel<<<dim3(num_classes, batch), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      mask, scores, boxes3D, n, num_classes, (n + 31) / 32, offsets, indices, votes, confidence);
+  PPB_CUDA(cudaGetLastError());
+  count_launch();
+  return kOk;
+}
+
+}  // extern "C"
