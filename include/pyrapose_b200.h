@@ -135,6 +135,48 @@ PPB_API int ppb_vote_gather(const uint32_t* mask, const float* scores, const flo
                             int num_classes, const long long* offsets, long long* indices, float* votes,
                             float* confidence, void* stream);
 
+/* ------------------------------------------------------------------ PFPN inference engine
+ * Replaces `model.predict_on_batch(images)` for the models built by Backbone.retinanet(num_classes)
+ * (PyraPose/models/resnet.py:79-110, PyraPose/models/retinanet.py:260-299) and models.convert_model
+ * (PyraPose/models/__init__.py:74-76 -> retinanet_bbox, retinanet.py:302-335).
+ *
+ * The handle owns weights (bf16, BatchNorm folded), the activation arena and a CUDA graph of the
+ * whole forward pass. Thread-compatible: one caller at a time per handle; calls cudaSetDevice on entry.
+ */
+typedef struct ppb_engine ppb_engine;
+
+PPB_API int ppb_engine_create(ppb_engine** out, int device, int max_batch, int height, int width, int num_classes,
+                              int num_anchors);
+PPB_API void ppb_engine_destroy(ppb_engine* engine);
+
+/* Layer table (Keras layer names; keras-resnet 0.1.0 for the backbone). */
+PPB_API int ppb_engine_num_layers(const ppb_engine* engine);
+PPB_API int ppb_engine_layer_info(const ppb_engine* engine, int index, char* name, int name_cap, int* ksize,
+                                  int* cin, int* cout, int* stride, int* has_bn, int* has_bias);
+/* Weights in Keras layout, all HOST pointers: kernel f32 [k,k,cin,cout] (HWIO); bias f32 [cout] or NULL;
+ * frozen BatchNorm gamma/beta/moving_mean/moving_variance f32 [cout] (NULL for layers without BN). */
+PPB_API int ppb_engine_set_layer(ppb_engine* engine, const char* name, const float* kernel_hwio_host,
+                                 const float* bias_host, const float* bn_gamma_host, const float* bn_beta_host,
+                                 const float* bn_mean_host, const float* bn_var_host, float bn_eps);
+/* Anchors layer parameters (PyraPose/layers/_misc.py:24-93): base anchors f32 [3, num_anchors, 4] already cast to
+ * float32 as keras.backend.variable does, strides f32 [3]; RegressBoxes3D mean/std f32 [16] or NULL (0 / 0.2). */
+PPB_API int ppb_engine_set_anchors(ppb_engine* engine, const float* base_anchors_host, const float* strides_host,
+                                   const float* mean16_host, const float* std16_host);
+/* Binds caller-owned DEVICE buffers and captures the graph for `batch` images:
+ *   images    f32 [batch,H,W,3]  BGR, ImageNet-mean-subtracted (PyraPose/utils/image.py:35-62)
+ *   out_box3d f32 [batch,N,16]   decode=1: decoded corners ('boxes3D'); decode=0: raw regression ('3Dbox')
+ *   out_cls   f32 [batch,N,C]    sigmoid scores ('cls')
+ *   out_mask  f32 [batch,H/8*W/8,C] or NULL to skip the mask head
+ *   out_hull  f32 [batch,N,4] or NULL: axis-aligned hull of the decoded corners (decode=1 only)
+ * N = 9 * sum over levels P3..P5 of ceil(H/2^l)*ceil(W/2^l). */
+PPB_API int ppb_engine_bind(ppb_engine* engine, int batch, const float* images, float* out_box3d, float* out_cls,
+                            float* out_mask, float* out_hull, int decode, void* stream);
+PPB_API int ppb_engine_run(ppb_engine* engine, void* stream);
+PPB_API int ppb_engine_run_eager(ppb_engine* engine, void* stream);
+PPB_API int ppb_engine_kernels_per_run(const ppb_engine* engine);
+PPB_API size_t ppb_engine_device_bytes(const ppb_engine* engine);
+PPB_API int ppb_engine_activation(ppb_engine* engine, const char* name, float* out_host, int* shape4_host);
+
 #ifdef __cplusplus
 }
 #endif

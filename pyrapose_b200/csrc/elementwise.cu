@@ -1,0 +1,197 @@
+// Bandwidth-bound helpers of the PFPN engine; see elementwise.h. Every thread moves one 16-byte vector
+// (8 bf16 channels), consecutive threads walk consecutive channels -> fully coalesced 128-bit accesses.
+#include "elementwise.h"
+
+#include <stdint.h>
+
+namespace ppb {
+namespace {
+
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float lo_f(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float hi_f(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
+
+constexpr int kStemK = 192;
+
+__global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restrict__ image,
+                                                          __nv_bfloat16* __restrict__ out, int B, int H, int W, int Ho,
+                                                          int Wo) {
+  // one thread per (output pixel, group of 8 K-columns): 24 groups per row
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long total = static_cast<long long>(B) * Ho * Wo * (kStemK / 8);
+  if (t >= total) return;
+  const int g = static_cast<int>(t % (kStemK / 8));
+  const long long pix = t / (kStemK / 8);
+  const int ox = static_cast<int>(pix % Wo);
+  const int oy = static_cast<int>((pix / Wo) % Ho);
+  const int b = static_cast<int>(pix / (static_cast<long long>(Wo) * Ho));
+  float v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int k = g * 8 + j;
+    float x = 0.0f;
+    if (k < 147) {
+      const int r = k / 21;
+      const int rem = k - r * 21;
+      const int s = rem / 3;
+      const int c = rem - s * 3;
+      const int iy = 2 * oy + r - 3, ix = 2 * ox + s - 3;
+      if (iy >= 0 && iy < H && ix >= 0 && ix < W)
+        x = __ldg(image + ((static_cast<long long>(b) * H + iy) * W + ix) * 3 + c);
+    }
+    v[j] = x;
+  }
+  uint4 o;
+  o.x = pack2(v[0], v[1]);
+  o.y = pack2(v[2], v[3]);
+  o.z = pack2(v[4], v[5]);
+  o.w = pack2(v[6], v[7]);
+  reinterpret_cast<uint4*>(out)[t] = o;
+}
+
+__device__ __forceinline__ uint4 max8(uint4 a, uint4 b) {
+  uint4 r;
+  r.x = pack2(fmaxf(lo_f(a.x), lo_f(b.x)), fmaxf(hi_f(a.x), hi_f(b.x)));
+  r.y = pack2(fmaxf(lo_f(a.y), lo_f(b.y)), fmaxf(hi_f(a.y), hi_f(b.y)));
+  r.z = pack2(fmaxf(lo_f(a.z), lo_f(b.z)), fmaxf(hi_f(a.z), hi_f(b.z)));
+  r.w = pack2(fmaxf(lo_f(a.w), lo_f(b.w)), fmaxf(hi_f(a.w), hi_f(b.w)));
+  return r;
+}
+
+__global__ void __launch_bounds__(256) maxpool_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int B,
+                                                      int Hi, int Wi, int C8, int Ho, int Wo, int pad_top,
+                                                      int pad_left) {
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int Hp = Ho + 2, Wp = Wo + 2;
+  const long long total = static_cast<long long>(B) * Hp * Wp * C8;
+  if (t >= total) return;
+  const int c = static_cast<int>(t % C8);
+  const long long pix = t / C8;
+  const int wx = static_cast<int>(pix % Wp);
+  const int hy = static_cast<int>((pix / Wp) % Hp);
+  const int b = static_cast<int>(pix / (static_cast<long long>(Wp) * Hp));
+  uint4 r = make_uint4(0, 0, 0, 0);
+  if (hy >= 1 && hy <= Ho && wx >= 1 && wx <= Wo) {
+    const int oy = hy - 1, ox = wx - 1;
+    bool first = true;
+    for (int dy = 0; dy < 3; ++dy) {
+      const int iy = 2 * oy + dy - pad_top;
+      if (iy < 0 || iy >= Hi) continue;  // TF 'same' max-pool ignores padded positions
+      for (int dx = 0; dx < 3; ++dx) {
+        const int ix = 2 * ox + dx - pad_left;
+        if (ix < 0 || ix >= Wi) continue;
+        const uint4 v = __ldg(in + ((static_cast<long long>(b) * Hi + iy) * Wi + ix) * C8 + c);
+        r = first ? v : max8(r, v);
+        first = false;
+      }
+    }
+  }
+  out[t] = r;
+}
+
+__global__ void __launch_bounds__(256) parity_planes_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int B,
+                                                            int H, int W, int C8, int Ho, int Wo, int n_planes) {
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int Hp = Ho + 2, Wp = Wo + 2;
+  const long long plane_elems = static_cast<long long>(B) * Hp * Wp * C8;
+  if (t >= plane_elems * n_planes) return;
+  const int plane = static_cast<int>(t / plane_elems);
+  const long long u = t - plane * plane_elems;
+  const int c = static_cast<int>(u % C8);
+  const long long pix = u / C8;
+  const int wx = static_cast<int>(pix % Wp);
+  const int hy = static_cast<int>((pix / Wp) % Hp);
+  const int b = static_cast<int>(pix / (static_cast<long long>(Wp) * Hp));
+  uint4 r = make_uint4(0, 0, 0, 0);
+  if (hy >= 1 && hy <= Ho && wx >= 1 && wx <= Wo) {
+    const int iy = 2 * (hy - 1) + (plane >> 1), ix = 2 * (wx - 1) + (plane & 1);
+    if (iy < H && ix < W) r = __ldg(in + ((static_cast<long long>(b) * (H + 2) + iy + 1) * (W + 2) + ix + 1) * C8 + c);
+  }
+  out[t] = r;
+}
+
+__device__ __forceinline__ void acc8(float (&f)[8], uint4 v) {
+  f[0] += lo_f(v.x); f[1] += hi_f(v.x); f[2] += lo_f(v.y); f[3] += hi_f(v.y);
+  f[4] += lo_f(v.z); f[5] += hi_f(v.z); f[6] += lo_f(v.w); f[7] += hi_f(v.w);
+}
+
+__global__ void __launch_bounds__(256) add_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b,
+                                                  const uint4* __restrict__ c, const uint4* __restrict__ u, int uH,
+                                                  int uW, uint4* __restrict__ out, int B, int H, int W, int C8) {
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int Hp = H + 2, Wp = W + 2;
+  const long long total = static_cast<long long>(B) * Hp * Wp * C8;
+  if (t >= total) return;
+  float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  // Keras Add sums its inputs left to right in fp32; the operands here are bf16 so the fp32 sums are exact
+  // up to the final rounding. Borders: all inputs carry zero borders, the sum keeps them zero.
+  acc8(f, __ldg(a + t));
+  if (b != nullptr) acc8(f, __ldg(b + t));
+  if (c != nullptr) acc8(f, __ldg(c + t));
+  if (u != nullptr) {
+    const int ch = static_cast<int>(t % C8);
+    const long long pix = t / C8;
+    const int wx = static_cast<int>(pix % Wp);
+    const int hy = static_cast<int>((pix / Wp) % Hp);
+    const int bi = static_cast<int>(pix / (static_cast<long long>(Wp) * Hp));
+    if (hy >= 1 && hy <= H && wx >= 1 && wx <= W) {
+      // tf.image.resize NEAREST, half_pixel_centers: src = min(floor((dst + 0.5) * in / out), in - 1)
+      int sy = static_cast<int>(floorf((static_cast<float>(hy - 1) + 0.5f) * (static_cast<float>(uH) / H)));
+      int sx = static_cast<int>(floorf((static_cast<float>(wx - 1) + 0.5f) * (static_cast<float>(uW) / W)));
+      sy = min(sy, uH - 1);
+      sx = min(sx, uW - 1);
+      acc8(f, __ldg(u + ((static_cast<long long>(bi) * (uH + 2) + sy + 1) * (uW + 2) + sx + 1) * C8 + ch));
+    }
+  }
+  uint4 o;
+  o.x = pack2(f[0], f[1]);
+  o.y = pack2(f[2], f[3]);
+  o.z = pack2(f[4], f[5]);
+  o.w = pack2(f[6], f[7]);
+  out[t] = o;
+}
+
+inline unsigned blocks_for(long long total) { return static_cast<unsigned>((total + 255) / 256); }
+
+}  // namespace
+
+cudaError_t launch_stem_im2col(const float* image, __nv_bfloat16* out, int B, int H, int W, int Ho, int Wo,
+                               cudaStream_t st) {
+  const long long total = static_cast<long long>(B) * Ho * Wo * (kStemK / 8);
+  stem_im2col_kernel<<<blocks_for(total), 256, 0, st>>>(image, out, B, H, W, Ho, Wo);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_maxpool3x3s2(const __nv_bfloat16* in, __nv_bfloat16* out, int B, int Hi, int Wi, int C, int Ho,
+                                int Wo, cudaStream_t st) {
+  const int pt = ((Ho - 1) * 2 + 3 - Hi) > 0 ? ((Ho - 1) * 2 + 3 - Hi) / 2 : 0;
+  const int pl = ((Wo - 1) * 2 + 3 - Wi) > 0 ? ((Wo - 1) * 2 + 3 - Wi) / 2 : 0;
+  const long long total = static_cast<long long>(B) * (Ho + 2) * (Wo + 2) * (C / 8);
+  maxpool_kernel<<<blocks_for(total), 256, 0, st>>>(reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(out), B,
+                                                    Hi, Wi, C / 8, Ho, Wo, pt, pl);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_parity_planes(const __nv_bfloat16* in, __nv_bfloat16* out, int B, int H, int W, int C, int Ho,
+                                 int Wo, int n_planes, cudaStream_t st) {
+  const long long total = static_cast<long long>(B) * (Ho + 2) * (Wo + 2) * (C / 8) * n_planes;
+  parity_planes_kernel<<<blocks_for(total), 256, 0, st>>>(reinterpret_cast<const uint4*>(in),
+                                                          reinterpret_cast<uint4*>(out), B, H, W, C / 8, Ho, Wo,
+                                                          n_planes);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_add(const __nv_bfloat16* a, const __nv_bfloat16* b, const __nv_bfloat16* c,
+                       const __nv_bfloat16* u, int uH, int uW, __nv_bfloat16* out, int B, int H, int W, int C,
+                       cudaStream_t st) {
+  const long long total = static_cast<long long>(B) * (H + 2) * (W + 2) * (C / 8);
+  add_kernel<<<blocks_for(total), 256, 0, st>>>(reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b),
+                                                reinterpret_cast<const uint4*>(c), reinterpret_cast<const uint4*>(u),
+                                                uH, uW, reinterpret_cast<uint4*>(out), B, H, W, C / 8);
+  return cudaGetLastError();
+}
+
+}  // namespace ppb

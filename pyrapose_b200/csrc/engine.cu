@@ -1,0 +1,786 @@
+// PFPN inference engine: owns the bf16 weights, the activation arena and the launch plan of the whole
+// network (ResNet-50 -> __create_sparceFPN -> heads -> decode) and replays it as one CUDA graph.
+//
+// Replaces what `model.predict_on_batch` executes for the graph built by
+//   PyraPose/models/resnet.py:79-110        (resnet_retinanet -> keras_resnet.models.ResNet50)
+//   PyraPose/models/retinanet.py:180-214    (__create_sparceFPN)
+//   PyraPose/models/retinanet.py:9-131      (classification / mask / 3D-regression sub-models)
+//   PyraPose/models/retinanet.py:260-335    (retinanet, retinanet_bbox: Anchors + RegressBoxes3D)
+// Every convolution is one launch of the tcgen05 implicit-GEMM kernel (conv_igemm.cu); BatchNorm is folded
+// into the weights, ReLU / residual add / sigmoid / Reshape+Concatenate / anchor decode live in its epilogue.
+// The three pyramid levels share each head convolution as ONE launch over a 3-segment row space.
+#include "../../include/pyrapose_b200.h"
+#include "conv_igemm.h"
+#include "elementwise.h"
+#include "errors.h"
+#include "launch_count.h"
+
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace ppb {
+
+void conv_fill_single_seg(ConvParams& p, int batch, int h, int w, int ksize);
+int conv_pick_block_n(int cout_pad);
+
+namespace {
+
+struct LayerW {
+  std::string name;
+  int ksize, cin, cout, stride;
+  bool has_bn, has_bias;
+  int k_total;   // columns of the device weight matrix (ksize*ksize*cin, stem: 192)
+  int cout_pad;  // rows, multiple of 16
+  __nv_bfloat16* w = nullptr;
+  float* bias = nullptr;
+  bool loaded = false;
+};
+
+struct Tensor {  // padded-flat (pad = 1) or plain (pad = 0) bf16 activation
+  std::string name;
+  __nv_bfloat16* ptr = nullptr;
+  int H = 0, W = 0, C = 0, pad = 1;
+  long long rows(int B) const { return static_cast<long long>(B) * (H + 2 * pad) * (W + 2 * pad); }
+};
+
+enum OpKind { kOpConv, kOpIm2col, kOpMaxpool, kOpPlanes, kOpAdd };
+
+struct Op {
+  OpKind kind;
+  // conv
+  CUtensorMap ta, tb;
+  ConvParams p;
+  // elementwise
+  const void* in0 = nullptr;
+  const void* in1 = nullptr;
+  const void* in2 = nullptr;
+  const void* in3 = nullptr;
+  void* out = nullptr;
+  int a[8] = {0};
+};
+
+int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+int same_pad_before(int in, int k, int stride) {
+  const int out = (in + stride - 1) / stride;
+  const int total = std::max((out - 1) * stride + k - in, 0);
+  return total / 2;
+}
+
+}  // namespace
+
+struct Engine {
+  int device = 0, max_batch = 0, H = 0, W = 0, num_classes = 0, num_anchors = 0;
+  std::vector<LayerW> layers;
+  std::map<std::string, int> layer_index;
+  std::vector<std::unique_ptr<Tensor>> tensors;
+  std::map<std::string, Tensor*> tensor_index;
+  std::vector<void*> allocations;
+  // anchors / decode parameters (host copies; baked into the head conv's params)
+  float base_anchor[kConvMaxSegs][9][4];
+  float stride[kConvMaxSegs];
+  float dec_mean[16], dec_std[16];
+  bool anchors_set = false;
+  // level geometry
+  int lvl_h[3], lvl_w[3];
+  int seg_row_begin[3], seg_tile_begin[3];
+  long long feat_rows_total = 0;
+  int feat_tiles_total = 0;
+  // plan
+  std::vector<Op> ops;
+  int bound_batch = 0;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t graph_exec = nullptr;
+  int graph_kernels = 0;
+  size_t arena_bytes = 0;
+
+  ~Engine() {
+    if (graph_exec) cudaGraphExecDestroy(graph_exec);
+    if (graph) cudaGraphDestroy(graph);
+    for (void* p : allocations) cudaFree(p);
+  }
+
+  int add_layer(const std::string& name, int ksize, int cin, int cout, int stride, bool bn, bool bias) {
+    LayerW l;
+    l.name = name;
+    l.ksize = ksize;
+    l.cin = cin;
+    l.cout = cout;
+    l.stride = stride;
+    l.has_bn = bn;
+    l.has_bias = bias;
+    l.k_total = (ksize == 7) ? 192 : ksize * ksize * cin;
+    l.cout_pad = round_up(cout, 16);
+    layer_index[name] = static_cast<int>(layers.size());
+    layers.push_back(l);
+    return static_cast<int>(layers.size()) - 1;
+  }
+
+  int device_alloc(void** p, size_t bytes) {
+    PPB_CUDA(cudaMalloc(p, bytes));
+    PPB_CUDA(cudaMemset(*p, 0, bytes));
+    allocations.push_back(*p);
+    arena_bytes += bytes;
+    return kOk;
+  }
+
+  Tensor* tensor(const std::string& name) {
+    auto it = tensor_index.find(name);
+    return it == tensor_index.end() ? nullptr : it->second;
+  }
+
+  int new_tensor(Tensor** out, const std::string& name, int h, int w, int c, int pad, int planes = 1,
+                 long long rows_override = 0) {
+    std::unique_ptr<Tensor> t(new Tensor);
+    t->name = name;
+    t->H = h;
+    t->W = w;
+    t->C = c;
+    t->pad = pad;
+    long long rows = rows_override ? rows_override : t->rows(max_batch) * planes;
+    rows = (rows + kConvBlockM - 1) / kConvBlockM * kConvBlockM;
+    void* p = nullptr;
+    int rc = device_alloc(&p, static_cast<size_t>(rows) * c * sizeof(__nv_bfloat16));
+    if (rc != kOk) return rc;
+    t->ptr = static_cast<__nv_bfloat16*>(p);
+    *out = t.get();
+    tensor_index[name] = t.get();
+    tensors.push_back(std::move(t));
+    return kOk;
+  }
+
+  void define_layers();
+  int allocate_weights();
+  int set_layer(const char* name, const float* kernel, const float* bias, const float* gamma, const float* beta,
+                const float* mean, const float* var, float eps);
+  int build_plan(int batch, const float* images, float* out_reg, float* out_cls, float* out_mask, float* out_hull,
+                 int decode);
+  int conv_op(const Tensor* x, int x_planes, const std::string& layer, const Tensor* res, Tensor* y, int relu, int batch,
+              int src_h = 0, int src_w = 0);
+  int head_conv_op(const __nv_bfloat16* x, int cin, const std::string& layer, __nv_bfloat16* y, int relu, int batch,
+                   int n_levels, int epi, float* out_f32, float* out_hull);
+  int capture(cudaStream_t st);
+  int launch_all(cudaStream_t st);
+};
+
+void Engine::define_layers() {
+  // keras-resnet 0.1.0 ResNet50 (Caffe-style bottlenecks, stride on the first 1x1 conv)
+  add_layer("conv1", 7, 3, 64, 2, true, false);
+  int cin = 64, features = 64;
+  const int blocks[4] = {3, 4, 6, 3};
+  for (int stage = 0; stage < 4; ++stage) {
+    for (int b = 0; b < blocks[stage]; ++b) {
+      char tag[8];
+      snprintf(tag, sizeof(tag), "%d%c", stage + 2, 'a' + b);
+      const int st = (b == 0 && stage > 0) ? 2 : 1;
+      add_layer(std::string("res") + tag + "_branch2a", 1, cin, features, st, true, false);
+      add_layer(std::string("res") + tag + "_branch2b", 3, features, features, 1, true, false);
+      add_layer(std::string("res") + tag + "_branch2c", 1, features, features * 4, 1, true, false);
+      if (b == 0) add_layer(std::string("res") + tag + "_branch1", 1, cin, features * 4, st, true, false);
+      cin = features * 4;
+    }
+    features *= 2;
+  }
+  // __create_sparceFPN (retinanet.py:180-214)
+  add_layer("P3_lateral", 1, 512, 256, 1, false, true);
+  add_layer("P4_lateral", 1, 1024, 256, 1, false, true);
+  add_layer("P5_lateral", 1, 2048, 256, 1, false, true);
+  add_layer("P4_mid", 3, 256, 256, 1, false, true);
+  add_layer("P3_mid", 3, 256, 256, 1, false, true);
+  add_layer("P3_down", 3, 256, 256, 2, false, true);
+  add_layer("P3", 3, 256, 256, 1, false, true);
+  add_layer("P4_down", 3, 256, 256, 2, false, true);
+  add_layer("P4", 3, 256, 256, 1, false, true);
+  add_layer("P5", 3, 256, 256, 1, false, true);
+  // heads (retinanet.py:9-131)
+  for (int i = 0; i < 4; ++i)
+    add_layer("pyramid_regression3D_" + std::to_string(i), 3, i == 0 ? 256 : 512, 512, 1, false, true);
+  add_layer("pyramid_regression3D", 3, 512, num_anchors * 16, 1, false, true);
+  for (int i = 0; i < 4; ++i) add_layer("pyramid_classification_" + std::to_string(i), 3, 256, 256, 1, false, true);
+  add_layer("pyramid_classification", 3, 256, num_classes * num_anchors, 1, false, true);
+  for (int i = 0; i < 4; ++i) add_layer("mask_" + std::to_string(i), 3, 256, 256, 1, false, true);
+  add_layer("mask_out", 3, 256, num_classes, 1, false, true);
+}
+
+int Engine::allocate_weights() {
+  for (LayerW& l : layers) {
+    void* p = nullptr;
+    int rc = device_alloc(&p, static_cast<size_t>(l.cout_pad) * l.k_total * sizeof(__nv_bfloat16));
+    if (rc != kOk) return rc;
+    l.w = static_cast<__nv_bfloat16*>(p);
+    rc = device_alloc(&p, static_cast<size_t>(l.cout_pad) * sizeof(float));
+    if (rc != kOk) return rc;
+    l.bias = static_cast<float*>(p);
+  }
+  return kOk;
+}
+
+// Keras HWIO fp32 kernel (+ optional frozen BatchNorm) -> bf16 [cout_pad][K] with K = (r*k + s)*cin + c.
+int Engine::set_layer(const char* name, const float* kernel, const float* bias, const float* gamma, const float* beta,
+                      const float* mean, const float* var, float eps) {
+  auto it = layer_index.find(name);
+  PPB_REQUIRE(it != layer_index.end(), "ppb_engine_set_layer: unknown layer '%s'", name);
+  LayerW& l = layers[it->second];
+  PPB_REQUIRE(kernel != nullptr, "ppb_engine_set_layer: null kernel for '%s'", name);
+  PPB_REQUIRE(!l.has_bn || (gamma && beta && mean && var), "ppb_engine_set_layer: '%s' needs BatchNorm parameters", name);
+  const int k = l.ksize, cin = l.cin, cout = l.cout;
+  std::vector<__nv_bfloat16> w(static_cast<size_t>(l.cout_pad) * l.k_total, __float2bfloat16(0.0f));
+  std::vector<float> b(l.cout_pad, 0.0f);
+  for (int o = 0; o < cout; ++o) {
+    float scale = 1.0f, shift = 0.0f;
+    if (l.has_bn) {  // y = gamma * (x - mean) / sqrt(var + eps) + beta
+      scale = gamma[o] / std::sqrt(var[o] + eps);
+      shift = beta[o] - mean[o] * scale;
+    }
+    const float b0 = (l.has_bias && bias != nullptr) ? bias[o] : 0.0f;
+    b[o] = b0 * scale + shift;
+    for (int r = 0; r < k; ++r)
+      for (int s = 0; s < k; ++s)
+        for (int c = 0; c < cin; ++c) {
+          const float v = kernel[((static_cast<size_t>(r) * k + s) * cin + c) * cout + o] * scale;
+          w[static_cast<size_t>(o) * l.k_total + (r * k + s) * cin + c] = __float2bfloat16(v);
+        }
+  }
+  PPB_CUDA(cudaMemcpy(l.w, w.data(), w.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
+  PPB_CUDA(cudaMemcpy(l.bias, b.data(), b.size() * sizeof(float), cudaMemcpyHostToDevice));
+  l.loaded = true;
+  return kOk;
+}
+
+}  // namespace ppb
+
+namespace ppb {
+
+// One convolution over a single padded-flat plane set. `x` has the OUTPUT geometry (for stride-2 layers it is the
+// parity-plane tensor produced by launch_parity_planes from a src_h x src_w input).
+int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, const Tensor* res, Tensor* y, int relu,
+                    int batch, int src_h, int src_w) {
+  const LayerW& l = layers[layer_index.at(layer)];
+  if (!l.loaded) return fail(kErrState, "layer '%s' has no weights (call ppb_engine_set_layer first)", l.name.c_str());
+  Op op;
+  op.kind = kOpConv;
+  ConvParams& p = op.p;
+  memset(&p, 0, sizeof(p));
+  if (x->pad == 0) {  // stem: plain im2col rows, one tap
+    p.n_segs = 1;
+    ConvSeg& s = p.seg[0];
+    s.row_begin = 0;
+    s.hp = y->H;
+    s.wp = y->W;
+    s.pad = 0;
+    s.rows = static_cast<int>(y->rows(batch));
+    s.tile_begin = 0;
+    s.tap_off[0] = 0;
+    p.n_taps = 1;
+    p.n_mtiles = (s.rows + kConvBlockM - 1) / kConvBlockM;
+  } else {
+    conv_fill_single_seg(p, batch, y->H, y->W, l.ksize);
+    if (l.stride == 2 && l.ksize == 3) {
+      // 3x3/2 'same' over four parity planes: input row 2i + r - pt lives in plane ((r-pt) mod 2) at row
+      // i + floor((r-pt)/2); TF puts the odd padding pixel at the bottom/right (pt = total/2).
+      ConvSeg& s = p.seg[0];
+      const long long plane_rows = static_cast<long long>(batch) * s.hp * s.wp;
+      const int pt = same_pad_before(src_h, 3, 2), pl = same_pad_before(src_w, 3, 2);
+      for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) {
+          const int u = r - pt, v = c - pl;
+          const int ph = ((u % 2) + 2) % 2, pw = ((v % 2) + 2) % 2;
+          const int dy = (u - ph) / 2, dx = (v - pw) / 2;
+          s.tap_off[r * 3 + c] = static_cast<int>((ph * 2 + pw) * plane_rows) + dy * s.wp + dx;
+        }
+    }
+  }
+  p.cin_blocks = x->C / kConvBlockK;
+  p.n_valid = l.cout;
+  p.block_n = conv_pick_block_n(l.cout_pad);
+  p.n_ntiles = (l.cout_pad + p.block_n - 1) / p.block_n;
+  p.epi = kEpiBf16;
+  p.relu = relu;
+  p.bias = l.bias;
+  p.residual = res ? res->ptr : nullptr;
+  p.res_ld = res ? res->C : 0;
+  p.out = y->ptr;
+  p.out_ld = y->C;
+  const long long a_rows = x->rows(batch) * (x_planes > 0 ? x_planes : 1);
+  int rc = conv_encode_tmaps(&op.ta, &op.tb, x->ptr, a_rows, x->C, x->C, l.w, l.cout_pad, l.k_total, p.block_n);
+  if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled failed for layer '%s' (%d)", l.name.c_str(), rc);
+  ops.push_back(op);
+  return kOk;
+}
+
+// A head convolution shared by `n_levels` pyramid levels: one launch over the multi-segment feature matrix.
+int Engine::head_conv_op(const __nv_bfloat16* x, int cin, const std::string& layer, __nv_bfloat16* y, int relu,
+                         int batch, int n_levels, int epi, float* out_f32, float* out_hull) {
+  const LayerW& l = layers[layer_index.at(layer)];
+  if (!l.loaded) return fail(kErrState, "layer '%s' has no weights (call ppb_engine_set_layer first)", l.name.c_str());
+  Op op;
+  op.kind = kOpConv;
+  ConvParams& p = op.p;
+  memset(&p, 0, sizeof(p));
+  p.n_segs = n_levels;
+  int tiles = 0, loc = 0;
+  long long last_row = 0;
+  for (int i = 0; i < n_levels; ++i) {
+    ConvSeg& s = p.seg[i];
+    s.hp = lvl_h[i] + 2;
+    s.wp = lvl_w[i] + 2;
+    s.pad = 1;
+    s.rows = batch * s.hp * s.wp;
+    s.row_begin = seg_row_begin[i];  // laid out for max_batch so the buffers never move
+    s.tile_begin = tiles;
+    s.loc_base = loc;
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) s.tap_off[r * 3 + c] = (r - 1) * s.wp + (c - 1);
+    tiles += (s.rows + kConvBlockM - 1) / kConvBlockM;
+    loc += lvl_h[i] * lvl_w[i];
+    last_row = s.row_begin + s.rows;
+  }
+  p.n_taps = 9;
+  p.n_mtiles = tiles;
+  p.cin_blocks = cin / kConvBlockK;
+  p.n_valid = l.cout;
+  p.block_n = conv_pick_block_n(l.cout_pad);
+  p.n_ntiles = (l.cout_pad + p.block_n - 1) / p.block_n;
+  p.epi = epi;
+  p.relu = relu;
+  p.bias = l.bias;
+  p.out = y;
+  p.out_ld = l.cout;
+  p.out_f32 = out_f32;
+  p.out_hull = out_hull;
+  int locs = 0;
+  for (int i = 0; i < 3; ++i) locs += lvl_h[i] * lvl_w[i];
+  p.locs_per_image = (n_levels == 1) ? lvl_h[0] * lvl_w[0] : locs;
+  p.vals_per_loc = l.cout;
+  memcpy(p.anchor, base_anchor, sizeof(base_anchor));
+  memcpy(p.stride, stride, sizeof(stride));
+  memcpy(p.dec_mean, dec_mean, sizeof(dec_mean));
+  memcpy(p.dec_std, dec_std, sizeof(dec_std));
+  int rc = conv_encode_tmaps(&op.ta, &op.tb, x, last_row, cin, cin, l.w, l.cout_pad, l.k_total, p.block_n);
+  if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled failed for layer '%s' (%d)", l.name.c_str(), rc);
+  ops.push_back(op);
+  return kOk;
+}
+
+}  // namespace ppb
+
+namespace ppb {
+
+int Engine::build_plan(int batch, const float* images, float* out_reg, float* out_cls, float* out_mask,
+                       float* out_hull, int decode) {
+  ops.clear();
+  auto get = [&](Tensor** t, const std::string& name, int h, int w, int c, int pad, int planes = 1) -> int {
+    *t = tensor(name);
+    if (*t != nullptr) return kOk;
+    return new_tensor(t, name, h, w, c, pad, planes);
+  };
+  auto elementwise = [&](OpKind kind, const void* i0, const void* i1, const void* i2, const void* i3, void* out,
+                         std::initializer_list<int> args) {
+    Op op;
+    op.kind = kind;
+    op.in0 = i0;
+    op.in1 = i1;
+    op.in2 = i2;
+    op.in3 = i3;
+    op.out = out;
+    int k = 0;
+    for (int v : args) op.a[k++] = v;
+    ops.push_back(op);
+  };
+#define PPB_TRY(expr)          \
+  do {                         \
+    int rc__ = (expr);         \
+    if (rc__ != kOk) return rc__; \
+  } while (0)
+
+  // ---- stem: ZeroPad(3) + 7x7/2 VALID + BN + ReLU, then MaxPool 3x3/2 'same'
+  const int h1 = (H + 1) / 2, w1 = (W + 1) / 2;
+  const int h2 = (h1 + 1) / 2, w2 = (w1 + 1) / 2;
+  Tensor *col, *stem, *x;
+  PPB_TRY(get(&col, "conv1_im2col", h1, w1, 192, 0));
+  PPB_TRY(get(&stem, "conv1_relu", h1, w1, 64, 0));
+  PPB_TRY(get(&x, "pool1", h2, w2, 64, 1));
+  elementwise(kOpIm2col, images, nullptr, nullptr, nullptr, col->ptr, {batch, H, W, h1, w1});
+  PPB_TRY(conv_op(col, 1, "conv1", nullptr, stem, 1, batch));
+  elementwise(kOpMaxpool, stem->ptr, nullptr, nullptr, nullptr, x->ptr, {batch, h1, w1, 64, h2, w2});
+
+  // ---- bottleneck stages
+  const int blocks[4] = {3, 4, 6, 3};
+  int features = 64, ch = h2, cw = w2;
+  Tensor* c_out[4] = {nullptr, nullptr, nullptr, nullptr};
+  for (int stage = 0; stage < 4; ++stage) {
+    for (int b = 0; b < blocks[stage]; ++b) {
+      char tagc[8];
+      snprintf(tagc, sizeof(tagc), "%d%c", stage + 2, 'a' + b);
+      const std::string tag(tagc);
+      const bool down = (b == 0 && stage > 0);
+      Tensor* xin = x;
+      if (down) {  // 1x1 stride-2 VALID: out(i,j) = in(2i,2j)
+        const int nh = (ch + 1) / 2, nw = (cw + 1) / 2;
+        Tensor* sub;
+        PPB_TRY(get(&sub, "res" + tag + "_sub", nh, nw, x->C, 1));
+        elementwise(kOpPlanes, x->ptr, nullptr, nullptr, nullptr, sub->ptr, {batch, ch, cw, x->C, nh, nw, 1});
+        xin = sub;
+        ch = nh;
+        cw = nw;
+      }
+      Tensor *y1, *y2, *y3, *sc = x;
+      PPB_TRY(get(&y1, "res" + tag + "_branch2a_relu", ch, cw, features, 1));
+      PPB_TRY(get(&y2, "res" + tag + "_branch2b_relu", ch, cw, features, 1));
+      PPB_TRY(get(&y3, "res" + tag + "_relu", ch, cw, features * 4, 1));
+      PPB_TRY(conv_op(xin, 1, "res" + tag + "_branch2a", nullptr, y1, 1, batch));
+      PPB_TRY(conv_op(y1, 1, "res" + tag + "_branch2b", nullptr, y2, 1, batch));
+      if (b == 0) {
+        PPB_TRY(get(&sc, "res" + tag + "_branch1_bn", ch, cw, features * 4, 1));
+        PPB_TRY(conv_op(xin, 1, "res" + tag + "_branch1", nullptr, sc, 0, batch));
+      }
+      PPB_TRY(conv_op(y2, 1, "res" + tag + "_branch2c", sc, y3, 1, batch));
+      x = y3;
+    }
+    c_out[stage] = x;
+    features *= 2;
+  }
+  Tensor *C3 = c_out[1], *C4 = c_out[2], *C5 = c_out[3];
+  PPB_REQUIRE(C3->H == lvl_h[0] && C3->W == lvl_w[0] && C5->H == lvl_h[2] && C5->W == lvl_w[2],
+              "internal: pyramid level shapes do not match the backbone outputs");
+
+  // ---- __create_sparceFPN (retinanet.py:180-214)
+  Tensor *P3l, *P4l, *P5l, *t4, *t3, *P4m, *P3m, *s3, *P3d, *t3f, *t4f, *s4, *P4d, *t5f;
+  PPB_TRY(get(&P3l, "P3_lateral", C3->H, C3->W, 256, 1));
+  PPB_TRY(get(&P4l, "P4_lateral", C4->H, C4->W, 256, 1));
+  PPB_TRY(get(&P5l, "P5_lateral", C5->H, C5->W, 256, 1));
+  PPB_TRY(conv_op(C3, 1, "P3_lateral", nullptr, P3l, 0, batch));                                   // :192
+  PPB_TRY(conv_op(C4, 1, "P4_lateral", nullptr, P4l, 0, batch));                                   // :193
+  PPB_TRY(conv_op(C5, 1, "P5_lateral", nullptr, P5l, 0, batch));                                   // :194
+  PPB_TRY(get(&t4, "P4_mid_in", C4->H, C4->W, 256, 1));
+  PPB_TRY(get(&t3, "P3_mid_in", C3->H, C3->W, 256, 1));
+  PPB_TRY(get(&P4m, "P4_mid", C4->H, C4->W, 256, 1));
+  PPB_TRY(get(&P3m, "P3_mid", C3->H, C3->W, 256, 1));
+  elementwise(kOpAdd, P4l->ptr, nullptr, nullptr, P5l->ptr, t4->ptr, {batch, C4->H, C4->W, 256, C5->H, C5->W});  // :196,198
+  PPB_TRY(conv_op(t4, 1, "P4_mid", nullptr, P4m, 0, batch));                                       // :199
+  elementwise(kOpAdd, P3l->ptr, nullptr, nullptr, P4l->ptr, t3->ptr, {batch, C3->H, C3->W, 256, C4->H, C4->W});  // :197,200
+  PPB_TRY(conv_op(t3, 1, "P3_mid", nullptr, P3m, 0, batch));                                       // :201
+  PPB_TRY(get(&s3, "P3_mid_planes", C4->H, C4->W, 256, 1, 4));
+  PPB_TRY(get(&P3d, "P3_down", C4->H, C4->W, 256, 1));
+  elementwise(kOpPlanes, P3m->ptr, nullptr, nullptr, nullptr, s3->ptr, {batch, C3->H, C3->W, 256, C4->H, C4->W, 4});
+  PPB_TRY(conv_op(s3, 4, "P3_down", nullptr, P3d, 0, batch, C3->H, C3->W));                        // :202
+  PPB_TRY(get(&t3f, "P3_fin", C3->H, C3->W, 256, 1));
+  elementwise(kOpAdd, P3m->ptr, P3l->ptr, nullptr, nullptr, t3f->ptr, {batch, C3->H, C3->W, 256, 0, 0});  // :203
+  PPB_TRY(get(&t4f, "P4_fin", C4->H, C4->W, 256, 1));
+  elementwise(kOpAdd, P3d->ptr, P4m->ptr, P4l->ptr, nullptr, t4f->ptr, {batch, C4->H, C4->W, 256, 0, 0});  // :206,208
+  PPB_TRY(get(&s4, "P4_mid_planes", C5->H, C5->W, 256, 1, 4));
+  PPB_TRY(get(&P4d, "P4_down", C5->H, C5->W, 256, 1));
+  elementwise(kOpPlanes, P4m->ptr, nullptr, nullptr, nullptr, s4->ptr, {batch, C4->H, C4->W, 256, C5->H, C5->W, 4});
+  PPB_TRY(conv_op(s4, 4, "P4_down", nullptr, P4d, 0, batch, C4->H, C4->W));                        // :207
+  PPB_TRY(get(&t5f, "P5_fin", C5->H, C5->W, 256, 1));
+  elementwise(kOpAdd, P4d->ptr, P5l->ptr, nullptr, nullptr, t5f->ptr, {batch, C5->H, C5->W, 256, 0, 0});  // :211
+
+  // ---- pyramid outputs P3, P4, P5 written into ONE multi-segment feature matrix
+  Tensor* feat = tensor("features");
+  if (feat == nullptr) PPB_TRY(new_tensor(&feat, "features", 0, 0, 256, 1, 1, feat_rows_total));
+  Tensor fview[3];
+  Tensor* fin[3] = {t3f, t4f, t5f};
+  const char* pname[3] = {"P3", "P4", "P5"};
+  for (int i = 0; i < 3; ++i) {
+    fview[i].ptr = feat->ptr + static_cast<size_t>(seg_row_begin[i]) * 256;
+    fview[i].H = lvl_h[i];
+    fview[i].W = lvl_w[i];
+    fview[i].C = 256;
+    fview[i].pad = 1;
+    PPB_TRY(conv_op(fin[i], 1, pname[i], nullptr, &fview[i], 0, batch));                           // :204,209,212
+  }
+
+  // ---- heads: every tower conv is one launch over the three levels (retinanet.py:224-225)
+  auto tower_buf = [&](Tensor** t, const std::string& name, int c) -> int {
+    *t = tensor(name);
+    if (*t != nullptr) return kOk;
+    return new_tensor(t, name, 0, 0, c, 1, 1, feat_rows_total);
+  };
+  Tensor *ra, *rb, *ca, *cb, *ma, *mb;
+  PPB_TRY(tower_buf(&ra, "reg_tower_a", 512));
+  PPB_TRY(tower_buf(&rb, "reg_tower_b", 512));
+  PPB_TRY(tower_buf(&ca, "cls_tower_a", 256));
+  PPB_TRY(tower_buf(&cb, "cls_tower_b", 256));
+  PPB_TRY(tower_buf(&ma, "mask_tower_a", 256));
+  PPB_TRY(tower_buf(&mb, "mask_tower_b", 256));
+  PPB_TRY(head_conv_op(feat->ptr, 256, "pyramid_regression3D_0", ra->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
+  PPB_TRY(head_conv_op(ra->ptr, 512, "pyramid_regression3D_1", rb->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
+  PPB_TRY(head_conv_op(rb->ptr, 512, "pyramid_regression3D_2", ra->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
+  PPB_TRY(head_conv_op(ra->ptr, 512, "pyramid_regression3D_3", rb->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
+  PPB_TRY(head_conv_op(rb->ptr, 512, "pyramid_regression3D", nullptr, 0, batch, 3,
+                       decode ? kEpiHeadDecode : kEpiHeadRaw, out_reg, decode ? out_hull : nullptr));
+  PPB_TRY(head_conv_op(feat->ptr, 256, "pyramid_classification_0", ca->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
+  PPB_TRY(head_conv_op(ca->ptr, 256, "pyramid_classification_1", cb->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
+  PPB_TRY(head_conv_op(cb->ptr, 256, "pyramid_classification_2", ca->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
+  PPB_TRY(head_conv_op(ca->ptr, 256, "pyramid_classification_3", cb->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
+  PPB_TRY(head_conv_op(cb->ptr, 256, "pyramid_classification", nullptr, 0, batch, 3, kEpiHeadSigmoid, out_cls, nullptr));
+  if (out_mask != nullptr) {  // mask head on P3 only (retinanet.py:296-297)
+    PPB_TRY(head_conv_op(feat->ptr, 256, "mask_0", ma->ptr, 1, batch, 1, kEpiBf16, nullptr, nullptr));
+    PPB_TRY(head_conv_op(ma->ptr, 256, "mask_1", mb->ptr, 1, batch, 1, kEpiBf16, nullptr, nullptr));
+    PPB_TRY(head_conv_op(mb->ptr, 256, "mask_2", ma->ptr, 1, batch, 1, kEpiBf16, nullptr, nullptr));
+    PPB_TRY(head_conv_op(ma->ptr, 256, "mask_3", mb->ptr, 1, batch, 1, kEpiBf16, nullptr, nullptr));
+    PPB_TRY(head_conv_op(mb->ptr, 256, "mask_out", nullptr, 0, batch, 1, kEpiHeadSigmoid, out_mask, nullptr));
+  }
+#undef PPB_TRY
+  bound_batch = batch;
+  return kOk;
+}
+
+int Engine::launch_all(cudaStream_t st) {
+  for (const Op& op : ops) {
+    switch (op.kind) {
+      case kOpConv:
+        PPB_CUDA(conv_launch(op.ta, op.tb, op.p, 0, st));
+        break;
+      case kOpIm2col:
+        PPB_CUDA(launch_stem_im2col(static_cast<const float*>(op.in0), static_cast<__nv_bfloat16*>(op.out), op.a[0],
+                                    op.a[1], op.a[2], op.a[3], op.a[4], st));
+        break;
+      case kOpMaxpool:
+        PPB_CUDA(launch_maxpool3x3s2(static_cast<const __nv_bfloat16*>(op.in0), static_cast<__nv_bfloat16*>(op.out),
+                                     op.a[0], op.a[1], op.a[2], op.a[3], op.a[4], op.a[5], st));
+        break;
+      case kOpPlanes:
+        PPB_CUDA(launch_parity_planes(static_cast<const __nv_bfloat16*>(op.in0), static_cast<__nv_bfloat16*>(op.out),
+                                      op.a[0], op.a[1], op.a[2], op.a[3], op.a[4], op.a[5], op.a[6], st));
+        break;
+      case kOpAdd:
+        PPB_CUDA(launch_add(static_cast<const __nv_bfloat16*>(op.in0), static_cast<const __nv_bfloat16*>(op.in1),
+                            static_cast<const __nv_bfloat16*>(op.in2), static_cast<const __nv_bfloat16*>(op.in3),
+                            op.a[4], op.a[5], static_cast<__nv_bfloat16*>(op.out), op.a[0], op.a[1], op.a[2], op.a[3],
+                            st));
+        break;
+    }
+  }
+  return kOk;
+}
+
+int Engine::capture(cudaStream_t st) {
+  if (graph_exec) {
+    cudaGraphExecDestroy(graph_exec);
+    graph_exec = nullptr;
+  }
+  if (graph) {
+    cudaGraphDestroy(graph);
+    graph = nullptr;
+  }
+  PPB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+  const int rc = launch_all(st);
+  cudaGraph_t g = nullptr;
+  const cudaError_t end = cudaStreamEndCapture(st, &g);
+  if (rc != kOk) {
+    if (g) cudaGraphDestroy(g);
+    return rc;
+  }
+  PPB_CUDA(end);
+  graph = g;
+  PPB_CUDA(cudaGraphInstantiate(&graph_exec, graph, 0));
+  graph_kernels = static_cast<int>(ops.size());
+  return kOk;
+}
+
+}  // namespace ppb
+
+using namespace ppb;
+
+extern "C" {
+
+struct ppb_engine {
+  Engine e;
+};
+
+int ppb_engine_create(ppb_engine** out, int device, int max_batch, int height, int width, int num_classes,
+                      int num_anchors) {
+  PPB_REQUIRE(out != nullptr, "ppb_engine_create: null out");
+  PPB_REQUIRE(max_batch > 0 && height >= 32 && width >= 32, "ppb_engine_create: bad shape batch=%d h=%d w=%d",
+              max_batch, height, width);
+  PPB_REQUIRE(num_classes > 0 && num_classes * num_anchors <= 256 && num_anchors > 0 && num_anchors * 16 <= 256 &&
+                  num_anchors <= 9,
+              "ppb_engine_create: unsupported head size classes=%d anchors=%d (classes*anchors <= 256, anchors <= 9)",
+              num_classes, num_anchors);
+  PPB_CUDA(cudaSetDevice(device));
+  std::unique_ptr<ppb_engine> h(new ppb_engine);
+  Engine& e = h->e;
+  e.device = device;
+  e.max_batch = max_batch;
+  e.H = height;
+  e.W = width;
+  e.num_classes = num_classes;
+  e.num_anchors = num_anchors;
+  int rows = 0, tiles = 0;
+  for (int i = 0; i < 3; ++i) {  // guess_shapes (PyraPose/utils/anchors.py:357-369): (dim + 2^l - 1) // 2^l
+    const int s = 8 << i;
+    e.lvl_h[i] = (height + s - 1) / s;
+    e.lvl_w[i] = (width + s - 1) / s;
+    e.seg_row_begin[i] = rows;
+    e.seg_tile_begin[i] = tiles;
+    const int r = max_batch * (e.lvl_h[i] + 2) * (e.lvl_w[i] + 2);
+    const int t = (r + kConvBlockM - 1) / kConvBlockM;
+    rows += t * kConvBlockM;
+    tiles += t;
+  }
+  e.feat_rows_total = rows;
+  e.feat_tiles_total = tiles;
+  for (int i = 0; i < 16; ++i) {
+    e.dec_mean[i] = 0.0f;
+    e.dec_std[i] = 0.2f;
+  }
+  memset(e.base_anchor, 0, sizeof(e.base_anchor));
+  memset(e.stride, 0, sizeof(e.stride));
+  e.define_layers();
+  int rc = e.allocate_weights();
+  if (rc != kOk) return rc;
+  *out = h.release();
+  return kOk;
+}
+
+void ppb_engine_destroy(ppb_engine* h) {
+  if (h == nullptr) return;
+  cudaSetDevice(h->e.device);
+  delete h;
+}
+
+int ppb_engine_num_layers(const ppb_engine* h) { return h ? static_cast<int>(h->e.layers.size()) : 0; }
+
+int ppb_engine_layer_info(const ppb_engine* h, int index, char* name, int name_cap, int* ksize, int* cin, int* cout,
+                          int* stride, int* has_bn, int* has_bias) {
+  PPB_REQUIRE(h != nullptr && index >= 0 && index < static_cast<int>(h->e.layers.size()),
+              "ppb_engine_layer_info: bad index %d", index);
+  const LayerW& l = h->e.layers[index];
+  if (name != nullptr && name_cap > 0) snprintf(name, name_cap, "%s", l.name.c_str());
+  if (ksize) *ksize = l.ksize;
+  if (cin) *cin = l.cin;
+  if (cout) *cout = l.cout;
+  if (stride) *stride = l.stride;
+  if (has_bn) *has_bn = l.has_bn;
+  if (has_bias) *has_bias = l.has_bias;
+  return kOk;
+}
+
+int ppb_engine_set_layer(ppb_engine* h, const char* name, const float* kernel_hwio_host, const float* bias_host,
+                         const float* bn_gamma_host, const float* bn_beta_host, const float* bn_mean_host,
+                         const float* bn_var_host, float bn_eps) {
+  PPB_REQUIRE(h != nullptr && name != nullptr, "ppb_engine_set_layer: null argument");
+  PPB_CUDA(cudaSetDevice(h->e.device));
+  return h->e.set_layer(name, kernel_hwio_host, bias_host, bn_gamma_host, bn_beta_host, bn_mean_host, bn_var_host,
+                        bn_eps);
+}
+
+int ppb_engine_set_anchors(ppb_engine* h, const float* base_anchors_host, const float* strides_host,
+                           const float* mean16_host, const float* std16_host) {
+  PPB_REQUIRE(h != nullptr && base_anchors_host != nullptr && strides_host != nullptr,
+              "ppb_engine_set_anchors: null argument");
+  Engine& e = h->e;
+  for (int l = 0; l < 3; ++l) {
+    for (int a = 0; a < e.num_anchors; ++a)
+      for (int j = 0; j < 4; ++j) e.base_anchor[l][a][j] = base_anchors_host[(l * e.num_anchors + a) * 4 + j];
+    e.stride[l] = strides_host[l];
+  }
+  if (mean16_host) memcpy(e.dec_mean, mean16_host, sizeof(e.dec_mean));
+  if (std16_host) memcpy(e.dec_std, std16_host, sizeof(e.dec_std));
+  e.anchors_set = true;
+  e.bound_batch = 0;  // parameters are baked into the plan: force a re-bind
+  return kOk;
+}
+
+int ppb_engine_bind(ppb_engine* h, int batch, const float* images, float* out_box3d, float* out_cls, float* out_mask,
+                    float* out_hull, int decode, void* stream) {
+  PPB_REQUIRE(h != nullptr, "ppb_engine_bind: null engine");
+  Engine& e = h->e;
+  PPB_REQUIRE(batch > 0 && batch <= e.max_batch, "ppb_engine_bind: batch %d outside [1, %d]", batch, e.max_batch);
+  PPB_REQUIRE(images != nullptr && out_box3d != nullptr && out_cls != nullptr, "ppb_engine_bind: null buffer");
+  PPB_REQUIRE((reinterpret_cast<uintptr_t>(out_box3d) & 15) == 0 && (reinterpret_cast<uintptr_t>(out_hull) & 15) == 0,
+              "ppb_engine_bind: outputs must be 16-byte aligned");
+  if (decode && !e.anchors_set) return fail(kErrState, "ppb_engine_bind: decode requested before ppb_engine_set_anchors");
+  PPB_CUDA(cudaSetDevice(e.device));
+  int rc = e.build_plan(batch, images, out_box3d, out_cls, out_mask, out_hull, decode);
+  if (rc != kOk) {
+    e.bound_batch = 0;
+    return rc;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaStream_t own = nullptr;
+  if (st == nullptr) {  // the legacy default stream cannot be captured
+    PPB_CUDA(cudaStreamCreateWithFlags(&own, cudaStreamNonBlocking));
+    st = own;
+  }
+  rc = e.capture(st);
+  if (own) cudaStreamDestroy(own);
+  if (rc != kOk) e.bound_batch = 0;
+  return rc;
+}
+
+int ppb_engine_run(ppb_engine* h, void* stream) {
+  PPB_REQUIRE(h != nullptr, "ppb_engine_run: null engine");
+  Engine& e = h->e;
+  if (e.bound_batch == 0 || e.graph_exec == nullptr) return fail(kErrState, "ppb_engine_run: call ppb_engine_bind first");
+  PPB_CUDA(cudaGraphLaunch(e.graph_exec, static_cast<cudaStream_t>(stream)));
+  count_launch(e.graph_kernels);
+  return kOk;
+}
+
+/* Same work as ppb_engine_run but as individual launches (no graph): for profiling with ncu. */
+int ppb_engine_run_eager(ppb_engine* h, void* stream) {
+  PPB_REQUIRE(h != nullptr, "ppb_engine_run_eager: null engine");
+  Engine& e = h->e;
+  if (e.bound_batch == 0) return fail(kErrState, "ppb_engine_run_eager: call ppb_engine_bind first");
+  PPB_CUDA(cudaSetDevice(e.device));
+  const int rc = e.launch_all(static_cast<cudaStream_t>(stream));
+  if (rc == kOk) count_launch(static_cast<int>(e.ops.size()));
+  return rc;
+}
+
+int ppb_engine_kernels_per_run(const ppb_engine* h) { return h ? static_cast<int>(h->e.ops.size()) : 0; }
+
+size_t ppb_engine_device_bytes(const ppb_engine* h) { return h ? h->e.arena_bytes : 0; }
+
+/* Debug/parity: copies a named intermediate activation to the host as fp32 NHWC [batch,H,W,C] (border removed).
+ * Synchronises the device. shape4_host receives {batch,H,W,C}; pass out_host = NULL to query the shape only. */
+int ppb_engine_activation(ppb_engine* h, const char* name, float* out_host, int* shape4_host) {
+  PPB_REQUIRE(h != nullptr && name != nullptr, "ppb_engine_activation: null argument");
+  Engine& e = h->e;
+  PPB_REQUIRE(e.bound_batch > 0, "ppb_engine_activation: nothing bound");
+  Tensor view;
+  Tensor* t = e.tensor(name);
+  const std::string nm(name);
+  if (t == nullptr && (nm == "P3" || nm == "P4" || nm == "P5")) {
+    Tensor* feat = e.tensor("features");
+    PPB_REQUIRE(feat != nullptr, "ppb_engine_activation: features not allocated");
+    const int i = nm[1] - '3';
+    view.ptr = feat->ptr + static_cast<size_t>(e.seg_row_begin[i]) * 256;
+    view.H = e.lvl_h[i];
+    view.W = e.lvl_w[i];
+    view.C = 256;
+    view.pad = 1;
+    t = &view;
+  }
+  PPB_REQUIRE(t != nullptr && t->H > 0, "ppb_engine_activation: unknown tensor '%s'", name);
+  const int B = e.bound_batch;
+  if (shape4_host) {
+    shape4_host[0] = B;
+    shape4_host[1] = t->H;
+    shape4_host[2] = t->W;
+    shape4_host[3] = t->C;
+  }
+  if (out_host == nullptr) return kOk;
+  PPB_CUDA(cudaSetDevice(e.device));
+  PPB_CUDA(cudaDeviceSynchronize());
+  const size_t n = static_cast<size_t>(t->rows(B)) * t->C;
+  std::vector<__nv_bfloat16> host(n);
+  PPB_CUDA(cudaMemcpy(host.data(), t->ptr, n * sizeof(__nv_bfloat16), cudaMemcpyDeviceToHost));
+  const int hp = t->H + 2 * t->pad, wp = t->W + 2 * t->pad;
+  for (int b = 0; b < B; ++b)
+    for (int y = 0; y < t->H; ++y)
+      for (int x = 0; x < t->W; ++x) {
+        const __nv_bfloat16* src = host.data() + ((static_cast<size_t>(b) * hp + y + t->pad) * wp + x + t->pad) * t->C;
+        float* dst = out_host + ((static_cast<size_t>(b) * t->H + y) * t->W + x) * t->C;
+        for (int c = 0; c < t->C; ++c) dst[c] = __bfloat162float(src[c]);
+      }
+  return kOk;
+}
+
+}  // extern "C"

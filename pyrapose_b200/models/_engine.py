@@ -1,0 +1,130 @@
+"""Python handle of the native PFPN engine (ppb_engine_* in include/pyrapose_b200.h).
+
+Owns the torch tensors the engine is bound to (input staging + outputs), so that predict_on_batch is:
+pinned host -> device copy, one CUDA-graph launch, device -> host copy."""
+import ctypes
+
+import numpy as np
+import torch
+
+from .. import _native as nat
+
+_f32p = ctypes.POINTER(ctypes.c_float)
+
+
+def _fp(a):
+    if a is None:
+        return None
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return a.ctypes.data_as(_f32p), a  # keep the array alive alongside the pointer
+
+
+class Engine(object):
+    def __init__(self, device, max_batch, height, width, num_classes, num_anchors):
+        self.lib = nat.load()
+        self.lib.ppb_engine_device_bytes.restype = ctypes.c_size_t
+        self.device = torch.device("cuda", device if device is not None else torch.cuda.current_device())
+        self.max_batch = int(max_batch)
+        self.height, self.width = int(height), int(width)
+        self.num_classes, self.num_anchors = int(num_classes), int(num_anchors)
+        self._h = ctypes.c_void_p()
+        nat.check(self.lib.ppb_engine_create(ctypes.byref(self._h), self.device.index, self.max_batch, self.height,
+                                             self.width, self.num_classes, self.num_anchors))
+        self.levels = [((self.height + (8 << i) - 1) // (8 << i), (self.width + (8 << i) - 1) // (8 << i))
+                       for i in range(3)]
+        self.num_locations = sum(h * w for h, w in self.levels)
+        self.num_boxes = self.num_locations * self.num_anchors
+        self._bound = None
+        self.buffers = {}
+
+    def close(self):
+        if self._h:
+            self.lib.ppb_engine_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ weights
+    def layer_table(self):
+        out = []
+        name = ctypes.create_string_buffer(128)
+        vals = [ctypes.c_int() for _ in range(6)]
+        for i in range(self.lib.ppb_engine_num_layers(self._h)):
+            nat.check(self.lib.ppb_engine_layer_info(self._h, i, name, 128, *[ctypes.byref(v) for v in vals]))
+            out.append((name.value.decode(),) + tuple(v.value for v in vals))
+        return out
+
+    def load_weights(self, weights, bn_names, bn_eps=1e-5):
+        """weights: {"<layer>/kernel": HWIO, "<layer>/bias", "<bn>/gamma|beta|moving_mean|moving_variance"};
+        bn_names: {conv layer name -> its BatchNorm layer name}."""
+        for (name, k, cin, cout, stride, has_bn, has_bias) in self.layer_table():
+            kern = weights[name + "/kernel"]
+            if tuple(kern.shape) != (k, k, cin, cout):
+                raise ValueError("layer %s: kernel shape %s, expected %s" % (name, tuple(kern.shape), (k, k, cin, cout)))
+            keep = []
+            args = []
+            for arr in ([kern, weights.get(name + "/bias") if has_bias else None] +
+                        ([weights[bn_names[name] + s] for s in ("/gamma", "/beta", "/moving_mean", "/moving_variance")]
+                         if has_bn else [None] * 4)):
+                if arr is None:
+                    args.append(None)
+                else:
+                    p, a = _fp(arr)
+                    keep.append(a)
+                    args.append(p)
+            nat.check(self.lib.ppb_engine_set_layer(self._h, name.encode(), *args, ctypes.c_float(bn_eps)))
+        self._bound = None
+
+    def set_anchors(self, base_anchors_f32, strides, mean=None, std=None):
+        b, keep_b = _fp(base_anchors_f32)
+        s, keep_s = _fp(strides)
+        m = _fp(mean) if mean is not None else (None, None)
+        d = _fp(std) if std is not None else (None, None)
+        nat.check(self.lib.ppb_engine_set_anchors(self._h, b, s, m[0], d[0]))
+        self._bound = None
+
+    # ------------------------------------------------------------------ execution
+    def bind(self, batch, decode=True, want_mask=True, want_hull=False):
+        key = (int(batch), bool(decode), bool(want_mask), bool(want_hull))
+        if self._bound == key:
+            return self.buffers
+        dev = self.device
+        B, N, C = int(batch), self.num_boxes, self.num_classes
+        mh, mw = self.levels[0]
+        buf = {
+            "images": torch.empty((B, self.height, self.width, 3), dtype=torch.float32, device=dev),
+            "boxes3D": torch.empty((B, N, 16), dtype=torch.float32, device=dev),
+            "cls": torch.empty((B, N, C), dtype=torch.float32, device=dev),
+            "mask": torch.empty((B, mh * mw, C), dtype=torch.float32, device=dev) if want_mask else None,
+            "hull": torch.empty((B, N, 4), dtype=torch.float32, device=dev) if want_hull else None,
+        }
+        with torch.cuda.device(dev):
+            torch.cuda.current_stream().synchronize()
+            nat.check(self.lib.ppb_engine_bind(self._h, B, nat.ptr(buf["images"]), nat.ptr(buf["boxes3D"]),
+                                               nat.ptr(buf["cls"]), nat.ptr(buf["mask"]), nat.ptr(buf["hull"]),
+                                               int(decode), None))
+        self.buffers = buf
+        self._bound = key
+        return buf
+
+    def run(self, eager=False):
+        with torch.cuda.device(self.device):
+            fn = self.lib.ppb_engine_run_eager if eager else self.lib.ppb_engine_run
+            nat.check(fn(self._h, nat.current_stream_ptr()))
+
+    def kernels_per_run(self):
+        return int(self.lib.ppb_engine_kernels_per_run(self._h))
+
+    def device_bytes(self):
+        return int(self.lib.ppb_engine_device_bytes(self._h))
+
+    def activation(self, name):
+        shape = (ctypes.c_int * 4)()
+        nat.check(self.lib.ppb_engine_activation(self._h, name.encode(), None, shape))
+        out = np.empty(tuple(shape), dtype=np.float32)
+        nat.check(self.lib.ppb_engine_activation(self._h, name.encode(), out.ctypes.data_as(_f32p), shape))
+        return out

@@ -1,0 +1,190 @@
+"""PFPN model objects — mirror of the builders in PyraPose/models/retinanet.py.
+
+  retinanet(inputs, backbone_layers, num_classes, ...)   -> training model, outputs ['3Dbox', 'cls', 'mask'] (:260-299)
+  retinanet_bbox(model, nms, class_specific_filter, ...) -> inference model, outputs [boxes3D, cls, mask]      (:302-335)
+
+The returned PFPNModel answers the calls the reference's callers make on a keras.Model for this path:
+predict_on_batch, output_names, load_weights(by_name=True), save / save_weights, summary, get_layer(name).weights.
+The graph itself runs in the native engine (tcgen05 implicit-GEMM convolutions, one CUDA graph per batch size).
+"""
+import numpy as np
+
+from . import assert_training_model, spec
+from ..utils.anchors import AnchorParameters, generate_anchors
+
+
+class _LayerView(object):
+    def __init__(self, model, name):
+        self.name = name
+        self._model = model
+
+    def get_weights(self):
+        keys = [k for k in self._model.weights if k.split("/")[0] == self.name]
+        order = {"kernel": 0, "bias": 1, "gamma": 0, "beta": 1, "moving_mean": 2, "moving_variance": 3}
+        return [self._model.weights[k] for k in sorted(keys, key=lambda k: order[k.split("/")[1]])]
+
+
+class PFPNModel(object):
+    def __init__(self, num_classes, num_anchors=None, name='retinanet', inference=False, anchor_params=None,
+                 weights=None, seed=None, device=None):
+        self.num_classes = int(num_classes)
+        self.num_anchors = int(num_anchors if num_anchors is not None else AnchorParameters.default.num_anchors())
+        self.name = name
+        self.inference = bool(inference)
+        self.anchor_params = anchor_params if anchor_params is not None else AnchorParameters.default
+        self.device = device
+        self.layers = spec.all_layers(self.num_classes, self.num_anchors)
+        self.weights = weights if weights is not None else spec.init_weights(
+            self.num_classes, self.num_anchors, seed=1 if seed is None else seed)
+        self._engines = {}
+        self.regress_mean = None   # RegressBoxes3D(mean, std) defaults: 0 / 0.2 (layers/_misc.py:176-179)
+        self.regress_std = None
+
+    # ------------------------------------------------------------------ keras.Model-like surface
+    @property
+    def output_names(self):
+        return ['boxes3D', 'cls', 'mask'] if self.inference else ['3Dbox', 'cls', 'mask']
+
+    def get_layer(self, name):
+        if not any(k.split("/")[0] == name for k in self.weights):
+            raise ValueError('No such layer: ' + name)
+        return _LayerView(self, name)
+
+    def summary(self, print_fn=print):
+        total = 0
+        print_fn('Model: "%s"' % self.name)
+        for l in self.layers:
+            n = l.ksize * l.ksize * l.cin * l.cout + (l.cout if l.use_bias else 0) + (4 * l.cout if l.bn else 0)
+            total += n
+            print_fn("%-28s conv %dx%d/%d  %4d -> %4d  params %d" % (l.name, l.ksize, l.ksize, l.stride, l.cin, l.cout, n))
+        print_fn("Total params: {:,}".format(total))
+
+    def get_weights_dict(self):
+        return self.weights
+
+    def set_weights_dict(self, weights, skip_mismatch=False):
+        for k, v in weights.items():
+            if k not in self.weights:
+                continue  # by_name semantics: unknown names are ignored
+            v = np.asarray(v, dtype=np.float32)
+            if v.shape != self.weights[k].shape:
+                if skip_mismatch:
+                    continue
+                raise ValueError("shape mismatch for %s: %s vs %s" % (k, v.shape, self.weights[k].shape))
+            self.weights[k] = v
+        for e in self._engines.values():
+            e.load_weights(self.weights, self._bn_names())
+
+    def load_weights(self, filepath, by_name=True, skip_mismatch=False):
+        """npz container keyed '<keras layer name>/<param>' (HWIO kernels). by_name=True semantics."""
+        with np.load(filepath) as z:
+            self.set_weights_dict({k: z[k] for k in z.files if not k.startswith("__")}, skip_mismatch=skip_mismatch)
+
+    def save_weights(self, filepath):
+        np.savez(filepath, **self.weights)
+
+    def save(self, filepath):
+        meta = np.array([self.num_classes, self.num_anchors, int(self.inference)], dtype=np.int64)
+        with open(filepath, "wb") as f:
+            np.savez(f, __meta__=meta, **self.weights)
+
+    @classmethod
+    def load(cls, filepath):
+        with np.load(filepath) as z:
+            meta = z["__meta__"]
+            weights = {k: z[k] for k in z.files if not k.startswith("__")}
+        return cls(int(meta[0]), int(meta[1]), inference=bool(meta[2]), weights=weights)
+
+    # ------------------------------------------------------------------ engine plumbing
+    def _bn_names(self):
+        return {l.name: l.bn for l in self.layers if l.bn}
+
+    def _engine(self, batch, height, width):
+        import torch
+        from ._engine import Engine
+        key = (height, width)
+        eng = self._engines.get(key)
+        if eng is None or eng.max_batch < batch:
+            if eng is not None:
+                eng.close()
+            dev = self.device if self.device is not None else torch.cuda.current_device()
+            eng = Engine(dev, batch, height, width, self.num_classes, self.num_anchors)
+            eng.load_weights(self.weights, self._bn_names())
+            p = self.anchor_params
+            # Anchors layer: float64 base anchors cast to float32 (layers/_misc.py:52-56)
+            base = np.stack([generate_anchors(p.sizes[i], p.ratios, p.scales).astype(np.float32) for i in range(3)])
+            eng.set_anchors(base, np.asarray(p.strides[:3], np.float32), self.regress_mean, self.regress_std)
+            self._engines[key] = eng
+        return eng
+
+    def forward_device(self, images, want_hull=False, eager=False):
+        """images: float32 (B,H,W,3) numpy (pinned or not) or CUDA tensor, BGR mean-subtracted.
+        Returns the engine's output tensors (valid until the next call): dict boxes3D / cls / mask / hull."""
+        import torch
+        if isinstance(images, np.ndarray):
+            if images.ndim != 4 or images.shape[3] != 3:
+                raise ValueError("expected images of shape (B, H, W, 3), got %s" % (images.shape,))
+            src = torch.from_numpy(np.ascontiguousarray(images, dtype=np.float32))
+        else:
+            if images.dim() != 4 or images.shape[3] != 3:
+                raise ValueError("expected images of shape (B, H, W, 3), got %s" % (tuple(images.shape),))
+            src = images.float() if images.dtype != torch.float32 else images
+        B, H, W = int(src.shape[0]), int(src.shape[1]), int(src.shape[2])
+        eng = self._engine(B, H, W)
+        buf = eng.bind(B, decode=self.inference, want_mask=True, want_hull=want_hull)
+        with torch.cuda.device(eng.device):
+            buf["images"].copy_(src, non_blocking=True)
+            eng.run(eager=eager)
+        return buf
+
+    def predict_on_batch(self, x):
+        """ Returns [boxes3D (B,N,16), classification (B,N,C), mask (B,H/8*W/8,C)] float32 numpy for an inference
+        model ([3Dbox, cls, mask] for a training model), as the reference's model.predict_on_batch does
+        (PyraPose/utils/linemod_eval.py:303)."""
+        buf = self.forward_device(x)
+        return [buf["boxes3D"].cpu().numpy(), buf["cls"].cpu().numpy(), buf["mask"].cpu().numpy()]
+
+    def detect_on_batch(self, x, score_threshold=0.05, max_detections=300, nms=True, nms_threshold=0.5,
+                        class_specific_filter=True):
+        """Forward + decode + FilterDetections entirely on the device; only the (B, max_detections, .) results are
+        copied to the host. FilterDetections' 2-D `boxes` input is the axis-aligned hull of the decoded corners
+        (the PyraPose heads produce no 2-D boxes). Returns [boxes, boxes3D, scores, labels] numpy."""
+        from .. import _kernels
+        if not self.inference:
+            raise ValueError("detect_on_batch needs an inference model (models.convert_model)")
+        buf = self.forward_device(x, want_hull=True)
+        out = _kernels.filter_detections(buf["hull"], buf["boxes3D"], buf["cls"],
+                                         class_specific_filter=class_specific_filter, nms=nms,
+                                         score_threshold=score_threshold, max_detections=max_detections,
+                                         nms_threshold=nms_threshold)
+        return [o.cpu().numpy() for o in out]
+
+    def activation(self, name, height, width):
+        return self._engines[(height, width)].activation(name)
+
+
+def retinanet(inputs=None, backbone_layers=None, num_classes=None, num_anchors=None, create_pyramid_features=None,
+              submodels=None, name='retinanet', seed=None, device=None):
+    """ Construct a PFPN training model (outputs '3Dbox', 'cls', 'mask'). `inputs`/`backbone_layers` are accepted for
+    signature compatibility; the ResNet-50 backbone and __create_sparceFPN are built into the engine."""
+    if num_classes is None:
+        raise ValueError("num_classes is required")
+    if create_pyramid_features is not None or submodels is not None:
+        raise NotImplementedError("custom pyramid builders / submodels are not part of the hot path")
+    return PFPNModel(num_classes, num_anchors, name=name, seed=seed, device=device)
+
+
+def retinanet_bbox(model=None, nms=True, class_specific_filter=True, name='retinanet-bbox', anchor_params=None,
+                   **kwargs):
+    """ Inference model: training model + Anchors + RegressBoxes3D. Like the reference (:302-335), `nms` and
+    `class_specific_filter` are accepted and not wired into the graph; use layers.FilterDetections or
+    model.detect_on_batch for filtering."""
+    if anchor_params is None:
+        anchor_params = AnchorParameters.default
+    if model is None:
+        model = retinanet(num_anchors=anchor_params.num_anchors(), **kwargs)
+    else:
+        assert_training_model(model)
+    out = PFPNModel(model.num_classes, model.num_anchors, name=name, inference=True, anchor_params=anchor_params,
+                    weights=model.weights, device=model.device)
+    return out
