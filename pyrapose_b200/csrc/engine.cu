@@ -783,4 +783,40 @@ int ppb_engine_activation(ppb_engine* h, const char* name, float* out_host, int*
   return kOk;
 }
 
+/* Times every launch of one forward pass individually (CUDA events on `stream`, eager launches).
+ * ms_out[i] / kind_out[i] (0 = tcgen05 conv, 1 = stem im2col, 2 = max-pool, 3 = parity planes, 4 = add) for
+ * i < min(cap, kernels_per_run). Synchronises the stream. Used by bench.py for the roofline numbers. */
+int ppb_engine_profile(ppb_engine* h, void* stream, float* ms_out_host, int* kind_out_host, int cap) {
+  PPB_REQUIRE(h != nullptr && ms_out_host != nullptr, "ppb_engine_profile: null argument");
+  Engine& e = h->e;
+  if (e.bound_batch == 0) return fail(kErrState, "ppb_engine_profile: call ppb_engine_bind first");
+  PPB_CUDA(cudaSetDevice(e.device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int n = static_cast<int>(e.ops.size());
+  std::vector<cudaEvent_t> ev(n + 1);
+  for (auto& x : ev) PPB_CUDA(cudaEventCreate(&x));
+  std::vector<Op> all;
+  all.swap(e.ops);
+  int rc = kOk;
+  PPB_CUDA(cudaEventRecord(ev[0], st));
+  for (int i = 0; i < n && rc == kOk; ++i) {
+    e.ops.assign(1, all[i]);
+    rc = e.launch_all(st);
+    cudaEventRecord(ev[i + 1], st);
+  }
+  e.ops.swap(all);
+  cudaError_t sync = cudaStreamSynchronize(st);
+  if (rc == kOk && sync == cudaSuccess) {
+    for (int i = 0; i < n && i < cap; ++i) {
+      cudaEventElapsedTime(&ms_out_host[i], ev[i], ev[i + 1]);
+      if (kind_out_host) kind_out_host[i] = static_cast<int>(e.ops[i].kind);
+    }
+    count_launch(n);
+  }
+  for (auto& x : ev) cudaEventDestroy(x);
+  if (rc != kOk) return rc;
+  PPB_CUDA(sync);
+  return kOk;
+}
+
 }  // extern "C"
