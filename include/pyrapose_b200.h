@@ -176,8 +176,10 @@ PPB_API int ppb_engine_run_eager(ppb_engine* engine, void* stream);
 PPB_API int ppb_engine_kernels_per_run(const ppb_engine* engine);
 PPB_API size_t ppb_engine_device_bytes(const ppb_engine* engine);
 PPB_API int ppb_engine_activation(ppb_engine* engine, const char* name, float* out_host, int* shape4_host);
-/* Per-launch device times of one eager forward pass (CUDA events); kinds: 0 conv, 1 im2col, 2 max-pool,
+/* Per-launch device times of one eager forward pass (CUDA events); kinds: 0 conv, 1 stem-s2d, 2 max-pool,
  * 3 parity planes, 4 add. Fills min(cap, kernels_per_run) entries of the HOST arrays. */
+/* Name (layer name for convolutions) and algorithmic FLOPs of launch `index` of the bound plan. */
+PPB_API int ppb_engine_op_info(const ppb_engine* engine, int index, char* name, int name_cap, double* flops);
 PPB_API int ppb_engine_profile(ppb_engine* engine, void* stream, float* ms_out_host, int* kind_out_host, int cap);
 
 #ifdef __cplusplus

@@ -6,6 +6,7 @@
 #include "launch_count.h"
 
 #include <atomic>
+#include <cstring>
 
 namespace ppb {
 
@@ -23,7 +24,8 @@ void conv_fill_single_seg(ConvParams& p, int batch, int h, int w, int ksize) {
   s.row_begin = 0;
   s.hp = h + 2;
   s.wp = w + 2;
-  s.pad = 1;
+  s.pad_lo = 1;
+  s.pad_hi = 1;
   s.rows = batch * s.hp * s.wp;
   s.tile_begin = 0;
   s.loc_base = 0;
@@ -73,10 +75,18 @@ int ppb_conv2d_bf16(const void* x, const void* weight, const float* bias, const 
   p.res_ld = cout;
   p.out = static_cast<__nv_bfloat16*>(y);
   p.out_ld = cout;
-  CUtensorMap ta, tb;
-  const int rc = conv_encode_tmaps(&ta, &tb, x, p.seg[0].rows, cin, cin, weight, cout, ksize * ksize * cin, p.block_n);
+  CUtensorMap ta, tb, to, tr;
+  int rc = conv_encode_tmaps(&ta, &tb, x, p.seg[0].rows, cin, cin, weight, cout, ksize * ksize * cin, p.block_n);
   if (rc != 0) return fail(kErrCuda, "ppb_conv2d_bf16: cuTensorMapEncodeTiled failed (%d)", rc);
-  PPB_CUDA(conv_launch(ta, tb, p, 0, static_cast<cudaStream_t>(stream)));
+  memset(&to, 0, sizeof(to));
+  memset(&tr, 0, sizeof(tr));
+  p.staged = (cout % 64 == 0 && p.block_n % 64 == 0) ? 1 : 0;
+  if (p.staged) {
+    rc = conv_encode_rows_tmap(&to, y, p.seg[0].rows, cout, cout);
+    if (rc == 0 && residual != nullptr) rc = conv_encode_rows_tmap(&tr, residual, p.seg[0].rows, cout, cout);
+    if (rc != 0) return fail(kErrCuda, "ppb_conv2d_bf16: cuTensorMapEncodeTiled (output) failed (%d)", rc);
+  }
+  PPB_CUDA(conv_launch(ta, tb, to, tr, p, 0, static_cast<cudaStream_t>(stream)));
   count_launch();
   return kOk;
 }

@@ -19,16 +19,24 @@ namespace ppb {
 
 namespace {
 
-constexpr int kStages = 4;
+constexpr int kMaxStages = 4;
 constexpr int kABytes = kConvBlockM * kConvBlockK * 2;        // 16 KiB
 constexpr int kBBytesMax = kConvMaxBlockN * kConvBlockK * 2;  // 32 KiB
 constexpr int kStageBytes = kABytes + kBBytesMax;
 constexpr int kTmemCols = 512;
 constexpr int kAccCols = 256;
 constexpr int kThreads = 256;
-constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
+// Shared memory map (after 1024-B alignment): direct epilogue = 4 pipeline stages; staged epilogue = 3 stages +
+// a 64 KiB output/residual tile R (four 128x64 bf16 chunks in the 128B-swizzled TMA layout). Barriers follow.
+constexpr int kRChunkBytes = kConvBlockM * 64 * 2;  // 16 KiB: 128 rows x 64 bf16
+constexpr int kRBytes = 4 * kRChunkBytes;
+constexpr int kBarOffset = 3 * kStageBytes + kRBytes;  // 208 KiB >= 4 * kStageBytes
+constexpr int kSmemBytes = kBarOffset + 1024 /*alignment slack*/ + 256 /*barriers*/;
+static_assert(kBarOffset >= kMaxStages * kStageBytes, "barriers must not overlap the 4-stage ring");
 
-enum Fault : uint32_t { kFaultEmpty = 1, kFaultFull = 2, kFaultTmemEmpty = 3, kFaultTmemFull = 4 };
+enum Fault : uint32_t {
+  kFaultEmpty = 1, kFaultFull = 2, kFaultTmemEmpty = 3, kFaultTmemFull = 4, kFaultResEmpty = 5, kFaultResFull = 6
+};
 
 struct TileCoord {
   int seg;
@@ -76,9 +84,9 @@ __device__ __forceinline__ RowInfo row_info(const ConvSeg& sg, int m) {
   const int rem = local - r.b * plane;
   const int hy = rem / sg.wp;
   const int wx = rem - hy * sg.wp;
-  r.y = hy - sg.pad;
-  r.x = wx - sg.pad;
-  if (sg.pad) r.interior = r.in_buf && hy >= 1 && hy <= sg.hp - 2 && wx >= 1 && wx <= sg.wp - 2;
+  r.y = hy - sg.pad_lo;
+  r.x = wx - sg.pad_lo;
+  r.interior = r.in_buf && hy >= sg.pad_lo && hy < sg.hp - sg.pad_hi && wx >= sg.pad_lo && wx < sg.wp - sg.pad_hi;
   return r;
 }
 
@@ -142,7 +150,7 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const RowInfo& ri,
 __device__ __forceinline__ void epi_head16(const ConvParams& p, const ConvSeg& sg, int seg_idx, const RowInfo& ri,
                                            int n0, const uint32_t* v) {
   if (!ri.interior || n0 >= p.n_valid) return;
-  const int w = sg.wp - 2 * sg.pad;
+  const int w = sg.wp - sg.pad_lo - sg.pad_hi;
   const size_t loc = static_cast<size_t>(ri.b) * p.locs_per_image + sg.loc_base + ri.y * w + ri.x;
   float* dst = p.out_f32 + loc * p.vals_per_loc + n0;
   float f[16];
@@ -201,15 +209,21 @@ __device__ __forceinline__ void epi_head16(const ConvParams& p, const ConvSeg& s
 
 __global__ void __launch_bounds__(kThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                  const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                   const __grid_constant__ ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kBarOffset);
   uint64_t* full_bar = bars;
-  uint64_t* empty_bar = bars + kStages;
-  uint64_t* tmem_full_bar = bars + 2 * kStages;
-  uint64_t* tmem_empty_bar = bars + 2 * kStages + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+  uint64_t* empty_bar = bars + kMaxStages;
+  uint64_t* tmem_full_bar = bars + 2 * kMaxStages;
+  uint64_t* tmem_empty_bar = bars + 2 * kMaxStages + 2;
+  uint64_t* res_full_bar = bars + 2 * kMaxStages + 4;
+  uint64_t* res_empty_bar = bars + 2 * kMaxStages + 5;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kMaxStages + 6);
+  const bool staged = p.staged != 0;
+  const int n_stages = staged ? 3 : kMaxStages;
+  uint8_t* rbuf = smem + 3 * kStageBytes;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -218,10 +232,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (elect_one()) {
       tma_prefetch_desc(&tmap_a);
       tma_prefetch_desc(&tmap_b);
+      if (staged) {
+        tma_prefetch_desc(&tmap_out);
+        if (p.residual != nullptr) tma_prefetch_desc(&tmap_res);
+      }
     }
   } else if (warp == 1) {
     if (elect_one()) {
-      for (int i = 0; i < kStages; ++i) {
+      for (int i = 0; i < kMaxStages; ++i) {
         mbar_init(&full_bar[i], 1);
         mbar_init(&empty_bar[i], 1);
       }
@@ -229,6 +247,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         mbar_init(&tmem_full_bar[i], 1);
         mbar_init(&tmem_empty_bar[i], 128);
       }
+      mbar_init(res_full_bar, 1);
+      mbar_init(res_empty_bar, 1);
       fence_mbar_init();
     }
   } else if (warp == 2) {
@@ -249,6 +269,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t tx_bytes = kABytes + p.block_n * (kConvBlockK * 2);
+      uint32_t res_phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const TileCoord tc = tile_coord(p, tile);
         const ConvSeg& sg = p.seg[tc.seg];
@@ -260,11 +281,24 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             uint8_t* sa = smem + stage * kStageBytes;
             tma_load_2d(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
             tma_load_2d(sa + kABytes, &tmap_b, (tap * p.cin_blocks + kb) * kConvBlockK, tc.n0, &full_bar[stage]);
-            if (++stage == kStages) {
+            if (++stage == n_stages) {
               stage = 0;
               phase ^= 1;
             }
           }
+        }
+        if (staged) {
+          // The R tile becomes free once the previous tile's TMA store has read it; then either fetch this
+          // tile's residual into it or just hand it to the epilogue warps.
+          mbar_wait(res_empty_bar, res_phase ^ 1, kFaultResEmpty);
+          if (p.residual != nullptr) {
+            mbar_arrive_expect_tx(res_full_bar, static_cast<uint32_t>(kConvBlockM * 2) * p.block_n);
+            for (int c = 0; c < p.block_n; c += 64)
+              tma_load_2d(rbuf + (c >> 6) * kRChunkBytes, &tmap_res, tc.n0 + c, tc.row0, res_full_bar);
+          } else {
+            mbar_arrive(res_full_bar);
+          }
+          res_phase ^= 1;
         }
       }
     }
@@ -291,7 +325,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                         (it | k) != 0 ? 1u : 0u);
           }
           tc_commit(&empty_bar[stage]);
-          if (++stage == kStages) {
+          if (++stage == n_stages) {
             stage = 0;
             phase ^= 1;
           }
@@ -306,6 +340,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int q = warp - 4;  // TMEM lane quadrant this warp may access
     int acc = 0;
     uint32_t acc_phase = 0;
+    uint32_t res_phase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const TileCoord tc = tile_coord(p, tile);
       const ConvSeg& sg = p.seg[tc.seg];
@@ -314,6 +349,61 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       mbar_wait(&tmem_full_bar[acc], acc_phase, kFaultTmemFull);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * kAccCols;
+      if (staged) {
+        // ---- staged bf16 epilogue: accumulators (+bias, +residual, ReLU) -> R tile in smem -> one TMA store
+        mbar_wait(res_full_bar, res_phase, kFaultResFull);
+        res_phase ^= 1;
+        const int row = q * 32 + lane;
+        const bool has_res = p.residual != nullptr;
+        for (int c0 = 0; c0 < p.block_n; c0 += 64) {
+          uint32_t v[64];
+          tmem_ld_32x32(taddr + c0, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+          tmem_ld_32x32(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+          tmem_ld_wait();
+          uint8_t* rowp = rbuf + (c0 >> 6) * kRChunkBytes + row * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint4* sp = reinterpret_cast<uint4*>(rowp + ((j ^ (row & 7)) << 4));  // 128B swizzle: 16-B piece j of row r
+            uint4 o = make_uint4(0u, 0u, 0u, 0u);
+            if (ri.interior) {
+              float f[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j * 8 + e]);
+              if (p.bias != nullptr) {
+                const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + tc.n0 + c0 + j * 8));
+                const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + tc.n0 + c0 + j * 8 + 4));
+                f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+                f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+              }
+              if (has_res) {
+                const uint4 r = *sp;
+                f[0] += bf16_lo(r.x); f[1] += bf16_hi(r.x); f[2] += bf16_lo(r.y); f[3] += bf16_hi(r.y);
+                f[4] += bf16_lo(r.z); f[5] += bf16_hi(r.z); f[6] += bf16_lo(r.w); f[7] += bf16_hi(r.w);
+              }
+              if (p.relu) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.0f);
+              }
+              o.x = pack_bf16x2(f[0], f[1]);
+              o.y = pack_bf16x2(f[2], f[3]);
+              o.z = pack_bf16x2(f[4], f[5]);
+              o.w = pack_bf16x2(f[6], f[7]);
+            }
+            *sp = o;  // border rows and rows past the segment end are stored as zeros
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&tmem_empty_bar[acc]);  // the accumulator is drained: the MMA warp may reuse it
+        fence_proxy_async_smem();           // make the generic-proxy writes to R visible to the TMA store
+        named_bar_sync(1, 128);
+        if (warp == 4 && lane == 0) {  // always the same thread: bulk-async groups are per thread
+          for (int c = 0; c < p.block_n; c += 64)
+            tma_store_2d(&tmap_out, tc.n0 + c, tc.row0, rbuf + (c >> 6) * kRChunkBytes);
+          tma_store_commit();
+          tma_store_wait_read();
+          mbar_arrive(res_empty_bar);
+        }
+      } else {
       for (int c0 = 0; c0 < p.block_n; c0 += 32) {
         if (p.block_n - c0 >= 32) {
           uint32_t v[32];
@@ -338,11 +428,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
       tc_fence_before();
       mbar_arrive(&tmem_empty_bar[acc]);
+      }
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
   }
 
+  if (staged && warp == 4 && lane == 0) tma_store_wait_all();
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
@@ -385,6 +477,10 @@ int encode_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, 
 
 }  // namespace
 
+int conv_encode_rows_tmap(CUtensorMap* tmap, const void* base, long rows, int cols, int ld) {
+  return encode_2d(tmap, base, static_cast<uint64_t>(rows), cols, ld, kConvBlockM);
+}
+
 int conv_encode_tmaps(CUtensorMap* tmap_a, CUtensorMap* tmap_b, const void* a, long a_rows, int a_cols, int a_ld,
                       const void* w, int w_rows, int w_cols, int block_n) {
   int rc = encode_2d(tmap_a, a, static_cast<uint64_t>(a_rows), a_cols, a_ld, kConvBlockM);
@@ -402,8 +498,8 @@ int conv_num_sms() {
   return sms;
 }
 
-cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const ConvParams& p, int max_ctas,
-                        cudaStream_t stream) {
+cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap& tmap_out,
+                        const CUtensorMap& tmap_res, const ConvParams& p, int max_ctas, cudaStream_t stream) {
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
@@ -414,7 +510,7 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
   if (total <= 0) return cudaSuccess;
   int ctas = max_ctas > 0 ? max_ctas : conv_num_sms();
   if (ctas > total) ctas = total;
-  conv_igemm_kernel<<<ctas, kThreads, kSmemBytes, stream>>>(tmap_a, tmap_b, p);
+  conv_igemm_kernel<<<ctas, kThreads, kSmemBytes, stream>>>(tmap_a, tmap_b, tmap_out, tmap_res, p);
   return cudaGetLastError();
 }
 

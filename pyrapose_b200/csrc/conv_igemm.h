@@ -33,7 +33,8 @@ struct ConvSeg {
   int row_begin;   // first row in the A / output matrix; multiple of 128
   int rows;        // valid rows = B*hp*wp
   int hp, wp;      // plane geometry including the border
-  int pad;         // border width: 1 (padded-flat) or 0 (plain rows, every row is an output)
+  int pad_lo;      // border rows/cols before the interior (1 for padded-flat, 0 for the stem's pixel grid)
+  int pad_hi;      // border rows/cols after the interior (1 for padded-flat, 3 for the stem's pixel grid)
   int tile_begin;  // index of this segment's first M tile
   int loc_base;    // head epilogues: first location index of this level inside one image
   int tap_off[kConvMaxTaps];  // signed row offset of each filter tap
@@ -50,6 +51,7 @@ struct ConvParams {
   int n_mtiles;     // over all segments
   int epi;          // ConvEpilogue
   int relu;
+  int staged;       // kEpiBf16 only: epilogue through the shared-memory R tile + TMA store (needs tmap_out / tmap_res)
   const float* bias;              // [n_valid] fp32, BatchNorm folded in; may be null
   const __nv_bfloat16* residual;  // kEpiBf16: added before ReLU; row stride res_ld; may be null
   int res_ld;
@@ -69,9 +71,13 @@ struct ConvParams {
 int conv_encode_tmaps(CUtensorMap* tmap_a, CUtensorMap* tmap_b, const void* a, long a_rows, int a_cols, int a_ld,
                       const void* w, int w_rows, int w_cols, int block_n);
 
-// Launches the persistent kernel on `stream` with at most `max_ctas` CTAs (0 = one per SM).
-cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const ConvParams& p, int max_ctas,
-                        cudaStream_t stream);
+// Tensor map over a row-major bf16 matrix with a {64 cols x 128 rows} box (output store / residual load).
+int conv_encode_rows_tmap(CUtensorMap* tmap, const void* base, long rows, int cols, int ld);
+
+// Launches the persistent kernel on `stream` with at most `max_ctas` CTAs (0 = one per SM). tmap_out / tmap_res are
+// only dereferenced when p.staged is set (tmap_res only when p.residual != nullptr).
+cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap& tmap_out,
+                        const CUtensorMap& tmap_res, const ConvParams& p, int max_ctas, cudaStream_t stream);
 
 // Reads (and clears) the fault record a kernel leaves before trapping on a barrier timeout.
 void conv_read_fault(unsigned int out[4]);

@@ -14,42 +14,39 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
 __device__ __forceinline__ float lo_f(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float hi_f(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
 
-constexpr int kStemK = 192;
-
-__global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restrict__ image,
-                                                          __nv_bfloat16* __restrict__ out, int B, int H, int W, int Ho,
-                                                          int Wo) {
-  // one thread per (output pixel, group of 8 K-columns): 24 groups per row
+__global__ void __launch_bounds__(256) stem_s2d_kernel(const float* __restrict__ image, uint4* __restrict__ out, int B,
+                                                       int H, int W, int Hs, int Ws) {
+  // one thread per S pixel: 2x2 input pixels x 3 channels -> 12 bf16 (+4 zero), two 16-byte stores
   const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const long long total = static_cast<long long>(B) * Ho * Wo * (kStemK / 8);
+  const long long total = static_cast<long long>(B) * Hs * Ws;
   if (t >= total) return;
-  const int g = static_cast<int>(t % (kStemK / 8));
-  const long long pix = t / (kStemK / 8);
-  const int ox = static_cast<int>(pix % Wo);
-  const int oy = static_cast<int>((pix / Wo) % Ho);
-  const int b = static_cast<int>(pix / (static_cast<long long>(Wo) * Ho));
-  float v[8];
+  const int X = static_cast<int>(t % Ws);
+  const int Y = static_cast<int>((t / Ws) % Hs);
+  const int b = static_cast<int>(t / (static_cast<long long>(Ws) * Hs));
+  float v[12];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int k = g * 8 + j;
-    float x = 0.0f;
-    if (k < 147) {
-      const int r = k / 21;
-      const int rem = k - r * 21;
-      const int s = rem / 3;
-      const int c = rem - s * 3;
-      const int iy = 2 * oy + r - 3, ix = 2 * ox + s - 3;
-      if (iy >= 0 && iy < H && ix >= 0 && ix < W)
-        x = __ldg(image + ((static_cast<long long>(b) * H + iy) * W + ix) * 3 + c);
+  for (int py = 0; py < 2; ++py) {
+    const int iy = 2 * (Y - 2) + py;
+#pragma unroll
+    for (int px = 0; px < 2; ++px) {
+      const int ix = 2 * (X - 2) + px;
+      const bool ok = iy >= 0 && iy < H && ix >= 0 && ix < W;
+      const float* src = image + ((static_cast<long long>(b) * H + (ok ? iy : 0)) * W + (ok ? ix : 0)) * 3;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[(py * 2 + px) * 3 + c] = ok ? __ldg(src + c) : 0.0f;
     }
-    v[j] = x;
   }
-  uint4 o;
-  o.x = pack2(v[0], v[1]);
-  o.y = pack2(v[2], v[3]);
-  o.z = pack2(v[4], v[5]);
-  o.w = pack2(v[6], v[7]);
-  reinterpret_cast<uint4*>(out)[t] = o;
+  uint4 lo, hi;
+  lo.x = pack2(v[0], v[1]);
+  lo.y = pack2(v[2], v[3]);
+  lo.z = pack2(v[4], v[5]);
+  lo.w = pack2(v[6], v[7]);
+  hi.x = pack2(v[8], v[9]);
+  hi.y = pack2(v[10], v[11]);
+  hi.z = 0u;
+  hi.w = 0u;
+  out[t * 2] = lo;
+  out[t * 2 + 1] = hi;
 }
 
 __device__ __forceinline__ uint4 max8(uint4 a, uint4 b) {
@@ -62,8 +59,8 @@ __device__ __forceinline__ uint4 max8(uint4 a, uint4 b) {
 }
 
 __global__ void __launch_bounds__(256) maxpool_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int B,
-                                                      int Hi, int Wi, int C8, int Ho, int Wo, int pad_top,
-                                                      int pad_left) {
+                                                      int Hi, int Wi, int in_hs, int in_ws, int C8, int Ho, int Wo,
+                                                      int pad_top, int pad_left) {
   const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const int Hp = Ho + 2, Wp = Wo + 2;
   const long long total = static_cast<long long>(B) * Hp * Wp * C8;
@@ -83,7 +80,7 @@ __global__ void __launch_bounds__(256) maxpool_kernel(const uint4* __restrict__ 
       for (int dx = 0; dx < 3; ++dx) {
         const int ix = 2 * ox + dx - pad_left;
         if (ix < 0 || ix >= Wi) continue;
-        const uint4 v = __ldg(in + ((static_cast<long long>(b) * Hi + iy) * Wi + ix) * C8 + c);
+        const uint4 v = __ldg(in + ((static_cast<long long>(b) * in_hs + iy) * in_ws + ix) * C8 + c);
         r = first ? v : max8(r, v);
         first = false;
       }
@@ -158,20 +155,20 @@ inline unsigned blocks_for(long long total) { return static_cast<unsigned>((tota
 
 }  // namespace
 
-cudaError_t launch_stem_im2col(const float* image, __nv_bfloat16* out, int B, int H, int W, int Ho, int Wo,
-                               cudaStream_t st) {
-  const long long total = static_cast<long long>(B) * Ho * Wo * (kStemK / 8);
-  stem_im2col_kernel<<<blocks_for(total), 256, 0, st>>>(image, out, B, H, W, Ho, Wo);
+cudaError_t launch_stem_s2d(const float* image, __nv_bfloat16* out, int B, int H, int W, int Ho, int Wo,
+                            cudaStream_t st) {
+  const long long total = static_cast<long long>(B) * (Ho + 3) * (Wo + 3);
+  stem_s2d_kernel<<<blocks_for(total), 256, 0, st>>>(image, reinterpret_cast<uint4*>(out), B, H, W, Ho + 3, Wo + 3);
   return cudaGetLastError();
 }
 
-cudaError_t launch_maxpool3x3s2(const __nv_bfloat16* in, __nv_bfloat16* out, int B, int Hi, int Wi, int C, int Ho,
-                                int Wo, cudaStream_t st) {
+cudaError_t launch_maxpool3x3s2(const __nv_bfloat16* in, __nv_bfloat16* out, int B, int Hi, int Wi, int in_hs,
+                                int in_ws, int C, int Ho, int Wo, cudaStream_t st) {
   const int pt = ((Ho - 1) * 2 + 3 - Hi) > 0 ? ((Ho - 1) * 2 + 3 - Hi) / 2 : 0;
   const int pl = ((Wo - 1) * 2 + 3 - Wi) > 0 ? ((Wo - 1) * 2 + 3 - Wi) / 2 : 0;
   const long long total = static_cast<long long>(B) * (Ho + 2) * (Wo + 2) * (C / 8);
   maxpool_kernel<<<blocks_for(total), 256, 0, st>>>(reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(out), B,
-                                                    Hi, Wi, C / 8, Ho, Wo, pt, pl);
+                                                    Hi, Wi, in_hs, in_ws, C / 8, Ho, Wo, pt, pl);
   return cudaGetLastError();
 }
 

@@ -6,14 +6,18 @@
 
 namespace ppb {
 
-// Stem im2col: fp32 NHWC image [B,H,W,3] -> bf16 [B*Ho*Wo, 192] for ZeroPadding2D(3) + 7x7/2 VALID
-// (keras-resnet conv1; PyraPose/models/resnet.py:87). K index = (r*7+s)*3 + c, columns 147..191 zero.
-cudaError_t launch_stem_im2col(const float* image, __nv_bfloat16* out, int B, int H, int W, int Ho, int Wo,
-                               cudaStream_t st);
+// Stem input transform: fp32 NHWC image [B,H,W,3] -> bf16 space-to-depth grid S [B, Ho+3, Wo+3, 16] with
+//   S[b, Y, X, (py*2+px)*3 + c] = image[b, 2*(Y-2)+py, 2*(X-2)+px, c]   (zero outside the image; channels 12..15 zero)
+// so that ZeroPadding2D(3) + 7x7/2 VALID (keras-resnet conv1; PyraPose/models/resnet.py:87) becomes four row-shifted
+// GEMM taps (dy = 0..3) whose A rows are the 64 contiguous values S[b, oy+dy, ox..ox+3, :] — read by TMA through a
+// tensor map whose row stride (32 B) is smaller than its row extent (128 B). No im2col matrix is materialised.
+cudaError_t launch_stem_s2d(const float* image, __nv_bfloat16* out, int B, int H, int W, int Ho, int Wo,
+                            cudaStream_t st);
 
-// MaxPooling2D(3, strides 2, 'same') (keras-resnet pool1): plain [B,Hi,Wi,C] -> padded-flat [B,Ho+2,Wo+2,C].
-cudaError_t launch_maxpool3x3s2(const __nv_bfloat16* in, __nv_bfloat16* out, int B, int Hi, int Wi, int C, int Ho,
-                                int Wo, cudaStream_t st);
+// MaxPooling2D(3, strides 2, 'same') (keras-resnet pool1): input pixel grid [B,in_hs,in_ws,C] of which the top-left
+// Hi x Wi region is valid -> padded-flat [B,Ho+2,Wo+2,C].
+cudaError_t launch_maxpool3x3s2(const __nv_bfloat16* in, __nv_bfloat16* out, int B, int Hi, int Wi, int in_hs,
+                                int in_ws, int C, int Ho, int Wo, cudaStream_t st);
 
 // Parity planes for stride-2 convolutions: plane (ph,pw)[b,i,j] = in[b, 2i+ph, 2j+pw] (zero outside), each plane
 // padded-flat [B,Ho+2,Wo+2,C], planes stored back to back (n_planes = 1: plain subsampling for 1x1/2 convs;

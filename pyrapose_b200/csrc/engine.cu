@@ -16,6 +16,7 @@
 #include "launch_count.h"
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -40,19 +41,21 @@ struct LayerW {
   bool loaded = false;
 };
 
-struct Tensor {  // padded-flat (pad = 1) or plain (pad = 0) bf16 activation
+struct Tensor {  // bf16 activation on a pixel grid with pad_lo border pixels before and pad_hi after the interior
   std::string name;
   __nv_bfloat16* ptr = nullptr;
-  int H = 0, W = 0, C = 0, pad = 1;
-  long long rows(int B) const { return static_cast<long long>(B) * (H + 2 * pad) * (W + 2 * pad); }
+  int H = 0, W = 0, C = 0, pad_lo = 1, pad_hi = 1;  // padded-flat: 1/1; stem grid: 0/3
+  int hp() const { return H + pad_lo + pad_hi; }
+  int wp() const { return W + pad_lo + pad_hi; }
+  long long rows(int B) const { return static_cast<long long>(B) * hp() * wp(); }
 };
 
-enum OpKind { kOpConv, kOpIm2col, kOpMaxpool, kOpPlanes, kOpAdd };
+enum OpKind { kOpConv, kOpStemS2d, kOpMaxpool, kOpPlanes, kOpAdd };
 
 struct Op {
   OpKind kind;
   // conv
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, to, tr;
   ConvParams p;
   // elementwise
   const void* in0 = nullptr;
@@ -61,6 +64,8 @@ struct Op {
   const void* in3 = nullptr;
   void* out = nullptr;
   int a[8] = {0};
+  char name[40] = {0};
+  double flops = 0.0;  // conv: 2 * interior pixels * Cout * K (algorithmic)
 };
 
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
@@ -97,6 +102,9 @@ struct Engine {
   cudaGraphExec_t graph_exec = nullptr;
   int graph_kernels = 0;
   size_t arena_bytes = 0;
+  // TMA-store epilogue (residual tile prefetched by TMA): 0 never; 1 convs with a residual input (measured best);
+  // 2 every backbone / PFPN conv; 3 head towers too. Override with PPB_STAGED_EPILOGUE for experiments.
+  int staged_epilogue = 1;
 
   ~Engine() {
     if (graph_exec) cudaGraphExecDestroy(graph_exec);
@@ -113,7 +121,7 @@ struct Engine {
     l.stride = stride;
     l.has_bn = bn;
     l.has_bias = bias;
-    l.k_total = (ksize == 7) ? 192 : ksize * ksize * cin;
+    l.k_total = (ksize == 7) ? 256 : ksize * ksize * cin;  // stem: 4 row taps x (4 px x 16 ch), see launch_stem_s2d
     l.cout_pad = round_up(cout, 16);
     layer_index[name] = static_cast<int>(layers.size());
     layers.push_back(l);
@@ -134,15 +142,16 @@ struct Engine {
   }
 
   int new_tensor(Tensor** out, const std::string& name, int h, int w, int c, int pad, int planes = 1,
-                 long long rows_override = 0) {
+                 long long rows_override = 0, int pad_hi = -1) {
     std::unique_ptr<Tensor> t(new Tensor);
     t->name = name;
     t->H = h;
     t->W = w;
     t->C = c;
-    t->pad = pad;
+    t->pad_lo = pad;
+    t->pad_hi = pad_hi >= 0 ? pad_hi : pad;
     long long rows = rows_override ? rows_override : t->rows(max_batch) * planes;
-    rows = (rows + kConvBlockM - 1) / kConvBlockM * kConvBlockM;
+    rows = (rows + kConvBlockM - 1) / kConvBlockM * kConvBlockM + kConvBlockM;  // slack: TMA rows may overlap the end
     void* p = nullptr;
     int rc = device_alloc(&p, static_cast<size_t>(rows) * c * sizeof(__nv_bfloat16));
     if (rc != kOk) return rc;
@@ -242,7 +251,14 @@ int Engine::set_layer(const char* name, const float* kernel, const float* bias, 
       for (int s = 0; s < k; ++s)
         for (int c = 0; c < cin; ++c) {
           const float v = kernel[((static_cast<size_t>(r) * k + s) * cin + c) * cout + o] * scale;
-          w[static_cast<size_t>(o) * l.k_total + (r * k + s) * cin + c] = __float2bfloat16(v);
+          size_t col = static_cast<size_t>(r * k + s) * cin + c;
+          if (k == 7) {
+            // stem over the space-to-depth grid: padded filter row r+1 = 2*dy + py, column s+1 = 2*dx + px;
+            // K index = dy*64 + dx*16 + (py*2+px)*3 + c
+            const int ry = r + 1, rx = s + 1;
+            col = static_cast<size_t>(ry >> 1) * 64 + (rx >> 1) * 16 + ((ry & 1) * 2 + (rx & 1)) * 3 + c;
+          }
+          w[static_cast<size_t>(o) * l.k_total + col] = __float2bfloat16(v);
         }
   }
   PPB_CUDA(cudaMemcpy(l.w, w.data(), w.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
@@ -265,18 +281,22 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
   op.kind = kOpConv;
   ConvParams& p = op.p;
   memset(&p, 0, sizeof(p));
-  if (x->pad == 0) {  // stem: plain im2col rows, one tap
+  int a_cols = x->C, a_ld = x->C;
+  if (l.ksize == 7) {  // stem over the space-to-depth grid: 4 row taps, A rows overlap (stride 16 < extent 64)
     p.n_segs = 1;
     ConvSeg& s = p.seg[0];
     s.row_begin = 0;
-    s.hp = y->H;
-    s.wp = y->W;
-    s.pad = 0;
+    s.hp = y->hp();
+    s.wp = y->wp();
+    s.pad_lo = y->pad_lo;
+    s.pad_hi = y->pad_hi;
     s.rows = static_cast<int>(y->rows(batch));
     s.tile_begin = 0;
-    s.tap_off[0] = 0;
-    p.n_taps = 1;
+    for (int dy = 0; dy < 4; ++dy) s.tap_off[dy] = dy * s.wp;
+    p.n_taps = 4;
     p.n_mtiles = (s.rows + kConvBlockM - 1) / kConvBlockM;
+    a_cols = 64;
+    a_ld = 16;
   } else {
     conv_fill_single_seg(p, batch, y->H, y->W, l.ksize);
     if (l.stride == 2 && l.ksize == 3) {
@@ -294,7 +314,7 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
         }
     }
   }
-  p.cin_blocks = x->C / kConvBlockK;
+  p.cin_blocks = a_cols / kConvBlockK;
   p.n_valid = l.cout;
   p.block_n = conv_pick_block_n(l.cout_pad);
   p.n_ntiles = (l.cout_pad + p.block_n - 1) / p.block_n;
@@ -306,8 +326,19 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
   p.out = y->ptr;
   p.out_ld = y->C;
   const long long a_rows = x->rows(batch) * (x_planes > 0 ? x_planes : 1);
-  int rc = conv_encode_tmaps(&op.ta, &op.tb, x->ptr, a_rows, x->C, x->C, l.w, l.cout_pad, l.k_total, p.block_n);
+  int rc = conv_encode_tmaps(&op.ta, &op.tb, x->ptr, a_rows, a_cols, a_ld, l.w, l.cout_pad, l.k_total, p.block_n);
   if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled failed for layer '%s' (%d)", l.name.c_str(), rc);
+  memset(&op.to, 0, sizeof(op.to));
+  memset(&op.tr, 0, sizeof(op.tr));
+  p.staged = (l.cout % 64 == 0 && p.block_n % 64 == 0 &&
+              (staged_epilogue >= 2 || (staged_epilogue == 1 && res != nullptr))) ? 1 : 0;
+  if (p.staged) {
+    rc = conv_encode_rows_tmap(&op.to, y->ptr, y->rows(batch), y->C, y->C);
+    if (rc == 0 && res != nullptr) rc = conv_encode_rows_tmap(&op.tr, res->ptr, res->rows(batch), res->C, res->C);
+    if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled (output) failed for layer '%s' (%d)", l.name.c_str(), rc);
+  }
+  snprintf(op.name, sizeof(op.name), "%s", l.name.c_str());
+  op.flops = 2.0 * batch * y->H * y->W * static_cast<double>(l.cout) * l.ksize * l.ksize * l.cin;
   ops.push_back(op);
   return kOk;
 }
@@ -328,7 +359,8 @@ int Engine::head_conv_op(const __nv_bfloat16* x, int cin, const std::string& lay
     ConvSeg& s = p.seg[i];
     s.hp = lvl_h[i] + 2;
     s.wp = lvl_w[i] + 2;
-    s.pad = 1;
+    s.pad_lo = 1;
+    s.pad_hi = 1;
     s.rows = batch * s.hp * s.wp;
     s.row_begin = seg_row_begin[i];  // laid out for max_batch so the buffers never move
     s.tile_begin = tiles;
@@ -362,6 +394,19 @@ int Engine::head_conv_op(const __nv_bfloat16* x, int cin, const std::string& lay
   memcpy(p.dec_std, dec_std, sizeof(dec_std));
   int rc = conv_encode_tmaps(&op.ta, &op.tb, x, last_row, cin, cin, l.w, l.cout_pad, l.k_total, p.block_n);
   if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled failed for layer '%s' (%d)", l.name.c_str(), rc);
+  memset(&op.to, 0, sizeof(op.to));
+  memset(&op.tr, 0, sizeof(op.tr));
+  p.staged = (epi == kEpiBf16 && l.cout % 64 == 0 && p.block_n % 64 == 0 && staged_epilogue >= 3) ? 1 : 0;
+  if (p.staged) {
+    rc = conv_encode_rows_tmap(&op.to, y, last_row, l.cout, l.cout);
+    if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled (output) failed for layer '%s' (%d)", l.name.c_str(), rc);
+  }
+  snprintf(op.name, sizeof(op.name), "%s", l.name.c_str());
+  {
+    double px = 0;
+    for (int i = 0; i < n_levels; ++i) px += static_cast<double>(lvl_h[i]) * lvl_w[i];
+    op.flops = 2.0 * batch * px * l.cout * 9.0 * cin;
+  }
   ops.push_back(op);
   return kOk;
 }
@@ -389,6 +434,8 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
     op.out = out;
     int k = 0;
     for (int v : args) op.a[k++] = v;
+    static const char* kNames[] = {"conv", "stem_s2d", "maxpool", "parity_planes", "add"};
+    snprintf(op.name, sizeof(op.name), "%s", kNames[kind]);
     ops.push_back(op);
   };
 #define PPB_TRY(expr)          \
@@ -400,13 +447,15 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
   // ---- stem: ZeroPad(3) + 7x7/2 VALID + BN + ReLU, then MaxPool 3x3/2 'same'
   const int h1 = (H + 1) / 2, w1 = (W + 1) / 2;
   const int h2 = (h1 + 1) / 2, w2 = (w1 + 1) / 2;
-  Tensor *col, *stem, *x;
-  PPB_TRY(get(&col, "conv1_im2col", h1, w1, 192, 0));
-  PPB_TRY(get(&stem, "conv1_relu", h1, w1, 64, 0));
+  Tensor *s2d, *stem, *x;
+  s2d = tensor("conv1_s2d");
+  if (s2d == nullptr) PPB_TRY(new_tensor(&s2d, "conv1_s2d", h1, w1, 16, 0, 1, 0, 3));
+  stem = tensor("conv1_relu");
+  if (stem == nullptr) PPB_TRY(new_tensor(&stem, "conv1_relu", h1, w1, 64, 0, 1, 0, 3));
   PPB_TRY(get(&x, "pool1", h2, w2, 64, 1));
-  elementwise(kOpIm2col, images, nullptr, nullptr, nullptr, col->ptr, {batch, H, W, h1, w1});
-  PPB_TRY(conv_op(col, 1, "conv1", nullptr, stem, 1, batch));
-  elementwise(kOpMaxpool, stem->ptr, nullptr, nullptr, nullptr, x->ptr, {batch, h1, w1, 64, h2, w2});
+  elementwise(kOpStemS2d, images, nullptr, nullptr, nullptr, s2d->ptr, {batch, H, W, h1, w1});
+  PPB_TRY(conv_op(s2d, 1, "conv1", nullptr, stem, 1, batch));
+  elementwise(kOpMaxpool, stem->ptr, nullptr, nullptr, nullptr, x->ptr, {batch, h1, w1, stem->hp(), stem->wp(), 64, h2, w2});
 
   // ---- bottleneck stages
   const int blocks[4] = {3, 4, 6, 3};
@@ -490,7 +539,6 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
     fview[i].H = lvl_h[i];
     fview[i].W = lvl_w[i];
     fview[i].C = 256;
-    fview[i].pad = 1;
     PPB_TRY(conv_op(fin[i], 1, pname[i], nullptr, &fview[i], 0, batch));                           // :204,209,212
   }
 
@@ -534,15 +582,15 @@ int Engine::launch_all(cudaStream_t st) {
   for (const Op& op : ops) {
     switch (op.kind) {
       case kOpConv:
-        PPB_CUDA(conv_launch(op.ta, op.tb, op.p, 0, st));
+        PPB_CUDA(conv_launch(op.ta, op.tb, op.to, op.tr, op.p, 0, st));
         break;
-      case kOpIm2col:
-        PPB_CUDA(launch_stem_im2col(static_cast<const float*>(op.in0), static_cast<__nv_bfloat16*>(op.out), op.a[0],
-                                    op.a[1], op.a[2], op.a[3], op.a[4], st));
+      case kOpStemS2d:
+        PPB_CUDA(launch_stem_s2d(static_cast<const float*>(op.in0), static_cast<__nv_bfloat16*>(op.out), op.a[0],
+                                 op.a[1], op.a[2], op.a[3], op.a[4], st));
         break;
       case kOpMaxpool:
         PPB_CUDA(launch_maxpool3x3s2(static_cast<const __nv_bfloat16*>(op.in0), static_cast<__nv_bfloat16*>(op.out),
-                                     op.a[0], op.a[1], op.a[2], op.a[3], op.a[4], op.a[5], st));
+                                     op.a[0], op.a[1], op.a[2], op.a[3], op.a[4], op.a[5], op.a[6], op.a[7], st));
         break;
       case kOpPlanes:
         PPB_CUDA(launch_parity_planes(static_cast<const __nv_bfloat16*>(op.in0), static_cast<__nv_bfloat16*>(op.out),
@@ -631,6 +679,7 @@ int ppb_engine_create(ppb_engine** out, int device, int max_batch, int height, i
   }
   memset(e.base_anchor, 0, sizeof(e.base_anchor));
   memset(e.stride, 0, sizeof(e.stride));
+  if (const char* env = getenv("PPB_STAGED_EPILOGUE")) e.staged_epilogue = atoi(env);
   e.define_layers();
   int rc = e.allocate_weights();
   if (rc != kOk) return rc;
@@ -755,7 +804,6 @@ int ppb_engine_activation(ppb_engine* h, const char* name, float* out_host, int*
     view.H = e.lvl_h[i];
     view.W = e.lvl_w[i];
     view.C = 256;
-    view.pad = 1;
     t = &view;
   }
   PPB_REQUIRE(t != nullptr && t->H > 0, "ppb_engine_activation: unknown tensor '%s'", name);
@@ -772,11 +820,11 @@ int ppb_engine_activation(ppb_engine* h, const char* name, float* out_host, int*
   const size_t n = static_cast<size_t>(t->rows(B)) * t->C;
   std::vector<__nv_bfloat16> host(n);
   PPB_CUDA(cudaMemcpy(host.data(), t->ptr, n * sizeof(__nv_bfloat16), cudaMemcpyDeviceToHost));
-  const int hp = t->H + 2 * t->pad, wp = t->W + 2 * t->pad;
+  const int hp = t->hp(), wp = t->wp();
   for (int b = 0; b < B; ++b)
     for (int y = 0; y < t->H; ++y)
       for (int x = 0; x < t->W; ++x) {
-        const __nv_bfloat16* src = host.data() + ((static_cast<size_t>(b) * hp + y + t->pad) * wp + x + t->pad) * t->C;
+        const __nv_bfloat16* src = host.data() + ((static_cast<size_t>(b) * hp + y + t->pad_lo) * wp + x + t->pad_lo) * t->C;
         float* dst = out_host + ((static_cast<size_t>(b) * t->H + y) * t->W + x) * t->C;
         for (int c = 0; c < t->C; ++c) dst[c] = __bfloat162float(src[c]);
       }
@@ -784,7 +832,7 @@ int ppb_engine_activation(ppb_engine* h, const char* name, float* out_host, int*
 }
 
 /* Times every launch of one forward pass individually (CUDA events on `stream`, eager launches).
- * ms_out[i] / kind_out[i] (0 = tcgen05 conv, 1 = stem im2col, 2 = max-pool, 3 = parity planes, 4 = add) for
+ * ms_out[i] / kind_out[i] (0 = tcgen05 conv, 1 = stem space-to-depth, 2 = max-pool, 3 = parity planes, 4 = add) for
  * i < min(cap, kernels_per_run). Synchronises the stream. Used by bench.py for the roofline numbers. */
 int ppb_engine_profile(ppb_engine* h, void* stream, float* ms_out_host, int* kind_out_host, int cap) {
   PPB_REQUIRE(h != nullptr && ms_out_host != nullptr, "ppb_engine_profile: null argument");
@@ -816,6 +864,13 @@ int ppb_engine_profile(ppb_engine* h, void* stream, float* ms_out_host, int* kin
   for (auto& x : ev) cudaEventDestroy(x);
   if (rc != kOk) return rc;
   PPB_CUDA(sync);
+  return kOk;
+}
+
+int ppb_engine_op_info(const ppb_engine* h, int index, char* name, int name_cap, double* flops) {
+  PPB_REQUIRE(h != nullptr && index >= 0 && index < static_cast<int>(h->e.ops.size()), "ppb_engine_op_info: bad index");
+  if (name != nullptr && name_cap > 0) snprintf(name, name_cap, "%s", h->e.ops[index].name);
+  if (flops) *flops = h->e.ops[index].flops;
   return kOk;
 }
 

@@ -130,10 +130,20 @@ class Engine(object):
         return out
 
     def profile(self):
-        """[(kind, ms)] for every launch of one eager forward pass (kinds: 0 conv, 1 im2col, 2 pool, 3 planes, 4 add)."""
+        """[(kind, ms)] for every launch of one eager forward pass (kinds: 0 conv, 1 stem-s2d, 2 pool, 3 planes, 4 add)."""
         n = self.kernels_per_run()
         ms = (ctypes.c_float * n)()
         kinds = (ctypes.c_int * n)()
         with torch.cuda.device(self.device):
             nat.check(self.lib.ppb_engine_profile(self._h, nat.current_stream_ptr(), ms, kinds, n))
         return [(int(kinds[i]), float(ms[i])) for i in range(n)]
+
+    def op_table(self):
+        """[(name, algorithmic flops)] per launch of the bound plan."""
+        out = []
+        name = ctypes.create_string_buffer(64)
+        fl = ctypes.c_double()
+        for i in range(self.kernels_per_run()):
+            nat.check(self.lib.ppb_engine_op_info(self._h, i, name, 64, ctypes.byref(fl)))
+            out.append((name.value.decode(), fl.value))
+        return out
