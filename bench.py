@@ -62,6 +62,17 @@ def conv_flops_per_image(h, w, num_classes, num_anchors=9):
     return total
 
 
+def bench_weights(args):
+    """Random-init weights of the reference architecture. The reference's own initialisers give every score
+    sigmoid(-4.595) = 0.01 and nothing passes the 0.05 threshold, so the heads are drawn
+    he-normal (logit std ~1.5) and the classification bias is set so that logits ~ N(cls_bias, 1.5^2):
+    -6.0 -> ~2 %% of the 850 500 scores per image pass 0.05 (primary setting), -4.6 -> ~13 %% (dense stress)."""
+    from pyrapose_b200.models import spec
+    w = spec.init_weights(C, A, seed=1, head_init="spread")
+    w["pyramid_classification/bias"] = np.full_like(w["pyramid_classification/bias"], args.cls_bias)
+    return w
+
+
 def make_images(seed, batch):
     rng = np.random.default_rng(seed)
     img = rng.integers(0, 256, (batch, H, W, 3)).astype(np.float32)
@@ -151,7 +162,7 @@ def run_reference(args):
         return
     import torch
     from pyrapose_b200.models import spec
-    weights = spec.init_weights(C, A, seed=1, head_init="spread")
+    weights = bench_weights(args)
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
     sample = 2
@@ -196,7 +207,7 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     B = args.batch
-    weights = spec.init_weights(C, A, seed=1, head_init="spread")
+    weights = bench_weights(args)
     train = models.backbone("resnet50").retinanet(num_classes=C)
     train.set_weights_dict(weights)
     model = models.convert_model(train)
@@ -266,16 +277,22 @@ def run_ours(args):
         peak = float(peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"]))
         # ---- secondary: HBM-bound score pass of the filter (reads B*N*C fp32 once)
         n_boxes = eng.num_boxes
+        pass_rate = float((buf["cls"] > 0.05).float().mean())
+        flush = torch.empty(1 << 30, dtype=torch.uint8, device=dev)  # L2 flush; also hides host launch latency
         for _ in range(3):
-            _kernels.score_mask(buf["cls"], 0.05)
-        s0 = torch.cuda.Event(enable_timing=True)
-        s1 = torch.cuda.Event(enable_timing=True)
-        s0.record()
-        for _ in range(20):
-            _kernels.score_mask(buf["cls"], 0.05)
-        s1.record()
-        torch.cuda.synchronize()
-        mask_ms = s0.elapsed_time(s1) / 20
+            _kernels.score_mask(buf["cls"], 0.05, want_counts=False)
+        ts = []
+        for _ in range(10):
+            flush.fill_(1)
+            s0 = torch.cuda.Event(enable_timing=True)
+            s1 = torch.cuda.Event(enable_timing=True)
+            s0.record()
+            _kernels.score_mask(buf["cls"], 0.05, want_counts=False)
+            s1.record()
+            torch.cuda.synchronize()
+            ts.append(s0.elapsed_time(s1))
+        del flush
+        mask_ms = statistics.median(ts)
         mask_gbs = B * n_boxes * C * 4 / (mask_ms * 1e-3) / 1e9
         # ---- CPU baseline on this box's host cores (bounded sample)
         threads = os.cpu_count() or 1
@@ -288,7 +305,8 @@ def run_ours(args):
             "config": {"workload": "PFPN ResNet-50 inference + 3D-box-corner decode + filter_detections (thr 0.05, NMS 0.5, "
                                    "max 300), batch %d per GPU, 480x640, 15 classes" % B,
                        "global_batch": world * B, "parallelism": "replicas x%d (no collective)" % world,
-                       "weights": "random-init (seed 1), he-normal heads so ~12%% of scores pass 0.05 (filter stress)",
+                       "weights": "random-init (seed 1), he-normal heads, cls bias %.1f: %.1f%% of scores pass 0.05"
+                                  % (args.cls_bias, 100 * pass_rate),
                        "l2": "working set per step (activations ~%.1f GB) far exceeds the 126 MB L2; no flush needed"
                              % (eng.device_bytes() / 1e9)},
             "e2e": {"value": world * B * args.steps / e2e_s, "unit": "images/s", "h2d_bytes_per_step": h2d,
@@ -321,6 +339,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--cpu-images", type=int, default=8)
+    ap.add_argument("--cls-bias", type=float, default=-6.0,
+                    help="classification output bias: -6.0 = ~2%% of scores > 0.05 (primary), -4.6 = ~13%% (dense stress)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -191,13 +191,13 @@ def gather_rows(src, indices):
     return out
 
 
-def score_mask(scores, threshold):
-    """scores f32 [B,N,C] -> (mask u32-as-i32 [B,C,ceil(N/32)], counts i32 [B,C])."""
+def score_mask(scores, threshold, want_counts=True):
+    """scores f32 [B,N,C] -> (mask u32-as-i32 [B,C,ceil(N/32)], counts i32 [B,C] or None)."""
     scores = _dev(scores, torch.float32, "scores")
     B, N, C = scores.shape
     W = (N + 31) // 32
     mask = torch.empty((B, C, W), dtype=torch.int32, device=scores.device)
-    counts = torch.empty((B, C), dtype=torch.int32, device=scores.device)
+    counts = torch.empty((B, C), dtype=torch.int32, device=scores.device) if want_counts else None
     with torch.cuda.device(scores.device):
         nat.check(nat.load().ppb_score_mask(nat.ptr(scores), B, N, C, ctypes.c_float(threshold), nat.ptr(mask),
                                             nat.ptr(counts), _stream()))

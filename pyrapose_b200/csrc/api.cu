@@ -86,6 +86,7 @@ int ppb_conv2d_bf16(const void* x, const void* weight, const float* bias, const 
     if (rc == 0 && residual != nullptr) rc = conv_encode_rows_tmap(&tr, residual, p.seg[0].rows, cout, cout);
     if (rc != 0) return fail(kErrCuda, "ppb_conv2d_bf16: cuTensorMapEncodeTiled (output) failed (%d)", rc);
   }
+  PPB_REQUIRE(conv_plan_smem(p) >= 0, "ppb_conv2d_bf16: cout=%d does not fit the shared-memory plan", cout);
   PPB_CUDA(conv_launch(ta, tb, to, tr, p, 0, static_cast<cudaStream_t>(stream)));
   count_launch();
   return kOk;

@@ -19,23 +19,30 @@ namespace ppb {
 
 namespace {
 
-constexpr int kMaxStages = 4;
-constexpr int kABytes = kConvBlockM * kConvBlockK * 2;        // 16 KiB
-constexpr int kBBytesMax = kConvMaxBlockN * kConvBlockK * 2;  // 32 KiB
-constexpr int kStageBytes = kABytes + kBBytesMax;
+constexpr int kMaxStages = 8;
+constexpr int kMaxRing = 8;
+constexpr int kABytes = kConvBlockM * kConvBlockK * 2;  // 16 KiB
 constexpr int kTmemCols = 512;
 constexpr int kAccCols = 256;
-constexpr int kThreads = 256;
-// Shared memory map (after 1024-B alignment): direct epilogue = 4 pipeline stages; staged epilogue = 3 stages +
-// a 64 KiB output/residual tile R (four 128x64 bf16 chunks in the 128B-swizzled TMA layout). Barriers follow.
-constexpr int kRChunkBytes = kConvBlockM * 64 * 2;  // 16 KiB: 128 rows x 64 bf16
-constexpr int kRBytes = 4 * kRChunkBytes;
-constexpr int kBarOffset = 3 * kStageBytes + kRBytes;  // 208 KiB >= 4 * kStageBytes
-constexpr int kSmemBytes = kBarOffset + 1024 /*alignment slack*/ + 256 /*barriers*/;
-static_assert(kBarOffset >= kMaxStages * kStageBytes, "barriers must not overlap the 4-stage ring");
+constexpr int kCtrlWarps = 4;
+constexpr int kEpiWarps = 8;  // two groups of four: a TMEM lane quadrant is only visible to warp (id % 4)
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kThreads = (kCtrlWarps + kEpiWarps) * 32;
+// Shared memory map (after 1024-B alignment), all sizes per launch (ConvParams::n_stages / ring_slots / block_n):
+//   [0, n_stages * stage_bytes)      TMA->MMA pipeline, stage = {A 128x64 bf16 | B block_n x 64 bf16}
+//   [ring_off, + ring_slots * 16 KiB) epilogue ring. kEpiBf16 staged: 128x64 bf16 chunks in the 128B-swizzled TMA
+//                                     layout (residual prefetched in, result stored out by TMA). Head epilogues:
+//                                     one fp32 [128][vals|1] tile + the row -> output-location table.
+//   [bias_off, + 8 KiB)               fp32 bias of the whole layer
+//   [bar_off, + 512 B)                mbarriers + the TMEM base address
+constexpr int kChunkBytes = kConvBlockM * 64 * 2;  // 16 KiB: 128 rows x 64 bf16
+constexpr int kBiasFloats = 2048;
+constexpr int kBarBytes = 512;
+constexpr int kSmemLimit = 232448;  // 227 KiB opt-in maximum per CTA on sm_100
+constexpr int kSmemBudget = kSmemLimit - 1024 - kBarBytes - kBiasFloats * 4;
 
 enum Fault : uint32_t {
-  kFaultEmpty = 1, kFaultFull = 2, kFaultTmemEmpty = 3, kFaultTmemFull = 4, kFaultResEmpty = 5, kFaultResFull = 6
+  kFaultEmpty = 1, kFaultFull = 2, kFaultTmemEmpty = 3, kFaultTmemFull = 4, kFaultSlotEmpty = 5, kFaultSlotFull = 6
 };
 
 struct TileCoord {
@@ -75,10 +82,6 @@ __device__ __forceinline__ RowInfo row_info(const ConvSeg& sg, int m) {
   RowInfo r;
   const int local = m - sg.row_begin;
   r.in_buf = local < sg.rows;
-  r.interior = r.in_buf;
-  r.b = 0;
-  r.y = 0;
-  r.x = 0;
   const int plane = sg.hp * sg.wp;
   r.b = local / plane;
   const int rem = local - r.b * plane;
@@ -90,9 +93,10 @@ __device__ __forceinline__ RowInfo row_info(const ConvSeg& sg, int m) {
   return r;
 }
 
-// bf16 epilogue for NC (16 or 32) accumulator columns of one row.
+// bf16 epilogue for NC (16 or 32) accumulator columns of one row, straight to global memory.
 template <int NC>
-__device__ __forceinline__ void epi_bf16(const ConvParams& p, const RowInfo& ri, int m, int n0, uint32_t (&v)[NC]) {
+__device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __restrict__ sbias, const RowInfo& ri, int m,
+                                         int n0, uint32_t (&v)[NC]) {
   if (!ri.in_buf || n0 >= p.n_valid) return;
   __nv_bfloat16* dst = p.out + static_cast<size_t>(m) * p.out_ld + n0;
   if (!ri.interior) {
@@ -103,16 +107,12 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const RowInfo& ri,
   }
   float f[NC];
 #pragma unroll
-  for (int j = 0; j < NC; ++j) f[j] = __uint_as_float(v[j]);
-  if (p.bias != nullptr) {
-#pragma unroll
-    for (int j = 0; j < NC; j += 4) {
-      const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + j));
-      f[j] += b4.x;
-      f[j + 1] += b4.y;
-      f[j + 2] += b4.z;
-      f[j + 3] += b4.w;
-    }
+  for (int j = 0; j < NC; j += 4) {
+    const float4 b4 = *reinterpret_cast<const float4*>(sbias + n0 + j);
+    f[j] = __uint_as_float(v[j]) + b4.x;
+    f[j + 1] = __uint_as_float(v[j + 1]) + b4.y;
+    f[j + 2] = __uint_as_float(v[j + 2]) + b4.z;
+    f[j + 3] = __uint_as_float(v[j + 3]) + b4.w;
   }
   if (p.residual != nullptr) {
     const uint4* rp = reinterpret_cast<const uint4*>(p.residual + static_cast<size_t>(m) * p.res_ld + n0);
@@ -144,22 +144,17 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const RowInfo& ri,
   }
 }
 
-// fp32 head epilogue for 16 accumulator columns (= the 16 regression values of one anchor when
-// decoding). Output element (b, loc, n) lives at ((b*locs + loc)*vals + n): Keras' Reshape((-1, 16)) /
-// Reshape((-1, C)) plus Concatenate(axis=1) over pyramid levels (retinanet.py:51, 129, 224-225).
-__device__ __forceinline__ void epi_head16(const ConvParams& p, const ConvSeg& sg, int seg_idx, const RowInfo& ri,
-                                           int n0, const uint32_t* v) {
-  if (!ri.interior || n0 >= p.n_valid) return;
-  const int w = sg.wp - sg.pad_lo - sg.pad_hi;
-  const size_t loc = static_cast<size_t>(ri.b) * p.locs_per_image + sg.loc_base + ri.y * w + ri.x;
-  float* dst = p.out_f32 + loc * p.vals_per_loc + n0;
+// fp32 head epilogue for 16 accumulator columns of one row (= the 16 regression values of one anchor when
+// decoding): bias, then sigmoid or box3D_transform_inv, into the fp32 staging tile `srow` (this row's [vals] slice).
+// The tile is written out afterwards in Keras' Reshape((-1, 16)) / Reshape((-1, C)) + Concatenate(axis=1) order
+// (retinanet.py:51, 129, 224-225), i.e. element (b, loc, n) at ((b*locs + loc)*vals + n).
+__device__ __forceinline__ void epi_head16(const ConvParams& p, const float* __restrict__ sbias, int seg_idx,
+                                           const RowInfo& ri, size_t loc, int n0, const uint32_t* v,
+                                           float* __restrict__ srow) {
+  if (n0 >= p.n_valid) return;
   float f[16];
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    const int n = n0 + j;
-    const float bias = (p.bias != nullptr && n < p.n_valid) ? __ldg(p.bias + n) : 0.0f;
-    f[j] = __uint_as_float(v[j]) + bias;
-  }
+  for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]) + sbias[n0 + j];
   if (p.epi == kEpiHeadSigmoid) {
 #pragma unroll
     for (int j = 0; j < 16; ++j) f[j] = 1.0f / (1.0f + expf(-f[j]));
@@ -183,7 +178,7 @@ __device__ __forceinline__ void epi_head16(const ConvParams& p, const ConvSeg& s
       const float d = __fadd_rn(__fmul_rn(f[j], p.dec_std[j]), p.dec_mean[j]);
       f[j] = __fadd_rn(base, __fmul_rn(d, size));
     }
-    if (p.out_hull != nullptr) {
+    if (p.out_hull != nullptr && ri.interior) {
       float xmin = f[0], xmax = f[0], ymin = f[1], ymax = f[1];
 #pragma unroll
       for (int j = 2; j < 16; j += 2) {
@@ -196,15 +191,9 @@ __device__ __forceinline__ void epi_head16(const ConvParams& p, const ConvSeg& s
       reinterpret_cast<float4*>(p.out_hull)[anchor_idx] = make_float4(xmin, ymin, xmax, ymax);
     }
   }
-  if ((p.vals_per_loc & 3) == 0 && n0 + 16 <= p.n_valid) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-      reinterpret_cast<float4*>(dst)[i] = make_float4(f[i * 4], f[i * 4 + 1], f[i * 4 + 2], f[i * 4 + 3]);
-  } else {
-#pragma unroll
-    for (int j = 0; j < 16; ++j)
-      if (n0 + j < p.n_valid) dst[j] = f[j];
-  }
+  for (int j = 0; j < 16; ++j)
+    if (n0 + j < p.n_valid) srow[n0 + j] = f[j];
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -213,17 +202,20 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                   const __grid_constant__ ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kBarOffset);
+  const int n_stages = p.n_stages;
+  const int stage_bytes = kABytes + p.block_n * (kConvBlockK * 2);
+  uint8_t* ring = smem + n_stages * stage_bytes;
+  float* sbias = reinterpret_cast<float*>(ring + p.ring_slots * kChunkBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sbias) + kBiasFloats * 4);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kMaxStages;
   uint64_t* tmem_full_bar = bars + 2 * kMaxStages;
   uint64_t* tmem_empty_bar = bars + 2 * kMaxStages + 2;
-  uint64_t* res_full_bar = bars + 2 * kMaxStages + 4;
-  uint64_t* res_empty_bar = bars + 2 * kMaxStages + 5;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kMaxStages + 6);
+  uint64_t* slot_full_bar = bars + 2 * kMaxStages + 4;
+  uint64_t* slot_empty_bar = slot_full_bar + kMaxRing;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(slot_empty_bar + kMaxRing);
   const bool staged = p.staged != 0;
-  const int n_stages = staged ? 3 : kMaxStages;
-  uint8_t* rbuf = smem + 3 * kStageBytes;
+  const bool has_res = p.residual != nullptr;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -234,7 +226,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       tma_prefetch_desc(&tmap_b);
       if (staged) {
         tma_prefetch_desc(&tmap_out);
-        if (p.residual != nullptr) tma_prefetch_desc(&tmap_res);
+        if (has_res) tma_prefetch_desc(&tmap_res);
       }
     }
   } else if (warp == 1) {
@@ -245,15 +237,22 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
       for (int i = 0; i < 2; ++i) {
         mbar_init(&tmem_full_bar[i], 1);
-        mbar_init(&tmem_empty_bar[i], 128);
+        mbar_init(&tmem_empty_bar[i], kEpiThreads);
       }
-      mbar_init(res_full_bar, 1);
-      mbar_init(res_empty_bar, 1);
+      for (int i = 0; i < kMaxRing; ++i) {
+        mbar_init(&slot_full_bar[i], 1);
+        mbar_init(&slot_empty_bar[i], 1);
+      }
       fence_mbar_init();
     }
   } else if (warp == 2) {
     tmem_alloc(tmem_slot, kTmemCols);
     tmem_relinquish();
+  }
+  {  // whole-layer bias -> shared memory (zeros when the layer has none / beyond n_valid)
+    const int nb = p.n_ntiles * p.block_n;
+    for (int i = threadIdx.x; i < nb; i += kThreads)
+      sbias[i] = (p.bias != nullptr && i < p.n_valid) ? __ldg(p.bias + i) : 0.0f;
   }
   tc_fence_before();
   __syncthreads();
@@ -262,14 +261,15 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 
   const int total_tiles = p.n_mtiles * p.n_ntiles;
   const int k_iters = p.n_taps * p.cin_blocks;
+  const int n_chunks = p.block_n >> 6;  // staged epilogue: 64-column chunks per tile
+  const int R = p.ring_slots;
 
   if (warp == 0) {
-    // ------------------------------------------------------------ TMA producer
+    // ------------------------------------------------------------ TMA producer (A / B tiles)
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      const uint32_t tx_bytes = kABytes + p.block_n * (kConvBlockK * 2);
-      uint32_t res_phase = 0;
+      const uint32_t tx_bytes = static_cast<uint32_t>(stage_bytes);
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const TileCoord tc = tile_coord(p, tile);
         const ConvSeg& sg = p.seg[tc.seg];
@@ -278,7 +278,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           for (int kb = 0; kb < p.cin_blocks; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1, kFaultEmpty);
             mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-            uint8_t* sa = smem + stage * kStageBytes;
+            uint8_t* sa = smem + stage * stage_bytes;
             tma_load_2d(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
             tma_load_2d(sa + kABytes, &tmap_b, (tap * p.cin_blocks + kb) * kConvBlockK, tc.n0, &full_bar[stage]);
             if (++stage == n_stages) {
@@ -286,19 +286,6 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               phase ^= 1;
             }
           }
-        }
-        if (staged) {
-          // The R tile becomes free once the previous tile's TMA store has read it; then either fetch this
-          // tile's residual into it or just hand it to the epilogue warps.
-          mbar_wait(res_empty_bar, res_phase ^ 1, kFaultResEmpty);
-          if (p.residual != nullptr) {
-            mbar_arrive_expect_tx(res_full_bar, static_cast<uint32_t>(kConvBlockM * 2) * p.block_n);
-            for (int c = 0; c < p.block_n; c += 64)
-              tma_load_2d(rbuf + (c >> 6) * kRChunkBytes, &tmap_res, tc.n0 + c, tc.row0, res_full_bar);
-          } else {
-            mbar_arrive(res_full_bar);
-          }
-          res_phase ^= 1;
         }
       }
     }
@@ -317,7 +304,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         for (int it = 0; it < k_iters; ++it) {
           mbar_wait(&full_bar[stage], phase, kFaultFull);
           tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
+          const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
           const uint32_t b_addr = a_addr + kABytes;
 #pragma unroll
           for (int k = 0; k < kConvBlockK / 16; ++k) {
@@ -335,46 +322,77 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         if (acc == 0) acc_phase ^= 1;
       }
     }
-  } else if (warp >= 4) {
-    // ------------------------------------------------------------ epilogue
-    const int q = warp - 4;  // TMEM lane quadrant this warp may access
+  } else if (warp == 3) {
+    // ------------------------------------------------------------ residual producer (staged epilogue only)
+    // Prefetches the residual chunk of every (tile, 64-column chunk) into the ring slot the epilogue will
+    // overwrite with the result; runs as far ahead as the ring allows.
+    if (staged && has_res && elect_one()) {
+      uint32_t k = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TileCoord tc = tile_coord(p, tile);
+        for (int c = 0; c < n_chunks; ++c, ++k) {
+          const uint32_t s = k % R;
+          const uint32_t ph = (k / R) & 1u;
+          mbar_wait(&slot_empty_bar[s], ph ^ 1u, kFaultSlotEmpty);
+          mbar_arrive_expect_tx(&slot_full_bar[s], kChunkBytes);
+          tma_load_2d(ring + s * kChunkBytes, &tmap_res, tc.n0 + c * 64, tc.row0, &slot_full_bar[s]);
+        }
+      }
+    }
+  } else if (warp >= kCtrlWarps) {
+    // ------------------------------------------------------------ epilogue: 2 groups x 4 lane quadrants
+    const int ew = warp - kCtrlWarps;
+    const int q = ew & 3;   // TMEM lane quadrant this warp may access
+    const int g = ew >> 2;  // group: owns every second column piece
+    const int row = q * 32 + lane;
     int acc = 0;
     uint32_t acc_phase = 0;
-    uint32_t res_phase = 0;
+    uint32_t chunk_base = 0;
+    int prev_slot = -1;  // store thread only: slot whose TMA store was committed last
+    const bool store_thread = (q == 0 && lane == 0);
+    // head epilogues: fp32 staging tile + row table inside the ring area
+    const int sstride = p.vals_per_loc | 1;  // odd stride: conflict-free column writes
+    float* stile = reinterpret_cast<float*>(ring);
+    long long* srow_loc = reinterpret_cast<long long*>(ring + static_cast<size_t>(kConvBlockM) * sstride * 4);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const TileCoord tc = tile_coord(p, tile);
       const ConvSeg& sg = p.seg[tc.seg];
-      const int m = tc.row0 + q * 32 + lane;
+      const int m = tc.row0 + row;
       const RowInfo ri = row_info(sg, m);
       mbar_wait(&tmem_full_bar[acc], acc_phase, kFaultTmemFull);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * kAccCols;
       if (staged) {
-        // ---- staged bf16 epilogue: accumulators (+bias, +residual, ReLU) -> R tile in smem -> one TMA store
-        mbar_wait(res_full_bar, res_phase, kFaultResFull);
-        res_phase ^= 1;
-        const int row = q * 32 + lane;
-        const bool has_res = p.residual != nullptr;
-        for (int c0 = 0; c0 < p.block_n; c0 += 64) {
+        // ---- staged bf16 epilogue: accumulators (+bias, +residual, ReLU) -> ring slot -> TMA store
+        for (int c = 0; c < n_chunks; ++c) {
+          const uint32_t k = chunk_base + c;
+          if ((k & 1u) != static_cast<uint32_t>(g)) continue;
+          const uint32_t s = k % R;
+          const uint32_t ph = (k / R) & 1u;
+          if (has_res) mbar_wait(&slot_full_bar[s], ph, kFaultSlotFull);
+          else mbar_wait(&slot_empty_bar[s], ph ^ 1u, kFaultSlotEmpty);
           uint32_t v[64];
-          tmem_ld_32x32(taddr + c0, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-          tmem_ld_32x32(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+          tmem_ld_32x32(taddr + c * 64, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+          tmem_ld_32x32(taddr + c * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
           tmem_ld_wait();
-          uint8_t* rowp = rbuf + (c0 >> 6) * kRChunkBytes + row * 128;
+          uint8_t* rowp = ring + s * kChunkBytes + row * 128;
+          const float* bsrc = sbias + tc.n0 + c * 64;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            uint4* sp = reinterpret_cast<uint4*>(rowp + ((j ^ (row & 7)) << 4));  // 128B swizzle: 16-B piece j of row r
+            uint4* sp = reinterpret_cast<uint4*>(rowp + ((j ^ (row & 7)) << 4));  // 128B swizzle: 16-B piece j of row
             uint4 o = make_uint4(0u, 0u, 0u, 0u);
             if (ri.interior) {
+              const float4 b0 = *reinterpret_cast<const float4*>(bsrc + j * 8);
+              const float4 b1 = *reinterpret_cast<const float4*>(bsrc + j * 8 + 4);
               float f[8];
-#pragma unroll
-              for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j * 8 + e]);
-              if (p.bias != nullptr) {
-                const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + tc.n0 + c0 + j * 8));
-                const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + tc.n0 + c0 + j * 8 + 4));
-                f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
-                f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
-              }
+              f[0] = __uint_as_float(v[j * 8 + 0]) + b0.x;
+              f[1] = __uint_as_float(v[j * 8 + 1]) + b0.y;
+              f[2] = __uint_as_float(v[j * 8 + 2]) + b0.z;
+              f[3] = __uint_as_float(v[j * 8 + 3]) + b0.w;
+              f[4] = __uint_as_float(v[j * 8 + 4]) + b1.x;
+              f[5] = __uint_as_float(v[j * 8 + 5]) + b1.y;
+              f[6] = __uint_as_float(v[j * 8 + 6]) + b1.z;
+              f[7] = __uint_as_float(v[j * 8 + 7]) + b1.w;
               if (has_res) {
                 const uint4 r = *sp;
                 f[0] += bf16_lo(r.x); f[1] += bf16_hi(r.x); f[2] += bf16_lo(r.y); f[3] += bf16_hi(r.y);
@@ -391,50 +409,83 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             }
             *sp = o;  // border rows and rows past the segment end are stored as zeros
           }
+          fence_proxy_async_smem();  // make the generic-proxy writes visible to the TMA store
+          named_bar_sync(1 + g, 128);
+          if (store_thread) {  // always the same thread per group: bulk-async groups are per thread
+            tma_store_2d(&tmap_out, tc.n0 + c * 64, tc.row0, ring + s * kChunkBytes);
+            tma_store_commit();
+            if (prev_slot >= 0) {
+              tma_store_wait_read1();  // every group but the newest has finished reading its slot
+              mbar_arrive(&slot_empty_bar[prev_slot]);
+            }
+            prev_slot = static_cast<int>(s);
+          }
+        }
+        chunk_base += n_chunks;
+        tc_fence_before();
+        mbar_arrive(&tmem_empty_bar[acc]);  // this thread's share of the accumulator is drained
+      } else if (p.epi == kEpiBf16) {
+        // ---- direct bf16 epilogue: 32-column pieces alternate between the two groups
+        int piece = 0;
+        for (int c0 = 0; c0 < p.block_n; c0 += 32, ++piece) {
+          if ((piece & 1) != g) continue;
+          if (p.block_n - c0 >= 32) {
+            uint32_t v[32];
+            tmem_ld_32x32(taddr + c0, v);
+            tmem_ld_wait();
+            epi_bf16<32>(p, sbias, ri, m, tc.n0 + c0, v);
+          } else {
+            uint32_t v[16];
+            tmem_ld_32x16(taddr + c0, v);
+            tmem_ld_wait();
+            epi_bf16<16>(p, sbias, ri, m, tc.n0 + c0, v);
+          }
         }
         tc_fence_before();
-        mbar_arrive(&tmem_empty_bar[acc]);  // the accumulator is drained: the MMA warp may reuse it
-        fence_proxy_async_smem();           // make the generic-proxy writes to R visible to the TMA store
-        named_bar_sync(1, 128);
-        if (warp == 4 && lane == 0) {  // always the same thread: bulk-async groups are per thread
-          for (int c = 0; c < p.block_n; c += 64)
-            tma_store_2d(&tmap_out, tc.n0 + c, tc.row0, rbuf + (c >> 6) * kRChunkBytes);
-          tma_store_commit();
-          tma_store_wait_read();
-          mbar_arrive(res_empty_bar);
-        }
+        mbar_arrive(&tmem_empty_bar[acc]);
       } else {
-      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
-        if (p.block_n - c0 >= 32) {
-          uint32_t v[32];
-          tmem_ld_32x32(taddr + c0, v);
-          tmem_ld_wait();
-          if (p.epi == kEpiBf16) {
-            epi_bf16<32>(p, ri, m, tc.n0 + c0, v);
+        // ---- head epilogues: fp32 tile staged in shared memory, then written out coalesced
+        const int w = sg.wp - sg.pad_lo - sg.pad_hi;
+        const size_t loc = static_cast<size_t>(ri.b) * p.locs_per_image + sg.loc_base + ri.y * w + ri.x;
+        named_bar_sync(3, kEpiThreads);  // the previous tile's write-out has finished reading the staging tile
+        if (g == 0) srow_loc[row] = ri.interior ? static_cast<long long>(loc) : -1ll;
+        float* srow = stile + static_cast<size_t>(row) * sstride;
+        int piece = 0;
+        for (int c0 = 0; c0 < p.block_n; c0 += 32, ++piece) {
+          if ((piece & 1) != g) continue;
+          if (p.block_n - c0 >= 32) {
+            uint32_t v[32];
+            tmem_ld_32x32(taddr + c0, v);
+            tmem_ld_wait();
+            epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0, v, srow);
+            epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0 + 16, v + 16, srow);
           } else {
-            epi_head16(p, sg, tc.seg, ri, tc.n0 + c0, v);
-            epi_head16(p, sg, tc.seg, ri, tc.n0 + c0 + 16, v + 16);
-          }
-        } else {
-          uint32_t v[16];
-          tmem_ld_32x16(taddr + c0, v);
-          tmem_ld_wait();
-          if (p.epi == kEpiBf16) {
-            epi_bf16<16>(p, ri, m, tc.n0 + c0, v);
-          } else {
-            epi_head16(p, sg, tc.seg, ri, tc.n0 + c0, v);
+            uint32_t v[16];
+            tmem_ld_32x16(taddr + c0, v);
+            tmem_ld_wait();
+            epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0, v, srow);
           }
         }
-      }
-      tc_fence_before();
-      mbar_arrive(&tmem_empty_bar[acc]);
+        tc_fence_before();
+        mbar_arrive(&tmem_empty_bar[acc]);
+        named_bar_sync(4, kEpiThreads);  // staging tile complete
+        // write-out: one warp per row, lanes walk the row's `vals` floats -> 128-byte coalesced stores; consecutive
+        // interior rows are consecutive locations, i.e. adjacent in the output as well
+        const int vals = p.vals_per_loc;
+        for (int r = ew; r < kConvBlockM; r += kEpiWarps) {
+          const long long rl = srow_loc[r];
+          if (rl < 0) continue;
+          float* dst = p.out_f32 + static_cast<size_t>(rl) * vals;
+          const float* src = stile + static_cast<size_t>(r) * sstride;
+          for (int e = lane; e < vals; e += 32) dst[e] = src[e];
+        }
       }
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    if (staged && store_thread) tma_store_wait_all();
   }
 
-  if (staged && warp == 4 && lane == 0) tma_store_wait_all();
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
@@ -498,19 +549,50 @@ int conv_num_sms() {
   return sms;
 }
 
+int conv_plan_smem(ConvParams& p) {
+  const int stage_bytes = kABytes + p.block_n * (kConvBlockK * 2);
+  const int k_iters = p.n_taps * p.cin_blocks;
+  int ring_min = 0, ring_max = 0;
+  if (p.epi == kEpiBf16) {
+    if (p.staged) {
+      ring_min = 4;
+      ring_max = kMaxRing;
+    }
+  } else {
+    const int need = kConvBlockM * (p.vals_per_loc | 1) * 4 + kConvBlockM * 8;
+    ring_min = ring_max = (need + kChunkBytes - 1) / kChunkBytes;
+    if (ring_min > kMaxRing) return -1;
+  }
+  int stages = k_iters < 2 ? 2 : (k_iters > kMaxStages ? kMaxStages : k_iters);
+  while (stages > 2 && stages * stage_bytes + ring_min * kChunkBytes > kSmemBudget) --stages;
+  if (stages * stage_bytes + ring_min * kChunkBytes > kSmemBudget) return -1;
+  // keep at least three pipeline stages for deep K loops, give the rest to the ring
+  int ring = (kSmemBudget - stages * stage_bytes) / kChunkBytes;
+  if (ring > ring_max) ring = ring_max;
+  if (p.epi == kEpiBf16 && p.staged) ring &= ~1;
+  if (ring < ring_min) return -1;
+  if (p.n_ntiles * p.block_n > kBiasFloats) return -1;
+  p.n_stages = stages;
+  p.ring_slots = ring;
+  return stages * stage_bytes + ring * kChunkBytes + kBiasFloats * 4 + kBarBytes + 1024;
+}
+
 cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap& tmap_out,
                         const CUtensorMap& tmap_res, const ConvParams& p, int max_ctas, cudaStream_t stream) {
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(conv_igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+    attr_err = cudaFuncSetAttribute(conv_igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
   });
   if (attr_err != cudaSuccess) return attr_err;
   const int total = p.n_mtiles * p.n_ntiles;
   if (total <= 0) return cudaSuccess;
+  ConvParams q = p;
+  const int smem_bytes = conv_plan_smem(q);
+  if (smem_bytes < 0 || q.n_stages != p.n_stages || q.ring_slots != p.ring_slots) return cudaErrorInvalidConfiguration;
   int ctas = max_ctas > 0 ? max_ctas : conv_num_sms();
   if (ctas > total) ctas = total;
-  conv_igemm_kernel<<<ctas, kThreads, kSmemBytes, stream>>>(tmap_a, tmap_b, tmap_out, tmap_res, p);
+  conv_igemm_kernel<<<ctas, kThreads, smem_bytes, stream>>>(tmap_a, tmap_b, tmap_out, tmap_res, p);
   return cudaGetLastError();
 }
 

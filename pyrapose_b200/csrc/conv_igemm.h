@@ -51,7 +51,9 @@ struct ConvParams {
   int n_mtiles;     // over all segments
   int epi;          // ConvEpilogue
   int relu;
-  int staged;       // kEpiBf16 only: epilogue through the shared-memory R tile + TMA store (needs tmap_out / tmap_res)
+  int staged;       // kEpiBf16 only: epilogue through the shared-memory chunk ring + TMA store (needs tmap_out / tmap_res)
+  int n_stages;     // TMA->MMA pipeline depth (2..8)   } filled by conv_plan_smem()
+  int ring_slots;   // 16 KiB epilogue ring slots        }
   const float* bias;              // [n_valid] fp32, BatchNorm folded in; may be null
   const __nv_bfloat16* residual;  // kEpiBf16: added before ReLU; row stride res_ld; may be null
   int res_ld;
@@ -73,6 +75,10 @@ int conv_encode_tmaps(CUtensorMap* tmap_a, CUtensorMap* tmap_b, const void* a, l
 
 // Tensor map over a row-major bf16 matrix with a {64 cols x 128 rows} box (output store / residual load).
 int conv_encode_rows_tmap(CUtensorMap* tmap, const void* base, long rows, int cols, int ld);
+
+// Chooses pipeline depth and epilogue-ring size for the shared-memory budget (needs block_n, n_taps, cin_blocks,
+// epi, staged, vals_per_loc, n_ntiles). Returns the dynamic shared-memory bytes, or -1 if the shape does not fit.
+int conv_plan_smem(ConvParams& p);
 
 // Launches the persistent kernel on `stream` with at most `max_ctas` CTAs (0 = one per SM). tmap_out / tmap_res are
 // only dereferenced when p.staged is set (tmap_res only when p.residual != nullptr).

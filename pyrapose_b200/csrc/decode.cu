@@ -19,19 +19,23 @@ struct Vec16 {
 };
 
 // groups = values per anchor / 4 (4 for the 16 corner values, 1 for plain boxes).
+// grid (ceil(anchors_per_image * GROUPS / 256), batch): the image index comes from blockIdx.y, so no 64-bit
+// division or modulo is needed to find the (shared) anchor of a thread.
 template <int GROUPS, bool DENORM>
 __global__ void __launch_bounds__(256) transform_inv_kernel(const float4* __restrict__ anchors,
                                                             const float4* __restrict__ deltas,
                                                             float4* __restrict__ out, float4* __restrict__ hull,
-                                                            long long total_anchors, long long anchors_per_image,
-                                                            int anchors_batched, Vec16 mean, Vec16 stdv) {
-  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const long long a = t / GROUPS;
+                                                            unsigned anchors_per_image, int anchors_batched, Vec16 mean,
+                                                            Vec16 stdv) {
+  const unsigned t = blockIdx.x * 256u + threadIdx.x;  // vector index inside the image
+  const unsigned a = t / GROUPS;
   const int g = static_cast<int>(t - a * GROUPS);
-  const bool valid = a < total_anchors;  // no early return: the hull reduction below shuffles across lanes
-  const long long a_src = anchors_batched ? a : (a % anchors_per_image);
+  const bool valid = a < anchors_per_image;  // no early return: the hull reduction below shuffles across lanes
+  const size_t img = static_cast<size_t>(blockIdx.y) * anchors_per_image;
+  const size_t a_src = anchors_batched ? img + a : a;
+  const size_t v = img * GROUPS + t;
   const float4 box = valid ? __ldg(anchors + a_src) : make_float4(0.f, 0.f, 0.f, 0.f);
-  const float4 d = valid ? __ldg(deltas + t) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const float4 d = valid ? __ldg(deltas + v) : make_float4(0.f, 0.f, 0.f, 0.f);
   const float w = box.z - box.x;   // common.py:33
   const float h = box.w - box.y;   // common.py:34
   float4 r;
@@ -45,7 +49,7 @@ __global__ void __launch_bounds__(256) transform_inv_kernel(const float4* __rest
     r.z = r.z / 320.0f;
     r.w = r.w / 240.0f;
   }
-  if (valid) out[t] = r;
+  if (valid) out[v] = r;
   if (GROUPS == 4 && hull != nullptr) {
     // axis-aligned hull of the 8 corners: min/max over the four threads of this anchor
     float xmin = fminf(r.x, r.z), xmax = fmaxf(r.x, r.z), ymin = fminf(r.y, r.w), ymax = fmaxf(r.y, r.w);
@@ -56,7 +60,7 @@ __global__ void __launch_bounds__(256) transform_inv_kernel(const float4* __rest
       ymin = fminf(ymin, __shfl_xor_sync(0xffffffffu, ymin, off));
       ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, off));
     }
-    if (valid && g == 0) hull[a] = make_float4(xmin, ymin, xmax, ymax);
+    if (valid && g == 0) hull[img + a] = make_float4(xmin, ymin, xmax, ymax);
   }
 }
 
@@ -93,18 +97,18 @@ int ppb_box3d_transform_inv_f32(const float* anchors, const float* deltas, float
   if (total == 0) return kOk;
   PPB_REQUIRE(anchors != nullptr && deltas != nullptr && out != nullptr, "ppb_box3d_transform_inv_f32: null buffer");
   const Vec16 mean = load16(mean_host, 0.0f, 16), stdv = load16(std_host, 0.2f, 16);
-  const unsigned blocks = static_cast<unsigned>((total * 4 + 255) / 256);
+  PPB_REQUIRE(anchors_per_image < (1ll << 29) && batch <= 65535, "ppb_box3d_transform_inv_f32: sizes out of range");
+  const dim3 grid(static_cast<unsigned>((anchors_per_image * 4 + 255) / 256), static_cast<unsigned>(batch));
+  const unsigned api = static_cast<unsigned>(anchors_per_image);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (denormalize)
-    transform_inv_kernel<4, true><<<blocks, 256, 0, st>>>(
+    transform_inv_kernel<4, true><<<grid, 256, 0, st>>>(
         reinterpret_cast<const float4*>(anchors), reinterpret_cast<const float4*>(deltas),
-        reinterpret_cast<float4*>(out), reinterpret_cast<float4*>(hull), total, anchors_per_image, anchors_batched,
-        mean, stdv);
+        reinterpret_cast<float4*>(out), reinterpret_cast<float4*>(hull), api, anchors_batched, mean, stdv);
   else
-    transform_inv_kernel<4, false><<<blocks, 256, 0, st>>>(
+    transform_inv_kernel<4, false><<<grid, 256, 0, st>>>(
         reinterpret_cast<const float4*>(anchors), reinterpret_cast<const float4*>(deltas),
-        reinterpret_cast<float4*>(out), reinterpret_cast<float4*>(hull), total, anchors_per_image, anchors_batched,
-        mean, stdv);
+        reinterpret_cast<float4*>(out), reinterpret_cast<float4*>(hull), api, anchors_batched, mean, stdv);
   PPB_CUDA(cudaGetLastError());
   count_launch();
   return kOk;
@@ -118,10 +122,11 @@ int ppb_bbox_transform_inv_f32(const float* anchors, const float* deltas, float*
   if (total == 0) return kOk;
   PPB_REQUIRE(anchors != nullptr && deltas != nullptr && out != nullptr, "ppb_bbox_transform_inv_f32: null buffer");
   const Vec16 mean = load16(mean_host, 0.0f, 4), stdv = load16(std_host, 0.2f, 4);
-  transform_inv_kernel<1, false><<<static_cast<unsigned>((total + 255) / 256), 256, 0,
-                                   static_cast<cudaStream_t>(stream)>>>(
+  PPB_REQUIRE(anchors_per_image < (1ll << 31) && batch <= 65535, "ppb_bbox_transform_inv_f32: sizes out of range");
+  const dim3 grid(static_cast<unsigned>((anchors_per_image + 255) / 256), static_cast<unsigned>(batch));
+  transform_inv_kernel<1, false><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const float4*>(anchors), reinterpret_cast<const float4*>(deltas),
-      reinterpret_cast<float4*>(out), nullptr, total, anchors_per_image, anchors_batched, mean, stdv);
+      reinterpret_cast<float4*>(out), nullptr, static_cast<unsigned>(anchors_per_image), anchors_batched, mean, stdv);
   PPB_CUDA(cudaGetLastError());
   count_launch();
   return kOk;

@@ -102,9 +102,10 @@ struct Engine {
   cudaGraphExec_t graph_exec = nullptr;
   int graph_kernels = 0;
   size_t arena_bytes = 0;
-  // TMA-store epilogue (residual tile prefetched by TMA): 0 never; 1 convs with a residual input (measured best);
-  // 2 every backbone / PFPN conv; 3 head towers too. Override with PPB_STAGED_EPILOGUE for experiments.
-  int staged_epilogue = 1;
+  // TMA-store epilogue through the shared-memory chunk ring (residual chunks prefetched by TMA): 0 never; 1 only convs
+  // with a residual input; 2 every backbone / PFPN conv (measured best, profiles/r01_per_op_staged_variants.txt);
+  // 3 head towers too. Override with PPB_STAGED_EPILOGUE for experiments.
+  int staged_epilogue = 2;
 
   ~Engine() {
     if (graph_exec) cudaGraphExecDestroy(graph_exec);
@@ -337,6 +338,7 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
     if (rc == 0 && res != nullptr) rc = conv_encode_rows_tmap(&op.tr, res->ptr, res->rows(batch), res->C, res->C);
     if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled (output) failed for layer '%s' (%d)", l.name.c_str(), rc);
   }
+  if (conv_plan_smem(p) < 0) return fail(kErrInvalid, "layer '%s' does not fit the shared-memory plan", l.name.c_str());
   snprintf(op.name, sizeof(op.name), "%s", l.name.c_str());
   op.flops = 2.0 * batch * y->H * y->W * static_cast<double>(l.cout) * l.ksize * l.ksize * l.cin;
   ops.push_back(op);
@@ -401,6 +403,7 @@ int Engine::head_conv_op(const __nv_bfloat16* x, int cin, const std::string& lay
     rc = conv_encode_rows_tmap(&op.to, y, last_row, l.cout, l.cout);
     if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled (output) failed for layer '%s' (%d)", l.name.c_str(), rc);
   }
+  if (conv_plan_smem(p) < 0) return fail(kErrInvalid, "layer '%s' does not fit the shared-memory plan", l.name.c_str());
   snprintf(op.name, sizeof(op.name), "%s", l.name.c_str());
   {
     double px = 0;

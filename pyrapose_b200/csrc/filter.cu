@@ -25,7 +25,7 @@
 namespace ppb {
 namespace {
 
-constexpr int kSortSmemKeys = 4096;
+constexpr int kSortSmemKeys = 8192;
 constexpr int kTopkSmemKeys = 16384;
 constexpr int kMaxDetCap = 1024;
 constexpr int kNmsChunk = 256;
@@ -97,10 +97,13 @@ __global__ void __launch_bounds__(256) class_max_kernel(const float* __restrict_
 }
 
 // ------------------------------------------------------------------ score -> bit mask
-// grid (ceil(N/TILE), B), 256 threads. mask[(b*C + c)*W + n/32] bit (n%32) = scores[b, n, c] > thr.
+// grid (ceil(N/TILE), B), TILE/32 warps. mask[(b*C + c)*W + n/32] bit (n%32) = scores[b, n, c] > thr.
+// The [TILE][C] slab of scores is contiguous in memory: it is copied to shared memory with coalesced 128-bit loads,
+// then warp g owns anchors [32g, 32g+32): one LDS + compare + ballot per class, no index arithmetic in the loop.
+// Lane c keeps the word of class c so that the C words leave in one store instruction.
 template <int TILE>
-__global__ void __launch_bounds__(256) score_mask_kernel(const float* __restrict__ scores, int N, int C, float thr,
-                                                         uint32_t* __restrict__ mask, int W) {
+__global__ void __launch_bounds__(TILE) score_mask_kernel(const float* __restrict__ scores, int N, int C, float thr,
+                                                          uint32_t* __restrict__ mask, int W) {
   extern __shared__ float tile[];  // [TILE][C]
   const int b = blockIdx.y;
   const int n0 = blockIdx.x * TILE;
@@ -111,23 +114,27 @@ __global__ void __launch_bounds__(256) score_mask_kernel(const float* __restrict
   if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
     const int vec = elems >> 2;
     const float4* s4 = reinterpret_cast<const float4*>(src);
-    for (int i = threadIdx.x; i < vec; i += 256) reinterpret_cast<float4*>(tile)[i] = __ldg(s4 + i);
-    for (int i = (vec << 2) + threadIdx.x; i < elems; i += 256) tile[i] = __ldg(src + i);
+    for (int i = threadIdx.x; i < vec; i += TILE) reinterpret_cast<float4*>(tile)[i] = __ldg(s4 + i);
+    for (int i = (vec << 2) + threadIdx.x; i < elems; i += TILE) tile[i] = __ldg(src + i);
   } else {
-    for (int i = threadIdx.x; i < elems; i += 256) tile[i] = __ldg(src + i);
+    for (int i = threadIdx.x; i < elems; i += TILE) tile[i] = __ldg(src + i);
   }
   __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int kGroups = TILE / 32;
-  const int items = kGroups * C;
-  for (int it = warp; it < items; it += 8) {
-    const int g = it / C;
-    const int c = it - g * C;
-    const int r = g * 32 + lane;
-    const bool pass = r < rows && tile[r * C + c] > thr;
-    const uint32_t word = __ballot_sync(0xffffffffu, pass);
-    const int widx = (n0 >> 5) + g;
-    if (lane == 0 && widx < W) mask[(static_cast<long long>(b) * C + c) * W + widx] = word;
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int r = g * 32 + lane;
+  const int widx = (n0 >> 5) + g;
+  if (widx >= W) return;
+  const bool in_rows = r < rows;
+  const float* my = tile + (in_rows ? r : 0) * C;
+  uint32_t* dst = mask + static_cast<long long>(b) * C * W + widx;
+  for (int c0 = 0; c0 < C; c0 += 32) {
+    uint32_t mine = 0u;
+    const int cn = min(32, C - c0);
+    for (int c = 0; c < cn; ++c) {
+      const uint32_t word = __ballot_sync(0xffffffffu, in_rows && my[c0 + c] > thr);
+      if (lane == c) mine = word;
+    }
+    if (lane < cn) dst[static_cast<long long>(c0 + lane) * W] = mine;
   }
 }
 
@@ -286,17 +293,23 @@ __device__ __forceinline__ bool iou_exceeds(const NBox& i, const NBox& j, float 
   return inter / (i.area + j.area - inter) > thr;
 }
 
-// grid (C, B), 256 threads. Reads the sorted keys of (b,c); writes up to max_det anchor indices in selection
-// order to sel_idx[(b*C+c)*max_det ...] and their number to sel_cnt.
-__global__ void __launch_bounds__(kNmsChunk) nms_kernel(const uint64_t* __restrict__ keys,
-                                                        const int* __restrict__ counts, int cap,
-                                                        const float* __restrict__ boxes, int N, int C, int do_nms,
-                                                        float thr, int max_det, int* __restrict__ sel_idx,
-                                                        int* __restrict__ sel_cnt) {
+// grid (C, B), 1024 threads = 256 candidates x 4 helpers. Reads the sorted keys of (b,c); writes up to max_det anchor
+// indices in selection order to sel_idx[(b*C+c)*max_det ...] and their number to sel_cnt.
+// Per 256-candidate chunk (descending score): (1) every candidate is tested against the boxes selected so far, the
+// list split four ways over its helpers; (2) the candidate-vs-earlier-candidate suppression bit matrix is built, two
+// 32-bit words per helper; (3) ONE warp resolves the greedy order 32 candidates at a time with ballots/shuffles.
+constexpr int kNmsThreads = 1024;
+constexpr int kNmsWords = kNmsChunk / 32;
+
+__global__ void __launch_bounds__(kNmsThreads) nms_kernel(const uint64_t* __restrict__ keys,
+                                                          const int* __restrict__ counts, int cap,
+                                                          const float* __restrict__ boxes, int N, int C, int do_nms,
+                                                          float thr, int max_det, int* __restrict__ sel_idx,
+                                                          int* __restrict__ sel_cnt) {
   __shared__ NBox sel_box[kMaxDetCap];
   __shared__ NBox chunk_box[kNmsChunk];
   __shared__ uint32_t chunk_idx[kNmsChunk];
-  __shared__ uint32_t supp[kNmsChunk][kNmsChunk / 32];
+  __shared__ uint32_t supp[kNmsChunk][kNmsWords + 1];  // +1: odd row stride, conflict-free row-parallel access
   __shared__ unsigned char alive_s[kNmsChunk];
   __shared__ int n_sel_s;
   const int c = blockIdx.x, b = blockIdx.y;
@@ -311,58 +324,87 @@ __global__ void __launch_bounds__(kNmsChunk) nms_kernel(const uint64_t* __restri
     if (tid == 0) sel_cnt[bc] = m;
     return;
   }
+  const int cand = tid & (kNmsChunk - 1);
+  const int sub = tid >> 8;  // warp-uniform helper index 0..3
   if (tid == 0) n_sel_s = 0;
   __syncthreads();
   for (int cs = 0; cs < n; cs += kNmsChunk) {
     const int n_sel = n_sel_s;
     if (n_sel >= max_det) break;
-    const int i = cs + tid;
+    const int i = cs + cand;
     const bool valid = i < n;
-    NBox me = {0.f, 0.f, 0.f, 0.f, 0.f};
-    uint32_t idx = 0;
+    if (sub == 0) {
+      NBox me = {0.f, 0.f, 0.f, 0.f, 0.f};
+      uint32_t idx = 0;
+      if (valid) {
+        idx = static_cast<uint32_t>(seg[i] & 0xffffffffu);
+        me = normalise(__ldg(reinterpret_cast<const float4*>(boxes) + static_cast<long long>(b) * N + idx));
+      }
+      chunk_box[cand] = me;
+      chunk_idx[cand] = idx;
+      alive_s[cand] = valid;
+    }
+    __syncthreads();
+    const NBox me = chunk_box[cand];
+    // phase 1: against boxes selected in earlier chunks (helper `sub` takes every fourth one)
     if (valid) {
-      idx = static_cast<uint32_t>(seg[i] & 0xffffffffu);
-      me = normalise(__ldg(reinterpret_cast<const float4*>(boxes) + static_cast<long long>(b) * N + idx));
+      bool dead = false;
+      for (int s = sub; s < n_sel && !dead; s += 4) dead = iou_exceeds(me, sel_box[s], thr);
+      if (dead) alive_s[cand] = 0;  // benign race: every writer stores 0
     }
-    // phase 1: against boxes selected in earlier chunks
-    bool alive = valid;
-    for (int s = 0; s < n_sel && alive; ++s)
-      if (iou_exceeds(me, sel_box[s], thr)) alive = false;
-    chunk_box[tid] = me;
-    chunk_idx[tid] = idx;
-    alive_s[tid] = alive;
     __syncthreads();
-    // phase 2: which earlier (higher-scored) members of this chunk would suppress me
-    uint32_t m[kNmsChunk / 32];
+    // phase 2: which earlier (higher-scored) alive members of this chunk would suppress me
+    const bool alive = alive_s[cand] != 0;
 #pragma unroll
-    for (int w = 0; w < kNmsChunk / 32; ++w) m[w] = 0u;
-    if (alive) {
-      for (int j = 0; j < tid; ++j)
-        if (alive_s[j] && iou_exceeds(me, chunk_box[j], thr)) m[j >> 5] |= 1u << (j & 31);
-    }
-#pragma unroll
-    for (int w = 0; w < kNmsChunk / 32; ++w) supp[tid][w] = m[w];
-    __syncthreads();
-    // phase 3: serial greedy resolution inside the chunk
-    if (tid == 0) {
-      uint32_t kept[kNmsChunk / 32];
-#pragma unroll
-      for (int w = 0; w < kNmsChunk / 32; ++w) kept[w] = 0u;
-      int ns = n_sel;
-      const int lim = min(kNmsChunk, n - cs);
-      for (int j = 0; j < lim && ns < max_det; ++j) {
-        if (!alive_s[j]) continue;
-        bool ok = true;
-#pragma unroll
-        for (int w = 0; w < kNmsChunk / 32; ++w) ok = ok && ((supp[j][w] & kept[w]) == 0u);
-        if (ok) {
-          kept[j >> 5] |= 1u << (j & 31);
-          sel_box[ns] = chunk_box[j];
-          out[ns] = static_cast<int>(chunk_idx[j]);
-          ++ns;
+    for (int wi = 0; wi < 2; ++wi) {
+      const int w = sub + wi * 4;
+      uint32_t bits = 0u;
+      if (alive && w * 32 < cand) {
+        const int jend = min(32, cand - w * 32);
+        for (int jj = 0; jj < jend; ++jj) {
+          const int j = w * 32 + jj;
+          if (alive_s[j] && iou_exceeds(me, chunk_box[j], thr)) bits |= 1u << jj;
         }
       }
-      n_sel_s = ns;
+      supp[cand][w] = bits;
+    }
+    __syncthreads();
+    // phase 3: greedy resolution by one warp, 32 candidates per step
+    if (tid < 32) {
+      const int lane = tid;
+      uint32_t kept_w[kNmsWords];
+#pragma unroll
+      for (int w = 0; w < kNmsWords; ++w) kept_w[w] = 0u;
+      int ns = n_sel;
+#pragma unroll
+      for (int sb = 0; sb < kNmsWords; ++sb) {
+        if (ns < max_det) {  // warp-uniform
+          const int cd = sb * 32 + lane;
+          bool a = alive_s[cd] != 0;
+#pragma unroll
+          for (int w = 0; w < kNmsWords; ++w)
+            if (w < sb) a = a && ((supp[cd][w] & kept_w[w]) == 0u);
+          const uint32_t intra = supp[cd][sb];
+          uint32_t rem = __ballot_sync(0xffffffffu, a);
+          uint32_t kept = 0u;
+          while (rem) {  // warp-uniform loop over the still-alive candidates in score order
+            const int li = __ffs(rem) - 1;
+            rem &= rem - 1;
+            const uint32_t wsup = __shfl_sync(0xffffffffu, intra, li);
+            if ((wsup & kept) == 0u) kept |= 1u << li;
+          }
+          kept_w[sb] = kept;
+          if ((kept >> lane) & 1u) {
+            const int pos = ns + __popc(kept & ((1u << lane) - 1u));
+            if (pos < max_det) {
+              sel_box[pos] = chunk_box[cd];
+              out[pos] = static_cast<int>(chunk_idx[cd]);
+            }
+          }
+          ns = min(ns + __popc(kept), max_det);
+        }
+      }
+      if (lane == 0) n_sel_s = ns;
     }
     __syncthreads();
   }
@@ -494,7 +536,7 @@ int launch_score_mask(const float* scores, int B, int N, int C, float thr, uint3
     score_mask_kernel<256><<<dim3((N + 255) / 256, B), 256, 256 * C * 4, st>>>(scores, N, C, thr, mask, W);
   } else {
     PPB_REQUIRE(C <= 352, "score mask: at most 352 classes are supported, got %d", C);
-    score_mask_kernel<32><<<dim3((N + 31) / 32, B), 256, 32 * C * 4, st>>>(scores, N, C, thr, mask, W);
+    score_mask_kernel<32><<<dim3((N + 31) / 32, B), 32, 32 * C * 4, st>>>(scores, N, C, thr, mask, W);
   }
   PPB_CUDA(cudaGetLastError());
   count_launch();
@@ -552,9 +594,14 @@ int ppb_filter_detections(const float* boxes, const float* boxes3D, const float*
   compact_keys_kernel<<<dim3(Ceff, batch), 256, 0, st>>>(w.mask, score_src, n, Ceff, W, score_stride, cap, w.keys,
                                                          w.counts);
   PPB_CUDA(cudaGetLastError());
+  static bool sort_attr_set = false;
+  if (!sort_attr_set) {
+    PPB_CUDA(cudaFuncSetAttribute(sort_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortSmemKeys * 8));
+    sort_attr_set = true;
+  }
   sort_keys_kernel<<<Ceff * batch, 1024, kSortSmemKeys * 8, st>>>(w.keys, w.counts, cap);
   PPB_CUDA(cudaGetLastError());
-  nms_kernel<<<dim3(Ceff, batch), kNmsChunk, 0, st>>>(w.keys, w.counts, cap, boxes, n, Ceff, nms, nms_threshold,
+  nms_kernel<<<dim3(Ceff, batch), kNmsThreads, 0, st>>>(w.keys, w.counts, cap, boxes, n, Ceff, nms, nms_threshold,
                                                       max_detections, w.sel_idx, w.sel_cnt);
   PPB_CUDA(cudaGetLastError());
   const int np2 = next_pow2(Ceff * max_detections);

@@ -30,35 +30,55 @@ __device__ __forceinline__ double iou_plus1(const double b0, const double b1, co
 
 constexpr int kQChunk = 512;  // query boxes staged per pass (512 * 5 doubles = 20 KiB)
 
-// grid: (ceil(N*K / (256*VEC)) , batch). boxes/query/out advance by their batch strides (0 = shared).
+// grid: (ceil(N / kRowsPerBlock), batch), 256 threads. A block owns kRowsPerBlock consecutive anchors = one contiguous
+// slab of the output; the image's query boxes and their areas (pyx:32-35, computed once instead of once per pair) sit
+// in shared memory. Threads walk the slab with 16-byte stores; all index arithmetic is 32-bit and block-local.
+constexpr int kRowsPerBlock = 32;
+constexpr int kQSmemMax = 1024;  // query boxes held in shared memory (5 doubles each = 40 KiB)
+
 template <int VEC>
 __global__ void __launch_bounds__(256) overlap_matrix_kernel(const double* __restrict__ boxes,
                                                              const double* __restrict__ query,
                                                              double* __restrict__ out, long long n, int k,
                                                              long long boxes_bstride, long long query_bstride,
                                                              long long out_bstride) {
+  extern __shared__ double sq[];  // [min(k, kQSmemMax)][5]
+  __shared__ double sb[kRowsPerBlock][4];
   const double* bx = boxes + blockIdx.y * boxes_bstride;
   const double* qx = query + blockIdx.y * query_bstride;
-  double* o = out + blockIdx.y * out_bstride;
-  const long long total = n * k;
-  const long long e0 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * VEC;
-  if (e0 >= total) return;
-  const long long row = e0 / k;
-  const int col = static_cast<int>(e0 - row * k);
-  const double2 b01 = *reinterpret_cast<const double2*>(bx + row * 4);
-  const double2 b23 = *reinterpret_cast<const double2*>(bx + row * 4 + 2);
-  double r[VEC];
-#pragma unroll
-  for (int v = 0; v < VEC; ++v) {
-    const double2 q01 = __ldg(reinterpret_cast<const double2*>(qx + (col + v) * 4));
-    const double2 q23 = __ldg(reinterpret_cast<const double2*>(qx + (col + v) * 4 + 2));
-    const double q_area = (q23.x - q01.x + 1) * (q23.y - q01.y + 1);  // pyx:32-35
-    r[v] = iou_plus1(b01.x, b01.y, b23.x, b23.y, q01.x, q01.y, q23.x, q23.y, q_area);
+  const long long row0 = static_cast<long long>(blockIdx.x) * kRowsPerBlock;
+  const int rows = static_cast<int>(min(static_cast<long long>(kRowsPerBlock), n - row0));
+  double* o = out + blockIdx.y * out_bstride + row0 * k;
+  const int ks = min(k, kQSmemMax);
+  for (int t = threadIdx.x; t < ks; t += 256) {
+    const double2 q01 = __ldg(reinterpret_cast<const double2*>(qx + t * 4));
+    const double2 q23 = __ldg(reinterpret_cast<const double2*>(qx + t * 4 + 2));
+    sq[t * 5 + 0] = q01.x; sq[t * 5 + 1] = q01.y; sq[t * 5 + 2] = q23.x; sq[t * 5 + 3] = q23.y;
+    sq[t * 5 + 4] = (q23.x - q01.x + 1) * (q23.y - q01.y + 1);  // pyx:32-35
   }
-  if (VEC == 2) {
-    *reinterpret_cast<double2*>(o + e0) = make_double2(r[0], r[VEC - 1]);
-  } else {
-    o[e0] = r[0];
+  if (threadIdx.x < rows * 4) (&sb[0][0])[threadIdx.x] = bx[row0 * 4 + threadIdx.x];
+  __syncthreads();
+  const unsigned total = static_cast<unsigned>(rows) * static_cast<unsigned>(k);
+  for (unsigned e0 = threadIdx.x * VEC; e0 < total; e0 += 256 * VEC) {
+    const unsigned row = e0 / static_cast<unsigned>(k);
+    const unsigned col = e0 - row * static_cast<unsigned>(k);
+    const double b0 = sb[row][0], b1 = sb[row][1], b2 = sb[row][2], b3 = sb[row][3];
+    double r[VEC];
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) {
+      const unsigned c = col + v;
+      if (c < static_cast<unsigned>(ks)) {
+        r[v] = iou_plus1(b0, b1, b2, b3, sq[c * 5], sq[c * 5 + 1], sq[c * 5 + 2], sq[c * 5 + 3], sq[c * 5 + 4]);
+      } else {  // more query boxes than the shared-memory window holds: read them from global memory
+        const double q0 = qx[c * 4], q1 = qx[c * 4 + 1], q2 = qx[c * 4 + 2], q3 = qx[c * 4 + 3];
+        r[v] = iou_plus1(b0, b1, b2, b3, q0, q1, q2, q3, (q2 - q0 + 1) * (q3 - q1 + 1));
+      }
+    }
+    if (VEC == 2) {
+      *reinterpret_cast<double2*>(o + e0) = make_double2(r[0], r[VEC - 1]);
+    } else {
+      o[e0] = r[0];
+    }
   }
 }
 
@@ -131,14 +151,16 @@ int ppb_compute_overlap_f64(const double* boxes, const double* query, double* ov
   const long long total = n * k;
   const long long bs = boxes_shared ? 0 : n * 4;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if ((k & 1) == 0) {
-    const unsigned blocks = static_cast<unsigned>((total / 2 + 255) / 256);
-    overlap_matrix_kernel<2><<<dim3(blocks, batch), 256, 0, st>>>(boxes, query, overlaps, n, k, bs,
-                                                                  static_cast<long long>(k) * 4, total);
+  PPB_REQUIRE(k <= (1 << 24) && batch <= 65535, "ppb_compute_overlap_f64: k or batch out of range");
+  const unsigned blocks = static_cast<unsigned>((n + kRowsPerBlock - 1) / kRowsPerBlock);
+  const size_t smem = static_cast<size_t>(k < kQSmemMax ? k : kQSmemMax) * 5 * sizeof(double);
+  // even k keeps every row's first element 16-byte aligned (the output base comes from the caller's allocator)
+  if ((k & 1) == 0 && (reinterpret_cast<uintptr_t>(overlaps) & 15) == 0) {
+    overlap_matrix_kernel<2><<<dim3(blocks, batch), 256, smem, st>>>(boxes, query, overlaps, n, k, bs,
+                                                                     static_cast<long long>(k) * 4, total);
   } else {
-    const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
-    overlap_matrix_kernel<1><<<dim3(blocks, batch), 256, 0, st>>>(boxes, query, overlaps, n, k, bs,
-                                                                  static_cast<long long>(k) * 4, total);
+    overlap_matrix_kernel<1><<<dim3(blocks, batch), 256, smem, st>>>(boxes, query, overlaps, n, k, bs,
+                                                                     static_cast<long long>(k) * 4, total);
   }
   PPB_CUDA(cudaGetLastError());
   count_launch();
