@@ -36,11 +36,37 @@ void conv_fill_single_seg(ConvParams& p, int batch, int h, int w, int ksize) {
   p.n_mtiles = (s.rows + kConvBlockM - 1) / kConvBlockM;
 }
 
-int conv_pick_block_n(int cout_pad) {
-  if (cout_pad <= kConvMaxBlockN) return cout_pad;
-  if (cout_pad % 256 == 0) return 256;
-  if (cout_pad % 128 == 0) return 128;
-  return 64;
+// UMMA N of one tile. Head output convolutions (fp32 epilogues) keep the whole padded Cout in one tile. bf16 layers
+// choose among 256 / 128 / 64 by a static model: wave quantisation over the SMs times the relative efficiency of
+// the tile shape -- K-deep (tensor-bound) layers prefer N = 256 (N = 64 MMAs are shared-memory-bandwidth bound),
+// shallow-K (HBM / epilogue-bound) layers prefer N = 128 so that the epilogue ring holds several tiles of
+// residual / output chunks in flight.
+int conv_pick_block_n(int cout_pad, int k_iters, long m_tiles, bool bf16_out) {
+  if (!bf16_out || cout_pad % 64 != 0) {
+    if (cout_pad <= kConvMaxBlockN) return cout_pad;
+    if (cout_pad % 256 == 0) return 256;
+    if (cout_pad % 128 == 0) return 128;
+    return 64;
+  }
+  const int sms = conv_num_sms() > 0 ? conv_num_sms() : 148;
+  const bool deep = k_iters > 8;
+  const int cand[3] = {256, 128, 64};
+  const double shape_eff_deep[3] = {1.0, 0.93, 0.67};
+  const double shape_eff_shallow[3] = {0.8, 1.0, 0.9};
+  int best = 64;
+  double best_score = -1.0;
+  for (int i = 0; i < 3; ++i) {
+    if (cout_pad % cand[i] != 0) continue;
+    const long tiles = m_tiles * (cout_pad / cand[i]);
+    const long waves = (tiles + sms - 1) / sms;
+    const double score = static_cast<double>(tiles) / static_cast<double>(waves * sms) *
+                         (deep ? shape_eff_deep[i] : shape_eff_shallow[i]);
+    if (score > best_score + 1e-9) {
+      best_score = score;
+      best = cand[i];
+    }
+  }
+  return best;
 }
 
 }  // namespace ppb
@@ -66,7 +92,7 @@ int ppb_conv2d_bf16(const void* x, const void* weight, const float* bias, const 
   conv_fill_single_seg(p, batch, h, w, ksize);
   p.cin_blocks = cin / kConvBlockK;
   p.n_valid = cout;
-  p.block_n = conv_pick_block_n(cout);
+  p.block_n = conv_pick_block_n(cout, p.n_taps * p.cin_blocks, p.n_mtiles, true);
   p.n_ntiles = (cout + p.block_n - 1) / p.block_n;
   p.epi = kEpiBf16;
   p.relu = relu;

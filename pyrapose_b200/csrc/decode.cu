@@ -38,11 +38,24 @@ __global__ void __launch_bounds__(256) transform_inv_kernel(const float4* __rest
   const float4 d = valid ? __ldg(deltas + v) : make_float4(0.f, 0.f, 0.f, 0.f);
   const float w = box.z - box.x;   // common.py:33
   const float h = box.w - box.y;   // common.py:34
+  // pick this thread's four (mean, std) pairs with selects: indexing a by-value parameter array with a runtime
+  // index would force the whole array into local memory
+  float m[4], sd[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    m[j] = mean.v[j];
+    sd[j] = stdv.v[j];
+#pragma unroll
+    for (int gg = 1; gg < GROUPS; ++gg) {
+      m[j] = g == gg ? mean.v[gg * 4 + j] : m[j];
+      sd[j] = g == gg ? stdv.v[gg * 4 + j] : sd[j];
+    }
+  }
   float4 r;
-  r.x = box.x + (d.x * stdv.v[g * 4 + 0] + mean.v[g * 4 + 0]) * w;
-  r.y = box.y + (d.y * stdv.v[g * 4 + 1] + mean.v[g * 4 + 1]) * h;
-  r.z = box.z + (d.z * stdv.v[g * 4 + 2] + mean.v[g * 4 + 2]) * w;
-  r.w = box.w + (d.w * stdv.v[g * 4 + 3] + mean.v[g * 4 + 3]) * h;
+  r.x = box.x + (d.x * sd[0] + m[0]) * w;
+  r.y = box.y + (d.y * sd[1] + m[1]) * h;
+  r.z = box.z + (d.z * sd[2] + m[2]) * w;
+  r.w = box.w + (d.w * sd[3] + m[3]) * h;
   if (DENORM) {  // common.py:69-84
     r.x = r.x / 320.0f;
     r.y = r.y / 240.0f;

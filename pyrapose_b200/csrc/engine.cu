@@ -26,7 +26,7 @@
 namespace ppb {
 
 void conv_fill_single_seg(ConvParams& p, int batch, int h, int w, int ksize);
-int conv_pick_block_n(int cout_pad);
+int conv_pick_block_n(int cout_pad, int k_iters, long m_tiles, bool bf16_out);
 
 namespace {
 
@@ -317,7 +317,7 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
   }
   p.cin_blocks = a_cols / kConvBlockK;
   p.n_valid = l.cout;
-  p.block_n = conv_pick_block_n(l.cout_pad);
+  p.block_n = conv_pick_block_n(l.cout_pad, p.n_taps * p.cin_blocks, p.n_mtiles, true);
   p.n_ntiles = (l.cout_pad + p.block_n - 1) / p.block_n;
   p.epi = kEpiBf16;
   p.relu = relu;
@@ -377,7 +377,7 @@ int Engine::head_conv_op(const __nv_bfloat16* x, int cin, const std::string& lay
   p.n_mtiles = tiles;
   p.cin_blocks = cin / kConvBlockK;
   p.n_valid = l.cout;
-  p.block_n = conv_pick_block_n(l.cout_pad);
+  p.block_n = conv_pick_block_n(l.cout_pad, p.n_taps * p.cin_blocks, p.n_mtiles, epi == kEpiBf16);
   p.n_ntiles = (l.cout_pad + p.block_n - 1) / p.block_n;
   p.epi = epi;
   p.relu = relu;

@@ -159,6 +159,67 @@ class PFPNModel(object):
                                          nms_threshold=nms_threshold)
         return [o.cpu().numpy() for o in out]
 
+    def detect_stream(self, batches, score_threshold=0.05, max_detections=300, nms=True, nms_threshold=0.5,
+                      class_specific_filter=True):
+        """Pipelined detect_on_batch over an iterable of host batches (the loop keras.Model.predict /
+        predict_generator runs over its batches): the host->device copy of batch i+1 runs on a copy stream while
+        batch i is in the engine, and the (B, max_detections, .) results come back through pinned buffers while
+        batch i+1 computes. Yields [boxes, boxes3D, scores, labels] numpy arrays per batch, in order.
+        Every batch still pays its own H2D and D2H; they are overlapped, not skipped."""
+        import torch
+        from .. import _kernels
+        if not self.inference:
+            raise ValueError("detect_stream needs an inference model (models.convert_model)")
+        kw = dict(class_specific_filter=class_specific_filter, nms=nms, score_threshold=score_threshold,
+                  max_detections=max_detections, nms_threshold=nms_threshold)
+        copy_stream = None
+        staging, staged_ev, consumed_ev, host_out, pending = [None, None], [None, None], [None, None], [None, None], []
+
+        def finish(item):
+            ev, outs = item
+            ev.synchronize()
+            return [o.numpy().copy() for o in outs]
+
+        for i, x in enumerate(batches):
+            src = torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)) if isinstance(x, np.ndarray) else x
+            if src.dim() != 4 or src.shape[3] != 3:
+                raise ValueError("expected images of shape (B, H, W, 3), got %s" % (tuple(src.shape),))
+            B, H, W = int(src.shape[0]), int(src.shape[1]), int(src.shape[2])
+            eng = self._engine(B, H, W)
+            buf = eng.bind(B, decode=True, want_mask=True, want_hull=True)
+            k = i & 1
+            with torch.cuda.device(eng.device):
+                main = torch.cuda.current_stream()
+                if copy_stream is None:
+                    copy_stream = torch.cuda.Stream()
+                if staging[k] is None or staging[k].shape != buf["images"].shape:
+                    staging[k] = torch.empty_like(buf["images"])
+                # the staging buffer was last read by the device-side copy of batch i-2: wait for THAT copy only, not
+                # for the forward pass of batch i-1 that is still running on `main`
+                if consumed_ev[k] is not None:
+                    copy_stream.wait_event(consumed_ev[k])
+                with torch.cuda.stream(copy_stream):
+                    staging[k].copy_(src, non_blocking=True)
+                    staged_ev[k] = torch.cuda.Event()
+                    staged_ev[k].record(copy_stream)
+                main.wait_event(staged_ev[k])
+                buf["images"].copy_(staging[k], non_blocking=True)
+                consumed_ev[k] = torch.cuda.Event()
+                consumed_ev[k].record(main)
+                eng.run()
+                outs = _kernels.filter_detections(buf["hull"], buf["boxes3D"], buf["cls"], **kw)
+                if host_out[k] is None or host_out[k][0].shape[0] != B or host_out[k][0].shape[1] != max_detections:
+                    host_out[k] = [torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs]
+                for h, o in zip(host_out[k], outs):
+                    h.copy_(o, non_blocking=True)
+                done = torch.cuda.Event()
+                done.record(main)
+            pending.append((done, host_out[k]))
+            if len(pending) == 2:  # results of batch i-1 are read while batch i runs
+                yield finish(pending.pop(0))
+        while pending:
+            yield finish(pending.pop(0))
+
     def activation(self, name, height, width):
         return self._engines[(height, width)].activation(name)
 

@@ -119,3 +119,27 @@ def test_detect_on_batch_matches_oracle_filter(cuda_device):
     for g, r in zip(det, ref):
         assert np.array_equal(g, r)
     assert (det[3] >= 0).sum() > 0
+
+
+def test_detect_stream_equals_detect_on_batch(cuda_device):
+    """The pipelined batch loop (copy of batch i+1 overlapped with the forward pass of batch i) returns, batch by
+    batch and in order, exactly what the synchronous call returns; numpy and pinned-tensor inputs both work."""
+    import torch
+    from pyrapose_b200 import models
+    from pyrapose_b200.models import spec
+    C = 4
+    weights = spec.init_weights(C, seed=7, head_init="spread", randomize_bn=True)
+    train = models.backbone("resnet50").retinanet(C)
+    train.set_weights_dict(weights)
+    infer = models.convert_model(train)
+    imgs = [make_images(20 + i, 2, 136, 200) for i in range(3)]
+    want = [infer.detect_on_batch(x) for x in imgs]
+    feed = [imgs[0], torch.from_numpy(imgs[1]).pin_memory(), imgs[2], torch.from_numpy(imgs[0]).pin_memory(), imgs[1]]
+    order = [0, 1, 2, 0, 1]
+    got = list(infer.detect_stream(feed))
+    assert len(got) == len(feed)
+    for g, k in zip(got, order):
+        for a, b in zip(g, want[k]):
+            assert np.array_equal(a, b)
+    with pytest.raises(ValueError):
+        list(train.detect_stream(imgs))
