@@ -42,6 +42,10 @@ void conv_fill_single_seg(ConvParams& p, int batch, int h, int w, int ksize) {
 // shallow-K (HBM / epilogue-bound) layers prefer N = 128 so that the epilogue ring holds several tiles of
 // residual / output chunks in flight.
 int conv_pick_block_n(int cout_pad, int k_iters, long m_tiles, bool bf16_out) {
+  if (!bf16_out && cout_pad > kConvMaxBlockN) {  // wide head output (e.g. 30 classes x 9 anchors): equal N tiles
+    const int nt = (cout_pad + kConvMaxBlockN - 1) / kConvMaxBlockN;
+    return ((cout_pad + nt - 1) / nt + 15) / 16 * 16;
+  }
   if (!bf16_out || cout_pad % 64 != 0) {
     if (cout_pad <= kConvMaxBlockN) return cout_pad;
     if (cout_pad % 256 == 0) return 256;

@@ -149,7 +149,7 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __res
 // The tile is written out afterwards in Keras' Reshape((-1, 16)) / Reshape((-1, C)) + Concatenate(axis=1) order
 // (retinanet.py:51, 129, 224-225), i.e. element (b, loc, n) at ((b*locs + loc)*vals + n).
 __device__ __forceinline__ void epi_head16(const ConvParams& p, const float* __restrict__ sbias, int seg_idx,
-                                           const RowInfo& ri, size_t loc, int n0, const uint32_t* v,
+                                           const RowInfo& ri, size_t loc, int n0, int tile_n0, const uint32_t* v,
                                            float* __restrict__ srow) {
   if (n0 >= p.n_valid) return;
   float f[16];
@@ -193,7 +193,7 @@ __device__ __forceinline__ void epi_head16(const ConvParams& p, const float* __r
   }
 #pragma unroll
   for (int j = 0; j < 16; ++j)
-    if (n0 + j < p.n_valid) srow[n0 + j] = f[j];
+    if (n0 + j < p.n_valid) srow[n0 - tile_n0 + j] = f[j];
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -351,7 +351,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     int prev_slot = -1;  // store thread only: slot whose TMA store was committed last
     const bool store_thread = (q == 0 && lane == 0);
     // head epilogues: fp32 staging tile + row table inside the ring area
-    const int sstride = p.vals_per_loc | 1;  // odd stride: conflict-free column writes
+    const int sstride = p.block_n | 1;  // odd stride: conflict-free column writes
     float* stile = reinterpret_cast<float*>(ring);
     long long* srow_loc = reinterpret_cast<long long*>(ring + static_cast<size_t>(kConvBlockM) * sstride * 4);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -457,13 +457,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             uint32_t v[32];
             tmem_ld_32x32(taddr + c0, v);
             tmem_ld_wait();
-            epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0, v, srow);
-            epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0 + 16, v + 16, srow);
+            epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0, tc.n0, v, srow);
+            epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0 + 16, tc.n0, v + 16, srow);
           } else {
             uint32_t v[16];
             tmem_ld_32x16(taddr + c0, v);
             tmem_ld_wait();
-            epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0, v, srow);
+            epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0, tc.n0, v, srow);
           }
         }
         tc_fence_before();
@@ -472,12 +472,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         // write-out: one warp per row, lanes walk the row's `vals` floats -> 128-byte coalesced stores; consecutive
         // interior rows are consecutive locations, i.e. adjacent in the output as well
         const int vals = p.vals_per_loc;
+        const int ncols = min(p.block_n, p.n_valid - tc.n0);  // this N tile's share of the row
         for (int r = ew; r < kConvBlockM; r += kEpiWarps) {
           const long long rl = srow_loc[r];
           if (rl < 0) continue;
-          float* dst = p.out_f32 + static_cast<size_t>(rl) * vals;
+          float* dst = p.out_f32 + static_cast<size_t>(rl) * vals + tc.n0;
           const float* src = stile + static_cast<size_t>(r) * sstride;
-          for (int e = lane; e < vals; e += 32) dst[e] = src[e];
+          for (int e = lane; e < ncols; e += 32) dst[e] = src[e];
         }
       }
       acc ^= 1;
@@ -559,7 +560,7 @@ int conv_plan_smem(ConvParams& p) {
       ring_max = kMaxRing;
     }
   } else {
-    const int need = kConvBlockM * (p.vals_per_loc | 1) * 4 + kConvBlockM * 8;
+    const int need = kConvBlockM * (p.block_n | 1) * 4 + kConvBlockM * 8;
     ring_min = ring_max = (need + kChunkBytes - 1) / kChunkBytes;
     if (ring_min > kMaxRing) return -1;
   }

@@ -649,9 +649,8 @@ int ppb_engine_create(ppb_engine** out, int device, int max_batch, int height, i
   PPB_REQUIRE(out != nullptr, "ppb_engine_create: null out");
   PPB_REQUIRE(max_batch > 0 && height >= 32 && width >= 32, "ppb_engine_create: bad shape batch=%d h=%d w=%d",
               max_batch, height, width);
-  PPB_REQUIRE(num_classes > 0 && num_classes * num_anchors <= 256 && num_anchors > 0 && num_anchors * 16 <= 256 &&
-                  num_anchors <= 9,
-              "ppb_engine_create: unsupported head size classes=%d anchors=%d (classes*anchors <= 256, anchors <= 9)",
+  PPB_REQUIRE(num_classes > 0 && num_classes * num_anchors <= 2000 && num_anchors > 0 && num_anchors <= 9,
+              "ppb_engine_create: unsupported head size classes=%d anchors=%d (classes*anchors <= 2000, anchors <= 9)",
               num_classes, num_anchors);
   PPB_CUDA(cudaSetDevice(device));
   std::unique_ptr<ppb_engine> h(new ppb_engine);

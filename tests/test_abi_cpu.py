@@ -69,7 +69,7 @@ def test_invalid_arguments_are_rejected_before_cuda(lib):
                                    None, None, None, None, None, None, ctypes.c_size_t(0), None)
     assert rc == nat.PPB_ERR_INVALID and b"max_detections" in lib.ppb_last_error()
     h = ctypes.c_void_p()
-    rc = lib.ppb_engine_create(ctypes.byref(h), 0, 1, 480, 640, 100, 9)  # 900 head channels > 256
+    rc = lib.ppb_engine_create(ctypes.byref(h), 0, 1, 480, 640, 300, 9)  # 2700 head channels > 2000
     assert rc == nat.PPB_ERR_INVALID
 
 

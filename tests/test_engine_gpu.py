@@ -60,7 +60,8 @@ def run_case(B, H, W, C, seed=1, head_init="spread"):
     return rows, outs, (b3, cls, mask), (ref_b3, ref_cls, ref_mask)
 
 
-@pytest.mark.parametrize("shape", [(1, 480, 640, 15), (2, 136, 200, 4)], ids=["480x640_C15", "136x200_C4_odd"])
+@pytest.mark.parametrize("shape", [(1, 480, 640, 15), (2, 136, 200, 4), (1, 960, 1280, 30), (3, 96, 128, 21)],
+                         ids=["480x640_C15", "136x200_C4_odd", "960x1280_C30_config5", "96x128_C21_ycbv"])
 def test_engine_matches_oracle(cuda_device, shape):
     B, H, W, C = shape
     rows, outs, got, ref = run_case(B, H, W, C)
