@@ -53,6 +53,16 @@ PPB_API long long ppb_launch_count(void);
 PPB_API int ppb_conv2d_bf16(const void* x, const void* weight, const float* bias, const void* residual, void* y,
                             int batch, int h, int w, int cin, int cout, int ksize, int relu, void* stream);
 
+/* Weight gradient of the same convolution (training step; the filter-gradient op TensorFlow runs under
+ * model.fit_generator, PyraPose/bin/train.py:381-390):
+ *   dw[co][(r*ksize+s)*cin + c] += sum over pixels of  g[b,y,x,co] * x[b,y+r-k/2,x+s-k/2,c]
+ * x : bf16 [batch,h+2,w+2,cin] padded-flat (zero border), g : bf16 [batch,h+2,w+2,g_ld] padded-flat with ZERO border,
+ * g_ld >= cout and a multiple of 8 (columns >= cout are ignored); dw : f32 [cout, ksize*ksize*cin], ACCUMULATED into
+ * (the caller zeroes it). cin % 64 == 0.
+ */
+PPB_API int ppb_conv2d_wgrad_bf16(const void* x, const void* g, float* dw, int batch, int h, int w, int cin, int cout,
+                                  int g_ld, int ksize, void* stream);
+
 /* ------------------------------------------------------------------ anchor <-> ground-truth IoU (float64, bit-exact)
  * ppb_compute_overlap_f64 replaces compute_overlap(boxes, query_boxes) -> overlaps
  * (PyraPose/utils/compute_overlap.pyx:13-53; call sites PyraPose/utils/anchors.py:310, utils/eval.py:201).

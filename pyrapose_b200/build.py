@@ -33,6 +33,9 @@ def _optional_sources():
         ("filter.cu", True),
         ("elementwise.cu", False),
         ("engine.cu", False),
+        ("conv_wgrad.cu", False),
+        ("losses.cu", True),
+        ("train.cu", False),
     ]
     return [(s, e) for s, e in extra if os.path.exists(os.path.join(CSRC, s))]
 

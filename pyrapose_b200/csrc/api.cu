@@ -2,6 +2,7 @@
 // stand-alone convolution call (used by the parity tests and by layer-level callers).
 #include "../../include/pyrapose_b200.h"
 #include "conv_igemm.h"
+#include "conv_wgrad.h"
 #include "errors.h"
 #include "launch_count.h"
 
@@ -118,6 +119,35 @@ int ppb_conv2d_bf16(const void* x, const void* weight, const float* bias, const 
   }
   PPB_REQUIRE(conv_plan_smem(p) >= 0, "ppb_conv2d_bf16: cout=%d does not fit the shared-memory plan", cout);
   PPB_CUDA(conv_launch(ta, tb, to, tr, p, 0, static_cast<cudaStream_t>(stream)));
+  count_launch();
+  return kOk;
+}
+
+int ppb_conv2d_wgrad_bf16(const void* x, const void* g, float* dw, int batch, int h, int w, int cin, int cout, int g_ld,
+                          int ksize, void* stream) {
+  PPB_REQUIRE(x != nullptr && g != nullptr && dw != nullptr, "ppb_conv2d_wgrad_bf16: null buffer");
+  PPB_REQUIRE(batch > 0 && h > 0 && w > 0, "ppb_conv2d_wgrad_bf16: bad shape batch=%d h=%d w=%d", batch, h, w);
+  PPB_REQUIRE(ksize == 1 || ksize == 3, "ppb_conv2d_wgrad_bf16: ksize must be 1 or 3, got %d", ksize);
+  PPB_REQUIRE(cin > 0 && cin % 64 == 0, "ppb_conv2d_wgrad_bf16: cin must be a multiple of 64, got %d", cin);
+  PPB_REQUIRE(cout > 0 && g_ld >= cout && g_ld % 8 == 0, "ppb_conv2d_wgrad_bf16: bad cout=%d g_ld=%d", cout, g_ld);
+  ConvParams cp = {};
+  conv_fill_single_seg(cp, batch, h, w, ksize);
+  WgradParams p = {};
+  p.n_segs = 1;
+  p.seg[0].row_begin = 0;
+  p.seg[0].k_iters = (cp.seg[0].rows + 63) / 64;
+  for (int t = 0; t < cp.n_taps; ++t) p.seg[0].tap_off[t] = cp.seg[0].tap_off[t];
+  p.total_k_iters = p.seg[0].k_iters;
+  p.n_taps = cp.n_taps;
+  p.cout = cout;
+  p.cin = cin;
+  p.dw = dw;
+  p.dw_ld = static_cast<long long>(cp.n_taps) * cin;
+  wgrad_plan(p);
+  CUtensorMap tg, tx;
+  const int rc = wgrad_encode_tmaps(&tg, &tx, g, cp.seg[0].rows, g_ld, g_ld, x, cp.seg[0].rows, cin, cin);
+  if (rc != 0) return fail(kErrCuda, "ppb_conv2d_wgrad_bf16: cuTensorMapEncodeTiled failed (%d)", rc);
+  PPB_CUDA(wgrad_launch(tg, tx, p, static_cast<cudaStream_t>(stream)));
   count_launch();
   return kOk;
 }

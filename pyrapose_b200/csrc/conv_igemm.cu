@@ -529,6 +529,10 @@ int encode_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, 
 
 }  // namespace
 
+int conv_encode_box_tmap(CUtensorMap* tmap, const void* base, long rows, int cols, int ld, int box_rows) {
+  return encode_2d(tmap, base, static_cast<uint64_t>(rows), cols, ld, static_cast<uint32_t>(box_rows));
+}
+
 int conv_encode_rows_tmap(CUtensorMap* tmap, const void* base, long rows, int cols, int ld) {
   return encode_2d(tmap, base, static_cast<uint64_t>(rows), cols, ld, kConvBlockM);
 }

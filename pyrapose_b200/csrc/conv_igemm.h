@@ -76,6 +76,9 @@ int conv_encode_tmaps(CUtensorMap* tmap_a, CUtensorMap* tmap_b, const void* a, l
 // Tensor map over a row-major bf16 matrix with a {64 cols x 128 rows} box (output store / residual load).
 int conv_encode_rows_tmap(CUtensorMap* tmap, const void* base, long rows, int cols, int ld);
 
+// Same with an explicit box height ({64 cols x box_rows rows}, 128B swizzle).
+int conv_encode_box_tmap(CUtensorMap* tmap, const void* base, long rows, int cols, int ld, int box_rows);
+
 // Chooses pipeline depth and epilogue-ring size for the shared-memory budget (needs block_n, n_taps, cin_blocks,
 // epi, staged, vals_per_loc, n_ntiles). Returns the dynamic shared-memory bytes, or -1 if the shape does not fit.
 int conv_plan_smem(ConvParams& p);

@@ -1,0 +1,244 @@
+// Weight-gradient kernel of the convolution for sm_100a: see conv_wgrad.h. Same skeleton as conv_igemm.cu (persistent
+// CTAs, TMA producer warp, single-thread tcgen05.mma issuer, double-buffered TMEM accumulators, epilogue warps), but
+// the reduction dimension is the pixel row, so both operands are MN-major [64 rows][64 channels] TMA boxes, and the
+// epilogue accumulates its fp32 tile into dW with 128-bit atomics (split-K across CTAs).
+// Replaces the filter-gradient ops TensorFlow runs for keras.layers.Conv2D during model.fit_generator
+// (PyraPose/bin/train.py:381-390).
+#include "conv_wgrad.h"
+#include "ptx.cuh"
+
+#include <mutex>
+
+namespace ppb {
+namespace {
+
+constexpr int kWgThreads = 256;
+constexpr int kWgBoxBytes = 64 * 64 * 2;    // one [64 rows][64 channels] bf16 box
+constexpr int kWgABytes = 2 * kWgBoxBytes;  // 128 output channels
+constexpr int kWgMaxStages = 6;
+constexpr int kWgTmemCols = 512;
+constexpr int kWgAccCols = 256;
+constexpr int kWgBarBytes = 256;
+constexpr int kWgSmemLimit = 232448;
+
+enum WgFault : uint32_t { kWgFaultEmpty = 11, kWgFaultFull = 12, kWgFaultTmemEmpty = 13, kWgFaultTmemFull = 14 };
+
+struct Task {
+  int m_tile, tap, n_tile, k_begin, k_end;
+};
+
+__device__ __forceinline__ Task decode_task(const WgradParams& p, int t) {
+  Task k;
+  const int split = t % p.k_splits;
+  t /= p.k_splits;
+  k.n_tile = t % p.n_ntiles;
+  t /= p.n_ntiles;
+  k.tap = t % p.n_taps;
+  k.m_tile = t / p.n_taps;
+  k.k_begin = static_cast<int>(static_cast<long long>(p.total_k_iters) * split / p.k_splits);
+  k.k_end = static_cast<int>(static_cast<long long>(p.total_k_iters) * (split + 1) / p.k_splits);
+  return k;
+}
+
+__global__ void __launch_bounds__(kWgThreads, 1)
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__ CUtensorMap tmap_x,
+                  const __grid_constant__ WgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int n_stages = p.n_stages;
+  const int n_boxes_b = p.block_n >> 6;
+  const int stage_bytes = kWgABytes + n_boxes_b * kWgBoxBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + n_stages * stage_bytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + kWgMaxStages;
+  uint64_t* tmem_full_bar = bars + 2 * kWgMaxStages;
+  uint64_t* tmem_empty_bar = bars + 2 * kWgMaxStages + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kWgMaxStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      tma_prefetch_desc(&tmap_g);
+      tma_prefetch_desc(&tmap_x);
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      for (int i = 0; i < kWgMaxStages; ++i) {
+        mbar_init(&full_bar[i], 1);
+        mbar_init(&empty_bar[i], 1);
+      }
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&tmem_full_bar[i], 1);
+        mbar_init(&tmem_empty_bar[i], 128);
+      }
+      fence_mbar_init();
+    }
+  } else if (warp == 2) {
+    tmem_alloc(tmem_slot, kWgTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int total_tasks = p.n_mtiles * p.n_taps * p.n_ntiles * p.k_splits;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tasks; t += gridDim.x) {
+        const Task k = decode_task(p, t);
+        // locate k_begin inside the segment list
+        int seg = 0, local = k.k_begin;
+        while (seg < p.n_segs - 1 && local >= p.seg[seg].k_iters) {
+          local -= p.seg[seg].k_iters;
+          ++seg;
+        }
+        for (int it = k.k_begin; it < k.k_end; ++it) {
+          const int row = p.seg[seg].row_begin + local * 64;
+          const int xrow = row + p.seg[seg].tap_off[k.tap];
+          mbar_wait(&empty_bar[stage], phase ^ 1, kWgFaultEmpty);
+          mbar_arrive_expect_tx(&full_bar[stage], static_cast<uint32_t>(stage_bytes));
+          uint8_t* sa = smem + stage * stage_bytes;
+          tma_load_2d(sa, &tmap_g, k.m_tile * 128, row, &full_bar[stage]);
+          tma_load_2d(sa + kWgBoxBytes, &tmap_g, k.m_tile * 128 + 64, row, &full_bar[stage]);
+          for (int j = 0; j < n_boxes_b; ++j)
+            tma_load_2d(sa + kWgABytes + j * kWgBoxBytes, &tmap_x, k.n_tile * p.block_n + j * 64, xrow,
+                        &full_bar[stage]);
+          if (++stage == n_stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+          if (++local == p.seg[seg].k_iters && seg < p.n_segs - 1) {
+            local = 0;
+            ++seg;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      const uint32_t idesc = umma_idesc_bf16_mn(128, p.block_n);
+      for (int t = blockIdx.x; t < total_tasks; t += gridDim.x) {
+        const Task k = decode_task(p, t);
+        if (k.k_end <= k.k_begin) continue;
+        mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1, kWgFaultTmemEmpty);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * kWgAccCols;
+        for (int it = k.k_begin; it < k.k_end; ++it) {
+          mbar_wait(&full_bar[stage], phase, kWgFaultFull);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
+          const uint32_t b_addr = a_addr + kWgABytes;
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {  // 16 rows (K) per MMA = two 8-row groups of 1024 B
+            tc_mma_bf16(d_tmem, umma_desc_mn128(a_addr + kk * 2048, kWgBoxBytes),
+                        umma_desc_mn128(b_addr + kk * 2048, kWgBoxBytes), idesc, (it > k.k_begin || kk > 0) ? 1u : 0u);
+          }
+          tc_commit(&empty_bar[stage]);
+          if (++stage == n_stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        tc_commit(&tmem_full_bar[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------ epilogue: fp32 tile -> atomics into dW
+    const int q = warp - 4;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < total_tasks; t += gridDim.x) {
+      const Task k = decode_task(p, t);
+      if (k.k_end <= k.k_begin) continue;
+      mbar_wait(&tmem_full_bar[acc], acc_phase, kWgFaultTmemFull);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * kWgAccCols;
+      const int co = k.m_tile * 128 + q * 32 + lane;
+      float* dst = p.dw + static_cast<long long>(co) * p.dw_ld + static_cast<long long>(k.tap) * p.cin +
+                   k.n_tile * p.block_n;
+      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + c0, v);
+        tmem_ld_wait();
+        if (co < p.cout) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            atomicAdd(reinterpret_cast<float4*>(dst + c0 + j),
+                      make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                                  __uint_as_float(v[j + 3])));
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tmem_empty_bar[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kWgTmemCols);
+  }
+}
+
+}  // namespace
+
+int wgrad_encode_tmaps(CUtensorMap* tmap_g, CUtensorMap* tmap_x, const void* g, long g_rows, int g_cols, int g_ld,
+                       const void* x, long x_rows, int x_cols, int x_ld) {
+  int rc = conv_encode_box_tmap(tmap_g, g, g_rows, g_cols, g_ld, 64);
+  if (rc != 0) return rc;
+  return conv_encode_box_tmap(tmap_x, x, x_rows, x_cols, x_ld, 64);
+}
+
+void wgrad_plan(WgradParams& p) {
+  p.block_n = (p.cin % 256 == 0) ? 256 : ((p.cin % 128 == 0) ? 128 : 64);
+  p.n_mtiles = (p.cout + 127) / 128;
+  p.n_ntiles = p.cin / p.block_n;
+  const int stage_bytes = kWgABytes + (p.block_n >> 6) * kWgBoxBytes;
+  int stages = (kWgSmemLimit - 1024 - kWgBarBytes) / stage_bytes;
+  if (stages > kWgMaxStages) stages = kWgMaxStages;
+  p.n_stages = stages;
+  const int tiles = p.n_mtiles * p.n_taps * p.n_ntiles;
+  const int sms = conv_num_sms() > 0 ? conv_num_sms() : 148;
+  int splits = (2 * sms + tiles - 1) / tiles;
+  const int max_splits = p.total_k_iters / 8 > 0 ? p.total_k_iters / 8 : 1;
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  p.k_splits = splits;
+}
+
+cudaError_t wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, const WgradParams& p,
+                         cudaStream_t stream) {
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] {
+    attr_err = cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemLimit);
+  });
+  if (attr_err != cudaSuccess) return attr_err;
+  const int total = p.n_mtiles * p.n_taps * p.n_ntiles * p.k_splits;
+  if (total <= 0 || p.total_k_iters <= 0) return cudaSuccess;
+  const int stage_bytes = kWgABytes + (p.block_n >> 6) * kWgBoxBytes;
+  const int smem_bytes = p.n_stages * stage_bytes + kWgBarBytes + 1024;
+  int ctas = conv_num_sms();
+  if (ctas > total) ctas = total;
+  conv_wgrad_kernel<<<ctas, kWgThreads, smem_bytes, stream>>>(tmap_g, tmap_x, p);
+  return cudaGetLastError();
+}
+
+}  // namespace ppb

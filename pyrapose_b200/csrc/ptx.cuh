@@ -191,6 +191,23 @@ __device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr) {
   d |= static_cast<uint64_t>(2) << 61;
   return d;
 }
+// MN-major operand (the contiguous dimension is M or N, rows of the shared-memory tile are K): tiles written by TMA
+// as [K rows][64 elements = 128 B] boxes with CU_TENSOR_MAP_SWIZZLE_128B. Canonical layout (CUTLASS "MN-major,
+// SW128"): ((8,8,m),(8,k)) : ((1,8,LBO),(64,SBO)) elements, i.e. LBO = byte distance between 64-element MN blocks
+// (one TMA box each), SBO = byte distance between groups of 8 K rows (1024 B for dense 128-B rows).
+__device__ __forceinline__ uint64_t umma_desc_mn128(uint32_t smem_addr, uint32_t lbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+// Instruction descriptor with both operands MN-major (bits 15 and 16 set).
+__host__ __device__ __forceinline__ uint32_t umma_idesc_bf16_mn(uint32_t m, uint32_t n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((n >> 3) << 17) | ((m >> 4) << 24);
+}
 // Instruction descriptor, kind::f16: D=f32 (bits 4-5 = 1), A=B=bf16 (bits 7-9, 10-12 = 1), both K-major
 // (bits 15, 16 = 0), N>>3 at bits [17,23), M>>4 at bits [24,29).
 __host__ __device__ __forceinline__ uint32_t umma_idesc_bf16(uint32_t m, uint32_t n) {
