@@ -63,6 +63,19 @@ PPB_API int ppb_conv2d_bf16(const void* x, const void* weight, const float* bias
 PPB_API int ppb_conv2d_wgrad_bf16(const void* x, const void* g, float* dw, int batch, int h, int w, int cin, int cout,
                                   int g_ld, int ksize, void* stream);
 
+/* Data gradient of the same convolution (the input-gradient op of Conv2D under model.fit_generator): the tcgen05
+ * implicit-GEMM kernel run over g with transposed weights and negated tap offsets,
+ *   dx[b,y,x,ci] = sum_{r,s,co} g[b, y-(r-k/2), x-(s-k/2), co] * w[co][(r*k+s)*cin + ci]   (+ residual) (masked)
+ * g        : bf16 [batch,h+2,w+2,g_ld] padded-flat with ZERO border; g_ld >= cout, multiple of 64, columns >= cout zero
+ * weight_t : bf16 [cin, ksize*ksize*g_ld] with weight_t[ci][(r*k+s)*g_ld + co] = w[co][(r*k+s)*cin + ci]
+ * residual : bf16 [batch,h+2,w+2,cin] or NULL, added (skip-connection gradient); may alias dx
+ * relu_mask: bf16 [batch,h+2,w+2,cin] or NULL: the forward activation; dx is zeroed where it is <= 0 (ReLU backward)
+ * dx       : bf16 [batch,h+2,w+2,cin], border written as zeros. cin % 64 == 0.
+ */
+PPB_API int ppb_conv2d_dgrad_bf16(const void* g, const void* weight_t, const void* residual, const void* relu_mask,
+                                  void* dx, int batch, int h, int w, int cin, int cout, int g_ld, int ksize,
+                                  void* stream);
+
 /* ------------------------------------------------------------------ anchor <-> ground-truth IoU (float64, bit-exact)
  * ppb_compute_overlap_f64 replaces compute_overlap(boxes, query_boxes) -> overlaps
  * (PyraPose/utils/compute_overlap.pyx:13-53; call sites PyraPose/utils/anchors.py:310, utils/eval.py:201).
@@ -191,6 +204,41 @@ PPB_API int ppb_engine_activation(ppb_engine* engine, const char* name, float* o
 /* Name (layer name for convolutions) and algorithmic FLOPs of launch `index` of the bound plan. */
 PPB_API int ppb_engine_op_info(const ppb_engine* engine, int index, char* name, int name_cap, double* flops);
 PPB_API int ppb_engine_profile(ppb_engine* engine, void* stream, float* ms_out_host, int* kind_out_host, int cap);
+
+/* ------------------------------------------------------------------ training step (BASELINE.json config 4)
+ * Replaces one batch of `training_model.fit_generator(...)` (PyraPose/bin/train.py:381-390) for the model compiled at
+ * train.py:95-102: loss = {'3Dbox': orthogonal_l1(), 'cls': focal(), 'mask': focal()} (PyraPose/losses.py:22-68,
+ * 321-408) + the l2(0.001) kernel regulariser of the regression sub-model (PyraPose/models/retinanet.py:108),
+ * optimizer = keras.optimizers.Adam(lr, clipnorm) (Keras 2.3.1: clip by the GLOBAL gradient norm). Trainable set as in
+ * PyraPose/models/resnet.py:87,100-103: BatchNorm frozen everywhere, conv1 and stage 2 frozen.
+ *
+ * ppb_engine_train_bind: binds caller-owned DEVICE buffers and captures forward + losses + backward as one CUDA graph.
+ *   images f32 [batch,H,W,3]; y_reg f32 [batch,N,17]; y_cls f32 [batch,N,C+1]; y_mask f32 [batch,H/8*W/8,C+1]
+ *   (the three arrays anchor_targets_bbox returns, PyraPose/utils/anchors.py:72-287; last column = anchor state)
+ *   out_reg f32 [batch,N,16] raw '3Dbox'; out_cls f32 [batch,N,C]; out_mask f32 [batch,H/8*W/8,C]  (model outputs)
+ * ppb_engine_train_forward_backward: one launch; afterwards the flat fp32 gradient buffer (ppb_engine_train_grads)
+ *   holds dLoss/dW of every trainable tensor (w.r.t. the BatchNorm-folded kernels; the fold is undone in _apply).
+ *   A data-parallel caller all-reduces (sums) that buffer over NCCL and passes grad_scale = 1/world_size to _apply.
+ * ppb_engine_train_apply: regulariser gradient, global-norm clip, Adam moments and step, refresh of the bf16 forward
+ *   and data-gradient weight matrices.
+ * ppb_engine_train_losses: synchronises `stream`; out5 = {3Dbox, cls, mask, l2 regulariser, squared gradient norm}
+ *   (the last two are valid after _apply), counts3 = positives of the three outputs.
+ */
+PPB_API int ppb_engine_train_bind(ppb_engine* engine, int batch, const float* images, const float* y_reg,
+                                  const float* y_cls, const float* y_mask, float* out_reg, float* out_cls,
+                                  float* out_mask, void* stream);
+PPB_API int ppb_engine_train_forward_backward(ppb_engine* engine, int eager, void* stream);
+PPB_API int ppb_engine_train_grads(ppb_engine* engine, float** grads, long long* count);
+PPB_API int ppb_engine_train_apply(ppb_engine* engine, float lr, float beta1, float beta2, float epsilon,
+                                   float clipnorm, float grad_scale, void* stream);
+PPB_API int ppb_engine_train_losses(ppb_engine* engine, double* out5_host, int* counts3_host, void* stream);
+/* Offsets (elements) of a layer's kernel [cout][k*k*cin] and bias [cout] inside the flat buffers; -1 if absent. */
+PPB_API int ppb_engine_train_param_info(const ppb_engine* engine, const char* layer, long long* kernel_offset,
+                                        long long* bias_offset, int* trainable);
+/* Copies a range of a flat buffer to the host (synchronises): which = 0 gradients, 1 master weights, 2 Adam m, 3 v. */
+PPB_API int ppb_engine_train_read(ppb_engine* engine, int which, long long offset, long long count, float* out_host);
+PPB_API int ppb_engine_train_num_ops(const ppb_engine* engine);
+PPB_API int ppb_engine_train_op_info(const ppb_engine* engine, int index, char* name, int name_cap, double* flops);
 
 #ifdef __cplusplus
 }

@@ -23,7 +23,19 @@ BN_EPS = 1e-5  # keras-resnet BatchNormalization(epsilon=1e-5)
 
 
 def _t(a):
+    if isinstance(a, torch.Tensor):  # oracle/train.py passes leaf tensors so that autograd supplies gradients
+        return a
     return torch.from_numpy(np.ascontiguousarray(a))
+
+
+# Rounding hook applied wherever the native engine stores an activation as bf16. Identity for the fp32 oracle;
+# oracle/train.py swaps in a bf16 round (straight-through, gradient rounded too) for its "bf16-emulating" mode, which
+# checks the backward arithmetic independently of ReLU-mask flips between an fp32 and a bf16 forward pass.
+_Q = [lambda x: x]
+
+
+def _q(x):
+    return _Q[0](x)
 
 
 def _kernel(w, name):
@@ -84,7 +96,7 @@ def upsample_like(src, target):
 def resnet50(x, w, taps=None):
     """Returns [C2, C3, C4, C5] (NCHW)."""
     x = conv_valid_nobias(x, w, "conv1", stride=2, pad=3)
-    x = torch.relu(frozen_bn(x, w, "bn_conv1"))
+    x = _q(torch.relu(frozen_bn(x, w, "bn_conv1")))
     if taps is not None:
         taps["conv1_relu"] = x
     x = maxpool_same_3x3_s2(x)
@@ -96,17 +108,17 @@ def resnet50(x, w, taps=None):
             tag = "%d%s" % (stage + 2, chr(ord("a") + block))
             stride = 2 if (block == 0 and stage > 0) else 1
             y = conv_valid_nobias(x, w, "res%s_branch2a" % tag, stride=stride)
-            y = torch.relu(frozen_bn(y, w, "bn%s_branch2a" % tag))
+            y = _q(torch.relu(frozen_bn(y, w, "bn%s_branch2a" % tag)))
             y = conv_valid_nobias(y, w, "res%s_branch2b" % tag, pad=1)
-            y = torch.relu(frozen_bn(y, w, "bn%s_branch2b" % tag))
+            y = _q(torch.relu(frozen_bn(y, w, "bn%s_branch2b" % tag)))
             y = conv_valid_nobias(y, w, "res%s_branch2c" % tag)
             y = frozen_bn(y, w, "bn%s_branch2c" % tag)
             if block == 0:
                 sc = conv_valid_nobias(x, w, "res%s_branch1" % tag, stride=stride)
-                sc = frozen_bn(sc, w, "bn%s_branch1" % tag)
+                sc = _q(frozen_bn(sc, w, "bn%s_branch1" % tag))
             else:
                 sc = x
-            x = torch.relu(y + sc)
+            x = _q(torch.relu(y + sc))
             if taps is not None:
                 taps["res%s_relu" % tag] = x
         outs.append(x)
@@ -115,19 +127,19 @@ def resnet50(x, w, taps=None):
 
 def sparce_fpn(C3, C4, C5, w, taps=None):
     """retinanet.py:180-214."""
-    P3 = conv_same(C3, w, "P3_lateral")                       # :192
-    P4 = conv_same(C4, w, "P4_lateral")                       # :193
-    P5 = conv_same(C5, w, "P5_lateral")                       # :194
-    P5_up = upsample_like(P5, P4)                             # :196
-    P4_up = upsample_like(P4, P3)                             # :197
-    P4_mid = conv_same(P5_up + P4, w, "P4_mid")               # :198-199
-    P3_mid = conv_same(P4_up + P3, w, "P3_mid")               # :200-201
-    P3_down = conv_same(P3_mid, w, "P3_down", stride=2)       # :202
-    P3_out = conv_same(P3_mid + P3, w, "P3")                  # :203-204
-    P4_fin = P3_down + P4_mid                                 # :206
-    P4_down = conv_same(P4_mid, w, "P4_down", stride=2)       # :207
-    P4_out = conv_same(P4_fin + P4, w, "P4")                  # :208-209
-    P5_out = conv_same(P4_down + P5, w, "P5")                 # :211-212
+    P3 = _q(conv_same(C3, w, "P3_lateral"))                       # :192
+    P4 = _q(conv_same(C4, w, "P4_lateral"))                       # :193
+    P5 = _q(conv_same(C5, w, "P5_lateral"))                       # :194
+    P5_up = upsample_like(P5, P4)                                 # :196
+    P4_up = upsample_like(P4, P3)                                 # :197
+    P4_mid = _q(conv_same(_q(P5_up + P4), w, "P4_mid"))           # :198-199
+    P3_mid = _q(conv_same(_q(P4_up + P3), w, "P3_mid"))           # :200-201
+    P3_down = _q(conv_same(P3_mid, w, "P3_down", stride=2))       # :202
+    P3_out = _q(conv_same(_q(P3_mid + P3), w, "P3"))              # :203-204
+    P4_fin = P3_down + P4_mid                                     # :206
+    P4_down = _q(conv_same(P4_mid, w, "P4_down", stride=2))       # :207
+    P4_out = _q(conv_same(_q(P4_fin + P4), w, "P4"))              # :208-209
+    P5_out = _q(conv_same(_q(P4_down + P5), w, "P5"))             # :211-212
     if taps is not None:
         taps.update({"P3_lateral": P3, "P4_lateral": P4, "P5_lateral": P5, "P4_mid": P4_mid, "P3_mid": P3_mid,
                      "P3_down": P3_down, "P4_down": P4_down, "P3": P3_out, "P4": P4_out, "P5": P5_out})
@@ -136,7 +148,7 @@ def sparce_fpn(C3, C4, C5, w, taps=None):
 
 def _tower(x, w, prefix, out_name):
     for i in range(4):
-        x = torch.relu(conv_same(x, w, "%s_%d" % (prefix, i)))
+        x = _q(torch.relu(conv_same(x, w, "%s_%d" % (prefix, i))))
     return conv_same(x, w, out_name)
 
 

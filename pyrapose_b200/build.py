@@ -34,7 +34,7 @@ def _optional_sources():
         ("elementwise.cu", False),
         ("engine.cu", False),
         ("conv_wgrad.cu", False),
-        ("losses.cu", True),
+        ("train_kernels.cu", False),
         ("train.cu", False),
     ]
     return [(s, e) for s, e in extra if os.path.exists(os.path.join(CSRC, s))]

@@ -152,4 +152,43 @@ int ppb_conv2d_wgrad_bf16(const void* x, const void* g, float* dw, int batch, in
   return kOk;
 }
 
+int ppb_conv2d_dgrad_bf16(const void* g, const void* weight_t, const void* residual, const void* relu_mask, void* dx,
+                          int batch, int h, int w, int cin, int cout, int g_ld, int ksize, void* stream) {
+  PPB_REQUIRE(g != nullptr && weight_t != nullptr && dx != nullptr, "ppb_conv2d_dgrad_bf16: null buffer");
+  PPB_REQUIRE(batch > 0 && h > 0 && w > 0, "ppb_conv2d_dgrad_bf16: bad shape batch=%d h=%d w=%d", batch, h, w);
+  PPB_REQUIRE(ksize == 1 || ksize == 3, "ppb_conv2d_dgrad_bf16: ksize must be 1 or 3, got %d", ksize);
+  PPB_REQUIRE(cin > 0 && cin % 64 == 0, "ppb_conv2d_dgrad_bf16: cin must be a multiple of 64, got %d", cin);
+  PPB_REQUIRE(cout > 0 && g_ld >= cout && g_ld % 64 == 0, "ppb_conv2d_dgrad_bf16: bad cout=%d g_ld=%d (multiple of 64)",
+              cout, g_ld);
+  ConvParams p = {};
+  conv_fill_single_seg(p, batch, h, w, ksize);
+  for (int t = 0; t < p.n_taps; ++t) p.seg[0].tap_off[t] = -p.seg[0].tap_off[t];  // transposed convolution
+  p.cin_blocks = g_ld / kConvBlockK;
+  p.n_valid = cin;
+  p.block_n = conv_pick_block_n(cin, p.n_taps * p.cin_blocks, p.n_mtiles, true);
+  p.n_ntiles = (cin + p.block_n - 1) / p.block_n;
+  p.epi = kEpiBf16;
+  p.residual = static_cast<const __nv_bfloat16*>(residual);
+  p.res_ld = cin;
+  p.mask = static_cast<const __nv_bfloat16*>(relu_mask);
+  p.mask_ld = cin;
+  p.out = static_cast<__nv_bfloat16*>(dx);
+  p.out_ld = cin;
+  CUtensorMap ta, tb, to, tr;
+  int rc = conv_encode_tmaps(&ta, &tb, g, p.seg[0].rows, g_ld, g_ld, weight_t, cin, ksize * ksize * g_ld, p.block_n);
+  if (rc != 0) return fail(kErrCuda, "ppb_conv2d_dgrad_bf16: cuTensorMapEncodeTiled failed (%d)", rc);
+  memset(&to, 0, sizeof(to));
+  memset(&tr, 0, sizeof(tr));
+  p.staged = (p.block_n % 64 == 0) ? 1 : 0;
+  if (p.staged) {
+    rc = conv_encode_rows_tmap(&to, dx, p.seg[0].rows, cin, cin);
+    if (rc == 0 && residual != nullptr) rc = conv_encode_rows_tmap(&tr, residual, p.seg[0].rows, cin, cin);
+    if (rc != 0) return fail(kErrCuda, "ppb_conv2d_dgrad_bf16: cuTensorMapEncodeTiled (output) failed (%d)", rc);
+  }
+  PPB_REQUIRE(conv_plan_smem(p) >= 0, "ppb_conv2d_dgrad_bf16: cin=%d does not fit the shared-memory plan", cin);
+  PPB_CUDA(conv_launch(ta, tb, to, tr, p, 0, static_cast<cudaStream_t>(stream)));
+  count_launch();
+  return kOk;
+}
+
 }  // extern "C"

@@ -133,6 +133,21 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __res
 #pragma unroll
     for (int j = 0; j < NC; ++j) f[j] = fmaxf(f[j], 0.0f);
   }
+  if (p.mask != nullptr) {  // ReLU backward: pass the gradient only where the forward activation was positive
+    const uint4* mp = reinterpret_cast<const uint4*>(p.mask + static_cast<size_t>(m) * p.mask_ld + n0);
+#pragma unroll
+    for (int i = 0; i < NC / 8; ++i) {
+      const uint4 r = __ldg(mp + i);
+      if (!(bf16_lo(r.x) > 0.0f)) f[i * 8 + 0] = 0.0f;
+      if (!(bf16_hi(r.x) > 0.0f)) f[i * 8 + 1] = 0.0f;
+      if (!(bf16_lo(r.y) > 0.0f)) f[i * 8 + 2] = 0.0f;
+      if (!(bf16_hi(r.y) > 0.0f)) f[i * 8 + 3] = 0.0f;
+      if (!(bf16_lo(r.z) > 0.0f)) f[i * 8 + 4] = 0.0f;
+      if (!(bf16_hi(r.z) > 0.0f)) f[i * 8 + 5] = 0.0f;
+      if (!(bf16_lo(r.w) > 0.0f)) f[i * 8 + 6] = 0.0f;
+      if (!(bf16_hi(r.w) > 0.0f)) f[i * 8 + 7] = 0.0f;
+    }
+  }
 #pragma unroll
   for (int i = 0; i < NC / 8; ++i) {
     uint4 o;
@@ -280,7 +295,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
             uint8_t* sa = smem + stage * stage_bytes;
             tma_load_2d(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
-            tma_load_2d(sa + kABytes, &tmap_b, (tap * p.cin_blocks + kb) * kConvBlockK, tc.n0, &full_bar[stage]);
+            tma_load_2d(sa + kABytes, &tmap_b, p.b_col_base + (tap * p.cin_blocks + kb) * kConvBlockK, tc.n0,
+                        &full_bar[stage]);
             if (++stage == n_stages) {
               stage = 0;
               phase ^= 1;
@@ -401,6 +417,18 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               if (p.relu) {
 #pragma unroll
                 for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.0f);
+              }
+              if (p.mask != nullptr) {
+                const uint4 r = __ldg(reinterpret_cast<const uint4*>(p.mask + static_cast<size_t>(m) * p.mask_ld +
+                                                                     tc.n0 + c * 64 + j * 8));
+                if (!(bf16_lo(r.x) > 0.0f)) f[0] = 0.0f;
+                if (!(bf16_hi(r.x) > 0.0f)) f[1] = 0.0f;
+                if (!(bf16_lo(r.y) > 0.0f)) f[2] = 0.0f;
+                if (!(bf16_hi(r.y) > 0.0f)) f[3] = 0.0f;
+                if (!(bf16_lo(r.z) > 0.0f)) f[4] = 0.0f;
+                if (!(bf16_hi(r.z) > 0.0f)) f[5] = 0.0f;
+                if (!(bf16_lo(r.w) > 0.0f)) f[6] = 0.0f;
+                if (!(bf16_hi(r.w) > 0.0f)) f[7] = 0.0f;
               }
               o.x = pack_bf16x2(f[0], f[1]);
               o.y = pack_bf16x2(f[2], f[3]);

@@ -57,6 +57,9 @@ struct ConvParams {
   const float* bias;              // [n_valid] fp32, BatchNorm folded in; may be null
   const __nv_bfloat16* residual;  // kEpiBf16: added before ReLU; row stride res_ld; may be null
   int res_ld;
+  const __nv_bfloat16* mask;      // kEpiBf16: ReLU backward — the result is zeroed where mask <= 0 (after the residual add)
+  int mask_ld;
+  int b_col_base;                 // first column of this launch's taps inside the weight matrix (multiple of 64)
   __nv_bfloat16* out;             // kEpiBf16
   int out_ld;
   float* out_f32;                 // head epilogues

@@ -9,173 +9,9 @@
 // Every convolution is one launch of the tcgen05 implicit-GEMM kernel (conv_igemm.cu); BatchNorm is folded
 // into the weights, ReLU / residual add / sigmoid / Reshape+Concatenate / anchor decode live in its epilogue.
 // The three pyramid levels share each head convolution as ONE launch over a 3-segment row space.
-#include "../../include/pyrapose_b200.h"
-#include "conv_igemm.h"
-#include "elementwise.h"
-#include "errors.h"
-#include "launch_count.h"
-
-#include <cmath>
-#include <cstdlib>
-#include <cstring>
-#include <map>
-#include <memory>
-#include <string>
-#include <vector>
+#include "engine.h"
 
 namespace ppb {
-
-void conv_fill_single_seg(ConvParams& p, int batch, int h, int w, int ksize);
-int conv_pick_block_n(int cout_pad, int k_iters, long m_tiles, bool bf16_out);
-
-namespace {
-
-struct LayerW {
-  std::string name;
-  int ksize, cin, cout, stride;
-  bool has_bn, has_bias;
-  int k_total;   // columns of the device weight matrix (ksize*ksize*cin, stem: 192)
-  int cout_pad;  // rows, multiple of 16
-  __nv_bfloat16* w = nullptr;
-  float* bias = nullptr;
-  bool loaded = false;
-};
-
-struct Tensor {  // bf16 activation on a pixel grid with pad_lo border pixels before and pad_hi after the interior
-  std::string name;
-  __nv_bfloat16* ptr = nullptr;
-  int H = 0, W = 0, C = 0, pad_lo = 1, pad_hi = 1;  // padded-flat: 1/1; stem grid: 0/3
-  int hp() const { return H + pad_lo + pad_hi; }
-  int wp() const { return W + pad_lo + pad_hi; }
-  long long rows(int B) const { return static_cast<long long>(B) * hp() * wp(); }
-};
-
-enum OpKind { kOpConv, kOpStemS2d, kOpMaxpool, kOpPlanes, kOpAdd };
-
-struct Op {
-  OpKind kind;
-  // conv
-  CUtensorMap ta, tb, to, tr;
-  ConvParams p;
-  // elementwise
-  const void* in0 = nullptr;
-  const void* in1 = nullptr;
-  const void* in2 = nullptr;
-  const void* in3 = nullptr;
-  void* out = nullptr;
-  int a[8] = {0};
-  char name[40] = {0};
-  double flops = 0.0;  // conv: 2 * interior pixels * Cout * K (algorithmic)
-};
-
-int round_up(int v, int m) { return (v + m - 1) / m * m; }
-
-int same_pad_before(int in, int k, int stride) {
-  const int out = (in + stride - 1) / stride;
-  const int total = std::max((out - 1) * stride + k - in, 0);
-  return total / 2;
-}
-
-}  // namespace
-
-struct Engine {
-  int device = 0, max_batch = 0, H = 0, W = 0, num_classes = 0, num_anchors = 0;
-  std::vector<LayerW> layers;
-  std::map<std::string, int> layer_index;
-  std::vector<std::unique_ptr<Tensor>> tensors;
-  std::map<std::string, Tensor*> tensor_index;
-  std::vector<void*> allocations;
-  // anchors / decode parameters (host copies; baked into the head conv's params)
-  float base_anchor[kConvMaxSegs][9][4];
-  float stride[kConvMaxSegs];
-  float dec_mean[16], dec_std[16];
-  bool anchors_set = false;
-  // level geometry
-  int lvl_h[3], lvl_w[3];
-  int seg_row_begin[3], seg_tile_begin[3];
-  long long feat_rows_total = 0;
-  int feat_tiles_total = 0;
-  // plan
-  std::vector<Op> ops;
-  int bound_batch = 0;
-  cudaGraph_t graph = nullptr;
-  cudaGraphExec_t graph_exec = nullptr;
-  int graph_kernels = 0;
-  size_t arena_bytes = 0;
-  // TMA-store epilogue through the shared-memory chunk ring (residual chunks prefetched by TMA): 0 never; 1 only convs
-  // with a residual input; 2 every backbone / PFPN conv (measured best, profiles/r01_per_op_staged_variants.txt);
-  // 3 head towers too. Override with PPB_STAGED_EPILOGUE for experiments.
-  int staged_epilogue = 2;
-
-  ~Engine() {
-    if (graph_exec) cudaGraphExecDestroy(graph_exec);
-    if (graph) cudaGraphDestroy(graph);
-    for (void* p : allocations) cudaFree(p);
-  }
-
-  int add_layer(const std::string& name, int ksize, int cin, int cout, int stride, bool bn, bool bias) {
-    LayerW l;
-    l.name = name;
-    l.ksize = ksize;
-    l.cin = cin;
-    l.cout = cout;
-    l.stride = stride;
-    l.has_bn = bn;
-    l.has_bias = bias;
-    l.k_total = (ksize == 7) ? 256 : ksize * ksize * cin;  // stem: 4 row taps x (4 px x 16 ch), see launch_stem_s2d
-    l.cout_pad = round_up(cout, 16);
-    layer_index[name] = static_cast<int>(layers.size());
-    layers.push_back(l);
-    return static_cast<int>(layers.size()) - 1;
-  }
-
-  int device_alloc(void** p, size_t bytes) {
-    PPB_CUDA(cudaMalloc(p, bytes));
-    PPB_CUDA(cudaMemset(*p, 0, bytes));
-    allocations.push_back(*p);
-    arena_bytes += bytes;
-    return kOk;
-  }
-
-  Tensor* tensor(const std::string& name) {
-    auto it = tensor_index.find(name);
-    return it == tensor_index.end() ? nullptr : it->second;
-  }
-
-  int new_tensor(Tensor** out, const std::string& name, int h, int w, int c, int pad, int planes = 1,
-                 long long rows_override = 0, int pad_hi = -1) {
-    std::unique_ptr<Tensor> t(new Tensor);
-    t->name = name;
-    t->H = h;
-    t->W = w;
-    t->C = c;
-    t->pad_lo = pad;
-    t->pad_hi = pad_hi >= 0 ? pad_hi : pad;
-    long long rows = rows_override ? rows_override : t->rows(max_batch) * planes;
-    rows = (rows + kConvBlockM - 1) / kConvBlockM * kConvBlockM + kConvBlockM;  // slack: TMA rows may overlap the end
-    void* p = nullptr;
-    int rc = device_alloc(&p, static_cast<size_t>(rows) * c * sizeof(__nv_bfloat16));
-    if (rc != kOk) return rc;
-    t->ptr = static_cast<__nv_bfloat16*>(p);
-    *out = t.get();
-    tensor_index[name] = t.get();
-    tensors.push_back(std::move(t));
-    return kOk;
-  }
-
-  void define_layers();
-  int allocate_weights();
-  int set_layer(const char* name, const float* kernel, const float* bias, const float* gamma, const float* beta,
-                const float* mean, const float* var, float eps);
-  int build_plan(int batch, const float* images, float* out_reg, float* out_cls, float* out_mask, float* out_hull,
-                 int decode);
-  int conv_op(const Tensor* x, int x_planes, const std::string& layer, const Tensor* res, Tensor* y, int relu, int batch,
-              int src_h = 0, int src_w = 0);
-  int head_conv_op(const __nv_bfloat16* x, int cin, const std::string& layer, __nv_bfloat16* y, int relu, int batch,
-                   int n_levels, int epi, float* out_f32, float* out_hull);
-  int capture(cudaStream_t st);
-  int launch_all(cudaStream_t st);
-};
 
 void Engine::define_layers() {
   // keras-resnet 0.1.0 ResNet50 (Caffe-style bottlenecks, stride on the first 1x1 conv)
@@ -240,6 +76,10 @@ int Engine::set_layer(const char* name, const float* kernel, const float* bias, 
   const int k = l.ksize, cin = l.cin, cout = l.cout;
   std::vector<__nv_bfloat16> w(static_cast<size_t>(l.cout_pad) * l.k_total, __float2bfloat16(0.0f));
   std::vector<float> b(l.cout_pad, 0.0f);
+  l.raw_kernel.assign(static_cast<size_t>(cout) * l.k_total, 0.0f);
+  l.raw_bias.assign(cout, 0.0f);
+  l.bn_scale.clear();
+  if (l.has_bn) l.bn_scale.assign(cout, 1.0f);
   for (int o = 0; o < cout; ++o) {
     float scale = 1.0f, shift = 0.0f;
     if (l.has_bn) {  // y = gamma * (x - mean) / sqrt(var + eps) + beta
@@ -248,6 +88,8 @@ int Engine::set_layer(const char* name, const float* kernel, const float* bias, 
     }
     const float b0 = (l.has_bias && bias != nullptr) ? bias[o] : 0.0f;
     b[o] = b0 * scale + shift;
+    l.raw_bias[o] = b0;
+    if (l.has_bn) l.bn_scale[o] = scale;
     for (int r = 0; r < k; ++r)
       for (int s = 0; s < k; ++s)
         for (int c = 0; c < cin; ++c) {
@@ -260,6 +102,7 @@ int Engine::set_layer(const char* name, const float* kernel, const float* bias, 
             col = static_cast<size_t>(ry >> 1) * 64 + (rx >> 1) * 16 + ((ry & 1) * 2 + (rx & 1)) * 3 + c;
           }
           w[static_cast<size_t>(o) * l.k_total + col] = __float2bfloat16(v);
+          l.raw_kernel[static_cast<size_t>(o) * l.k_total + col] = kernel[((static_cast<size_t>(r) * k + s) * cin + c) * cout + o];
         }
   }
   PPB_CUDA(cudaMemcpy(l.w, w.data(), w.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
@@ -345,18 +188,10 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
   return kOk;
 }
 
-// A head convolution shared by `n_levels` pyramid levels: one launch over the multi-segment feature matrix.
-int Engine::head_conv_op(const __nv_bfloat16* x, int cin, const std::string& layer, __nv_bfloat16* y, int relu,
-                         int batch, int n_levels, int epi, float* out_f32, float* out_hull) {
-  const LayerW& l = layers[layer_index.at(layer)];
-  if (!l.loaded) return fail(kErrState, "layer '%s' has no weights (call ppb_engine_set_layer first)", l.name.c_str());
-  Op op;
-  op.kind = kOpConv;
-  ConvParams& p = op.p;
-  memset(&p, 0, sizeof(p));
+// Row segments of the multi-level feature matrix (one per pyramid level) with the 3x3 'same' tap offsets.
+void Engine::fill_head_segs(ConvParams& p, int batch, int n_levels) const {
   p.n_segs = n_levels;
   int tiles = 0, loc = 0;
-  long long last_row = 0;
   for (int i = 0; i < n_levels; ++i) {
     ConvSeg& s = p.seg[i];
     s.hp = lvl_h[i] + 2;
@@ -371,10 +206,22 @@ int Engine::head_conv_op(const __nv_bfloat16* x, int cin, const std::string& lay
       for (int c = 0; c < 3; ++c) s.tap_off[r * 3 + c] = (r - 1) * s.wp + (c - 1);
     tiles += (s.rows + kConvBlockM - 1) / kConvBlockM;
     loc += lvl_h[i] * lvl_w[i];
-    last_row = s.row_begin + s.rows;
   }
   p.n_taps = 9;
   p.n_mtiles = tiles;
+}
+
+// A head convolution shared by `n_levels` pyramid levels: one launch over the multi-segment feature matrix.
+int Engine::head_conv_op(const __nv_bfloat16* x, int cin, const std::string& layer, __nv_bfloat16* y, int relu,
+                         int batch, int n_levels, int epi, float* out_f32, float* out_hull) {
+  const LayerW& l = layers[layer_index.at(layer)];
+  if (!l.loaded) return fail(kErrState, "layer '%s' has no weights (call ppb_engine_set_layer first)", l.name.c_str());
+  Op op;
+  op.kind = kOpConv;
+  ConvParams& p = op.p;
+  memset(&p, 0, sizeof(p));
+  fill_head_segs(p, batch, n_levels);
+  const long long last_row = p.seg[n_levels - 1].row_begin + p.seg[n_levels - 1].rows;
   p.cin_blocks = cin / kConvBlockK;
   p.n_valid = l.cout;
   p.block_n = conv_pick_block_n(l.cout_pad, p.n_taps * p.cin_blocks, p.n_mtiles, epi == kEpiBf16);
@@ -551,30 +398,32 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
     if (*t != nullptr) return kOk;
     return new_tensor(t, name, 0, 0, c, 1, 1, feat_rows_total);
   };
-  Tensor *ra, *rb, *ca, *cb, *ma, *mb;
-  PPB_TRY(tower_buf(&ra, "reg_tower_a", 512));
-  PPB_TRY(tower_buf(&rb, "reg_tower_b", 512));
-  PPB_TRY(tower_buf(&ca, "cls_tower_a", 256));
-  PPB_TRY(tower_buf(&cb, "cls_tower_b", 256));
-  PPB_TRY(tower_buf(&ma, "mask_tower_a", 256));
-  PPB_TRY(tower_buf(&mb, "mask_tower_b", 256));
-  PPB_TRY(head_conv_op(feat->ptr, 256, "pyramid_regression3D_0", ra->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
-  PPB_TRY(head_conv_op(ra->ptr, 512, "pyramid_regression3D_1", rb->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
-  PPB_TRY(head_conv_op(rb->ptr, 512, "pyramid_regression3D_2", ra->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
-  PPB_TRY(head_conv_op(ra->ptr, 512, "pyramid_regression3D_3", rb->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
-  PPB_TRY(head_conv_op(rb->ptr, 512, "pyramid_regression3D", nullptr, 0, batch, 3,
-                       decode ? kEpiHeadDecode : kEpiHeadRaw, out_reg, decode ? out_hull : nullptr));
-  PPB_TRY(head_conv_op(feat->ptr, 256, "pyramid_classification_0", ca->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
-  PPB_TRY(head_conv_op(ca->ptr, 256, "pyramid_classification_1", cb->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
-  PPB_TRY(head_conv_op(cb->ptr, 256, "pyramid_classification_2", ca->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
-  PPB_TRY(head_conv_op(ca->ptr, 256, "pyramid_classification_3", cb->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
-  PPB_TRY(head_conv_op(cb->ptr, 256, "pyramid_classification", nullptr, 0, batch, 3, kEpiHeadSigmoid, out_cls, nullptr));
+  // inference ping-pongs two buffers per tower; the training plan keeps all four activations (ReLU masks / wgrad inputs)
+  Tensor *rt[4], *ct[4], *mt[4];
+  for (int i = 0; i < 4; ++i) {
+    const std::string sfx = training_plan ? "_t" + std::to_string(i) : ((i & 1) ? "_b" : "_a");
+    PPB_TRY(tower_buf(&rt[i], "reg_tower" + sfx, 512));
+    PPB_TRY(tower_buf(&ct[i], "cls_tower" + sfx, 256));
+    PPB_TRY(tower_buf(&mt[i], "mask_tower" + sfx, 256));
+  }
+  const int kRaw = decode ? kEpiHeadDecode : kEpiHeadRaw;
+  PPB_TRY(head_conv_op(feat->ptr, 256, "pyramid_regression3D_0", rt[0]->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
+  for (int i = 1; i < 4; ++i)
+    PPB_TRY(head_conv_op(rt[i - 1]->ptr, 512, "pyramid_regression3D_" + std::to_string(i), rt[i]->ptr, 1, batch, 3,
+                         kEpiBf16, nullptr, nullptr));
+  PPB_TRY(head_conv_op(rt[3]->ptr, 512, "pyramid_regression3D", nullptr, 0, batch, 3, kRaw, out_reg,
+                       decode ? out_hull : nullptr));
+  PPB_TRY(head_conv_op(feat->ptr, 256, "pyramid_classification_0", ct[0]->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
+  for (int i = 1; i < 4; ++i)
+    PPB_TRY(head_conv_op(ct[i - 1]->ptr, 256, "pyramid_classification_" + std::to_string(i), ct[i]->ptr, 1, batch, 3,
+                         kEpiBf16, nullptr, nullptr));
+  PPB_TRY(head_conv_op(ct[3]->ptr, 256, "pyramid_classification", nullptr, 0, batch, 3, kEpiHeadSigmoid, out_cls, nullptr));
   if (out_mask != nullptr) {  // mask head on P3 only (retinanet.py:296-297)
-    PPB_TRY(head_conv_op(feat->ptr, 256, "mask_0", ma->ptr, 1, batch, 1, kEpiBf16, nullptr, nullptr));
-    PPB_TRY(head_conv_op(ma->ptr, 256, "mask_1", mb->ptr, 1, batch, 1, kEpiBf16, nullptr, nullptr));
-    PPB_TRY(head_conv_op(mb->ptr, 256, "mask_2", ma->ptr, 1, batch, 1, kEpiBf16, nullptr, nullptr));
-    PPB_TRY(head_conv_op(ma->ptr, 256, "mask_3", mb->ptr, 1, batch, 1, kEpiBf16, nullptr, nullptr));
-    PPB_TRY(head_conv_op(mb->ptr, 256, "mask_out", nullptr, 0, batch, 1, kEpiHeadSigmoid, out_mask, nullptr));
+    PPB_TRY(head_conv_op(feat->ptr, 256, "mask_0", mt[0]->ptr, 1, batch, 1, kEpiBf16, nullptr, nullptr));
+    for (int i = 1; i < 4; ++i)
+      PPB_TRY(head_conv_op(mt[i - 1]->ptr, 256, "mask_" + std::to_string(i), mt[i]->ptr, 1, batch, 1, kEpiBf16, nullptr,
+                           nullptr));
+    PPB_TRY(head_conv_op(mt[3]->ptr, 256, "mask_out", nullptr, 0, batch, 1, kEpiHeadSigmoid, out_mask, nullptr));
   }
 #undef PPB_TRY
   bound_batch = batch;
@@ -639,10 +488,6 @@ int Engine::capture(cudaStream_t st) {
 using namespace ppb;
 
 extern "C" {
-
-struct ppb_engine {
-  Engine e;
-};
 
 int ppb_engine_create(ppb_engine** out, int device, int max_batch, int height, int width, int num_classes,
                       int num_anchors) {

@@ -1,0 +1,179 @@
+// PFPN engine internals shared by engine.cu (inference plan) and train.cu (training step).
+#pragma once
+#include "../../include/pyrapose_b200.h"
+#include "conv_igemm.h"
+#include "elementwise.h"
+#include "errors.h"
+#include "launch_count.h"
+
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace ppb {
+
+void conv_fill_single_seg(ConvParams& p, int batch, int h, int w, int ksize);
+int conv_pick_block_n(int cout_pad, int k_iters, long m_tiles, bool bf16_out);
+
+struct LayerW {
+  std::string name;
+  int ksize, cin, cout, stride;
+  bool has_bn, has_bias;
+  int k_total;   // columns of the device weight matrix (ksize*ksize*cin, stem: 192)
+  int cout_pad;  // rows, multiple of 16
+  __nv_bfloat16* w = nullptr;
+  float* bias = nullptr;
+  bool loaded = false;
+  // host copies kept for the training step (master weights start from them): raw Keras kernel as [cout][k_total]
+  // (un-folded), raw bias [cout], frozen-BatchNorm scale [cout] (empty without BN)
+  std::vector<float> raw_kernel, raw_bias, bn_scale;
+};
+
+struct Tensor {  // bf16 activation on a pixel grid with pad_lo border pixels before and pad_hi after the interior
+  std::string name;
+  __nv_bfloat16* ptr = nullptr;
+  int H = 0, W = 0, C = 0, pad_lo = 1, pad_hi = 1;  // padded-flat: 1/1; stem grid: 0/3
+  int hp() const { return H + pad_lo + pad_hi; }
+  int wp() const { return W + pad_lo + pad_hi; }
+  long long rows(int B) const { return static_cast<long long>(B) * hp() * wp(); }
+};
+
+enum OpKind { kOpConv, kOpStemS2d, kOpMaxpool, kOpPlanes, kOpAdd };
+
+struct Op {
+  OpKind kind;
+  // conv
+  CUtensorMap ta, tb, to, tr;
+  ConvParams p;
+  // elementwise
+  const void* in0 = nullptr;
+  const void* in1 = nullptr;
+  const void* in2 = nullptr;
+  const void* in3 = nullptr;
+  void* out = nullptr;
+  int a[8] = {0};
+  char name[40] = {0};
+  double flops = 0.0;  // conv: 2 * interior pixels * Cout * K (algorithmic)
+};
+
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+inline int same_pad_before(int in, int k, int stride) {
+  const int out = (in + stride - 1) / stride;
+  const int total = std::max((out - 1) * stride + k - in, 0);
+  return total / 2;
+}
+
+struct Engine {
+  int device = 0, max_batch = 0, H = 0, W = 0, num_classes = 0, num_anchors = 0;
+  std::vector<LayerW> layers;
+  std::map<std::string, int> layer_index;
+  std::vector<std::unique_ptr<Tensor>> tensors;
+  std::map<std::string, Tensor*> tensor_index;
+  std::vector<void*> allocations;
+  // anchors / decode parameters (host copies; baked into the head conv's params)
+  float base_anchor[kConvMaxSegs][9][4];
+  float stride[kConvMaxSegs];
+  float dec_mean[16], dec_std[16];
+  bool anchors_set = false;
+  // level geometry
+  int lvl_h[3], lvl_w[3];
+  int seg_row_begin[3], seg_tile_begin[3];
+  long long feat_rows_total = 0;
+  int feat_tiles_total = 0;
+  // plan
+  std::vector<Op> ops;
+  int bound_batch = 0;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t graph_exec = nullptr;
+  int graph_kernels = 0;
+  size_t arena_bytes = 0;
+  // TMA-store epilogue through the shared-memory chunk ring (residual chunks prefetched by TMA): 0 never; 1 only convs
+  // with a residual input; 2 every backbone / PFPN conv (measured best, profiles/r01_per_op_staged_variants.txt);
+  // 3 head towers too. Override with PPB_STAGED_EPILOGUE for experiments.
+  int staged_epilogue = 2;
+  // training step (train.cu): every head-tower activation keeps its own buffer so the backward pass can read it
+  bool training_plan = false;
+  std::shared_ptr<struct TrainState> train;
+
+  ~Engine() {
+    if (graph_exec) cudaGraphExecDestroy(graph_exec);
+    if (graph) cudaGraphDestroy(graph);
+    for (void* p : allocations) cudaFree(p);
+  }
+
+  int add_layer(const std::string& name, int ksize, int cin, int cout, int stride, bool bn, bool bias) {
+    LayerW l;
+    l.name = name;
+    l.ksize = ksize;
+    l.cin = cin;
+    l.cout = cout;
+    l.stride = stride;
+    l.has_bn = bn;
+    l.has_bias = bias;
+    l.k_total = (ksize == 7) ? 256 : ksize * ksize * cin;  // stem: 4 row taps x (4 px x 16 ch), see launch_stem_s2d
+    l.cout_pad = round_up(cout, 16);
+    layer_index[name] = static_cast<int>(layers.size());
+    layers.push_back(l);
+    return static_cast<int>(layers.size()) - 1;
+  }
+
+  int device_alloc(void** p, size_t bytes) {
+    PPB_CUDA(cudaMalloc(p, bytes));
+    PPB_CUDA(cudaMemset(*p, 0, bytes));
+    allocations.push_back(*p);
+    arena_bytes += bytes;
+    return kOk;
+  }
+
+  Tensor* tensor(const std::string& name) {
+    auto it = tensor_index.find(name);
+    return it == tensor_index.end() ? nullptr : it->second;
+  }
+
+  int new_tensor(Tensor** out, const std::string& name, int h, int w, int c, int pad, int planes = 1,
+                 long long rows_override = 0, int pad_hi = -1) {
+    std::unique_ptr<Tensor> t(new Tensor);
+    t->name = name;
+    t->H = h;
+    t->W = w;
+    t->C = c;
+    t->pad_lo = pad;
+    t->pad_hi = pad_hi >= 0 ? pad_hi : pad;
+    long long rows = rows_override ? rows_override : t->rows(max_batch) * planes;
+    rows = (rows + kConvBlockM - 1) / kConvBlockM * kConvBlockM + kConvBlockM;  // slack: TMA rows may overlap the end
+    void* p = nullptr;
+    int rc = device_alloc(&p, static_cast<size_t>(rows) * c * sizeof(__nv_bfloat16));
+    if (rc != kOk) return rc;
+    t->ptr = static_cast<__nv_bfloat16*>(p);
+    *out = t.get();
+    tensor_index[name] = t.get();
+    tensors.push_back(std::move(t));
+    return kOk;
+  }
+
+  void define_layers();
+  int allocate_weights();
+  int set_layer(const char* name, const float* kernel, const float* bias, const float* gamma, const float* beta,
+                const float* mean, const float* var, float eps);
+  int build_plan(int batch, const float* images, float* out_reg, float* out_cls, float* out_mask, float* out_hull,
+                 int decode);
+  int conv_op(const Tensor* x, int x_planes, const std::string& layer, const Tensor* res, Tensor* y, int relu, int batch,
+              int src_h = 0, int src_w = 0);
+  int head_conv_op(const __nv_bfloat16* x, int cin, const std::string& layer, __nv_bfloat16* y, int relu, int batch,
+                   int n_levels, int epi, float* out_f32, float* out_hull);
+  int capture(cudaStream_t st);
+  int launch_all(cudaStream_t st);
+  void fill_head_segs(ConvParams& p, int batch, int n_levels) const;
+};
+
+}  // namespace ppb
+
+// The opaque C handle (include/pyrapose_b200.h).
+struct ppb_engine {
+  ppb::Engine e;
+};

@@ -147,3 +147,101 @@ class Engine(object):
             nat.check(self.lib.ppb_engine_op_info(self._h, i, name, 64, ctypes.byref(fl)))
             out.append((name.value.decode(), fl.value))
         return out
+
+    # ------------------------------------------------------------------ training step (ppb_engine_train_*)
+    def train_bind(self, batch):
+        """Allocates the step's device buffers (inputs, targets, the three model outputs) and captures
+        forward + losses + backward as one CUDA graph. Returns the buffer dict."""
+        key = ("train", int(batch))
+        if self._bound == key:
+            return self.buffers
+        dev = self.device
+        B, N, C = int(batch), self.num_boxes, self.num_classes
+        mh, mw = self.levels[0]
+        f32 = dict(dtype=torch.float32, device=dev)
+        buf = {
+            "images": torch.empty((B, self.height, self.width, 3), **f32),
+            "y_reg": torch.zeros((B, N, 17), **f32),
+            "y_cls": torch.zeros((B, N, C + 1), **f32),
+            "y_mask": torch.zeros((B, mh * mw, C + 1), **f32),
+            "3Dbox": torch.empty((B, N, 16), **f32),
+            "cls": torch.empty((B, N, C), **f32),
+            "mask": torch.empty((B, mh * mw, C), **f32),
+        }
+        with torch.cuda.device(dev):
+            torch.cuda.current_stream().synchronize()
+            nat.check(self.lib.ppb_engine_train_bind(self._h, B, nat.ptr(buf["images"]), nat.ptr(buf["y_reg"]),
+                                                     nat.ptr(buf["y_cls"]), nat.ptr(buf["y_mask"]),
+                                                     nat.ptr(buf["3Dbox"]), nat.ptr(buf["cls"]), nat.ptr(buf["mask"]),
+                                                     None))
+        self.buffers = buf
+        self._bound = key
+        self._grads = None
+        return buf
+
+    def train_forward_backward(self, eager=False):
+        with torch.cuda.device(self.device):
+            nat.check(self.lib.ppb_engine_train_forward_backward(self._h, int(eager), nat.current_stream_ptr()))
+
+    def grads_tensor(self):
+        """The engine's flat fp32 gradient buffer as a torch tensor sharing the device memory (for NCCL all-reduce)."""
+        if getattr(self, "_grads", None) is None:
+            p = ctypes.c_void_p()
+            n = ctypes.c_longlong()
+            nat.check(self.lib.ppb_engine_train_grads(self._h, ctypes.byref(p), ctypes.byref(n)))
+
+            class _Flat(object):
+                __cuda_array_interface__ = {"shape": (int(n.value),), "typestr": "<f4", "data": (int(p.value), False),
+                                            "version": 2, "strides": None}
+            with torch.cuda.device(self.device):
+                self._grads = torch.as_tensor(_Flat(), device=self.device)
+        return self._grads
+
+    def train_apply(self, lr, beta_1=0.9, beta_2=0.999, epsilon=1e-7, clipnorm=0.0, grad_scale=1.0):
+        f = ctypes.c_float
+        with torch.cuda.device(self.device):
+            nat.check(self.lib.ppb_engine_train_apply(self._h, f(lr), f(beta_1), f(beta_2), f(epsilon), f(clipnorm),
+                                                      f(grad_scale), nat.current_stream_ptr()))
+
+    def train_losses(self):
+        """Synchronises. -> dict 3Dbox / cls / mask / l2 / grad_norm and the positive counts."""
+        out = (ctypes.c_double * 5)()
+        cnt = (ctypes.c_int * 3)()
+        with torch.cuda.device(self.device):
+            nat.check(self.lib.ppb_engine_train_losses(self._h, out, cnt, nat.current_stream_ptr()))
+        return {"3Dbox": out[0], "cls": out[1], "mask": out[2], "l2": out[3], "grad_norm": float(np.sqrt(out[4])),
+                "positives": (cnt[0], cnt[1], cnt[2])}
+
+    def train_param_info(self, layer):
+        ko, bo = ctypes.c_longlong(), ctypes.c_longlong()
+        tr = ctypes.c_int()
+        nat.check(self.lib.ppb_engine_train_param_info(self._h, layer.encode(), ctypes.byref(ko), ctypes.byref(bo),
+                                                       ctypes.byref(tr)))
+        return ko.value, bo.value, bool(tr.value)
+
+    def train_read(self, which, offset, count):
+        """which: 'grads' | 'weights' | 'm' | 'v' -> float32 numpy copy of [offset, offset+count) of that flat buffer."""
+        idx = {"grads": 0, "weights": 1, "m": 2, "v": 3}[which]
+        out = np.empty(int(count), dtype=np.float32)
+        nat.check(self.lib.ppb_engine_train_read(self._h, idx, ctypes.c_longlong(offset), ctypes.c_longlong(count),
+                                                 out.ctypes.data_as(_f32p)))
+        return out
+
+    def train_layer_tensor(self, which, name, ksize, cin, cout, bias=False):
+        """One layer's kernel (as Keras HWIO) or bias from a flat training buffer."""
+        ko, bo, _ = self.train_param_info(name)
+        if bias:
+            return self.train_read(which, bo, cout) if bo >= 0 else None
+        if ko < 0:
+            return None
+        flat = self.train_read(which, ko, cout * ksize * ksize * cin)
+        return np.ascontiguousarray(flat.reshape(cout, ksize, ksize, cin).transpose(1, 2, 3, 0))  # O,HWI -> HWIO
+
+    def train_op_table(self):
+        out = []
+        name = ctypes.create_string_buffer(64)
+        fl = ctypes.c_double()
+        for i in range(self.lib.ppb_engine_train_num_ops(self._h)):
+            nat.check(self.lib.ppb_engine_train_op_info(self._h, i, name, 64, ctypes.byref(fl)))
+            out.append((name.value.decode(), fl.value))
+        return out

@@ -60,6 +60,7 @@ class PFPNModel(object):
         print_fn("Total params: {:,}".format(total))
 
     def get_weights_dict(self):
+        self.sync_weights()
         return self.weights
 
     def set_weights_dict(self, weights, skip_mismatch=False):
@@ -81,9 +82,11 @@ class PFPNModel(object):
             self.set_weights_dict({k: z[k] for k in z.files if not k.startswith("__")}, skip_mismatch=skip_mismatch)
 
     def save_weights(self, filepath):
+        self.sync_weights()
         np.savez(filepath, **self.weights)
 
     def save(self, filepath):
+        self.sync_weights()
         meta = np.array([self.num_classes, self.num_anchors, int(self.inference)], dtype=np.int64)
         with open(filepath, "wb") as f:
             np.savez(f, __meta__=meta, **self.weights)
@@ -222,6 +225,88 @@ class PFPNModel(object):
 
     def activation(self, name, height, width):
         return self._engines[(height, width)].activation(name)
+
+    # ------------------------------------------------------------------ training (keras.Model.compile / train_on_batch)
+    def compile(self, loss=None, optimizer=None, **kwargs):
+        """ Mirror of `training_model.compile(loss={'3Dbox': orthogonal_l1(), 'cls': focal(), 'mask': focal()},
+        optimizer=Adam(lr, clipnorm=0.001))` (PyraPose/bin/train.py:95-102). Only that configuration exists in the
+        native step; anything else raises ValueError."""
+        from .. import losses, optimizers
+        if self.inference:
+            raise ValueError("compile() needs a training model")
+        loss = loss if loss is not None else {'3Dbox': losses.orthogonal_l1(), 'cls': losses.focal(),
+                                              'mask': losses.focal()}
+        want = {'3Dbox': ('orthogonal_l1', {'weight': 0.125, 'sigma': 3.0}),
+                'cls': ('focal', {'alpha': 0.25, 'gamma': 2.0}), 'mask': ('focal', {'alpha': 0.25, 'gamma': 2.0})}
+        if set(loss) != set(want):
+            raise ValueError("loss must name the outputs %s" % sorted(want))
+        for k, (kind, params) in want.items():
+            if getattr(loss[k], 'kind', None) != kind or loss[k].params != params:
+                raise ValueError("output %s: the native training step implements %s(%s) only" % (k, kind, params))
+        self.optimizer = optimizer if optimizer is not None else optimizers.Adam(lr=1e-5, clipnorm=0.001)
+        if not isinstance(self.optimizer, optimizers.Adam):
+            raise ValueError("optimizer must be pyrapose_b200.optimizers.Adam")
+        self._compiled = True
+        self._train_engine = None
+        self.metrics_names = ['loss', '3Dbox_loss', 'cls_loss', 'mask_loss']
+
+    def train_on_batch(self, x, y, sync_losses=True):
+        """ One optimisation step on a batch, as `fit_generator` runs it for every batch of the reference generator.
+
+        x: images (B,H,W,3) float32; y: [regression_3D (B,N,17), labels (B,N,C+1), mask (B,H/8*W/8,C+1)] — the three
+        arrays anchor_targets_bbox returns. numpy or CUDA tensors. With torch.distributed initialised the flat
+        gradient buffer is all-reduced (NCCL) and averaged before the Adam step (one replica per GPU).
+        Returns [loss, 3Dbox_loss, cls_loss, mask_loss] (loss includes the l2 regulariser) — of the local replica's
+        batch, like Keras — or None when sync_losses=False (no host synchronisation)."""
+        import torch
+        if not getattr(self, '_compiled', False):
+            raise RuntimeError("You must compile a model before training/testing. Use `model.compile(optimizer, loss)`.")
+        if not isinstance(y, (list, tuple)) or len(y) != 3:
+            raise ValueError("expected y = [regression_3D, labels, mask]")
+        B, H, W = int(x.shape[0]), int(x.shape[1]), int(x.shape[2])
+        eng = self._engine(B, H, W)
+        buf = eng.train_bind(B)
+        self._train_engine = eng
+
+        def put(dst, src):
+            src = torch.from_numpy(np.ascontiguousarray(src, dtype=np.float32)) if isinstance(src, np.ndarray) else src
+            if tuple(src.shape) != tuple(dst.shape):
+                raise ValueError("expected an array of shape %s, got %s" % (tuple(dst.shape), tuple(src.shape)))
+            dst.copy_(src, non_blocking=True)
+
+        opt = self.optimizer
+        with torch.cuda.device(eng.device):
+            put(buf["images"], x)
+            put(buf["y_reg"], y[0])
+            put(buf["y_cls"], y[1])
+            put(buf["y_mask"], y[2])
+            eng.train_forward_backward()
+            scale = 1.0
+            if torch.distributed.is_available() and torch.distributed.is_initialized() and \
+                    torch.distributed.get_world_size() > 1:
+                torch.distributed.all_reduce(eng.grads_tensor())
+                scale = 1.0 / torch.distributed.get_world_size()
+            eng.train_apply(opt.lr, opt.beta_1, opt.beta_2, opt.epsilon, opt.clipnorm, scale)
+        self._weights_stale = True
+        if not sync_losses:
+            return None
+        l = eng.train_losses()
+        self.last_step = l
+        return [l["3Dbox"] + l["cls"] + l["mask"] + l["l2"], l["3Dbox"], l["cls"], l["mask"]]
+
+    def sync_weights(self):
+        """Copies the trained master weights from the engine back into `self.weights` (Keras HWIO layout)."""
+        eng = getattr(self, '_train_engine', None)
+        if eng is None or not getattr(self, '_weights_stale', False):
+            return
+        for l in self.layers:
+            k = eng.train_layer_tensor("weights", l.name, l.ksize, l.cin, l.cout)
+            if k is None:
+                continue
+            self.weights[l.name + "/kernel"] = k
+            if l.use_bias:
+                self.weights[l.name + "/bias"] = eng.train_layer_tensor("weights", l.name, l.ksize, l.cin, l.cout, bias=True)
+        self._weights_stale = False
 
 
 def retinanet(inputs=None, backbone_layers=None, num_classes=None, num_anchors=None, create_pyramid_features=None,
