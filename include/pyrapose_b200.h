@@ -239,6 +239,8 @@ PPB_API int ppb_engine_train_param_info(const ppb_engine* engine, const char* la
 PPB_API int ppb_engine_train_read(ppb_engine* engine, int which, long long offset, long long count, float* out_host);
 PPB_API int ppb_engine_train_num_ops(const ppb_engine* engine);
 PPB_API int ppb_engine_train_op_info(const ppb_engine* engine, int index, char* name, int name_cap, double* flops);
+/* Per-launch device times (ms) of one eager training step, in op order; synchronises `stream`. */
+PPB_API int ppb_engine_train_profile(ppb_engine* engine, void* stream, float* ms_out_host, int cap);
 
 #ifdef __cplusplus
 }

@@ -31,11 +31,17 @@ def _t(a):
 # Rounding hook applied wherever the native engine stores an activation as bf16. Identity for the fp32 oracle;
 # oracle/train.py swaps in a bf16 round (straight-through, gradient rounded too) for its "bf16-emulating" mode, which
 # checks the backward arithmetic independently of ReLU-mask flips between an fp32 and a bf16 forward pass.
-_Q = [lambda x: x]
+_Q = [lambda x, name: x, lambda z, name: torch.relu(z)]
 
 
-def _q(x):
-    return _Q[0](x)
+def _q(x, name=None):
+    """A stored linear activation (convolution or Add output); `name` is the engine's tensor name."""
+    return _Q[0](x, name)
+
+
+def _qrelu(z, name=None):
+    """A stored ReLU activation."""
+    return _Q[0](_Q[1](z, name), name) if _Q[1] is not None else _Q[0](z, name)
 
 
 def _kernel(w, name):
@@ -96,7 +102,7 @@ def upsample_like(src, target):
 def resnet50(x, w, taps=None):
     """Returns [C2, C3, C4, C5] (NCHW)."""
     x = conv_valid_nobias(x, w, "conv1", stride=2, pad=3)
-    x = _q(torch.relu(frozen_bn(x, w, "bn_conv1")))
+    x = _qrelu(frozen_bn(x, w, "bn_conv1"), "conv1_relu")
     if taps is not None:
         taps["conv1_relu"] = x
     x = maxpool_same_3x3_s2(x)
@@ -108,17 +114,17 @@ def resnet50(x, w, taps=None):
             tag = "%d%s" % (stage + 2, chr(ord("a") + block))
             stride = 2 if (block == 0 and stage > 0) else 1
             y = conv_valid_nobias(x, w, "res%s_branch2a" % tag, stride=stride)
-            y = _q(torch.relu(frozen_bn(y, w, "bn%s_branch2a" % tag)))
+            y = _qrelu(frozen_bn(y, w, "bn%s_branch2a" % tag), "res%s_branch2a_relu" % tag)
             y = conv_valid_nobias(y, w, "res%s_branch2b" % tag, pad=1)
-            y = _q(torch.relu(frozen_bn(y, w, "bn%s_branch2b" % tag)))
+            y = _qrelu(frozen_bn(y, w, "bn%s_branch2b" % tag), "res%s_branch2b_relu" % tag)
             y = conv_valid_nobias(y, w, "res%s_branch2c" % tag)
             y = frozen_bn(y, w, "bn%s_branch2c" % tag)
             if block == 0:
                 sc = conv_valid_nobias(x, w, "res%s_branch1" % tag, stride=stride)
-                sc = _q(frozen_bn(sc, w, "bn%s_branch1" % tag))
+                sc = _q(frozen_bn(sc, w, "bn%s_branch1" % tag), "res%s_branch1_bn" % tag)
             else:
                 sc = x
-            x = _q(torch.relu(y + sc))
+            x = _qrelu(y + sc, "res%s_relu" % tag)
             if taps is not None:
                 taps["res%s_relu" % tag] = x
         outs.append(x)
@@ -127,46 +133,48 @@ def resnet50(x, w, taps=None):
 
 def sparce_fpn(C3, C4, C5, w, taps=None):
     """retinanet.py:180-214."""
-    P3 = _q(conv_same(C3, w, "P3_lateral"))                       # :192
-    P4 = _q(conv_same(C4, w, "P4_lateral"))                       # :193
-    P5 = _q(conv_same(C5, w, "P5_lateral"))                       # :194
-    P5_up = upsample_like(P5, P4)                                 # :196
-    P4_up = upsample_like(P4, P3)                                 # :197
-    P4_mid = _q(conv_same(_q(P5_up + P4), w, "P4_mid"))           # :198-199
-    P3_mid = _q(conv_same(_q(P4_up + P3), w, "P3_mid"))           # :200-201
-    P3_down = _q(conv_same(P3_mid, w, "P3_down", stride=2))       # :202
-    P3_out = _q(conv_same(_q(P3_mid + P3), w, "P3"))              # :203-204
-    P4_fin = P3_down + P4_mid                                     # :206
-    P4_down = _q(conv_same(P4_mid, w, "P4_down", stride=2))       # :207
-    P4_out = _q(conv_same(_q(P4_fin + P4), w, "P4"))              # :208-209
-    P5_out = _q(conv_same(_q(P4_down + P5), w, "P5"))             # :211-212
+    P3 = _q(conv_same(C3, w, "P3_lateral"), "P3_lateral")                        # :192
+    P4 = _q(conv_same(C4, w, "P4_lateral"), "P4_lateral")                        # :193
+    P5 = _q(conv_same(C5, w, "P5_lateral"), "P5_lateral")                        # :194
+    P5_up = upsample_like(P5, P4)                                                # :196
+    P4_up = upsample_like(P4, P3)                                                # :197
+    P4_mid = _q(conv_same(_q(P5_up + P4, "P4_mid_in"), w, "P4_mid"), "P4_mid")   # :198-199
+    P3_mid = _q(conv_same(_q(P4_up + P3, "P3_mid_in"), w, "P3_mid"), "P3_mid")   # :200-201
+    P3_down = _q(conv_same(P3_mid, w, "P3_down", stride=2), "P3_down")           # :202
+    P3_out = _q(conv_same(_q(P3_mid + P3, "P3_fin"), w, "P3"), "P3")             # :203-204
+    P4_fin = P3_down + P4_mid                                                    # :206
+    P4_down = _q(conv_same(P4_mid, w, "P4_down", stride=2), "P4_down")           # :207
+    P4_out = _q(conv_same(_q(P4_fin + P4, "P4_fin"), w, "P4"), "P4")             # :208-209
+    P5_out = _q(conv_same(_q(P4_down + P5, "P5_fin"), w, "P5"), "P5")            # :211-212
     if taps is not None:
         taps.update({"P3_lateral": P3, "P4_lateral": P4, "P5_lateral": P5, "P4_mid": P4_mid, "P3_mid": P3_mid,
                      "P3_down": P3_down, "P4_down": P4_down, "P3": P3_out, "P4": P4_out, "P5": P5_out})
     return [P3_out, P4_out, P5_out]
 
 
-def _tower(x, w, prefix, out_name):
+def _tower(x, w, prefix, out_name, tname=None):
     for i in range(4):
-        x = _q(torch.relu(conv_same(x, w, "%s_%d" % (prefix, i))))
+        x = _qrelu(conv_same(x, w, "%s_%d" % (prefix, i)), None if tname is None else tname % i)
     return conv_same(x, w, out_name)
 
 
-def regression_head(feat, w):
-    """retinanet.py:101-131: NHWC Reshape((-1, 16))."""
-    y = _tower(feat, w, "pyramid_regression3D", "pyramid_regression3D")
+def regression_head(feat, w, level=None):
+    """retinanet.py:101-131: NHWC Reshape((-1, 16)). `level` only names the engine tensors for the rounding hooks."""
+    y = _tower(feat, w, "pyramid_regression3D", "pyramid_regression3D",
+               None if level is None else "reg_tower_t%%d@%d" % level)
     return y.permute(0, 2, 3, 1).reshape(y.shape[0], -1, 16)
 
 
-def classification_head(feat, w, num_classes):
+def classification_head(feat, w, num_classes, level=None):
     """retinanet.py:9-54: Reshape((-1, C)) then sigmoid."""
-    y = _tower(feat, w, "pyramid_classification", "pyramid_classification")
+    y = _tower(feat, w, "pyramid_classification", "pyramid_classification",
+               None if level is None else "cls_tower_t%%d@%d" % level)
     return torch.sigmoid(y.permute(0, 2, 3, 1).reshape(y.shape[0], -1, num_classes))
 
 
-def mask_head(feat, w, num_classes):
+def mask_head(feat, w, num_classes, level=None):
     """retinanet.py:57-98."""
-    y = _tower(feat, w, "mask", "mask_out")
+    y = _tower(feat, w, "mask", "mask_out", None if level is None else "mask_tower_t%%d@%d" % level)
     return torch.sigmoid(y.permute(0, 2, 3, 1).reshape(y.shape[0], -1, num_classes))
 
 

@@ -31,6 +31,34 @@ class _RoundBF16(torch.autograd.Function):
         return g.to(torch.bfloat16).to(torch.float32)
 
 
+class _PinLinear(torch.autograd.Function):
+    """Replaces a stored activation by the tensor the native engine holds for it; the gradient passes through
+    (rounded to bf16 like the engine's gradient maps). Used by step(pinned=...)."""
+
+    @staticmethod
+    def forward(ctx, x, pinned):
+        return pinned
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).to(torch.float32), None
+
+
+class _PinRelu(torch.autograd.Function):
+    """Same for a ReLU output: the backward mask is the ENGINE's (pinned > 0), so both sides differentiate the same
+    piecewise-linear function."""
+
+    @staticmethod
+    def forward(ctx, z, pinned):
+        ctx.save_for_backward(pinned)
+        return pinned
+
+    @staticmethod
+    def backward(ctx, g):
+        (pinned,) = ctx.saved_tensors
+        return (g * (pinned > 0)).to(torch.bfloat16).to(torch.float32), None
+
+
 class _RoundWeightSTE(torch.autograd.Function):
     """bf16 round of a (BatchNorm-folded) kernel, straight-through gradient (fp32 weight gradients)."""
 
@@ -80,21 +108,30 @@ def is_trainable(key):
     return not (layer == "conv1" or layer.startswith("res2"))
 
 
-def forward_losses(images_nhwc, weights_t, targets, num_classes, emulate_bf16=False):
+def forward_losses(images_nhwc, weights_t, targets, num_classes, emulate_bf16=False, pinned=None):
     x = torch.from_numpy(np.ascontiguousarray(images_nhwc, dtype=np.float32)).permute(0, 3, 1, 2).contiguous()
     net_w = weights_t
-    if emulate_bf16:
+    saved = list(pfpn._Q)
+    if emulate_bf16 or pinned is not None:
         net_w = _emulated_weights(weights_t)
         x = x.to(torch.bfloat16).to(torch.float32)  # the stem reads the image as bf16 (launch_stem_s2d)
-        pfpn._Q[0] = _RoundBF16.apply
+        pfpn._Q[0] = lambda t, name: _RoundBF16.apply(t)
+    if pinned is not None:
+        def pin(name):
+            return torch.from_numpy(np.ascontiguousarray(pinned[name])).permute(0, 3, 1, 2).contiguous()
+        relu_names = set(n for n in pinned if n.endswith("_relu") or "_tower_t" in n)
+        # ReLU points go to _PinRelu (pfpn._qrelu hands over the PRE-activation when _Q[1] is None), the rest to
+        # _PinLinear
+        pfpn._Q[0] = lambda t, name: (_PinRelu if name in relu_names else _PinLinear).apply(t, pin(name))
+        pfpn._Q[1] = None
     try:
         _, C3, C4, C5 = pfpn.resnet50(x, net_w)
         feats = pfpn.sparce_fpn(C3, C4, C5, net_w)
-        reg = torch.cat([pfpn.regression_head(f, net_w) for f in feats], dim=1)
-        cls = torch.cat([pfpn.classification_head(f, net_w, num_classes) for f in feats], dim=1)
-        msk = pfpn.mask_head(feats[0], net_w, num_classes)
+        reg = torch.cat([pfpn.regression_head(f, net_w, i) for i, f in enumerate(feats)], dim=1)
+        cls = torch.cat([pfpn.classification_head(f, net_w, num_classes, i) for i, f in enumerate(feats)], dim=1)
+        msk = pfpn.mask_head(feats[0], net_w, num_classes, 0)
     finally:
-        pfpn._Q[0] = lambda t: t
+        pfpn._Q[0], pfpn._Q[1] = saved
     y_reg, y_cls, y_mask = [torch.from_numpy(np.ascontiguousarray(t, dtype=np.float32)) for t in targets]
     l_reg = olosses.orthogonal_l1(y_reg, reg)
     l_cls = olosses.focal(y_cls, cls)
@@ -105,11 +142,14 @@ def forward_losses(images_nhwc, weights_t, targets, num_classes, emulate_bf16=Fa
 
 
 def step(images_nhwc, weights, targets, num_classes, lr=1e-5, clipnorm=0.001, beta_1=0.9, beta_2=0.999, eps=1e-7,
-         num_threads=None, emulate_bf16=False):
+         num_threads=None, emulate_bf16=False, pinned=None):
     """One Adam step from zero moments. Returns dict with losses, raw gradients {key: HWIO/bias numpy}, the global
     gradient norm and the updated weights {key: numpy}.
     emulate_bf16=True rounds weights (after the BatchNorm fold), stored activations and gradient maps to bf16 at the
-    points where the native engine does, so that both sides see the same ReLU masks; everything else stays fp32."""
+    points where the native engine does; everything else stays fp32.
+    pinned={engine tensor name: NHWC float32} replaces every stored activation by the engine's own copy (and uses its
+    ReLU masks in the backward pass), so that the comparison isolates the backward arithmetic and the wiring of the
+    gradient graph from the ~1e-2 forward noise of bf16: see tests/test_train_gpu.py."""
     if num_threads:
         torch.set_num_threads(num_threads)
     wt = {}
@@ -118,7 +158,7 @@ def step(images_nhwc, weights, targets, num_classes, lr=1e-5, clipnorm=0.001, be
         if is_trainable(k):
             t.requires_grad_(True)
         wt[k] = t
-    l_reg, l_cls, l_mask, l2, outs = forward_losses(images_nhwc, wt, targets, num_classes, emulate_bf16)
+    l_reg, l_cls, l_mask, l2, outs = forward_losses(images_nhwc, wt, targets, num_classes, emulate_bf16, pinned)
     total = l_reg + l_cls + l_mask + l2
     total.backward()
     keys = [k for k in wt if wt[k].requires_grad]

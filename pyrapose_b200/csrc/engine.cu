@@ -427,6 +427,7 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
   }
 #undef PPB_TRY
   bound_batch = batch;
+  plan_batch = batch;
   return kOk;
 }
 
@@ -639,10 +640,21 @@ size_t ppb_engine_device_bytes(const ppb_engine* h) { return h ? h->e.arena_byte
 int ppb_engine_activation(ppb_engine* h, const char* name, float* out_host, int* shape4_host) {
   PPB_REQUIRE(h != nullptr && name != nullptr, "ppb_engine_activation: null argument");
   Engine& e = h->e;
-  PPB_REQUIRE(e.bound_batch > 0, "ppb_engine_activation: nothing bound");
+  PPB_REQUIRE(e.plan_batch > 0, "ppb_engine_activation: nothing bound");
   Tensor view;
   Tensor* t = e.tensor(name);
   const std::string nm(name);
+  const size_t at = nm.find('@');
+  if (t == nullptr && at != std::string::npos) {  // "<multi-level tensor>@<level>": one pyramid level of a head buffer
+    Tensor* base = e.tensor(nm.substr(0, at));
+    const int i = atoi(nm.c_str() + at + 1);
+    PPB_REQUIRE(base != nullptr && i >= 0 && i < 3, "ppb_engine_activation: unknown tensor '%s'", name);
+    view.ptr = base->ptr + static_cast<size_t>(e.seg_row_begin[i]) * base->C;
+    view.H = e.lvl_h[i];
+    view.W = e.lvl_w[i];
+    view.C = base->C;
+    t = &view;
+  }
   if (t == nullptr && (nm == "P3" || nm == "P4" || nm == "P5")) {
     Tensor* feat = e.tensor("features");
     PPB_REQUIRE(feat != nullptr, "ppb_engine_activation: features not allocated");
@@ -654,7 +666,7 @@ int ppb_engine_activation(ppb_engine* h, const char* name, float* out_host, int*
     t = &view;
   }
   PPB_REQUIRE(t != nullptr && t->H > 0, "ppb_engine_activation: unknown tensor '%s'", name);
-  const int B = e.bound_batch;
+  const int B = e.plan_batch;
   if (shape4_host) {
     shape4_host[0] = B;
     shape4_host[1] = t->H;

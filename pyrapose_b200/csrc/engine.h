@@ -87,7 +87,8 @@ struct Engine {
   int feat_tiles_total = 0;
   // plan
   std::vector<Op> ops;
-  int bound_batch = 0;
+  int bound_batch = 0;  // batch of the captured inference graph (0 = none)
+  int plan_batch = 0;   // batch of the last build_plan (inference or training)
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t graph_exec = nullptr;
   int graph_kernels = 0;

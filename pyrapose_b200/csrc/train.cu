@@ -883,4 +883,49 @@ int ppb_engine_train_op_info(const ppb_engine* h, int index, char* name, int nam
   return kOk;
 }
 
+/* Per-launch device times of one eager training step (forward ops first, then losses + backward), CUDA events on
+ * `stream`; fills min(cap, ppb_engine_train_num_ops) entries. Synchronises the stream. */
+int ppb_engine_train_profile(ppb_engine* h, void* stream, float* ms_out_host, int cap) {
+  PPB_REQUIRE(h != nullptr && ms_out_host != nullptr, "ppb_engine_train_profile: null argument");
+  Engine& e = h->e;
+  if (!e.train || e.train->bound_batch == 0) return fail(kErrState, "ppb_engine_train_profile: call ppb_engine_train_bind first");
+  PPB_CUDA(cudaSetDevice(e.device));
+  TrainState& t = *e.train;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nf = static_cast<int>(e.ops.size()), nb = static_cast<int>(t.bwd.size());
+  std::vector<cudaEvent_t> ev(nf + nb + 1);
+  for (auto& x : ev) PPB_CUDA(cudaEventCreate(&x));
+  PPB_CUDA(cudaMemsetAsync(t.grads, 0, t.n_params * sizeof(float), st));
+  PPB_CUDA(cudaMemsetAsync(t.loss, 0, 8 * sizeof(double), st));
+  PPB_CUDA(cudaMemsetAsync(t.counts, 0, 4 * sizeof(int), st));
+  std::vector<Op> all_f;
+  std::vector<TOp> all_b;
+  all_f.swap(e.ops);
+  all_b.swap(t.bwd);
+  int rc = kOk;
+  cudaEventRecord(ev[0], st);
+  for (int i = 0; i < nf && rc == kOk; ++i) {
+    e.ops.assign(1, all_f[i]);
+    rc = e.launch_all(st);
+    cudaEventRecord(ev[i + 1], st);
+  }
+  e.ops.clear();
+  for (int i = 0; i < nb && rc == kOk; ++i) {
+    t.bwd.assign(1, all_b[i]);
+    rc = launch_backward(e, st);
+    cudaEventRecord(ev[nf + i + 1], st);
+  }
+  e.ops.swap(all_f);
+  t.bwd.swap(all_b);
+  const cudaError_t sync = cudaStreamSynchronize(st);
+  if (rc == kOk && sync == cudaSuccess) {
+    for (int i = 0; i < nf + nb && i < cap; ++i) cudaEventElapsedTime(&ms_out_host[i], ev[i], ev[i + 1]);
+    count_launch(nf + nb);
+  }
+  for (auto& x : ev) cudaEventDestroy(x);
+  if (rc != kOk) return rc;
+  PPB_CUDA(sync);
+  return kOk;
+}
+
 }  // extern "C"

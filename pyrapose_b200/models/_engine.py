@@ -245,3 +245,11 @@ class Engine(object):
             nat.check(self.lib.ppb_engine_train_op_info(self._h, i, name, 64, ctypes.byref(fl)))
             out.append((name.value.decode(), fl.value))
         return out
+
+    def train_profile(self):
+        """[(op name, algorithmic flops, ms)] for one eager training step (forward, losses, backward)."""
+        ops = self.train_op_table()
+        ms = (ctypes.c_float * len(ops))()
+        with torch.cuda.device(self.device):
+            nat.check(self.lib.ppb_engine_train_profile(self._h, nat.current_stream_ptr(), ms, len(ops)))
+        return [(n, f, float(ms[i])) for i, (n, f) in enumerate(ops)]
