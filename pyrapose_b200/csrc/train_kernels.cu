@@ -89,13 +89,17 @@ focal_loss_grad_kernel(const float* __restrict__ prob, const float* __restrict__
       const float q = pos ? 1.0f - p : p;          // focal_weight base (losses.py:55)
       const float pc = fminf(fmaxf(p, 1e-7f), 1.0f - 1e-7f);  // keras.backend.binary_crossentropy clips to [eps, 1-eps]
       const bool inside = p > 1e-7f && p < 1.0f - 1e-7f;       // gradient of the clip
-      const float lp = logf(pc), l1p = logf(1.0f - pc);
-      const float bce = -(label * lp + (1.0f - label) * l1p);
-      const float fw = af * powf(q, gamma);
+      // labels are one-hot in practice: one logarithm suffices; the general expression is kept for soft labels
+      float bce;
+      if (label == 1.0f) bce = -logf(pc);
+      else if (label == 0.0f) bce = -logf(1.0f - pc);
+      else bce = -(label * logf(pc) + (1.0f - label) * logf(1.0f - pc));
+      const bool g2 = gamma == 2.0f;
+      const float fw = af * (g2 ? q * q : powf(q, gamma));
       local += static_cast<double>(fw * bce);
       // d/dp: focal_weight' * bce + focal_weight * bce'
       const float dq = pos ? -1.0f : 1.0f;
-      const float dfw = af * gamma * powf(q, gamma - 1.0f) * dq;
+      const float dfw = af * (g2 ? 2.0f * q : gamma * powf(q, gamma - 1.0f)) * dq;
       const float dbce = inside ? -(label / pc - (1.0f - label) / (1.0f - pc)) : 0.0f;
       const float dp = dfw * bce + fw * dbce;
       gz[e] = dp * p * (1.0f - p) * inv_norm;  // through the sigmoid
