@@ -149,3 +149,61 @@ def test_shard_range_partitions_exactly():
             assert max(sizes) - min(sizes) <= 1
     with pytest.raises(ValueError):
         shard.shard_range(4, 2, 2)
+
+
+def test_compile_mirrors_the_reference_training_configuration():
+    """models.PFPNModel.compile accepts exactly what PyraPose/bin/train.py:95-102 compiles and nothing else; no CUDA
+    is touched until train_on_batch."""
+    from pyrapose_b200 import losses, models, optimizers
+    from pyrapose_b200.models.retinanet import PFPNModel
+    m = PFPNModel(3, weights={})
+    with pytest.raises(RuntimeError):
+        m.train_on_batch(np.zeros((1, 64, 64, 3), np.float32), [None, None, None])
+    m.compile(loss={'3Dbox': losses.orthogonal_l1(), 'cls': losses.focal(), 'mask': losses.focal()},
+              optimizer=optimizers.Adam(lr=1e-5, clipnorm=0.001))
+    assert m.metrics_names == ['loss', '3Dbox_loss', 'cls_loss', 'mask_loss']
+    assert m.optimizer.get_config() == {'lr': 1e-5, 'beta_1': 0.9, 'beta_2': 0.999, 'epsilon': 1e-7, 'clipnorm': 0.001}
+    with pytest.raises(ValueError):
+        m.compile(loss={'3Dbox': losses.focal(), 'cls': losses.focal(), 'mask': losses.focal()})
+    with pytest.raises(ValueError):
+        m.compile(loss={'3Dbox': losses.orthogonal_l1(weight=1.0), 'cls': losses.focal(), 'mask': losses.focal()})
+    with pytest.raises(ValueError):
+        m.compile(loss={'cls': losses.focal()})
+    with pytest.raises(ValueError):
+        m.compile(optimizer="sgd")
+    with pytest.raises(ValueError):
+        models.convert_model(m).compile()
+    with pytest.raises(TypeError):
+        optimizers.Adam(nesterov=True)
+    with pytest.raises(ValueError):
+        m.train_on_batch(np.zeros((1, 64, 64, 3), np.float32), [None, None])
+
+
+def test_training_oracle_modes_agree_on_a_tiny_case():
+    """oracle/train.py: the bf16-emulating pass stays within 2e-2 of the fp32 pass on the losses (it only rounds), and
+    frozen tensors get no gradient."""
+    from oracle import train as otrain
+    from pyrapose_b200.models import spec
+    C, B, H, W = 2, 1, 64, 64
+    w = spec.init_weights(C, seed=2, head_init="spread", randomize_bn=True)
+    rng = np.random.default_rng(0)
+    img = rng.integers(0, 256, (B, H, W, 3)).astype(np.float32) - 110.0
+    N = 9 * (8 * 8 + 4 * 4 + 2 * 2)
+    y_reg = np.zeros((B, N, 17), np.float32)
+    y_cls = np.zeros((B, N, C + 1), np.float32)
+    y_mask = np.zeros((B, 64, C + 1), np.float32)
+    state = rng.choice([-1, 0, 1], size=(B, N), p=[.1, .7, .2]).astype(np.float32)
+    y_reg[..., :16] = rng.normal(0, 1, (B, N, 16))
+    y_reg[..., 16] = state
+    y_cls[..., C] = state
+    y_cls[..., 0] = state == 1
+    y_mask[..., C] = 1
+    y_mask[..., 1] = 1
+    a = otrain.step(img, w, (y_reg, y_cls, y_mask), C, num_threads=4)
+    b = otrain.step(img, w, (y_reg, y_cls, y_mask), C, emulate_bf16=True, num_threads=4)
+    for k in ("3Dbox", "cls", "mask"):
+        assert abs(a["losses"][k] - b["losses"][k]) <= 2e-2 * abs(a["losses"][k])
+    assert a["losses"]["l2"] == b["losses"]["l2"]
+    assert not any(k.startswith("conv1") or k.startswith("res2") or "bn" in k.split("/")[0] for k in a["grads"])
+    assert "res3a_branch2a/kernel" in a["grads"] and "mask_out/bias" in a["grads"]
+    assert a["grad_norm"] > 0 and np.isfinite(a["grad_norm"])
