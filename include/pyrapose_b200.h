@@ -98,6 +98,25 @@ PPB_API int ppb_gt_assign_f64(const double* boxes, const double* query, const in
                               long long* argmax, unsigned char* positive, unsigned char* ignore,
                               double* max_overlap, void* stream);
 
+/* Per-anchor part of anchor_targets_bbox (PyraPose/utils/anchors.py:72-287: states :138-145, one-hot labels :148,
+ * box3D_transform of the matched object's projected corners :267 / :515-559, out-of-image ignore :279-285), from the
+ * outputs of ppb_gt_assign_f64. All DEVICE pointers.
+ *   anchors f64 [n,4]; argmax i64 / positive u8 / ignore u8 [batch,n]; labels i32 [batch,k_max];
+ *   boxes16 f64 [batch,k_max,16] projected 3D-box corners per object; counts i32 [batch] objects per image;
+ *   image_wh i32 [batch,2] (width, height; width < 0: image without a shape -> no out-of-image rule)
+ *   out_regression f32 [batch,n,17], out_labels f32 [batch,n,num_classes+1]   (last column = anchor state)
+ */
+PPB_API int ppb_anchor_targets(const double* anchors, const long long* argmax, const unsigned char* positive,
+                               const unsigned char* ignore, const int* labels, const double* boxes16,
+                               const int* counts, const int* image_wh, int n, int k_max, int batch, int num_classes,
+                               float* out_regression, float* out_labels, void* stream);
+/* Mask targets of anchor_targets_bbox (anchors.py:152-164): masks u8 [batch,height,width] instance-id images, resized
+ * to the P3 grid (mask_h x mask_w) with PIL's NEAREST rule; an object marks its cells when it covers more than one.
+ *   mask_ids / labels i32 [batch,k_max]; cells i32 [batch,k_max] workspace; out_mask f32 [batch,mask_h*mask_w,C+1] */
+PPB_API int ppb_mask_targets(const unsigned char* masks, int height, int width, const int* mask_ids, const int* labels,
+                             const int* counts, int k_max, int batch, int mask_h, int mask_w, int num_classes,
+                             int* cells, float* out_mask, void* stream);
+
 /* ------------------------------------------------------------------ anchors
  * One pyramid level: out[(y*fw + x)*num_base + a] = base[a] + ((x|y)+0.5)*stride.
  * f64: PyraPose/utils/anchors.py:415-444 (shift), level loop :402-412.
@@ -185,6 +204,12 @@ PPB_API int ppb_engine_set_layer(ppb_engine* engine, const char* name, const flo
  * float32 as keras.backend.variable does, strides f32 [3]; RegressBoxes3D mean/std f32 [16] or NULL (0 / 0.2). */
 PPB_API int ppb_engine_set_anchors(ppb_engine* engine, const float* base_anchors_host, const float* strides_host,
                                    const float* mean16_host, const float* std16_host);
+/* Input staging (the step before the path: read_image_bgr -> preprocess_image, PyraPose/utils/image.py:35-62;
+ * call sites utils/linemod_eval.py:265-267, preprocessing/generator.py:320-336): with enable=1 the `images` pointer of
+ * the next ppb_engine_bind / ppb_engine_train_bind is read as RAW uint8 BGR pixels [batch,H,W,3] and
+ * preprocess_image(mode='caffe') — float32(pixel) - mean[c], mean3 = {103.939, 116.779, 123.68} when NULL — is fused
+ * into the stem's loader. Bit-identical activations to the float32 path, a quarter of the host->device bytes. */
+PPB_API int ppb_engine_set_input_u8(ppb_engine* engine, int enable, const float* mean3_host);
 /* Binds caller-owned DEVICE buffers and captures the graph for `batch` images:
  *   images    f32 [batch,H,W,3]  BGR, ImageNet-mean-subtracted (PyraPose/utils/image.py:35-62)
  *   out_box3d f32 [batch,N,16]   decode=1: decoded corners ('boxes3D'); decode=0: raw regression ('3Dbox')

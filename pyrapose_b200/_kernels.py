@@ -70,6 +70,55 @@ def gt_assign(boxes, query, query_count=None, negative_overlap=0.4, positive_ove
     return res if batched else tuple(r[0] for r in res)
 
 
+
+def anchor_targets(anchors, query, counts, labels, boxes16, image_wh, num_classes, negative_overlap=0.4,
+                   positive_overlap=0.5):
+    """Per-anchor targets of anchor_targets_bbox on the device: fused IoU assignment (ppb_gt_assign_f64) followed by
+    ppb_anchor_targets. anchors f64 [N,4]; query f64 [B,K,4]; counts i32 [B]; labels i32 [B,K]; boxes16 f64 [B,K,16];
+    image_wh i32 [B,2]. Returns CUDA tensors regression_3D f32 [B,N,17], labels f32 [B,N,C+1]."""
+    anchors = _dev(anchors, torch.float64, "anchors")
+    query = _dev(query, torch.float64, "bboxes")
+    counts = _dev(counts, torch.int32, "counts")
+    labels = _dev(labels, torch.int32, "labels")
+    boxes16 = _dev(boxes16, torch.float64, "boxes16")
+    image_wh = _dev(image_wh, torch.int32, "image_wh")
+    B, K = int(query.shape[0]), int(query.shape[1])
+    N = int(anchors.shape[0])
+    dev = anchors.device
+    argmax = torch.empty((B, N), dtype=torch.int64, device=dev)
+    pos = torch.empty((B, N), dtype=torch.uint8, device=dev)
+    ign = torch.empty((B, N), dtype=torch.uint8, device=dev)
+    reg = torch.empty((B, N, 17), dtype=torch.float32, device=dev)
+    cls = torch.empty((B, N, num_classes + 1), dtype=torch.float32, device=dev)
+    lib = nat.load()
+    with torch.cuda.device(dev):
+        nat.check(lib.ppb_gt_assign_f64(nat.ptr(anchors), nat.ptr(query), nat.ptr(counts), N, K, B, 1,
+                                        ctypes.c_double(negative_overlap), ctypes.c_double(positive_overlap),
+                                        nat.ptr(argmax), nat.ptr(pos), nat.ptr(ign), None, _stream()))
+        nat.check(lib.ppb_anchor_targets(nat.ptr(anchors), nat.ptr(argmax), nat.ptr(pos), nat.ptr(ign), nat.ptr(labels),
+                                         nat.ptr(boxes16), nat.ptr(counts), nat.ptr(image_wh), N, K, B,
+                                         int(num_classes), nat.ptr(reg), nat.ptr(cls), _stream()))
+    return reg, cls
+
+
+def mask_targets(masks, mask_ids, labels, counts, mask_h, mask_w, num_classes):
+    """Mask targets of anchor_targets_bbox on the device. masks u8 [B,H,W] instance-id images; mask_ids / labels
+    i32 [B,K]; counts i32 [B]. Returns a CUDA tensor f32 [B, mask_h*mask_w, C+1]."""
+    masks = _dev(masks, torch.uint8, "mask")
+    mask_ids = _dev(mask_ids, torch.int32, "mask_ids")
+    labels = _dev(labels, torch.int32, "labels")
+    counts = _dev(counts, torch.int32, "counts")
+    B, H, W = int(masks.shape[0]), int(masks.shape[1]), int(masks.shape[2])
+    K = int(mask_ids.shape[1])
+    dev = masks.device
+    cells = torch.empty((B, max(K, 1)), dtype=torch.int32, device=dev)
+    out = torch.empty((B, mask_h * mask_w, num_classes + 1), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        nat.check(nat.load().ppb_mask_targets(nat.ptr(masks), H, W, nat.ptr(mask_ids), nat.ptr(labels), nat.ptr(counts),
+                                              K, B, int(mask_h), int(mask_w), int(num_classes), nat.ptr(cells),
+                                              nat.ptr(out), _stream()))
+    return out
+
 # --------------------------------------------------------------------------- anchors
 def anchors_shift(base, fh, fw, stride, out=None):
     """base [A,4] f32/f64 CUDA -> [fh*fw*A, 4] shifted anchors of one level."""

@@ -14,8 +14,9 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
 __device__ __forceinline__ float lo_f(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float hi_f(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
 
-__global__ void __launch_bounds__(256) stem_s2d_kernel(const float* __restrict__ image, uint4* __restrict__ out, int B,
-                                                       int H, int W, int Hs, int Ws) {
+template <typename T>
+__global__ void __launch_bounds__(256) stem_s2d_kernel(const T* __restrict__ image, uint4* __restrict__ out, int B,
+                                                       int H, int W, int Hs, int Ws, float m0, float m1, float m2) {
   // one thread per S pixel: 2x2 input pixels x 3 channels -> 12 bf16 (+4 zero), two 16-byte stores
   const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long total = static_cast<long long>(B) * Hs * Ws;
@@ -31,9 +32,12 @@ __global__ void __launch_bounds__(256) stem_s2d_kernel(const float* __restrict__
     for (int px = 0; px < 2; ++px) {
       const int ix = 2 * (X - 2) + px;
       const bool ok = iy >= 0 && iy < H && ix >= 0 && ix < W;
-      const float* src = image + ((static_cast<long long>(b) * H + (ok ? iy : 0)) * W + (ok ? ix : 0)) * 3;
-#pragma unroll
-      for (int c = 0; c < 3; ++c) v[(py * 2 + px) * 3 + c] = ok ? __ldg(src + c) : 0.0f;
+      const T* src = image + ((static_cast<long long>(b) * H + (ok ? iy : 0)) * W + (ok ? ix : 0)) * 3;
+      // uint8 input: preprocess_image(mode='caffe') (PyraPose/utils/image.py:52-60) fused in: float32(pixel) - mean[c],
+      // the same float32 subtraction the host code does, so the bf16 values are identical to the float32 input path
+      v[(py * 2 + px) * 3 + 0] = ok ? __fsub_rn(static_cast<float>(__ldg(src + 0)), m0) : 0.0f;
+      v[(py * 2 + px) * 3 + 1] = ok ? __fsub_rn(static_cast<float>(__ldg(src + 1)), m1) : 0.0f;
+      v[(py * 2 + px) * 3 + 2] = ok ? __fsub_rn(static_cast<float>(__ldg(src + 2)), m2) : 0.0f;
     }
   }
   uint4 lo, hi;
@@ -158,7 +162,16 @@ inline unsigned blocks_for(long long total) { return static_cast<unsigned>((tota
 cudaError_t launch_stem_s2d(const float* image, __nv_bfloat16* out, int B, int H, int W, int Ho, int Wo,
                             cudaStream_t st) {
   const long long total = static_cast<long long>(B) * (Ho + 3) * (Wo + 3);
-  stem_s2d_kernel<<<blocks_for(total), 256, 0, st>>>(image, reinterpret_cast<uint4*>(out), B, H, W, Ho + 3, Wo + 3);
+  stem_s2d_kernel<float><<<blocks_for(total), 256, 0, st>>>(image, reinterpret_cast<uint4*>(out), B, H, W, Ho + 3,
+                                                            Wo + 3, 0.0f, 0.0f, 0.0f);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_stem_s2d_u8(const unsigned char* image, const float mean[3], __nv_bfloat16* out, int B, int H, int W,
+                               int Ho, int Wo, cudaStream_t st) {
+  const long long total = static_cast<long long>(B) * (Ho + 3) * (Wo + 3);
+  stem_s2d_kernel<unsigned char><<<blocks_for(total), 256, 0, st>>>(image, reinterpret_cast<uint4*>(out), B, H, W,
+                                                                    Ho + 3, Wo + 3, mean[0], mean[1], mean[2]);
   return cudaGetLastError();
 }
 

@@ -13,6 +13,10 @@ namespace ppb {
 // tensor map whose row stride (32 B) is smaller than its row extent (128 B). No im2col matrix is materialised.
 cudaError_t launch_stem_s2d(const float* image, __nv_bfloat16* out, int B, int H, int W, int Ho, int Wo,
                             cudaStream_t st);
+// Same from raw uint8 BGR pixels with preprocess_image(mode='caffe') fused in (PyraPose/utils/image.py:35-62):
+// value = float32(pixel) - mean[c]. Input staging of SURVEY.md §8f-2: a quarter of the host->device bytes.
+cudaError_t launch_stem_s2d_u8(const unsigned char* image, const float mean[3], __nv_bfloat16* out, int B, int H, int W,
+                               int Ho, int Wo, cudaStream_t st);
 
 // MaxPooling2D(3, strides 2, 'same') (keras-resnet pool1): input pixel grid [B,in_hs,in_ws,C] of which the top-left
 // Hi x Wi region is valid -> padded-flat [B,Ho+2,Wo+2,C].

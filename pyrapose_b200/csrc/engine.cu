@@ -303,7 +303,7 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
   stem = tensor("conv1_relu");
   if (stem == nullptr) PPB_TRY(new_tensor(&stem, "conv1_relu", h1, w1, 64, 0, 1, 0, 3));
   PPB_TRY(get(&x, "pool1", h2, w2, 64, 1));
-  elementwise(kOpStemS2d, images, nullptr, nullptr, nullptr, s2d->ptr, {batch, H, W, h1, w1});
+  elementwise(kOpStemS2d, images, nullptr, nullptr, nullptr, s2d->ptr, {batch, H, W, h1, w1, input_u8 ? 1 : 0});
   PPB_TRY(conv_op(s2d, 1, "conv1", nullptr, stem, 1, batch));
   elementwise(kOpMaxpool, stem->ptr, nullptr, nullptr, nullptr, x->ptr, {batch, h1, w1, stem->hp(), stem->wp(), 64, h2, w2});
 
@@ -438,8 +438,13 @@ int Engine::launch_all(cudaStream_t st) {
         PPB_CUDA(conv_launch(op.ta, op.tb, op.to, op.tr, op.p, 0, st));
         break;
       case kOpStemS2d:
-        PPB_CUDA(launch_stem_s2d(static_cast<const float*>(op.in0), static_cast<__nv_bfloat16*>(op.out), op.a[0],
-                                 op.a[1], op.a[2], op.a[3], op.a[4], st));
+        if (op.a[5])
+          PPB_CUDA(launch_stem_s2d_u8(static_cast<const unsigned char*>(op.in0), input_mean,
+                                      static_cast<__nv_bfloat16*>(op.out), op.a[0], op.a[1], op.a[2], op.a[3], op.a[4],
+                                      st));
+        else
+          PPB_CUDA(launch_stem_s2d(static_cast<const float*>(op.in0), static_cast<__nv_bfloat16*>(op.out), op.a[0],
+                                   op.a[1], op.a[2], op.a[3], op.a[4], st));
         break;
       case kOpMaxpool:
         PPB_CUDA(launch_maxpool3x3s2(static_cast<const __nv_bfloat16*>(op.in0), static_cast<__nv_bfloat16*>(op.out),
@@ -581,6 +586,16 @@ int ppb_engine_set_anchors(ppb_engine* h, const float* base_anchors_host, const 
   if (std16_host) memcpy(e.dec_std, std16_host, sizeof(e.dec_std));
   e.anchors_set = true;
   e.bound_batch = 0;  // parameters are baked into the plan: force a re-bind
+  return kOk;
+}
+
+int ppb_engine_set_input_u8(ppb_engine* h, int enable, const float* mean3_host) {
+  PPB_REQUIRE(h != nullptr, "ppb_engine_set_input_u8: null engine");
+  Engine& e = h->e;
+  e.input_u8 = enable != 0;
+  if (mean3_host != nullptr)
+    for (int i = 0; i < 3; ++i) e.input_mean[i] = mean3_host[i];
+  e.bound_batch = 0;  // the input type is baked into the plan: force a re-bind
   return kOk;
 }
 

@@ -98,6 +98,9 @@ struct Engine {
   // 3 head towers too. Override with PPB_STAGED_EPILOGUE for experiments.
   int staged_epilogue = 2;
   // training step (train.cu): every head-tower activation keeps its own buffer so the backward pass can read it
+  // input staging: images bound as raw uint8 BGR with the 'caffe' mean subtraction fused into the stem loader
+  bool input_u8 = false;
+  float input_mean[3] = {103.939f, 116.779f, 123.68f};
   bool training_plan = false;
   std::shared_ptr<struct TrainState> train;
 

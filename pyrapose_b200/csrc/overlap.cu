@@ -136,6 +136,93 @@ __global__ void __launch_bounds__(256) gt_assign_kernel(const double* __restrict
   }
 }
 
+// ------------------------------------------------------------------ anchor_targets_bbox, per-anchor part
+// (PyraPose/utils/anchors.py:136-148, 267, 279-285). One thread per (image, anchor): anchor state from the fused
+// assignment, one-hot label of the matched box, the 16 corner regression targets
+//   ((gt16[argmax][j] - anchor[j % 4]) / (w | h) - 0) / 0.2     (box3D_transform, anchors.py:515-559; float64, then
+// stored as float32 exactly like the assignment into the float32 `regression_3D` array), and the "centre outside the
+// image" override. boxes16 are the projected 3D-box corners the host computes per object (anchors.py:207-215).
+__global__ void __launch_bounds__(256)
+anchor_targets_kernel(const double* __restrict__ anchors, const long long* __restrict__ argmax,
+                      const unsigned char* __restrict__ positive, const unsigned char* __restrict__ ignore,
+                      const int* __restrict__ labels, const double* __restrict__ boxes16,
+                      const int* __restrict__ counts, const int* __restrict__ image_wh, int n, int k_max,
+                      int num_classes, float* __restrict__ out_reg, float* __restrict__ out_cls) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (i >= n) return;
+  const double a0 = anchors[i * 4 + 0], a1 = anchors[i * 4 + 1], a2 = anchors[i * 4 + 2], a3 = anchors[i * 4 + 3];
+  const long long o = static_cast<long long>(b) * n + i;
+  float* reg = out_reg + o * 17;
+  float* cls = out_cls + o * (num_classes + 1);
+  const int cnt = counts[b];
+  float state = 0.0f;
+  int label = -1;
+  if (cnt > 0) {
+    const bool pos = positive[o] != 0;
+    if (ignore[o]) state = -1.0f;
+    if (pos) state = 1.0f;
+    const long long k = argmax[o];
+    if (pos) label = labels[static_cast<long long>(b) * k_max + k];
+    const double* g = boxes16 + (static_cast<long long>(b) * k_max + k) * 16;
+    const double w = a2 - a0, h = a3 - a1;
+    const double base[4] = {a0, a1, a2, a3};
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const double t = (g[j] - base[j & 3]) / ((j & 1) ? h : w);
+      reg[j] = static_cast<float>((t - 0.0) / 0.2);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) reg[j] = 0.0f;
+  }
+  // anchors whose centre lies outside the image are ignored (anchors.py:279-285); width < 0 = image without a shape
+  const int iw = image_wh[b * 2], ih = image_wh[b * 2 + 1];
+  if (iw >= 0 && ((a0 + a2) / 2 >= iw || (a1 + a3) / 2 >= ih)) state = -1.0f;
+  reg[16] = state;
+  for (int c = 0; c < num_classes; ++c) cls[c] = (c == label) ? 1.0f : 0.0f;
+  cls[num_classes] = state;
+}
+
+// ------------------------------------------------------------------ anchor_targets_bbox, mask part (anchors.py:152-164)
+// The instance-id image is resized to the P3 grid with PIL's NEAREST rule (src = floor((dst + 0.5) * in / out)); every
+// object whose id covers MORE THAN ONE cell marks those cells with its class and state 1.
+__device__ __forceinline__ int nearest_index(int dst, int in, int out) {
+  int s = static_cast<int>(floor((static_cast<double>(dst) + 0.5) * static_cast<double>(in) / static_cast<double>(out)));
+  return s < in - 1 ? s : in - 1;
+}
+
+__global__ void __launch_bounds__(256)
+mask_count_cells_kernel(const unsigned char* __restrict__ masks, int H, int W, int mh, int mw,
+                        const int* __restrict__ mask_ids, const int* __restrict__ counts, int k_max,
+                        int* __restrict__ cells) {
+  const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (cell >= mh * mw) return;
+  const int y = cell / mw, x = cell - y * mw;
+  const int id = masks[(static_cast<long long>(b) * H + nearest_index(y, H, mh)) * W + nearest_index(x, W, mw)];
+  for (int k = 0; k < counts[b]; ++k)
+    if (mask_ids[b * k_max + k] == id) atomicAdd(cells + b * k_max + k, 1);
+}
+
+__global__ void __launch_bounds__(256)
+mask_targets_kernel(const unsigned char* __restrict__ masks, int H, int W, int mh, int mw,
+                    const int* __restrict__ mask_ids, const int* __restrict__ labels, const int* __restrict__ counts,
+                    const int* __restrict__ cells, int k_max, int num_classes, float* __restrict__ out) {
+  const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (cell >= mh * mw) return;
+  const int y = cell / mw, x = cell - y * mw;
+  const int id = masks[(static_cast<long long>(b) * H + nearest_index(y, H, mh)) * W + nearest_index(x, W, mw)];
+  float* row = out + (static_cast<long long>(b) * mh * mw + cell) * (num_classes + 1);
+  for (int c = 0; c <= num_classes; ++c) row[c] = 0.0f;
+  for (int k = 0; k < counts[b]; ++k)
+    if (mask_ids[b * k_max + k] == id && cells[b * k_max + k] > 1) {
+      row[labels[b * k_max + k]] = 1.0f;
+      row[num_classes] = 1.0f;
+    }
+}
+
 }  // namespace
 }  // namespace ppb
 
@@ -179,6 +266,47 @@ int ppb_gt_assign_f64(const double* boxes, const double* query, const int* query
   gt_assign_kernel<<<dim3((n + 255) / 256, batch), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       boxes, query, query_count, n, k_max, bs, negative_overlap, positive_overlap, argmax, positive, ignore,
       max_overlap);
+  PPB_CUDA(cudaGetLastError());
+  count_launch();
+  return kOk;
+}
+
+int ppb_anchor_targets(const double* anchors, const long long* argmax, const unsigned char* positive,
+                       const unsigned char* ignore, const int* labels, const double* boxes16, const int* counts,
+                       const int* image_wh, int n, int k_max, int batch, int num_classes, float* out_regression,
+                       float* out_labels, void* stream) {
+  PPB_REQUIRE(n >= 0 && k_max >= 0 && batch >= 1 && num_classes >= 1, "ppb_anchor_targets: bad sizes n=%d k=%d batch=%d",
+              n, k_max, batch);
+  if (n == 0) return kOk;
+  PPB_REQUIRE(anchors && argmax && positive && ignore && counts && image_wh && out_regression && out_labels,
+              "ppb_anchor_targets: null buffer");
+  PPB_REQUIRE(k_max == 0 || (labels != nullptr && boxes16 != nullptr), "ppb_anchor_targets: null annotations");
+  PPB_REQUIRE(batch <= 65535, "ppb_anchor_targets: batch out of range");
+  anchor_targets_kernel<<<dim3((n + 255) / 256, batch), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      anchors, argmax, positive, ignore, labels, boxes16, counts, image_wh, n, k_max, num_classes, out_regression,
+      out_labels);
+  PPB_CUDA(cudaGetLastError());
+  count_launch();
+  return kOk;
+}
+
+int ppb_mask_targets(const unsigned char* masks, int height, int width, const int* mask_ids, const int* labels,
+                     const int* counts, int k_max, int batch, int mask_h, int mask_w, int num_classes, int* cells,
+                     float* out_mask, void* stream) {
+  PPB_REQUIRE(height > 0 && width > 0 && mask_h > 0 && mask_w > 0 && batch >= 1 && batch <= 65535 && num_classes >= 1,
+              "ppb_mask_targets: bad sizes");
+  PPB_REQUIRE(masks && counts && out_mask && (k_max == 0 || (mask_ids && labels && cells)),
+              "ppb_mask_targets: null buffer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const dim3 grid((mask_h * mask_w + 255) / 256, batch);
+  if (k_max > 0) {
+    PPB_CUDA(cudaMemsetAsync(cells, 0, static_cast<size_t>(batch) * k_max * sizeof(int), st));
+    mask_count_cells_kernel<<<grid, 256, 0, st>>>(masks, height, width, mask_h, mask_w, mask_ids, counts, k_max, cells);
+    PPB_CUDA(cudaGetLastError());
+    count_launch();
+  }
+  mask_targets_kernel<<<grid, 256, 0, st>>>(masks, height, width, mask_h, mask_w, mask_ids, labels, counts, cells, k_max,
+                                            num_classes, out_mask);
   PPB_CUDA(cudaGetLastError());
   count_launch();
   return kOk;

@@ -88,15 +88,20 @@ class Engine(object):
         self._bound = None
 
     # ------------------------------------------------------------------ execution
-    def bind(self, batch, decode=True, want_mask=True, want_hull=False):
-        key = (int(batch), bool(decode), bool(want_mask), bool(want_hull))
+    def _set_input(self, input_u8):
+        nat.check(self.lib.ppb_engine_set_input_u8(self._h, int(bool(input_u8)), None))
+
+    def bind(self, batch, decode=True, want_mask=True, want_hull=False, input_u8=False):
+        """input_u8: `images` holds raw uint8 BGR pixels; preprocess_image('caffe') runs inside the stem loader."""
+        key = (int(batch), bool(decode), bool(want_mask), bool(want_hull), bool(input_u8))
         if self._bound == key:
             return self.buffers
         dev = self.device
         B, N, C = int(batch), self.num_boxes, self.num_classes
         mh, mw = self.levels[0]
         buf = {
-            "images": torch.empty((B, self.height, self.width, 3), dtype=torch.float32, device=dev),
+            "images": torch.empty((B, self.height, self.width, 3), dtype=torch.uint8 if input_u8 else torch.float32,
+                                  device=dev),
             "boxes3D": torch.empty((B, N, 16), dtype=torch.float32, device=dev),
             "cls": torch.empty((B, N, C), dtype=torch.float32, device=dev),
             "mask": torch.empty((B, mh * mw, C), dtype=torch.float32, device=dev) if want_mask else None,
@@ -104,6 +109,7 @@ class Engine(object):
         }
         with torch.cuda.device(dev):
             torch.cuda.current_stream().synchronize()
+            self._set_input(input_u8)
             nat.check(self.lib.ppb_engine_bind(self._h, B, nat.ptr(buf["images"]), nat.ptr(buf["boxes3D"]),
                                                nat.ptr(buf["cls"]), nat.ptr(buf["mask"]), nat.ptr(buf["hull"]),
                                                int(decode), None))
@@ -149,10 +155,10 @@ class Engine(object):
         return out
 
     # ------------------------------------------------------------------ training step (ppb_engine_train_*)
-    def train_bind(self, batch):
+    def train_bind(self, batch, input_u8=False):
         """Allocates the step's device buffers (inputs, targets, the three model outputs) and captures
         forward + losses + backward as one CUDA graph. Returns the buffer dict."""
-        key = ("train", int(batch))
+        key = ("train", int(batch), bool(input_u8))
         if self._bound == key:
             return self.buffers
         dev = self.device
@@ -160,7 +166,8 @@ class Engine(object):
         mh, mw = self.levels[0]
         f32 = dict(dtype=torch.float32, device=dev)
         buf = {
-            "images": torch.empty((B, self.height, self.width, 3), **f32),
+            "images": torch.empty((B, self.height, self.width, 3), dtype=torch.uint8 if input_u8 else torch.float32,
+                                  device=dev),
             "y_reg": torch.zeros((B, N, 17), **f32),
             "y_cls": torch.zeros((B, N, C + 1), **f32),
             "y_mask": torch.zeros((B, mh * mw, C + 1), **f32),
@@ -170,6 +177,7 @@ class Engine(object):
         }
         with torch.cuda.device(dev):
             torch.cuda.current_stream().synchronize()
+            self._set_input(input_u8)
             nat.check(self.lib.ppb_engine_train_bind(self._h, B, nat.ptr(buf["images"]), nat.ptr(buf["y_reg"]),
                                                      nat.ptr(buf["y_cls"]), nat.ptr(buf["y_mask"]),
                                                      nat.ptr(buf["3Dbox"]), nat.ptr(buf["cls"]), nat.ptr(buf["mask"]),

@@ -120,21 +120,32 @@ class PFPNModel(object):
             self._engines[key] = eng
         return eng
 
-    def forward_device(self, images, want_hull=False, eager=False):
-        """images: float32 (B,H,W,3) numpy (pinned or not) or CUDA tensor, BGR mean-subtracted.
-        Returns the engine's output tensors (valid until the next call): dict boxes3D / cls / mask / hull."""
+    @staticmethod
+    def _as_input(images):
+        """-> (torch tensor, is_uint8). float arrays are BGR mean-subtracted images (what the reference's callers pass
+        after preprocess_image); uint8 arrays are RAW BGR images: preprocess_image(mode='caffe') then runs fused in the
+        stem's loader on the device (utils/image.py:35-62), with identical results and a quarter of the copy."""
         import torch
         if isinstance(images, np.ndarray):
             if images.ndim != 4 or images.shape[3] != 3:
                 raise ValueError("expected images of shape (B, H, W, 3), got %s" % (images.shape,))
-            src = torch.from_numpy(np.ascontiguousarray(images, dtype=np.float32))
-        else:
-            if images.dim() != 4 or images.shape[3] != 3:
-                raise ValueError("expected images of shape (B, H, W, 3), got %s" % (tuple(images.shape),))
-            src = images.float() if images.dtype != torch.float32 else images
+            if images.dtype == np.uint8:
+                return torch.from_numpy(np.ascontiguousarray(images)), True
+            return torch.from_numpy(np.ascontiguousarray(images, dtype=np.float32)), False
+        if images.dim() != 4 or images.shape[3] != 3:
+            raise ValueError("expected images of shape (B, H, W, 3), got %s" % (tuple(images.shape),))
+        if images.dtype == torch.uint8:
+            return images, True
+        return (images.float() if images.dtype != torch.float32 else images), False
+
+    def forward_device(self, images, want_hull=False, eager=False):
+        """images: (B,H,W,3) numpy (pinned or not) or CUDA tensor; float32 BGR mean-subtracted, or raw uint8 BGR.
+        Returns the engine's output tensors (valid until the next call): dict boxes3D / cls / mask / hull."""
+        import torch
+        src, u8 = self._as_input(images)
         B, H, W = int(src.shape[0]), int(src.shape[1]), int(src.shape[2])
         eng = self._engine(B, H, W)
-        buf = eng.bind(B, decode=self.inference, want_mask=True, want_hull=want_hull)
+        buf = eng.bind(B, decode=self.inference, want_mask=True, want_hull=want_hull, input_u8=u8)
         with torch.cuda.device(eng.device):
             buf["images"].copy_(src, non_blocking=True)
             eng.run(eager=eager)
@@ -184,18 +195,16 @@ class PFPNModel(object):
             return [o.numpy().copy() for o in outs]
 
         for i, x in enumerate(batches):
-            src = torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)) if isinstance(x, np.ndarray) else x
-            if src.dim() != 4 or src.shape[3] != 3:
-                raise ValueError("expected images of shape (B, H, W, 3), got %s" % (tuple(src.shape),))
+            src, u8 = self._as_input(x)
             B, H, W = int(src.shape[0]), int(src.shape[1]), int(src.shape[2])
             eng = self._engine(B, H, W)
-            buf = eng.bind(B, decode=True, want_mask=True, want_hull=True)
+            buf = eng.bind(B, decode=True, want_mask=True, want_hull=True, input_u8=u8)
             k = i & 1
             with torch.cuda.device(eng.device):
                 main = torch.cuda.current_stream()
                 if copy_stream is None:
                     copy_stream = torch.cuda.Stream()
-                if staging[k] is None or staging[k].shape != buf["images"].shape:
+                if staging[k] is None or staging[k].shape != buf["images"].shape or staging[k].dtype != buf["images"].dtype:
                     staging[k] = torch.empty_like(buf["images"])
                 # the staging buffer was last read by the device-side copy of batch i-2: wait for THAT copy only, not
                 # for the forward pass of batch i-1 that is still running on `main`
@@ -253,7 +262,7 @@ class PFPNModel(object):
     def train_on_batch(self, x, y, sync_losses=True):
         """ One optimisation step on a batch, as `fit_generator` runs it for every batch of the reference generator.
 
-        x: images (B,H,W,3) float32; y: [regression_3D (B,N,17), labels (B,N,C+1), mask (B,H/8*W/8,C+1)] — the three
+        x: images (B,H,W,3) float32 (mean-subtracted) or raw uint8 BGR; y: [regression_3D (B,N,17), labels (B,N,C+1), mask (B,H/8*W/8,C+1)] — the three
         arrays anchor_targets_bbox returns. numpy or CUDA tensors. With torch.distributed initialised the flat
         gradient buffer is all-reduced (NCCL) and averaged before the Adam step (one replica per GPU).
         Returns [loss, 3Dbox_loss, cls_loss, mask_loss] (loss includes the l2 regulariser) — of the local replica's
@@ -263,13 +272,15 @@ class PFPNModel(object):
             raise RuntimeError("You must compile a model before training/testing. Use `model.compile(optimizer, loss)`.")
         if not isinstance(y, (list, tuple)) or len(y) != 3:
             raise ValueError("expected y = [regression_3D, labels, mask]")
+        x, u8 = self._as_input(x)
         B, H, W = int(x.shape[0]), int(x.shape[1]), int(x.shape[2])
         eng = self._engine(B, H, W)
-        buf = eng.train_bind(B)
+        buf = eng.train_bind(B, input_u8=u8)
         self._train_engine = eng
 
         def put(dst, src):
-            src = torch.from_numpy(np.ascontiguousarray(src, dtype=np.float32)) if isinstance(src, np.ndarray) else src
+            if isinstance(src, np.ndarray):
+                src = torch.from_numpy(np.ascontiguousarray(src, dtype=np.uint8 if src.dtype == np.uint8 else np.float32))
             if tuple(src.shape) != tuple(dst.shape):
                 raise ValueError("expected an array of shape %s, got %s" % (tuple(dst.shape), tuple(src.shape)))
             dst.copy_(src, non_blocking=True)

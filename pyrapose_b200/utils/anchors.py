@@ -175,13 +175,25 @@ def _nearest_resize(mask, out_w, out_h):
     return mask[ys][:, xs]
 
 
-def anchor_targets_bbox(anchors, image_group, annotations_group, num_classes, negative_overlap=0.4,
-                        positive_overlap=0.5):
-    """ Generate anchor targets for bbox detection (same contract as anchors.py:72-287).
+def _projected_corners(ann):
+    """(n, 16) float64: image projections of the 8 corners of every object's 3D box (anchors.py:207-215)."""
+    out = np.empty((len(ann['poses']), 16))
+    for idx, pose in enumerate(ann['poses']):
+        rot = np.asarray(_quat2mat(pose[3:]), dtype=np.float32)
+        corners = rot[:3, :3].dot(ann['segmentations'][idx].T).T + np.repeat(pose[np.newaxis, 0:3], 8, axis=0)
+        cam = ann['cam_params'][idx]
+        out[idx] = np.reshape(toPix_array(corners, fx=cam[0], fy=cam[1], cx=cam[2], cy=cam[3]), (16))
+    return out
 
-    Returns (regression_3D (B, N, 17), labels_batch (B, N, num_classes + 1), mask_batch (B, H/8*W/8, num_classes + 1));
-    the last column is the anchor state (-1 ignore, 0 background, 1 foreground).
-    """
+
+def anchor_targets_bbox_device(anchors, image_group, annotations_group, num_classes, negative_overlap=0.4,
+                               positive_overlap=0.5):
+    """ anchor_targets_bbox with the targets left on the GPU: returns three CUDA tensors
+    (regression_3D (B, N, 17), labels (B, N, C + 1), mask (B, H/8*W/8, C + 1)) that model.train_on_batch consumes
+    without a host round trip. The host only packs the annotation lists (a few hundred numbers per image: boxes,
+    labels, the projected 3D-box corners of anchors.py:207-215 in float64, mask ids); the N x K IoU assignment, the
+    per-anchor states / one-hot labels / 16 regression targets and the mask targets run in CUDA kernels
+    (ppb_gt_assign_f64, ppb_anchor_targets, ppb_mask_targets) with the reference's float64 arithmetic."""
     import torch
     from .. import _kernels
     assert (len(image_group) == len(annotations_group)), "The length of the images and annotations need to be equal."
@@ -190,59 +202,52 @@ def anchor_targets_bbox(anchors, image_group, annotations_group, num_classes, ne
         for key in ('bboxes', 'labels', 'poses', 'segmentations'):
             assert (key in annotations), "Annotations should contain %s." % key
 
-    batch, n = len(image_group), anchors.shape[0]
-    labels_batch = np.zeros((batch, n, num_classes + 1), dtype=np.float32)
-    regression_3D = np.zeros((batch, n, 16 + 1), dtype=np.float32)
+    batch = len(image_group)
+    dev = anchors.device if isinstance(anchors, torch.Tensor) else _device()
+    kmax = max(1, max(a['bboxes'].shape[0] for a in annotations_group))
+    q = np.zeros((batch, kmax, 4), dtype=np.float64)
+    b16 = np.zeros((batch, kmax, 16), dtype=np.float64)
+    lab = np.zeros((batch, kmax), dtype=np.int32)
+    ids = np.full((batch, kmax), -1, dtype=np.int32)
+    cnt = np.zeros(batch, dtype=np.int32)
+    wh = np.full((batch, 2), -1, dtype=np.int32)
     mh, mw = [int(v) for v in guess_shapes(image_group[0].shape[:2], [3])[0]]
-    mask_batch = np.zeros((batch, mh * mw, num_classes + 1), dtype=np.float32)
+    masks = None
+    for i, (image, ann) in enumerate(zip(image_group, annotations_group)):
+        k = ann['bboxes'].shape[0]
+        if np.shape(image):
+            wh[i] = (image.shape[1], image.shape[0])
+        if not k:
+            continue
+        cnt[i] = k
+        q[i, :k] = ann['bboxes'][:, :4]
+        lab[i, :k] = np.asarray(ann['labels']).astype(int)
+        b16[i, :k] = _projected_corners(ann)
+        ids[i, :k] = np.asarray(ann['mask_ids']).astype(int)
+        m = np.asarray(ann['mask'][0])
+        if masks is None:
+            masks = np.zeros((batch,) + m.shape[:2], dtype=np.uint8)
+        masks[i] = m
+    a_dev = anchors if isinstance(anchors, torch.Tensor) else \
+        torch.from_numpy(np.ascontiguousarray(anchors, dtype=np.float64)).to(dev)
+    t = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
+    cnt_d, lab_d = t(cnt), t(lab)
+    reg, cls = _kernels.anchor_targets(a_dev, t(q), cnt_d, lab_d, t(b16), t(wh), num_classes, negative_overlap,
+                                       positive_overlap)
+    if masks is None:
+        mask = torch.zeros((batch, mh * mw, num_classes + 1), dtype=torch.float32, device=dev)
+    else:
+        mask = _kernels.mask_targets(t(masks), t(ids), lab_d, cnt_d, mh, mw, num_classes)
+    return reg, cls, mask
 
-    # one fused IoU/argmax launch for every image that has boxes
-    with_boxes = [i for i, a in enumerate(annotations_group) if a['bboxes'].shape[0]]
-    assign = {}
-    if with_boxes:
-        dev = _device()
-        kmax = max(annotations_group[i]['bboxes'].shape[0] for i in with_boxes)
-        q = np.zeros((len(with_boxes), kmax, 4), dtype=np.float64)
-        cnt = np.zeros(len(with_boxes), dtype=np.int32)
-        for j, i in enumerate(with_boxes):
-            bb = annotations_group[i]['bboxes']
-            q[j, :bb.shape[0]] = bb[:, :4]
-            cnt[j] = bb.shape[0]
-        pos, ign, arg = _kernels.gt_assign(torch.from_numpy(np.ascontiguousarray(anchors.astype(np.float64))).to(dev),
-                                           torch.from_numpy(q).to(dev), torch.from_numpy(cnt).to(dev),
-                                           negative_overlap, positive_overlap)
-        pos, ign, arg = pos.cpu().numpy(), ign.cpu().numpy(), arg.cpu().numpy()
-        for j, i in enumerate(with_boxes):
-            assign[i] = (pos[j], ign[j], arg[j])
 
-    centers_x = (anchors[:, 0] + anchors[:, 2]) / 2
-    centers_y = (anchors[:, 1] + anchors[:, 3]) / 2
-    for index, (image, ann) in enumerate(zip(image_group, annotations_group)):
-        if index in assign:
-            positive, ignore, argmax = assign[index]
-            for arr in (labels_batch, regression_3D):
-                arr[index, ignore, -1] = -1
-                arr[index, positive, -1] = 1
-            labels_batch[index, positive, ann['labels'][argmax[positive]].astype(int)] = 1
+def anchor_targets_bbox(anchors, image_group, annotations_group, num_classes, negative_overlap=0.4,
+                        positive_overlap=0.5):
+    """ Generate anchor targets for bbox detection (same contract as anchors.py:72-287).
 
-            mask = ann['mask'][0]
-            boxes16 = np.empty((0, 16))
-            for idx, pose in enumerate(ann['poses']):
-                cls = int(ann['labels'][idx])
-                hit = np.where(_nearest_resize(mask, mw, mh).flatten() == int(ann['mask_ids'][idx]))[0]
-                if len(hit) > 1:
-                    mask_batch[index, hit, cls] = 1
-                    mask_batch[index, hit, -1] = 1
-                rot = np.asarray(_quat2mat(pose[3:]), dtype=np.float32)
-                corners = rot[:3, :3].dot(ann['segmentations'][idx].T).T + np.repeat(pose[np.newaxis, 0:3], 8, axis=0)
-                cam = ann['cam_params'][idx]
-                px = toPix_array(corners, fx=cam[0], fy=cam[1], cx=cam[2], cy=cam[3])
-                boxes16 = np.concatenate([boxes16, [np.reshape(px, (16))]], axis=0)
-            regression_3D[index, :, :-1] = box3D_transform(anchors, boxes16[argmax, :], num_classes)
-
-        if image.shape:  # anchors whose centre lies outside the image are ignored
-            outside = np.logical_or(centers_x >= image.shape[1], centers_y >= image.shape[0])
-            labels_batch[index, outside, -1] = -1
-            regression_3D[index, outside, -1] = -1
-
-    return regression_3D, labels_batch, mask_batch
+    Returns (regression_3D (B, N, 17), labels_batch (B, N, num_classes + 1), mask_batch (B, H/8*W/8, num_classes + 1))
+    float32 numpy; the last column is the anchor state (-1 ignore, 0 background, 1 foreground). Computed on the GPU
+    (anchor_targets_bbox_device) and copied back.
+    """
+    return tuple(x.cpu().numpy() for x in anchor_targets_bbox_device(anchors, image_group, annotations_group,
+                                                                     num_classes, negative_overlap, positive_overlap))

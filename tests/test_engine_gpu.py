@@ -144,3 +144,30 @@ def test_detect_stream_equals_detect_on_batch(cuda_device):
             assert np.array_equal(a, b)
     with pytest.raises(ValueError):
         list(train.detect_stream(imgs))
+
+
+def test_uint8_input_staging_is_bit_identical(cuda_device):
+    """Raw uint8 BGR images with preprocess_image('caffe') fused into the stem loader give exactly the
+    outputs of the float32 path fed with utils.image.preprocess_image(images) — same float32 subtraction, same bf16
+    rounding — for predict_on_batch and detect_on_batch."""
+    from pyrapose_b200 import models
+    from pyrapose_b200.models import spec
+    from pyrapose_b200.utils.image import preprocess_image
+    C, B, H, W = 4, 2, 136, 200
+    weights = spec.init_weights(C, seed=3, head_init="spread", randomize_bn=True)
+    train = models.backbone("resnet50").retinanet(C)
+    train.set_weights_dict(weights)
+    infer = models.convert_model(train)
+    rng = np.random.default_rng(11)
+    raw = rng.integers(0, 256, (B, H, W, 3)).astype(np.uint8)
+    ref = [o.copy() for o in infer.predict_on_batch(np.stack([preprocess_image(im) for im in raw]))]
+    got = infer.predict_on_batch(raw)
+    for g, r in zip(got, ref):
+        assert np.array_equal(g, r)
+    det_ref = infer.detect_on_batch(np.stack([preprocess_image(im) for im in raw]))
+    det = infer.detect_on_batch(raw)
+    for g, r in zip(det, det_ref):
+        assert np.array_equal(g, r)
+    outs = list(infer.detect_stream([raw, raw]))
+    for g, r in zip(outs[1], det_ref):
+        assert np.array_equal(g, r)
