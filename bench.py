@@ -327,7 +327,7 @@ def run_ours(args):
             "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": "PFPN ResNet-50 inference + 3D-box-corner decode + filter_detections (thr 0.05, NMS 0.5, "
-                                   "max 300), batch %d per GPU, 480x640, 15 classes" % B,
+                                   "max 300), batch %d per GPU, %dx%d, %d classes" % (B, H, W, C),
                        "global_batch": world * B, "parallelism": "replicas x%d (no collective)" % world,
                        "weights": "random-init (seed 1), he-normal heads, cls bias %.1f: %.1f%% of scores pass 0.05"
                                   % (args.cls_bias, 100 * pass_rate),
@@ -344,7 +344,7 @@ def run_ours(args):
                          # ncu --set full capture (profiles/r01_full_convs.txt, launch 64; B=32): 227.7 + 179.5 MB against
                          # 2 x 222k rows x 512 ch x 2 B = 455 MB of algorithmic input + output (the tail of the output
                          # is still in L2 when the kernel ends): no wasted re-reads
-                         "traffic": 407275776 if B == 32 else None,
+                         "traffic": 407275776 if (B, H, W, C) == (32, 480, 640, 15) else None,
                          "traffic_launch": "pyramid_regression3D_1, profiles/r01_full_convs.txt", "top_launch": top,
                          "launches_per_step": n_conv, "conv_ms_per_step": conv_ms, "other_ms_per_step": other_ms,
                          "flops_per_image": flops_img, "peak_source": peak_src + " bf16_tflops_sustained",
@@ -370,9 +370,14 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--cpu-images", type=int, default=8)
+    ap.add_argument("--height", type=int, default=H, help="other BASELINE.json configs, e.g. config 5: 960 x 1280, 30 classes")
+    ap.add_argument("--width", type=int, default=W)
+    ap.add_argument("--classes", type=int, default=C)
     ap.add_argument("--cls-bias", type=float, default=-6.0,
                     help="classification output bias: -6.0 = ~2%% of scores > 0.05 (primary), -4.6 = ~13%% (dense stress)")
     args = ap.parse_args()
+    globals().update(H=args.height, W=args.width, C=args.classes,
+                     METRIC="images_per_sec_pfpn_%dx%d_infer_decode_filter" % (args.height, args.width))
     if args.impl == "reference":
         run_reference(args)
     else:
