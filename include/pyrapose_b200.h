@@ -177,6 +177,29 @@ PPB_API int ppb_vote_gather(const uint32_t* mask, const float* scores, const flo
                             int num_classes, const long long* offsets, long long* indices, float* votes,
                             float* confidence, void* stream);
 
+/* ------------------------------------------------------------------ pose from corner votes (the step after the path)
+ * Replaces, for ALL (image, class) groups of a batch in one call, the evaluators' per-class
+ *   cv2.solvePnPRansac(obj_points (k*8,1,3), est_points (k*8,1,2), K, iterationsCount=300, reprojectionError=5.0,
+ *                      confidence=0.99, flags=cv2.SOLVEPNP_ITERATIVE)
+ * (PyraPose/utils/linemod_eval.py:479-485; PyraPose_ROS_wrapper/scripts/pyrapose_node.py:652-659) on the votes that
+ * ppb_vote_gather compacted. Hypotheses = POSIT on single votes (a vote holds all 8 box corners), scored against every
+ * correspondence of the group (inlier <=> reprojection error <= reprojection_error px), best one refined on its
+ * inliers by damped Gauss-Newton on the reprojection error. All pointers DEVICE.
+ *   votes      f32 [total_votes,16]   (x0,y0,...,x7,y7 per vote; 16-byte aligned)
+ *   offsets    i64 [groups+1]         votes of group g are rows offsets[g] .. offsets[g+1]
+ *   obj_points f32 [groups,8,3]       the 3D box corners of the group's class, in the votes' corner order
+ *   cam        f32 [groups,4]         fx, fy, cx, cy
+ *   out_rt     f32 [groups,6]         Rodrigues rotation vector, translation (zeros when no pose)
+ *   out_inliers i32 [groups]          inlier correspondences of the best hypothesis; 0 = no pose (retval False):
+ *                                     fewer than min_inliers (cv2 needs >= 5 model points)
+ *   out_rmse   f32 [groups] or NULL   RMS reprojection error over the inliers after refinement
+ */
+PPB_API size_t ppb_pnp_workspace_bytes(int groups, long long total_votes, int iterations);
+PPB_API int ppb_pnp_ransac_votes(const float* votes, const long long* offsets, const float* obj_points,
+                                 const float* cam, int groups, long long total_votes, int iterations,
+                                 float reprojection_error, int min_inliers, float* out_rt, int* out_inliers,
+                                 float* out_rmse, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------ PFPN inference engine
  * Replaces `model.predict_on_batch(images)` for the models built by Backbone.retinanet(num_classes)
  * (PyraPose/models/resnet.py:79-110, PyraPose/models/retinanet.py:260-299) and models.convert_model

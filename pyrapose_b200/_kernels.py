@@ -283,3 +283,34 @@ def conv2d_bf16(x_padded, weight, bias=None, residual=None, ksize=3, relu=False)
         nat.check(nat.load().ppb_conv2d_bf16(nat.ptr(x), nat.ptr(w), nat.ptr(b), nat.ptr(r), nat.ptr(y), B, Hp - 2,
                                              Wp - 2, Cin, Cout, int(ksize), int(relu), _stream()))
     return y
+
+
+# --------------------------------------------------------------------------- pose from votes
+def pnp_ransac_votes(votes, offsets, obj_points, cam, iterations=300, reprojection_error=5.0, min_inliers=5):
+    """Batched cv2.solvePnPRansac replacement over vote groups (ppb_pnp_ransac_votes). votes f32 [T,16];
+    offsets i64 [G+1]; obj_points f32 [G,8,3]; cam f32 [G,4] (fx, fy, cx, cy).
+    Returns rt f32 [G,6] (Rodrigues vector, translation), inliers i32 [G] (0 = no pose), rmse f32 [G]."""
+    votes = _dev(votes, torch.float32, "votes")
+    offsets = _dev(offsets, torch.int64, "offsets")
+    obj_points = _dev(obj_points, torch.float32, "obj_points")
+    cam = _dev(cam, torch.float32, "cam")
+    G = int(offsets.shape[0]) - 1
+    T = int(votes.shape[0])
+    dev = offsets.device
+    rt = torch.zeros((max(G, 0), 6), dtype=torch.float32, device=dev)
+    inl = torch.zeros((max(G, 0),), dtype=torch.int32, device=dev)
+    rmse = torch.zeros((max(G, 0),), dtype=torch.float32, device=dev)
+    if G <= 0:
+        return rt, inl, rmse
+    if tuple(obj_points.shape) != (G, 8, 3) or tuple(cam.shape) != (G, 4):
+        raise ValueError("obj_points must be [G,8,3] and cam [G,4] for G = %d groups" % G)
+    lib = nat.load()
+    lib.ppb_pnp_workspace_bytes.restype = ctypes.c_size_t
+    need = int(lib.ppb_pnp_workspace_bytes(G, ctypes.c_longlong(T), int(iterations)))
+    ws = _workspace(dev, need)
+    with torch.cuda.device(dev):
+        nat.check(lib.ppb_pnp_ransac_votes(nat.ptr(votes), nat.ptr(offsets), nat.ptr(obj_points), nat.ptr(cam), G,
+                                           ctypes.c_longlong(T), int(iterations), ctypes.c_float(reprojection_error),
+                                           int(min_inliers), nat.ptr(rt), nat.ptr(inl), nat.ptr(rmse), nat.ptr(ws),
+                                           ctypes.c_size_t(ws.numel()), _stream()))
+    return rt, inl, rmse

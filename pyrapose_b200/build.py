@@ -34,6 +34,7 @@ def _optional_sources():
         ("elementwise.cu", False),
         ("engine.cu", False),
         ("conv_wgrad.cu", False),
+        ("pnp.cu", False),
         ("train_kernels.cu", False),
         ("train.cu", False),
     ]

@@ -173,6 +173,18 @@ class PFPNModel(object):
                                          nms_threshold=nms_threshold)
         return [o.cpu().numpy() for o in out]
 
+    def estimate_poses_on_batch(self, x, threeD_boxes, camera, threshold=0.5, min_votes=10, iterations=300,
+                                reprojection_error=5.0):
+        """ predict_on_batch + the evaluators' vote filter + pose from votes, all on the device
+        (PyraPose/utils/linemod_eval.py:303-334, 427-430, 479-485): per image a list of
+        {cls, rvec, R, t, votes, inliers, confidence, rmse}. See utils/pose.py."""
+        from ..utils import pose
+        if not self.inference:
+            raise ValueError("estimate_poses_on_batch needs an inference model (models.convert_model)")
+        buf = self.forward_device(x)
+        return pose.estimate_poses(buf["cls"], buf["boxes3D"], threeD_boxes, camera, threshold, min_votes, iterations,
+                                   reprojection_error)
+
     def detect_stream(self, batches, score_threshold=0.05, max_detections=300, nms=True, nms_threshold=0.5,
                       class_specific_filter=True):
         """Pipelined detect_on_batch over an iterable of host batches (the loop keras.Model.predict /

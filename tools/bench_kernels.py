@@ -90,5 +90,24 @@ print("   gt_assign: %.1f G pairs/s" % r["gpairs_per_s"])
 # ---- anchors
 timed("anchors_for_shape f64 960x1280", lambda: ua.anchors_for_shape_device((960, 1280, 3)), 226800 * 32, flush=False,
       note="3 launches + allocation; launch-latency bound")
+# ---- pose from votes: 32 images x 3 detected classes, 200 votes each (1 px noise, 25 % outlier votes)
+import time
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+import test_pnp_gpu as TP
+rng = np.random.default_rng(3)
+pg = [TP._group(rng, 200, 1.0, 0.25) for _ in range(96)]
+p_off = torch.from_numpy(np.arange(97, dtype=np.int64) * 200).to(dev)
+p_votes = torch.from_numpy(np.concatenate([g[3] for g in pg])).to(dev)
+p_obj = torch.from_numpy(np.stack([g[0] for g in pg])).to(dev)
+p_cam = torch.from_numpy(np.tile(np.asarray(TP.CAM, np.float32), (96, 1))).to(dev)
+timed("pnp_ransac_votes 96 groups x 200 votes", lambda: _kernels.pnp_ransac_votes(p_votes, p_off, p_obj, p_cam),
+      96 * 200 * 64, flush=False, note="300 hypotheses/group; latency-bound (3 launches), ms is the figure")
+from oracle import pnp as opnp
+t0 = time.perf_counter()
+for g in pg[:24]:
+    opnp.solve_pnp_ransac_votes(g[3], g[0], TP.CAM)
+cv_ms = (time.perf_counter() - t0) * 1e3 / 24 * 96
+results[-1]["cv2_ms_same_work_1core"] = cv_ms
+print("   cv2.solvePnPRansac, same 96 groups on one host core: %.1f ms (sampled on 24) -> x%.0f" % (cv_ms, cv_ms / results[-1]["ms"]))
 if "--json" in sys.argv:
     json.dump(results, open(sys.argv[sys.argv.index("--json") + 1], "w"), indent=1)
