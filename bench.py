@@ -303,10 +303,23 @@ def run_ours(args):
         n_boxes = eng.num_boxes
         pass_rate = float((buf["cls"] > 0.05).float().mean())
         flush = torch.empty(1 << 30, dtype=torch.uint8, device=dev)  # L2 flush; also hides host launch latency
-        for _ in range(3):
-            _kernels.score_mask(buf["cls"], 0.05, want_counts=False)
-        ts = []
+        # four distinct score tensors (435 MB > the 126 MB L2), launched back to back inside ONE event pair: the
+        # per-launch time is then the kernel's own (a lone launch between two events carries ~6 us of launch floor
+        # on this box, tools/probe_hbm.py); the lone-launch figure is reported beside it
+        score_set = [buf["cls"]] + [buf["cls"].clone() for _ in range(3)]
+        for sc in score_set:
+            _kernels.score_mask(sc, 0.05, want_counts=False)
+        ts, ts1 = [], []
         for _ in range(10):
+            flush.fill_(1)
+            s0 = torch.cuda.Event(enable_timing=True)
+            s1 = torch.cuda.Event(enable_timing=True)
+            s0.record()
+            for sc in score_set:
+                _kernels.score_mask(sc, 0.05, want_counts=False)
+            s1.record()
+            torch.cuda.synchronize()
+            ts.append(s0.elapsed_time(s1) / len(score_set))
             flush.fill_(1)
             s0 = torch.cuda.Event(enable_timing=True)
             s1 = torch.cuda.Event(enable_timing=True)
@@ -314,9 +327,10 @@ def run_ours(args):
             _kernels.score_mask(buf["cls"], 0.05, want_counts=False)
             s1.record()
             torch.cuda.synchronize()
-            ts.append(s0.elapsed_time(s1))
-        del flush
+            ts1.append(s0.elapsed_time(s1))
+        del flush, score_set
         mask_ms = statistics.median(ts)
+        mask_ms_single = statistics.median(ts1)
         mask_gbs = B * n_boxes * C * 4 / (mask_ms * 1e-3) / 1e9
         # ---- CPU baseline on this box's host cores (bounded sample)
         threads = os.cpu_count() or 1
@@ -351,7 +365,12 @@ def run_ours(args):
                          "frac_of_burst": achieved / float(peaks["bf16_tflops"])},
             "roofline_hbm": {"kernel": "score_mask_kernel", "bound": "hbm", "achieved": mask_gbs,
                              "peak": float(peaks["hbm_gbs"]), "unit": "GB/s", "frac": mask_gbs / float(peaks["hbm_gbs"]),
-                             "bytes_per_launch": B * n_boxes * C * 4, "ms": mask_ms},
+                             "bytes_per_launch": B * n_boxes * C * 4, "ms": mask_ms,
+                             "timing": "4 launches back to back over 4 distinct score tensors (435 MB > L2), L2 flushed "
+                                       "before, one CUDA-event pair, / 4",
+                             "ms_single_launch": mask_ms_single,
+                             "frac_single_launch": B * n_boxes * C * 4 / (mask_ms_single * 1e-3) / 1e9
+                                                   / float(peaks["hbm_gbs"])},
             "cpu_baseline": {"value": cpu_ips, "unit": "images/s", "cores": threads, "kind": "port",
                              "sample": "%d images (batch 1 each) forward+decode+filter, torch-CPU fp32 oracle, %.1f s"
                                        % (args.cpu_images, cpu_s)},

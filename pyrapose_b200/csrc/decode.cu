@@ -19,25 +19,30 @@ struct Vec16 {
 };
 
 // groups = values per anchor / 4 (4 for the 16 corner values, 1 for plain boxes).
-// grid (ceil(anchors_per_image * GROUPS / 256), batch): the image index comes from blockIdx.y, so no 64-bit
-// division or modulo is needed to find the (shared) anchor of a thread.
+// grid (ceil(anchors_per_image * GROUPS / (256 * kDecodeUnroll)), batch): the image index comes from blockIdx.y, so no
+// 64-bit division or modulo is needed to find the (shared) anchor of a thread. Every thread owns kDecodeUnroll vectors
+// 256 apart and issues all of its loads before the first use: 2 x kDecodeUnroll x 16 B in flight per thread is what it
+// takes to cover the HBM latency at full occupancy.
+constexpr int kDecodeUnroll = 4;
+
 template <int GROUPS, bool DENORM>
 __global__ void __launch_bounds__(256) transform_inv_kernel(const float4* __restrict__ anchors,
                                                             const float4* __restrict__ deltas,
                                                             float4* __restrict__ out, float4* __restrict__ hull,
                                                             unsigned anchors_per_image, int anchors_batched, Vec16 mean,
                                                             Vec16 stdv) {
-  const unsigned t = blockIdx.x * 256u + threadIdx.x;  // vector index inside the image
-  const unsigned a = t / GROUPS;
-  const int g = static_cast<int>(t - a * GROUPS);
-  const bool valid = a < anchors_per_image;  // no early return: the hull reduction below shuffles across lanes
+  const unsigned t0 = blockIdx.x * (256u * kDecodeUnroll) + threadIdx.x;  // first vector index inside the image
+  const int g = static_cast<int>(t0 % GROUPS);                             // 256 % GROUPS == 0: the same for every u
   const size_t img = static_cast<size_t>(blockIdx.y) * anchors_per_image;
-  const size_t a_src = anchors_batched ? img + a : a;
-  const size_t v = img * GROUPS + t;
-  const float4 box = valid ? __ldg(anchors + a_src) : make_float4(0.f, 0.f, 0.f, 0.f);
-  const float4 d = valid ? __ldg(deltas + v) : make_float4(0.f, 0.f, 0.f, 0.f);
-  const float w = box.z - box.x;   // common.py:33
-  const float h = box.w - box.y;   // common.py:34
+  float4 box[kDecodeUnroll], d[kDecodeUnroll];
+#pragma unroll
+  for (int u = 0; u < kDecodeUnroll; ++u) {
+    const unsigned t = t0 + u * 256u;
+    const unsigned a = t / GROUPS;
+    const bool valid = a < anchors_per_image;  // no early return: the hull reduction below shuffles across lanes
+    box[u] = valid ? __ldg(anchors + (anchors_batched ? img + a : a)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    d[u] = valid ? __ldg(deltas + img * GROUPS + t) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   // pick this thread's four (mean, std) pairs with selects: indexing a by-value parameter array with a runtime
   // index would force the whole array into local memory
   float m[4], sd[4];
@@ -51,29 +56,37 @@ __global__ void __launch_bounds__(256) transform_inv_kernel(const float4* __rest
       sd[j] = g == gg ? stdv.v[gg * 4 + j] : sd[j];
     }
   }
-  float4 r;
-  r.x = box.x + (d.x * sd[0] + m[0]) * w;
-  r.y = box.y + (d.y * sd[1] + m[1]) * h;
-  r.z = box.z + (d.z * sd[2] + m[2]) * w;
-  r.w = box.w + (d.w * sd[3] + m[3]) * h;
-  if (DENORM) {  // common.py:69-84
-    r.x = r.x / 320.0f;
-    r.y = r.y / 240.0f;
-    r.z = r.z / 320.0f;
-    r.w = r.w / 240.0f;
-  }
-  if (valid) out[v] = r;
-  if (GROUPS == 4 && hull != nullptr) {
-    // axis-aligned hull of the 8 corners: min/max over the four threads of this anchor
-    float xmin = fminf(r.x, r.z), xmax = fmaxf(r.x, r.z), ymin = fminf(r.y, r.w), ymax = fmaxf(r.y, r.w);
 #pragma unroll
-    for (int off = 1; off < 4; off <<= 1) {
-      xmin = fminf(xmin, __shfl_xor_sync(0xffffffffu, xmin, off));
-      xmax = fmaxf(xmax, __shfl_xor_sync(0xffffffffu, xmax, off));
-      ymin = fminf(ymin, __shfl_xor_sync(0xffffffffu, ymin, off));
-      ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, off));
+  for (int u = 0; u < kDecodeUnroll; ++u) {
+    const unsigned t = t0 + u * 256u;
+    const unsigned a = t / GROUPS;
+    const bool valid = a < anchors_per_image;
+    const float w = box[u].z - box[u].x;   // common.py:33
+    const float h = box[u].w - box[u].y;   // common.py:34
+    float4 r;
+    r.x = box[u].x + (d[u].x * sd[0] + m[0]) * w;
+    r.y = box[u].y + (d[u].y * sd[1] + m[1]) * h;
+    r.z = box[u].z + (d[u].z * sd[2] + m[2]) * w;
+    r.w = box[u].w + (d[u].w * sd[3] + m[3]) * h;
+    if (DENORM) {  // common.py:69-84
+      r.x = r.x / 320.0f;
+      r.y = r.y / 240.0f;
+      r.z = r.z / 320.0f;
+      r.w = r.w / 240.0f;
     }
-    if (valid && g == 0) hull[img + a] = make_float4(xmin, ymin, xmax, ymax);
+    if (valid) out[img * GROUPS + t] = r;
+    if (GROUPS == 4 && hull != nullptr) {
+      // axis-aligned hull of the 8 corners: min/max over the four threads of this anchor
+      float xmin = fminf(r.x, r.z), xmax = fmaxf(r.x, r.z), ymin = fminf(r.y, r.w), ymax = fmaxf(r.y, r.w);
+#pragma unroll
+      for (int off = 1; off < 4; off <<= 1) {
+        xmin = fminf(xmin, __shfl_xor_sync(0xffffffffu, xmin, off));
+        xmax = fmaxf(xmax, __shfl_xor_sync(0xffffffffu, xmax, off));
+        ymin = fminf(ymin, __shfl_xor_sync(0xffffffffu, ymin, off));
+        ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, off));
+      }
+      if (valid && g == 0) hull[img + a] = make_float4(xmin, ymin, xmax, ymax);
+    }
   }
 }
 
@@ -111,7 +124,8 @@ int ppb_box3d_transform_inv_f32(const float* anchors, const float* deltas, float
   PPB_REQUIRE(anchors != nullptr && deltas != nullptr && out != nullptr, "ppb_box3d_transform_inv_f32: null buffer");
   const Vec16 mean = load16(mean_host, 0.0f, 16), stdv = load16(std_host, 0.2f, 16);
   PPB_REQUIRE(anchors_per_image < (1ll << 29) && batch <= 65535, "ppb_box3d_transform_inv_f32: sizes out of range");
-  const dim3 grid(static_cast<unsigned>((anchors_per_image * 4 + 255) / 256), static_cast<unsigned>(batch));
+  const dim3 grid(static_cast<unsigned>((anchors_per_image * 4 + 256 * kDecodeUnroll - 1) / (256 * kDecodeUnroll)),
+                  static_cast<unsigned>(batch));
   const unsigned api = static_cast<unsigned>(anchors_per_image);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (denormalize)
@@ -136,7 +150,8 @@ int ppb_bbox_transform_inv_f32(const float* anchors, const float* deltas, float*
   PPB_REQUIRE(anchors != nullptr && deltas != nullptr && out != nullptr, "ppb_bbox_transform_inv_f32: null buffer");
   const Vec16 mean = load16(mean_host, 0.0f, 4), stdv = load16(std_host, 0.2f, 4);
   PPB_REQUIRE(anchors_per_image < (1ll << 31) && batch <= 65535, "ppb_bbox_transform_inv_f32: sizes out of range");
-  const dim3 grid(static_cast<unsigned>((anchors_per_image + 255) / 256), static_cast<unsigned>(batch));
+  const dim3 grid(static_cast<unsigned>((anchors_per_image + 256 * kDecodeUnroll - 1) / (256 * kDecodeUnroll)),
+                  static_cast<unsigned>(batch));
   transform_inv_kernel<1, false><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const float4*>(anchors), reinterpret_cast<const float4*>(deltas),
       reinterpret_cast<float4*>(out), nullptr, static_cast<unsigned>(anchors_per_image), anchors_batched, mean, stdv);

@@ -30,11 +30,14 @@ __device__ __forceinline__ double iou_plus1(const double b0, const double b1, co
 
 constexpr int kQChunk = 512;  // query boxes staged per pass (512 * 5 doubles = 20 KiB)
 
-// grid: (ceil(N / kRowsPerBlock), batch), 256 threads. A block owns kRowsPerBlock consecutive anchors = one contiguous
-// slab of the output; the image's query boxes and their areas (pyx:32-35, computed once instead of once per pair) sit
-// in shared memory. Threads walk the slab with 16-byte stores; all index arithmetic is 32-bit and block-local.
-constexpr int kRowsPerBlock = 32;
-constexpr int kQSmemMax = 1024;  // query boxes held in shared memory (5 doubles each = 40 KiB)
+// grid: (ceil(N / 32), batch), 256 threads = 8 warps. A block owns 32 consecutive anchors = one contiguous slab of the
+// output. Compute phase: lane = anchor (its box and area live in registers), warp w takes query boxes w, w+8, ... of the
+// staged chunk, so all 32 lanes of a warp test neighbouring anchors against the SAME query box: the iw > 0 / ih > 0
+// branches (pyx:41, 46) are almost always warp-uniform and the IEEE fp64 division only runs where boxes really
+// overlap. Results go to a [32][chunk | 1] shared tile (odd row stride: conflict-free column writes); write phase:
+// one warp per row, 16-byte stores of consecutive k -> every store instruction covers 512 contiguous bytes.
+constexpr int kOvRows = 32;
+constexpr int kOvQChunk = 128;  // query boxes per pass: 5 KiB of queries + 33 KiB of results
 
 template <int VEC>
 __global__ void __launch_bounds__(256) overlap_matrix_kernel(const double* __restrict__ boxes,
@@ -42,42 +45,58 @@ __global__ void __launch_bounds__(256) overlap_matrix_kernel(const double* __res
                                                              double* __restrict__ out, long long n, int k,
                                                              long long boxes_bstride, long long query_bstride,
                                                              long long out_bstride) {
-  extern __shared__ double sq[];  // [min(k, kQSmemMax)][5]
-  __shared__ double sb[kRowsPerBlock][4];
-  const double* bx = boxes + blockIdx.y * boxes_bstride;
+  extern __shared__ double sm[];
+  const int qc = min(k, kOvQChunk);
+  const int ts = qc | 1;
+  double* sq = sm;             // [qc][5]: x1, y1, x2, y2, area (pyx:32-35, computed once instead of once per pair)
+  double* tile = sm + qc * 5;  // [32][ts]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const double* qx = query + blockIdx.y * query_bstride;
-  const long long row0 = static_cast<long long>(blockIdx.x) * kRowsPerBlock;
-  const int rows = static_cast<int>(min(static_cast<long long>(kRowsPerBlock), n - row0));
+  const long long row0 = static_cast<long long>(blockIdx.x) * kOvRows;
+  const int rows = static_cast<int>(min(static_cast<long long>(kOvRows), n - row0));
   double* o = out + blockIdx.y * out_bstride + row0 * k;
-  const int ks = min(k, kQSmemMax);
-  for (int t = threadIdx.x; t < ks; t += 256) {
-    const double2 q01 = __ldg(reinterpret_cast<const double2*>(qx + t * 4));
-    const double2 q23 = __ldg(reinterpret_cast<const double2*>(qx + t * 4 + 2));
-    sq[t * 5 + 0] = q01.x; sq[t * 5 + 1] = q01.y; sq[t * 5 + 2] = q23.x; sq[t * 5 + 3] = q23.y;
-    sq[t * 5 + 4] = (q23.x - q01.x + 1) * (q23.y - q01.y + 1);  // pyx:32-35
+  double b0 = 0, b1 = 0, b2 = 0, b3 = 0;
+  if (lane < rows) {
+    const double* bp = boxes + blockIdx.y * boxes_bstride + (row0 + lane) * 4;
+    const double2 b01 = __ldg(reinterpret_cast<const double2*>(bp));
+    const double2 b23 = __ldg(reinterpret_cast<const double2*>(bp + 2));
+    b0 = b01.x; b1 = b01.y; b2 = b23.x; b3 = b23.y;
   }
-  if (threadIdx.x < rows * 4) (&sb[0][0])[threadIdx.x] = bx[row0 * 4 + threadIdx.x];
-  __syncthreads();
-  const unsigned total = static_cast<unsigned>(rows) * static_cast<unsigned>(k);
-  for (unsigned e0 = threadIdx.x * VEC; e0 < total; e0 += 256 * VEC) {
-    const unsigned row = e0 / static_cast<unsigned>(k);
-    const unsigned col = e0 - row * static_cast<unsigned>(k);
-    const double b0 = sb[row][0], b1 = sb[row][1], b2 = sb[row][2], b3 = sb[row][3];
-    double r[VEC];
-#pragma unroll
-    for (int v = 0; v < VEC; ++v) {
-      const unsigned c = col + v;
-      if (c < static_cast<unsigned>(ks)) {
-        r[v] = iou_plus1(b0, b1, b2, b3, sq[c * 5], sq[c * 5 + 1], sq[c * 5 + 2], sq[c * 5 + 3], sq[c * 5 + 4]);
-      } else {  // more query boxes than the shared-memory window holds: read them from global memory
-        const double q0 = qx[c * 4], q1 = qx[c * 4 + 1], q2 = qx[c * 4 + 2], q3 = qx[c * 4 + 3];
-        r[v] = iou_plus1(b0, b1, b2, b3, q0, q1, q2, q3, (q2 - q0 + 1) * (q3 - q1 + 1));
-      }
+  const double b_area = (b2 - b0 + 1) * (b3 - b1 + 1);  // first product of pyx:47-49, same operands for every k
+  double* trow = tile + lane * ts;
+  for (int base = 0; base < k; base += kOvQChunk) {
+    const int chunk = min(kOvQChunk, k - base);
+    __syncthreads();  // the previous pass has finished reading sq / tile
+    for (int t = threadIdx.x; t < chunk; t += 256) {
+      const double2 q01 = __ldg(reinterpret_cast<const double2*>(qx + (base + t) * 4));
+      const double2 q23 = __ldg(reinterpret_cast<const double2*>(qx + (base + t) * 4 + 2));
+      sq[t * 5 + 0] = q01.x; sq[t * 5 + 1] = q01.y; sq[t * 5 + 2] = q23.x; sq[t * 5 + 3] = q23.y;
+      sq[t * 5 + 4] = (q23.x - q01.x + 1) * (q23.y - q01.y + 1);
     }
-    if (VEC == 2) {
-      *reinterpret_cast<double2*>(o + e0) = make_double2(r[0], r[VEC - 1]);
-    } else {
-      o[e0] = r[0];
+    __syncthreads();
+    for (int q = warp; q < chunk; q += 8) {
+      const double q0 = sq[q * 5], q1 = sq[q * 5 + 1], q2 = sq[q * 5 + 2], q3 = sq[q * 5 + 3];
+      double r = 0.0;
+      const double iw = (b2 < q2 ? b2 : q2) - (b0 > q0 ? b0 : q0) + 1;  // pyx:37-40
+      if (iw > 0) {
+        const double ih = (b3 < q3 ? b3 : q3) - (b1 > q1 ? b1 : q1) + 1;  // pyx:42-45
+        if (ih > 0) {
+          const double ua = b_area + sq[q * 5 + 4] - iw * ih;  // pyx:47-51
+          r = iw * ih / ua;                                    // pyx:52
+        }
+      }
+      trow[q] = r;
+    }
+    __syncthreads();
+    for (int r = warp; r < rows; r += 8) {
+      const double* src = tile + r * ts;
+      double* dst = o + static_cast<long long>(r) * k + base;
+      if (VEC == 2) {  // k and base even, output base 16-byte aligned: every row segment starts 16-byte aligned
+        for (int c = lane * 2; c < chunk; c += 64)
+          *reinterpret_cast<double2*>(dst + c) = make_double2(src[c], src[c + 1]);
+      } else {
+        for (int c = lane; c < chunk; c += 32) dst[c] = src[c];
+      }
     }
   }
 }
@@ -239,8 +258,9 @@ int ppb_compute_overlap_f64(const double* boxes, const double* query, double* ov
   const long long bs = boxes_shared ? 0 : n * 4;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   PPB_REQUIRE(k <= (1 << 24) && batch <= 65535, "ppb_compute_overlap_f64: k or batch out of range");
-  const unsigned blocks = static_cast<unsigned>((n + kRowsPerBlock - 1) / kRowsPerBlock);
-  const size_t smem = static_cast<size_t>(k < kQSmemMax ? k : kQSmemMax) * 5 * sizeof(double);
+  const unsigned blocks = static_cast<unsigned>((n + kOvRows - 1) / kOvRows);
+  const int qc = k < kOvQChunk ? k : kOvQChunk;
+  const size_t smem = (static_cast<size_t>(qc) * 5 + static_cast<size_t>(kOvRows) * (qc | 1)) * sizeof(double);
   // even k keeps every row's first element 16-byte aligned (the output base comes from the caller's allocator)
   if ((k & 1) == 0 && (reinterpret_cast<uintptr_t>(overlaps) & 15) == 0) {
     overlap_matrix_kernel<2><<<dim3(blocks, batch), 256, smem, st>>>(boxes, query, overlaps, n, k, bs,
