@@ -334,7 +334,10 @@ def run_ours(args):
         mask_gbs = B * n_boxes * C * 4 / (mask_ms * 1e-3) / 1e9
         # ---- CPU baseline on this box's host cores (bounded sample)
         threads = os.cpu_count() or 1
-        cpu_ips, cpu_s = cpu_reference(weights, args.cpu_images, threads)
+        if world == 1:
+            cpu_ips, cpu_s = cpu_reference(weights, args.cpu_images, threads)
+        else:  # the CPU baseline is an N=1 leg: at N>1 the other ranks' barrier spinning would share its cores
+            cpu_ips, cpu_s = None, 0.0
         value = world * B * args.steps / (dev_ms * 1e-3)
         line = {
             "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
@@ -373,7 +376,7 @@ def run_ours(args):
                                                    / float(peaks["hbm_gbs"])},
             "cpu_baseline": {"value": cpu_ips, "unit": "images/s", "cores": threads, "kind": "port",
                              "sample": "%d images (batch 1 each) forward+decode+filter, torch-CPU fp32 oracle, %.1f s"
-                                       % (args.cpu_images, cpu_s)},
+                                       % (args.cpu_images, cpu_s)} if world == 1 else None,
         }
         print(json.dumps(line))
     if world > 1:

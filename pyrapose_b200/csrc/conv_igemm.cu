@@ -13,6 +13,7 @@
 #include "conv_igemm.h"
 #include "ptx.cuh"
 
+#include <cstdio>
 #include <cstdlib>
 #include <mutex>
 
@@ -212,6 +213,7 @@ __device__ __forceinline__ void epi_head16(const ConvParams& p, const float* __r
     if (n0 + j < p.n_valid) srow[n0 - tile_n0 + j] = f[j];
 }
 
+template <bool kPair>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
@@ -219,7 +221,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int n_stages = p.n_stages;
-  const int stage_bytes = kABytes + p.block_n * (kConvBlockK * 2);
+  // CTA pair (p.pair): this CTA stages its own 128 A rows and HALF of the tile's B rows; rank 0 issues one
+  // cta_group::2 MMA over M = 256 (rows of both CTAs) that reads the B halves from both shared memories.
+  constexpr bool pair = kPair;  // a separate instantiation: a kernel that contains cta_group::2 code cannot be launched
+                                // without a cluster ("cluster misconfiguration")
+  const uint32_t rank = pair ? cluster_ctarank() : 0u;
+  const int b_rows = pair ? (p.block_n >> 1) : p.block_n;
+  const int stage_bytes = kABytes + b_rows * (kConvBlockK * 2);
   uint8_t* ring = smem + n_stages * stage_bytes;
   float* sbias = reinterpret_cast<float*>(ring + p.ring_slots * kChunkBytes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sbias) + kBiasFloats * 4);
@@ -253,7 +261,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
       for (int i = 0; i < 2; ++i) {
         mbar_init(&tmem_full_bar[i], 1);
-        mbar_init(&tmem_empty_bar[i], kEpiThreads);
+        mbar_init(&tmem_empty_bar[i], pair ? 2 * kEpiThreads : kEpiThreads);  // pair: both CTAs' epilogues arrive on rank 0
       }
       for (int i = 0; i < kMaxRing; ++i) {
         mbar_init(&slot_full_bar[i], 1);
@@ -262,8 +270,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       fence_mbar_init();
     }
   } else if (warp == 2) {
-    tmem_alloc(tmem_slot, kTmemCols);
-    tmem_relinquish();
+    if (pair) {
+      tmem_alloc2(tmem_slot, kTmemCols);
+      tmem_relinquish2();
+    } else {
+      tmem_alloc(tmem_slot, kTmemCols);
+      tmem_relinquish();
+    }
   }
   {  // whole-layer bias -> shared memory (zeros when the layer has none / beyond n_valid)
     const int nb = p.n_ntiles * p.block_n;
@@ -272,32 +285,62 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   }
   tc_fence_before();
   __syncthreads();
+  if (pair) cluster_sync_all();  // the peer's barriers are initialised before anything arrives on them remotely
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Everything above touches only this kernel's own state and the layer's constant bias: with programmatic dependent
+  // launch it overlaps the tail of the previous kernel. From here on the activations of earlier layers are read and
+  // buffers they may still be reading are written, so every thread waits for the prerequisite grid first.
+  pdl_wait();
+  pdl_launch_dependents();
 
   const int total_tiles = p.n_mtiles * p.n_ntiles;
   const int k_iters = p.n_taps * p.cin_blocks;
+  // Tile walk. Single CTA: tile = it. Pair: `it` walks (M-tile pair, N tile); this CTA owns M tile 2*pair + rank.
+  const int it_begin = pair ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int it_step = pair ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  // An odd M-tile count leaves rank 1 of the last pair a ghost tile past the end of the matrix: its TMA loads are
+  // zero-filled, its TMA stores clipped, and row_info() marks every row as outside the buffer.
+  const int it_end = pair ? ((p.n_mtiles + 1) >> 1) * p.n_ntiles : total_tiles;
+  auto tile_of = [&](int it) {
+    if (!pair) return it;
+    const int mp = it / p.n_ntiles;
+    return ((mp << 1) + static_cast<int>(rank)) * p.n_ntiles + (it - mp * p.n_ntiles);
+  };
   const int n_chunks = p.block_n >> 6;  // staged epilogue: 64-column chunks per tile
   const int R = p.ring_slots;
 
+  // The MMA issuer (rank 0 in a pair) may overwrite an accumulator once every epilogue thread that reads it — in both
+  // CTAs of a pair — has arrived on ITS barrier.
+  auto tmem_release = [&](uint64_t* bar) {
+    if (pair) mbar_arrive_rank0(bar);
+    else mbar_arrive(bar);
+  };
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (A / B tiles)
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      const uint32_t tx_bytes = static_cast<uint32_t>(stage_bytes);
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const TileCoord tc = tile_coord(p, tile);
+      const uint32_t tx_bytes = static_cast<uint32_t>(pair ? 2 * stage_bytes : stage_bytes);
+      for (int it = it_begin; it < it_end; it += it_step) {
+        const TileCoord tc = tile_coord(p, tile_of(it));
         const ConvSeg& sg = p.seg[tc.seg];
+        const int b_row = tc.n0 + static_cast<int>(rank) * b_rows;
         for (int tap = 0; tap < p.n_taps; ++tap) {
           const int a_row = tc.row0 + sg.tap_off[tap];
           for (int kb = 0; kb < p.cin_blocks; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1, kFaultEmpty);
-            mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
             uint8_t* sa = smem + stage * stage_bytes;
-            tma_load_2d(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
-            tma_load_2d(sa + kABytes, &tmap_b, p.b_col_base + (tap * p.cin_blocks + kb) * kConvBlockK, tc.n0,
-                        &full_bar[stage]);
+            const int b_col = p.b_col_base + (tap * p.cin_blocks + kb) * kConvBlockK;
+            if (pair) {  // both CTAs' bytes are counted on rank 0's barrier, armed by rank 0 for the two stages
+              if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+              tma_load_2d_pair(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
+              tma_load_2d_pair(sa + kABytes, &tmap_b, b_col, b_row, &full_bar[stage]);
+            } else {
+              mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+              tma_load_2d(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
+              tma_load_2d(sa + kABytes, &tmap_b, b_col, tc.n0, &full_bar[stage]);
+            }
             if (++stage == n_stages) {
               stage = 0;
               phase ^= 1;
@@ -308,33 +351,43 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    if (elect_one()) {
+    if (rank == 0 && elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      const uint32_t idesc = umma_idesc_bf16(kConvBlockM, p.block_n);
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const uint32_t idesc = umma_idesc_bf16(pair ? 2 * kConvBlockM : kConvBlockM, p.block_n);
+      for (int it = it_begin; it < it_end; it += it_step) {
         mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1, kFaultTmemEmpty);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kAccCols;
-        for (int it = 0; it < k_iters; ++it) {
+        for (int ki = 0; ki < k_iters; ++ki) {
           mbar_wait(&full_bar[stage], phase, kFaultFull);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
           const uint32_t b_addr = a_addr + kABytes;
+          if (pair) {
 #pragma unroll
-          for (int k = 0; k < kConvBlockK / 16; ++k) {
-            tc_mma_bf16(d_tmem, umma_desc_k128(a_addr + k * 32), umma_desc_k128(b_addr + k * 32), idesc,
-                        (it | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < kConvBlockK / 16; ++k) {
+              tc_mma_bf16_2cta(d_tmem, umma_desc_k128(a_addr + k * 32), umma_desc_k128(b_addr + k * 32), idesc,
+                               (ki | k) != 0 ? 1u : 0u);
+            }
+            tc_commit2(&empty_bar[stage]);  // frees this stage in both CTAs
+          } else {
+#pragma unroll
+            for (int k = 0; k < kConvBlockK / 16; ++k) {
+              tc_mma_bf16(d_tmem, umma_desc_k128(a_addr + k * 32), umma_desc_k128(b_addr + k * 32), idesc,
+                          (ki | k) != 0 ? 1u : 0u);
+            }
+            tc_commit(&empty_bar[stage]);
           }
-          tc_commit(&empty_bar[stage]);
           if (++stage == n_stages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        tc_commit(&tmem_full_bar[acc]);
+        if (pair) tc_commit2(&tmem_full_bar[acc]);
+        else tc_commit(&tmem_full_bar[acc]);
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
@@ -345,8 +398,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     // overwrite with the result; runs as far ahead as the ring allows.
     if (staged && has_res && elect_one()) {
       uint32_t k = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const TileCoord tc = tile_coord(p, tile);
+      for (int it = it_begin; it < it_end; it += it_step) {
+        const TileCoord tc = tile_coord(p, tile_of(it));
         for (int c = 0; c < n_chunks; ++c, ++k) {
           const uint32_t s = k % R;
           const uint32_t ph = (k / R) & 1u;
@@ -371,8 +424,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int sstride = p.block_n | 1;  // odd stride: conflict-free column writes
     float* stile = reinterpret_cast<float*>(ring);
     long long* srow_loc = reinterpret_cast<long long*>(ring + static_cast<size_t>(kConvBlockM) * sstride * 4);
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const TileCoord tc = tile_coord(p, tile);
+    for (int it = it_begin; it < it_end; it += it_step) {
+      const TileCoord tc = tile_coord(p, tile_of(it));
       const ConvSeg& sg = p.seg[tc.seg];
       const int m = tc.row0 + row;
       const RowInfo ri = row_info(sg, m);
@@ -452,7 +505,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         chunk_base += n_chunks;
         tc_fence_before();
-        mbar_arrive(&tmem_empty_bar[acc]);  // this thread's share of the accumulator is drained
+        tmem_release(&tmem_empty_bar[acc]);  // this thread's share of the accumulator is drained
       } else if (p.epi == kEpiBf16) {
         // ---- direct bf16 epilogue: 32-column pieces alternate between the two groups
         int piece = 0;
@@ -471,7 +524,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           }
         }
         tc_fence_before();
-        mbar_arrive(&tmem_empty_bar[acc]);
+        tmem_release(&tmem_empty_bar[acc]);
       } else {
         // ---- head epilogues: fp32 tile staged in shared memory, then written out coalesced
         const int w = sg.wp - sg.pad_lo - sg.pad_hi;
@@ -496,7 +549,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           }
         }
         tc_fence_before();
-        mbar_arrive(&tmem_empty_bar[acc]);
+        tmem_release(&tmem_empty_bar[acc]);
         named_bar_sync(4, kEpiThreads);  // staging tile complete
         // write-out: one warp per row, lanes walk the row's `vals` floats -> 128-byte coalesced stores; consecutive
         // interior rows are consecutive locations, i.e. adjacent in the output as well
@@ -518,9 +571,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 
   tc_fence_before();
   __syncthreads();
+  if (pair) cluster_sync_all();  // the peer has drained its accumulators and no remote arrive is still in flight
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, kTmemCols);
+    if (pair) tmem_dealloc2(tmem_base, kTmemCols);
+    else tmem_dealloc(tmem_base, kTmemCols);
   }
 }
 
@@ -583,8 +638,19 @@ int conv_num_sms() {
   return sms;
 }
 
+bool conv_pair_ok(const ConvParams& p) {
+  static const int mode = [] {
+    const char* e = getenv("PPB_PAIR");
+    return e != nullptr ? atoi(e) : 1;
+  }();
+  if (mode == 0) return false;
+  const int k_iters = p.n_taps * p.cin_blocks;
+  // shallow K loops are epilogue / HBM bound: the pair only adds a cluster barrier there (mode 2 forces it on)
+  return p.n_mtiles >= 2 && (p.block_n & 31) == 0 && (mode >= 2 || k_iters >= 8);
+}
+
 int conv_plan_smem(ConvParams& p) {
-  const int stage_bytes = kABytes + p.block_n * (kConvBlockK * 2);
+  const int stage_bytes = kABytes + (p.pair ? p.block_n / 2 : p.block_n) * (kConvBlockK * 2);
   const int k_iters = p.n_taps * p.cin_blocks;
   int ring_min = 0, ring_max = 0;
   if (p.epi == kEpiBf16) {
@@ -621,7 +687,9 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(conv_igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    attr_err = cudaFuncSetAttribute(conv_igemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(conv_igemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
   });
   if (attr_err != cudaSuccess) return attr_err;
   const int total = p.n_mtiles * p.n_ntiles;
@@ -631,8 +699,70 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
   if (smem_bytes < 0 || q.n_stages != p.n_stages || q.ring_slots != p.ring_slots) return cudaErrorInvalidConfiguration;
   int ctas = max_ctas > 0 ? max_ctas : conv_num_sms();
   if (ctas > total) ctas = total;
-  conv_igemm_kernel<<<ctas, kThreads, smem_bytes, stream>>>(tmap_a, tmap_b, tmap_out, tmap_res, p);
-  return cudaGetLastError();
+  if (p.pair) {
+    ctas &= ~1;
+    if (ctas < 2) return cudaErrorInvalidConfiguration;
+  }
+  static const bool pdl = [] {
+    // Off by default: inside the engine's CUDA graph the launch gap is already hidden and the prologue is ~1 us, so
+    // the measured forward time is the same with and without it (8.73 vs 8.71 ms at B=32); PPB_PDL=1 turns it on.
+    const char* e = getenv("PPB_PDL");
+    return e != nullptr && atoi(e) != 0;
+  }();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(ctas);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = static_cast<size_t>(smem_bytes);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (p.pair) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  if (p.pair) {
+    // a persistent grid must not exceed the pairs that can be resident at once (a GPC with an odd number of free
+    // SMs leaves one unpaired); cached per shared-memory size
+    static std::mutex mu;
+    static int cached_smem[8], cached_clusters[8], n_cached = 0;
+    int max_clusters = -1;
+    {
+      std::lock_guard<std::mutex> lock(mu);
+      for (int i = 0; i < n_cached; ++i)
+        if (cached_smem[i] == smem_bytes) max_clusters = cached_clusters[i];
+      if (max_clusters < 0) {
+        cudaLaunchConfig_t probe = cfg;
+        probe.gridDim = dim3(conv_num_sms() & ~1);
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, conv_igemm_kernel<true>, &probe) != cudaSuccess || n <= 0) {
+          cudaGetLastError();
+          n = conv_num_sms() / 2;
+        }
+        max_clusters = n;
+        if (n_cached < 8) {
+          cached_smem[n_cached] = smem_bytes;
+          cached_clusters[n_cached++] = n;
+        }
+      }
+    }
+    if (ctas > 2 * max_clusters) cfg.gridDim = dim3(2 * max_clusters);
+  }
+  const cudaError_t err = p.pair ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<true>, tmap_a, tmap_b, tmap_out, tmap_res, p)
+                                 : cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false>, tmap_a, tmap_b, tmap_out, tmap_res, p);
+  if (err != cudaSuccess)
+    fprintf(stderr, "conv_launch failed: %s (grid %u, smem %d, pair %d, attrs %d, block_n %d, m tiles %d, n tiles %d)\n",
+            cudaGetErrorString(err), cfg.gridDim.x, smem_bytes, p.pair, na, p.block_n, p.n_mtiles, p.n_ntiles);
+  return err;
 }
 
 void conv_read_fault(unsigned int out[4]) {

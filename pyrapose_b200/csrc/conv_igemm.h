@@ -52,6 +52,8 @@ struct ConvParams {
   int epi;          // ConvEpilogue
   int relu;
   int staged;       // kEpiBf16 only: epilogue through the shared-memory chunk ring + TMA store (needs tmap_out / tmap_res)
+  int pair;         // 1: CTA pairs (cluster of 2, tcgen05 cta_group::2, M = 256 per MMA); needs tmap_b encoded with a
+                    // block_n / 2 row box (pass block_n / 2 to conv_encode_tmaps) — see conv_pair_ok()
   int n_stages;     // TMA->MMA pipeline depth (2..8)   } filled by conv_plan_smem()
   int ring_slots;   // 16 KiB epilogue ring slots        }
   const float* bias;              // [n_valid] fp32, BatchNorm folded in; may be null
@@ -95,5 +97,9 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
 void conv_read_fault(unsigned int out[4]);
 
 int conv_num_sms();
+
+// CTA-pair mode is usable for this shape (N tile a multiple of 32 so that each half is a legal UMMA operand, K loop
+// deep enough to be operand-feed bound) and enabled (PPB_PAIR: 0 off, 1 default, 2 every eligible shape).
+bool conv_pair_ok(const ConvParams& p);
 
 }  // namespace ppb

@@ -128,8 +128,9 @@ struct Builder {
     p.b_col_base = b_col_base;
     p.out = out;
     p.out_ld = l.cin;
+    p.pair = conv_pair_ok(p) ? 1 : 0;
     int rc = conv_encode_tmaps(&op.ta, &op.tb, g, g_rows, tl.g_ld, tl.g_ld, tl.w_dgrad, l.cin, tl.n_taps * tl.g_ld,
-                               p.block_n);
+                               p.pair ? p.block_n / 2 : p.block_n);
     if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled failed for dgrad of '%s' (%d)", layer.c_str(), rc);
     memset(&op.to, 0, sizeof(op.to));
     memset(&op.tr, 0, sizeof(op.tr));
