@@ -645,8 +645,10 @@ bool conv_pair_ok(const ConvParams& p) {
   }();
   if (mode == 0) return false;
   const int k_iters = p.n_taps * p.cin_blocks;
-  // shallow K loops are epilogue / HBM bound: the pair only adds a cluster barrier there (mode 2 forces it on)
-  return p.n_mtiles >= 2 && (p.block_n & 31) == 0 && (mode >= 2 || k_iters >= 8);
+  // Shallow K loops are epilogue / HBM bound and lose with the pair (measured per layer at B=32, 480x640: every
+  // 1x1 with K <= 512 and the 3x3 64->64 of stage 2 got slower, everything with >= 16 k-iterations faster; the
+  // 3x3 512->512 tower convolutions 0.67 -> 0.59 ms). Mode 2 forces the pair on for every eligible shape.
+  return p.n_mtiles >= 2 && (p.block_n & 15) == 0 && (mode >= 2 || k_iters >= 16);
 }
 
 int conv_plan_smem(ConvParams& p) {

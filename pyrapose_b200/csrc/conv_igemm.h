@@ -98,7 +98,7 @@ void conv_read_fault(unsigned int out[4]);
 
 int conv_num_sms();
 
-// CTA-pair mode is usable for this shape (N tile a multiple of 32 so that each half is a legal UMMA operand, K loop
+// CTA-pair mode is usable for this shape (N tile a multiple of 16: each CTA stages N/2 rows = whole 8-row swizzle atoms, K loop
 // deep enough to be operand-feed bound) and enabled (PPB_PAIR: 0 off, 1 default, 2 every eligible shape).
 bool conv_pair_ok(const ConvParams& p);
 
