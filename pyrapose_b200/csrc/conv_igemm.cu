@@ -171,10 +171,18 @@ __device__ __forceinline__ void epi_head16(const ConvParams& p, const float* __r
   if (n0 >= p.n_valid) return;
   float f[16];
 #pragma unroll
-  for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]) + sbias[n0 + j];
+  for (int j = 0; j < 16; j += 4) {
+    const float4 b4 = *reinterpret_cast<const float4*>(sbias + n0 + j);
+    f[j] = __uint_as_float(v[j]) + b4.x;
+    f[j + 1] = __uint_as_float(v[j + 1]) + b4.y;
+    f[j + 2] = __uint_as_float(v[j + 2]) + b4.z;
+    f[j + 3] = __uint_as_float(v[j + 3]) + b4.w;
+  }
   if (p.epi == kEpiHeadSigmoid) {
+    // ex2 + rcp on the SFU (relative error ~1e-6, far inside the 1e-2 score tolerance of the bf16 path): the
+    // IEEE expf + division pair was a third of this epilogue's instructions with two warps per scheduler to hide them
 #pragma unroll
-    for (int j = 0; j < 16; ++j) f[j] = 1.0f / (1.0f + expf(-f[j]));
+    for (int j = 0; j < 16; ++j) f[j] = __fdividef(1.0f, 1.0f + __expf(-f[j]));
   } else if (p.epi == kEpiHeadDecode) {
     // box3D_transform_inv (PyraPose/backend/common.py:25-56) against the Anchors layer's boxes
     // (PyraPose/layers/_misc.py:52-69, backend/common.py:93-116): fp32 base anchor + fp32 shift.
@@ -219,7 +227,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                   const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                   const __grid_constant__ ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte alignment by OFFSET from the declared array, so the compiler still knows every derived pointer is
+  // shared memory (round-tripping through uintptr_t turned all of them into generic LD.E / ST.E accesses)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int n_stages = p.n_stages;
   // CTA pair (p.pair): this CTA stages its own 128 A rows and HALF of the tile's B rows; rank 0 issues one
   // cta_group::2 MMA over M = 256 (rows of both CTAs) that reads the B halves from both shared memories.
@@ -558,9 +568,15 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         for (int r = ew; r < kConvBlockM; r += kEpiWarps) {
           const long long rl = srow_loc[r];
           if (rl < 0) continue;
-          float* dst = p.out_f32 + static_cast<size_t>(rl) * vals + tc.n0;
-          const float* src = stile + static_cast<size_t>(r) * sstride;
-          for (int e = lane; e < ncols; e += 32) dst[e] = src[e];
+          float* dst = p.out_f32 + static_cast<size_t>(rl) * vals + tc.n0 + lane;
+          const float* src = stile + r * sstride + lane;
+          float t[kConvMaxBlockN / 32];
+#pragma unroll
+          for (int k = 0; k < kConvMaxBlockN / 32; ++k)
+            if (lane + 32 * k < ncols) t[k] = src[32 * k];
+#pragma unroll
+          for (int k = 0; k < kConvMaxBlockN / 32; ++k)
+            if (lane + 32 * k < ncols) dst[32 * k] = t[k];
         }
       }
       acc ^= 1;

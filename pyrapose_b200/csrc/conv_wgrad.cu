@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(kWgThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__ CUtensorMap tmap_x,
                   const __grid_constant__ WgradParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // by offset: pointers stay shared-space
   const int n_stages = p.n_stages;
   const int n_boxes_b = p.block_n >> 6;
   const int stage_bytes = kWgABytes + n_boxes_b * kWgBoxBytes;
