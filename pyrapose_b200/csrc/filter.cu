@@ -101,16 +101,31 @@ __global__ void __launch_bounds__(256) class_max_kernel(const float* __restrict_
 // One warp, one slab row per lane: one LDS + compare + ballot per class (row stride C words: conflict-free for odd
 // C); lane c keeps the word of class c so that the C words leave in one store instruction. (Building a per-row bit
 // field first and transposing it afterwards measured slower: 30.0 vs 24.3 us at B=32, N=56700, C=15.)
+template <int CT>
 __device__ __forceinline__ void ballot_rows(const float* __restrict__ my, bool in_rows, int C, float thr,
                                             uint32_t* __restrict__ dst, int W, int lane) {
-  for (int c0 = 0; c0 < C; c0 += 32) {
+  if constexpr (CT > 0) {  // class count known at compile time (15 / 21 / 30: LineMOD, YCB-V, T-LESS): the loop unrolls fully and
+                 // the CT shared-memory loads are all in flight before the first ballot
+    float v[CT];
+#pragma unroll
+    for (int c = 0; c < CT; ++c) v[c] = my[c];
     uint32_t mine = 0u;
-    const int cn = min(32, C - c0);
-    for (int c = 0; c < cn; ++c) {
-      const uint32_t word = __ballot_sync(0xffffffffu, in_rows && my[c0 + c] > thr);
+#pragma unroll
+    for (int c = 0; c < CT; ++c) {
+      const uint32_t word = __ballot_sync(0xffffffffu, in_rows && v[c] > thr);
       if (lane == c) mine = word;
     }
-    if (lane < cn) dst[static_cast<long long>(c0 + lane) * W] = mine;
+    if (lane < CT) dst[static_cast<long long>(lane) * W] = mine;
+  } else {
+    for (int c0 = 0; c0 < C; c0 += 32) {
+      uint32_t mine = 0u;
+      const int cn = min(32, C - c0);
+      for (int c = 0; c < cn; ++c) {
+        const uint32_t word = __ballot_sync(0xffffffffu, in_rows && my[c0 + c] > thr);
+        if (lane == c) mine = word;
+      }
+      if (lane < cn) dst[static_cast<long long>(c0 + lane) * W] = mine;
+    }
   }
 }
 
@@ -122,7 +137,7 @@ __device__ __forceinline__ void ballot_rows(const float* __restrict__ my, bool i
 // before the first shared-memory write. Then warp g owns anchors [32g, 32g+32): one LDS + compare + ballot per
 // class (row stride C words: conflict-free for odd C). Lane c keeps the word of class c so that the C words leave in
 // one store instruction.
-template <int TILE>
+template <int TILE, int CT>
 __global__ void __launch_bounds__(TILE) score_mask_kernel(const float* __restrict__ scores, int N, int C, float thr,
                                                           uint32_t* __restrict__ mask, int W) {
   extern __shared__ __align__(128) float tile[];  // [TILE][C]
@@ -169,7 +184,7 @@ __global__ void __launch_bounds__(TILE) score_mask_kernel(const float* __restric
   if (widx >= W) return;
   const bool in_rows = r < rows;
   const float* my = tile + (in_rows ? r : 0) * C;
-  ballot_rows(my, in_rows, C, thr, mask + static_cast<long long>(b) * C * W + widx, W, lane);
+  ballot_rows<CT>(my, in_rows, C, thr, mask + static_cast<long long>(b) * C * W + widx, W, lane);
 }
 
 // Persistent form of the same pass for 16-byte aligned score tensors (every slab a legal bulk-copy source):
@@ -217,7 +232,7 @@ __global__ void __launch_bounds__(256) score_mask_stream_kernel(const float* __r
     if (widx < W) {
       const bool in_rows = r < rows;
       const float* my = ring + stage * stage_elems + (in_rows ? r : 0) * C;
-      ballot_rows(my, in_rows, C, thr, mask + static_cast<long long>(b) * C * W + widx, W, lane);
+      ballot_rows<0>(my, in_rows, C, thr, mask + static_cast<long long>(b) * C * W + widx, W, lane);
     }
     __syncthreads();  // every warp has finished reading this stage
     if (threadIdx.x == 0) {
@@ -649,10 +664,15 @@ int launch_score_mask(const float* scores, int B, int N, int C, float thr, uint3
     score_mask_stream_kernel<<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W, tiles_per_image,
                                                       static_cast<int>(total));
   } else if (C <= 44) {
-    score_mask_kernel<256><<<dim3((N + 255) / 256, B), 256, 256 * C * 4, st>>>(scores, N, C, thr, mask, W);
+    const dim3 grid((N + 255) / 256, B);
+    const size_t smem = 256 * static_cast<size_t>(C) * 4;
+    if (C == 15) score_mask_kernel<256, 15><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W);
+    else if (C == 21) score_mask_kernel<256, 21><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W);
+    else if (C == 30) score_mask_kernel<256, 30><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W);
+    else score_mask_kernel<256, 0><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W);
   } else {
     PPB_REQUIRE(C <= 352, "score mask: at most 352 classes are supported, got %d", C);
-    score_mask_kernel<32><<<dim3((N + 31) / 32, B), 32, 32 * C * 4, st>>>(scores, N, C, thr, mask, W);
+    score_mask_kernel<32, 0><<<dim3((N + 31) / 32, B), 32, 32 * C * 4, st>>>(scores, N, C, thr, mask, W);
   }
   PPB_CUDA(cudaGetLastError());
   count_launch();

@@ -274,3 +274,25 @@ def test_vote_filter(cuda_device):
             assert idx[s:e].dtype == np.int64
             assert np.array_equal(votes[s:e], ref[cl][1])
             assert np.isclose(conf[b, cl], cls[b, ref[cl][0], cl].sum(), rtol=1e-5)
+
+
+@pytest.mark.parametrize("B,N,C", [(3, 333, 5), (1, 301, 3), (2, 1000, 40), (2, 257, 50), (1, 31, 1), (2, 4097, 15)])
+def test_score_mask_ragged_shapes(cuda_device, B, N, C):
+    """Every staging path of the score pass: bulk-copy slab (aligned), bulk + scalar tail (slab bytes % 16 != 0),
+    misaligned image base (plain loads), C > 32 (two ballot words per row) and C > 44 (one-warp tiles).
+    Bit-exact against numpy `scores > thr` packed LSB-first per 32 anchors (linemod_eval.py:317-319 semantics)."""
+    from pyrapose_b200 import _kernels as K
+    rng = np.random.default_rng(B * 1000 + N + C)
+    sc = rng.uniform(0, 1, (B, N, C)).astype(np.float32)
+    sc[0, 0, 0] = 0.5  # exactly at the threshold: strict '>' must drop it
+    mask, counts = K.score_mask(_t(sc, cuda_device), 0.5)
+    W = (N + 31) // 32
+    hit = sc > np.float32(0.5)
+    pad = np.zeros((B, W * 32, C), bool)
+    pad[:, :N] = hit
+    ref = (pad.reshape(B, W, 32, C).astype(np.uint64) << np.arange(32, dtype=np.uint64)[None, None, :, None]).sum(2)
+    ref = ref.transpose(0, 2, 1).astype(np.uint32)  # [B, C, W]
+    got = mask.cpu().numpy().view(np.uint32)
+    assert got.shape == ref.shape
+    assert np.array_equal(got, ref)
+    assert np.array_equal(counts.cpu().numpy(), hit.sum(1).astype(np.int32))
