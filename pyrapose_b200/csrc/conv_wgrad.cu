@@ -7,6 +7,7 @@
 #include "conv_wgrad.h"
 #include "ptx.cuh"
 
+#include <cstdlib>
 #include <mutex>
 
 namespace ppb {
@@ -40,13 +41,18 @@ __device__ __forceinline__ Task decode_task(const WgradParams& p, int t) {
   return k;
 }
 
+template <bool kPair>
 __global__ void __launch_bounds__(kWgThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__ CUtensorMap tmap_x,
                   const __grid_constant__ WgradParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // by offset: pointers stay shared-space
+  // CTA pair (see conv_igemm.cu): the pair owns two consecutive Cout tiles (M = 256); each CTA stages its own 128
+  // gradient columns and HALF of the input-channel boxes, rank 0 issues the cta_group::2 MMAs.
+  constexpr bool pair = kPair;
+  const uint32_t rank = pair ? cluster_ctarank() : 0u;
   const int n_stages = p.n_stages;
-  const int n_boxes_b = p.block_n >> 6;
+  const int n_boxes_b = pair ? (p.block_n >> 7) : (p.block_n >> 6);
   const int stage_bytes = kWgABytes + n_boxes_b * kWgBoxBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + n_stages * stage_bytes);
   uint64_t* full_bar = bars;
@@ -71,27 +77,41 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
       }
       for (int i = 0; i < 2; ++i) {
         mbar_init(&tmem_full_bar[i], 1);
-        mbar_init(&tmem_empty_bar[i], 128);
+        mbar_init(&tmem_empty_bar[i], pair ? 256 : 128);
       }
       fence_mbar_init();
     }
   } else if (warp == 2) {
-    tmem_alloc(tmem_slot, kWgTmemCols);
-    tmem_relinquish();
+    if (pair) {
+      tmem_alloc2(tmem_slot, kWgTmemCols);
+      tmem_relinquish2();
+    } else {
+      tmem_alloc(tmem_slot, kWgTmemCols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
   __syncthreads();
+  if (pair) cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int total_tasks = p.n_mtiles * p.n_taps * p.n_ntiles * p.k_splits;
+  // pair: tasks enumerate (Cout-tile PAIR, tap, n tile, split); this CTA's Cout tile is 2 * pair + rank
+  const int total_tasks = (pair ? p.n_mtiles >> 1 : p.n_mtiles) * p.n_taps * p.n_ntiles * p.k_splits;
+  const int t_begin = pair ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int t_step = pair ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  auto my_task = [&](int t) {
+    Task k = decode_task(p, t);
+    if (pair) k.m_tile = (k.m_tile << 1) + static_cast<int>(rank);
+    return k;
+  };
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_tasks; t += gridDim.x) {
-        const Task k = decode_task(p, t);
+      for (int t = t_begin; t < total_tasks; t += t_step) {
+        const Task k = my_task(t);
         // locate k_begin inside the segment list
         int seg = 0, local = k.k_begin;
         while (seg < p.n_segs - 1 && local >= p.seg[seg].k_iters) {
@@ -102,13 +122,22 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
           const int row = p.seg[seg].row_begin + local * 64;
           const int xrow = row + p.seg[seg].tap_off[k.tap];
           mbar_wait(&empty_bar[stage], phase ^ 1, kWgFaultEmpty);
-          mbar_arrive_expect_tx(&full_bar[stage], static_cast<uint32_t>(stage_bytes));
           uint8_t* sa = smem + stage * stage_bytes;
-          tma_load_2d(sa, &tmap_g, k.m_tile * 128, row, &full_bar[stage]);
-          tma_load_2d(sa + kWgBoxBytes, &tmap_g, k.m_tile * 128 + 64, row, &full_bar[stage]);
-          for (int j = 0; j < n_boxes_b; ++j)
-            tma_load_2d(sa + kWgABytes + j * kWgBoxBytes, &tmap_x, k.n_tile * p.block_n + j * 64, xrow,
-                        &full_bar[stage]);
+          if (pair) {
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], static_cast<uint32_t>(2 * stage_bytes));
+            tma_load_2d_pair(sa, &tmap_g, k.m_tile * 128, row, &full_bar[stage]);
+            tma_load_2d_pair(sa + kWgBoxBytes, &tmap_g, k.m_tile * 128 + 64, row, &full_bar[stage]);
+            const int x_col = k.n_tile * p.block_n + static_cast<int>(rank) * (p.block_n >> 1);
+            for (int j = 0; j < n_boxes_b; ++j)
+              tma_load_2d_pair(sa + kWgABytes + j * kWgBoxBytes, &tmap_x, x_col + j * 64, xrow, &full_bar[stage]);
+          } else {
+            mbar_arrive_expect_tx(&full_bar[stage], static_cast<uint32_t>(stage_bytes));
+            tma_load_2d(sa, &tmap_g, k.m_tile * 128, row, &full_bar[stage]);
+            tma_load_2d(sa + kWgBoxBytes, &tmap_g, k.m_tile * 128 + 64, row, &full_bar[stage]);
+            for (int j = 0; j < n_boxes_b; ++j)
+              tma_load_2d(sa + kWgABytes + j * kWgBoxBytes, &tmap_x, k.n_tile * p.block_n + j * 64, xrow,
+                          &full_bar[stage]);
+          }
           if (++stage == n_stages) {
             stage = 0;
             phase ^= 1;
@@ -122,14 +151,14 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    if (elect_one()) {
+    if (rank == 0 && elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      const uint32_t idesc = umma_idesc_bf16_mn(128, p.block_n);
-      for (int t = blockIdx.x; t < total_tasks; t += gridDim.x) {
-        const Task k = decode_task(p, t);
+      const uint32_t idesc = umma_idesc_bf16_mn(pair ? 256 : 128, p.block_n);
+      for (int t = t_begin; t < total_tasks; t += t_step) {
+        const Task k = my_task(t);
         if (k.k_end <= k.k_begin) continue;
         mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1, kWgFaultTmemEmpty);
         tc_fence_after();
@@ -141,16 +170,21 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
           const uint32_t b_addr = a_addr + kWgABytes;
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {  // 16 rows (K) per MMA = two 8-row groups of 1024 B
-            tc_mma_bf16(d_tmem, umma_desc_mn128(a_addr + kk * 2048, kWgBoxBytes),
-                        umma_desc_mn128(b_addr + kk * 2048, kWgBoxBytes), idesc, (it > k.k_begin || kk > 0) ? 1u : 0u);
+            const uint64_t da = umma_desc_mn128(a_addr + kk * 2048, kWgBoxBytes);
+            const uint64_t db = umma_desc_mn128(b_addr + kk * 2048, kWgBoxBytes);
+            const uint32_t accum = (it > k.k_begin || kk > 0) ? 1u : 0u;
+            if (pair) tc_mma_bf16_2cta(d_tmem, da, db, idesc, accum);
+            else tc_mma_bf16(d_tmem, da, db, idesc, accum);
           }
-          tc_commit(&empty_bar[stage]);
+          if (pair) tc_commit2(&empty_bar[stage]);
+          else tc_commit(&empty_bar[stage]);
           if (++stage == n_stages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        tc_commit(&tmem_full_bar[acc]);
+        if (pair) tc_commit2(&tmem_full_bar[acc]);
+        else tc_commit(&tmem_full_bar[acc]);
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
@@ -160,8 +194,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
     const int q = warp - 4;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int t = blockIdx.x; t < total_tasks; t += gridDim.x) {
-      const Task k = decode_task(p, t);
+    for (int t = t_begin; t < total_tasks; t += t_step) {
+      const Task k = my_task(t);
       if (k.k_end <= k.k_begin) continue;
       mbar_wait(&tmem_full_bar[acc], acc_phase, kWgFaultTmemFull);
       tc_fence_after();
@@ -183,7 +217,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
         }
       }
       tc_fence_before();
-      mbar_arrive(&tmem_empty_bar[acc]);
+      if (pair) mbar_arrive_rank0(&tmem_empty_bar[acc]);
+      else mbar_arrive(&tmem_empty_bar[acc]);
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
@@ -191,9 +226,11 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
 
   tc_fence_before();
   __syncthreads();
+  if (pair) cluster_sync_all();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, kWgTmemCols);
+    if (pair) tmem_dealloc2(tmem_base, kWgTmemCols);
+    else tmem_dealloc(tmem_base, kWgTmemCols);
   }
 }
 
@@ -210,12 +247,17 @@ void wgrad_plan(WgradParams& p) {
   p.block_n = (p.cin % 256 == 0) ? 256 : ((p.cin % 128 == 0) ? 128 : 64);
   p.n_mtiles = (p.cout + 127) / 128;
   p.n_ntiles = p.cin / p.block_n;
-  const int stage_bytes = kWgABytes + (p.block_n >> 6) * kWgBoxBytes;
+  static const int pair_mode = [] {
+    const char* e = getenv("PPB_PAIR");
+    return e != nullptr ? atoi(e) : 1;
+  }();
+  p.pair = (pair_mode != 0 && p.cout % 256 == 0 && p.block_n >= 128) ? 1 : 0;
+  const int stage_bytes = kWgABytes + (p.pair ? p.block_n >> 7 : p.block_n >> 6) * kWgBoxBytes;
   int stages = (kWgSmemLimit - 1024 - kWgBarBytes) / stage_bytes;
   if (stages > kWgMaxStages) stages = kWgMaxStages;
   p.n_stages = stages;
-  const int tiles = p.n_mtiles * p.n_taps * p.n_ntiles;
-  const int sms = conv_num_sms() > 0 ? conv_num_sms() : 148;
+  const int tiles = (p.pair ? p.n_mtiles / 2 : p.n_mtiles) * p.n_taps * p.n_ntiles;
+  const int sms = (conv_num_sms() > 0 ? conv_num_sms() : 148) / (p.pair ? 2 : 1);
   int splits = (2 * sms + tiles - 1) / tiles;
   const int max_splits = p.total_k_iters / 8 > 0 ? p.total_k_iters / 8 : 1;
   if (splits > max_splits) splits = max_splits;
@@ -228,17 +270,35 @@ cudaError_t wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, c
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemLimit);
+    attr_err = cudaFuncSetAttribute(conv_wgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemLimit);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(conv_wgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemLimit);
   });
   if (attr_err != cudaSuccess) return attr_err;
-  const int total = p.n_mtiles * p.n_taps * p.n_ntiles * p.k_splits;
+  const int total = (p.pair ? p.n_mtiles / 2 : p.n_mtiles) * p.n_taps * p.n_ntiles * p.k_splits;
   if (total <= 0 || p.total_k_iters <= 0) return cudaSuccess;
-  const int stage_bytes = kWgABytes + (p.block_n >> 6) * kWgBoxBytes;
+  const int stage_bytes = kWgABytes + (p.pair ? p.block_n >> 7 : p.block_n >> 6) * kWgBoxBytes;
   const int smem_bytes = p.n_stages * stage_bytes + kWgBarBytes + 1024;
   int ctas = conv_num_sms();
-  if (ctas > total) ctas = total;
-  conv_wgrad_kernel<<<ctas, kWgThreads, smem_bytes, stream>>>(tmap_g, tmap_x, p);
-  return cudaGetLastError();
+  if (!p.pair) {
+    if (ctas > total) ctas = total;
+    conv_wgrad_kernel<false><<<ctas, kWgThreads, smem_bytes, stream>>>(tmap_g, tmap_x, p);
+    return cudaGetLastError();
+  }
+  ctas = (ctas / 2 < total ? ctas / 2 : total) * 2;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(ctas);
+  cfg.blockDim = dim3(kWgThreads);
+  cfg.dynamicSmemBytes = static_cast<size_t>(smem_bytes);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, conv_wgrad_kernel<true>, tmap_g, tmap_x, p);
 }
 
 }  // namespace ppb

@@ -25,6 +25,8 @@ struct WgradParams {
   int n_ntiles;       // cin / block_n
   int k_splits;       // CTAs sharing one (m, tap, n) tile along K
   int n_stages;
+  int pair;           // 1: CTA pairs over two Cout tiles (tcgen05 cta_group::2), set by wgrad_plan() when cout % 256 == 0,
+                      // cin tile >= 128 and PPB_PAIR != 0
   float* dw;          // fp32 [cout][n_taps * cin], accumulated with atomics (caller zeroes it)
   long long dw_ld;    // n_taps * cin
 };
