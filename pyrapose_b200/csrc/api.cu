@@ -108,8 +108,10 @@ int ppb_conv2d_bf16(const void* x, const void* weight, const float* bias, const 
   p.out_ld = cout;
   CUtensorMap ta, tb, to, tr;
   p.pair = conv_pair_ok(p) ? 1 : 0;
+  p.staged = (cout % 64 == 0 && p.block_n % 64 == 0) ? 1 : 0;
+  p.slab3 = conv_slab3_mode(p);
   int rc = conv_encode_tmaps(&ta, &tb, x, p.seg[0].rows, cin, cin, weight, cout, ksize * ksize * cin,
-                             p.pair ? p.block_n / 2 : p.block_n);
+                             p.pair ? p.block_n / 2 : p.block_n, p.slab3 ? kConvSlabRows : kConvBlockM);
   if (rc != 0) return fail(kErrCuda, "ppb_conv2d_bf16: cuTensorMapEncodeTiled failed (%d)", rc);
   memset(&to, 0, sizeof(to));
   memset(&tr, 0, sizeof(tr));
@@ -178,8 +180,10 @@ int ppb_conv2d_dgrad_bf16(const void* g, const void* weight_t, const void* resid
   p.out_ld = cin;
   CUtensorMap ta, tb, to, tr;
   p.pair = conv_pair_ok(p) ? 1 : 0;
+  p.staged = (p.block_n % 64 == 0) ? 1 : 0;
+  p.slab3 = conv_slab3_mode(p);
   int rc = conv_encode_tmaps(&ta, &tb, g, p.seg[0].rows, g_ld, g_ld, weight_t, cin, ksize * ksize * g_ld,
-                             p.pair ? p.block_n / 2 : p.block_n);
+                             p.pair ? p.block_n / 2 : p.block_n, p.slab3 ? kConvSlabRows : kConvBlockM);
   if (rc != 0) return fail(kErrCuda, "ppb_conv2d_dgrad_bf16: cuTensorMapEncodeTiled failed (%d)", rc);
   memset(&to, 0, sizeof(to));
   memset(&tr, 0, sizeof(tr));

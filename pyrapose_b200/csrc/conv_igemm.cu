@@ -24,6 +24,7 @@ namespace {
 constexpr int kMaxStages = 8;
 constexpr int kMaxRing = 8;
 constexpr int kABytes = kConvBlockM * kConvBlockK * 2;  // 16 KiB
+constexpr int kSlabBytes = kConvSlabRows * kConvBlockK * 2;  // 17 KiB: 136 rows x 128 B
 constexpr int kTmemCols = 512;
 constexpr int kAccCols = 256;
 constexpr int kCtrlWarps = 4;
@@ -237,7 +238,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                                 // without a cluster ("cluster misconfiguration")
   const uint32_t rank = pair ? cluster_ctarank() : 0u;
   const int b_rows = pair ? (p.block_n >> 1) : p.block_n;
-  const int stage_bytes = kABytes + b_rows * (kConvBlockK * 2);
+  // slab mode (ConvParams::slab3): a stage holds one 136-row A slab and the B tiles of the three taps of a filter row
+  const int taps_per_stage = p.slab3 != 0 ? 3 : 1;
+  const int a_bytes = p.slab3 != 0 ? kSlabBytes : kABytes;
+  const int b_tile_bytes = b_rows * (kConvBlockK * 2);
+  const int stage_bytes = a_bytes + taps_per_stage * b_tile_bytes;
   uint8_t* ring = smem + n_stages * stage_bytes;
   float* sbias = reinterpret_cast<float*>(ring + p.ring_slots * kChunkBytes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sbias) + kBiasFloats * 4);
@@ -305,7 +310,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   pdl_launch_dependents();
 
   const int total_tiles = p.n_mtiles * p.n_ntiles;
-  const int k_iters = p.n_taps * p.cin_blocks;
+  const int k_iters = (p.n_taps / taps_per_stage) * p.cin_blocks;
   // Tile walk. Single CTA: tile = it. Pair: `it` walks (M-tile pair, N tile); this CTA owns M tile 2*pair + rank.
   const int it_begin = pair ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
   const int it_step = pair ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
@@ -336,20 +341,24 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         const TileCoord tc = tile_coord(p, tile_of(it));
         const ConvSeg& sg = p.seg[tc.seg];
         const int b_row = tc.n0 + static_cast<int>(rank) * b_rows;
-        for (int tap = 0; tap < p.n_taps; ++tap) {
-          const int a_row = tc.row0 + sg.tap_off[tap];
+        for (int tap = 0; tap < p.n_taps; tap += taps_per_stage) {
+          // slab mode: the slab starts at the lowest of the row's three tap offsets (the last tap when they descend)
+          const int a_row = tc.row0 + sg.tap_off[p.slab3 < 0 ? tap + 2 : tap];
           for (int kb = 0; kb < p.cin_blocks; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1, kFaultEmpty);
             uint8_t* sa = smem + stage * stage_bytes;
-            const int b_col = p.b_col_base + (tap * p.cin_blocks + kb) * kConvBlockK;
             if (pair) {  // both CTAs' bytes are counted on rank 0's barrier, armed by rank 0 for the two stages
               if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
               tma_load_2d_pair(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
-              tma_load_2d_pair(sa + kABytes, &tmap_b, b_col, b_row, &full_bar[stage]);
+              for (int j = 0; j < taps_per_stage; ++j)
+                tma_load_2d_pair(sa + a_bytes + j * b_tile_bytes, &tmap_b,
+                                 p.b_col_base + ((tap + j) * p.cin_blocks + kb) * kConvBlockK, b_row, &full_bar[stage]);
             } else {
               mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
               tma_load_2d(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
-              tma_load_2d(sa + kABytes, &tmap_b, b_col, tc.n0, &full_bar[stage]);
+              for (int j = 0; j < taps_per_stage; ++j)
+                tma_load_2d(sa + a_bytes + j * b_tile_bytes, &tmap_b,
+                            p.b_col_base + ((tap + j) * p.cin_blocks + kb) * kConvBlockK, tc.n0, &full_bar[stage]);
             }
             if (++stage == n_stages) {
               stage = 0;
@@ -375,22 +384,20 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           mbar_wait(&full_bar[stage], phase, kFaultFull);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
-          const uint32_t b_addr = a_addr + kABytes;
-          if (pair) {
+          const uint32_t b_addr = a_addr + a_bytes;
+          for (int j = 0; j < taps_per_stage; ++j) {
+            // slab mode: tap j of the filter row reads the slab from row j (ascending taps) or 2 - j (descending)
+            const uint32_t a_tap = a_addr + (p.slab3 == 0 ? 0u : (p.slab3 > 0 ? j : 2 - j) * 128u);
+            const uint32_t b_tap = b_addr + j * b_tile_bytes;
 #pragma unroll
             for (int k = 0; k < kConvBlockK / 16; ++k) {
-              tc_mma_bf16_2cta(d_tmem, umma_desc_k128(a_addr + k * 32), umma_desc_k128(b_addr + k * 32), idesc,
-                               (ki | k) != 0 ? 1u : 0u);
+              const uint32_t accum = (ki | j | k) != 0 ? 1u : 0u;
+              if (pair) tc_mma_bf16_2cta(d_tmem, umma_desc_k128(a_tap + k * 32), umma_desc_k128(b_tap + k * 32), idesc, accum);
+              else tc_mma_bf16(d_tmem, umma_desc_k128(a_tap + k * 32), umma_desc_k128(b_tap + k * 32), idesc, accum);
             }
-            tc_commit2(&empty_bar[stage]);  // frees this stage in both CTAs
-          } else {
-#pragma unroll
-            for (int k = 0; k < kConvBlockK / 16; ++k) {
-              tc_mma_bf16(d_tmem, umma_desc_k128(a_addr + k * 32), umma_desc_k128(b_addr + k * 32), idesc,
-                          (ki | k) != 0 ? 1u : 0u);
-            }
-            tc_commit(&empty_bar[stage]);
           }
+          if (pair) tc_commit2(&empty_bar[stage]);  // frees this stage in both CTAs
+          else tc_commit(&empty_bar[stage]);
           if (++stage == n_stages) {
             stage = 0;
             phase ^= 1;
@@ -638,8 +645,8 @@ int conv_encode_rows_tmap(CUtensorMap* tmap, const void* base, long rows, int co
 }
 
 int conv_encode_tmaps(CUtensorMap* tmap_a, CUtensorMap* tmap_b, const void* a, long a_rows, int a_cols, int a_ld,
-                      const void* w, int w_rows, int w_cols, int block_n) {
-  int rc = encode_2d(tmap_a, a, static_cast<uint64_t>(a_rows), a_cols, a_ld, kConvBlockM);
+                      const void* w, int w_rows, int w_cols, int block_n, int a_box_rows) {
+  int rc = encode_2d(tmap_a, a, static_cast<uint64_t>(a_rows), a_cols, a_ld, static_cast<uint32_t>(a_box_rows));
   if (rc != 0) return rc;
   return encode_2d(tmap_b, w, w_rows, w_cols, w_cols, block_n);
 }
@@ -667,9 +674,42 @@ bool conv_pair_ok(const ConvParams& p) {
   return p.n_mtiles >= 2 && (p.block_n & 15) == 0 && (mode >= 2 || k_iters >= 16);
 }
 
+namespace {
+int stage_bytes_of(const ConvParams& p) {
+  const int b_tile = (p.pair ? p.block_n / 2 : p.block_n) * (kConvBlockK * 2);
+  return p.slab3 != 0 ? kSlabBytes + 3 * b_tile : kABytes + b_tile;
+}
+int ring_min_of(const ConvParams& p) {
+  if (p.epi == kEpiBf16) return p.staged ? 4 : 0;
+  return (kConvBlockM * (p.block_n | 1) * 4 + kConvBlockM * 8 + kChunkBytes - 1) / kChunkBytes;
+}
+}  // namespace
+
+int conv_slab3_mode(const ConvParams& p) {
+  static const int mode = [] {
+    const char* e = getenv("PPB_SLAB3");
+    return e != nullptr ? atoi(e) : 1;
+  }();
+  if (mode == 0 || p.n_taps != 9) return 0;
+  int dir = 0;
+  for (int sgi = 0; sgi < p.n_segs; ++sgi)
+    for (int r = 0; r < 3; ++r) {
+      const int* t = p.seg[sgi].tap_off + 3 * r;
+      const int d = t[1] - t[0];
+      if ((d != 1 && d != -1) || t[2] - t[1] != d || (dir != 0 && d != dir)) return 0;
+      dir = d;
+    }
+  // three stages of {136-row slab + three B tiles} must fit beside the epilogue's ring (a 256-wide N tile only fits as
+  // a CTA pair with the direct epilogue: the head towers)
+  ConvParams q = p;
+  q.slab3 = dir;
+  if (3 * stage_bytes_of(q) + ring_min_of(q) * kChunkBytes > kSmemBudget) return 0;
+  return dir;
+}
+
 int conv_plan_smem(ConvParams& p) {
-  const int stage_bytes = kABytes + (p.pair ? p.block_n / 2 : p.block_n) * (kConvBlockK * 2);
-  const int k_iters = p.n_taps * p.cin_blocks;
+  const int stage_bytes = stage_bytes_of(p);
+  const int k_iters = (p.slab3 != 0 ? 3 : p.n_taps) * p.cin_blocks;
   int ring_min = 0, ring_max = 0;
   if (p.epi == kEpiBf16) {
     if (p.staged) {

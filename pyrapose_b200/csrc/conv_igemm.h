@@ -54,6 +54,12 @@ struct ConvParams {
   int staged;       // kEpiBf16 only: epilogue through the shared-memory chunk ring + TMA store (needs tmap_out / tmap_res)
   int pair;         // 1: CTA pairs (cluster of 2, tcgen05 cta_group::2, M = 256 per MMA); needs tmap_b encoded with a
                     // block_n / 2 row box (pass block_n / 2 to conv_encode_tmaps) — see conv_pair_ok()
+  int slab3;        // 3x3 stride-1 layers: one pipeline stage = one filter ROW of one 64-channel block. The A operand is
+                    // ONE slab of 136 rows (tmap_a encoded with a 136-row box) and the three taps of the row are three
+                    // MMAs whose descriptors start 0 / 1 / 2 rows (128 B) into it — the swizzle is a function of the
+                    // shared-memory address, so a row-shifted start reads the right data (tools/probe_shift.py). Cuts
+                    // the A bytes an SM pulls from L2 by 3x. +1 / -1: the taps of a row ascend / descend (dgrad) in
+                    // row offset; 0: off. Set by conv_slab3_mode().
   int n_stages;     // TMA->MMA pipeline depth (2..8)   } filled by conv_plan_smem()
   int ring_slots;   // 16 KiB epilogue ring slots        }
   const float* bias;              // [n_valid] fp32, BatchNorm folded in; may be null
@@ -76,7 +82,13 @@ struct ConvParams {
 // Encodes the two TMA descriptors for one convolution. a_rows x a_cols is the activation matrix
 // (bf16, row stride a_ld elements); w is [w_rows, w_cols] bf16 row-major (Cout_pad x taps*Cin).
 int conv_encode_tmaps(CUtensorMap* tmap_a, CUtensorMap* tmap_b, const void* a, long a_rows, int a_cols, int a_ld,
-                      const void* w, int w_rows, int w_cols, int block_n);
+                      const void* w, int w_rows, int w_cols, int block_n, int a_box_rows = kConvBlockM);
+
+constexpr int kConvSlabRows = 136;  // 128 + 2 rows of halo, rounded up to whole 8-row swizzle atoms
+
+// +1 / -1 when the layer can run in slab mode (see ConvParams::slab3; needs n_taps == 9 with unit-spaced taps per
+// filter row in every segment, p.pair and p.block_n already chosen), else 0. PPB_SLAB3=0 disables it.
+int conv_slab3_mode(const ConvParams& p);
 
 // Tensor map over a row-major bf16 matrix with a {64 cols x 128 rows} box (output store / residual load).
 int conv_encode_rows_tmap(CUtensorMap* tmap, const void* base, long rows, int cols, int ld);

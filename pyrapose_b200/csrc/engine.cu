@@ -171,8 +171,11 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
   p.out_ld = y->C;
   const long long a_rows = x->rows(batch) * (x_planes > 0 ? x_planes : 1);
   p.pair = conv_pair_ok(p) ? 1 : 0;
+  p.staged = (l.cout % 64 == 0 && p.block_n % 64 == 0 &&
+              (staged_epilogue >= 2 || (staged_epilogue == 1 && res != nullptr))) ? 1 : 0;
+  p.slab3 = conv_slab3_mode(p);
   int rc = conv_encode_tmaps(&op.ta, &op.tb, x->ptr, a_rows, a_cols, a_ld, l.w, l.cout_pad, l.k_total,
-                             p.pair ? p.block_n / 2 : p.block_n);
+                             p.pair ? p.block_n / 2 : p.block_n, p.slab3 ? kConvSlabRows : kConvBlockM);
   if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled failed for layer '%s' (%d)", l.name.c_str(), rc);
   memset(&op.to, 0, sizeof(op.to));
   memset(&op.tr, 0, sizeof(op.tr));
@@ -244,8 +247,10 @@ int Engine::head_conv_op(const __nv_bfloat16* x, int cin, const std::string& lay
   memcpy(p.dec_mean, dec_mean, sizeof(dec_mean));
   memcpy(p.dec_std, dec_std, sizeof(dec_std));
   p.pair = conv_pair_ok(p) ? 1 : 0;
+  p.staged = (epi == kEpiBf16 && l.cout % 64 == 0 && p.block_n % 64 == 0 && staged_epilogue >= 3) ? 1 : 0;
+  p.slab3 = conv_slab3_mode(p);
   int rc = conv_encode_tmaps(&op.ta, &op.tb, x, last_row, cin, cin, l.w, l.cout_pad, l.k_total,
-                             p.pair ? p.block_n / 2 : p.block_n);
+                             p.pair ? p.block_n / 2 : p.block_n, p.slab3 ? kConvSlabRows : kConvBlockM);
   if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled failed for layer '%s' (%d)", l.name.c_str(), rc);
   memset(&op.to, 0, sizeof(op.to));
   memset(&op.tr, 0, sizeof(op.tr));

@@ -129,8 +129,10 @@ struct Builder {
     p.out = out;
     p.out_ld = l.cin;
     p.pair = conv_pair_ok(p) ? 1 : 0;
+    p.staged = (l.cin % 64 == 0 && p.block_n % 64 == 0) ? 1 : 0;
+    p.slab3 = conv_slab3_mode(p);
     int rc = conv_encode_tmaps(&op.ta, &op.tb, g, g_rows, tl.g_ld, tl.g_ld, tl.w_dgrad, l.cin, tl.n_taps * tl.g_ld,
-                               p.pair ? p.block_n / 2 : p.block_n);
+                               p.pair ? p.block_n / 2 : p.block_n, p.slab3 ? kConvSlabRows : kConvBlockM);
     if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled failed for dgrad of '%s' (%d)", layer.c_str(), rc);
     memset(&op.to, 0, sizeof(op.to));
     memset(&op.tr, 0, sizeof(op.tr));
