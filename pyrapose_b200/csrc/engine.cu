@@ -174,12 +174,21 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
   p.staged = (l.cout % 64 == 0 && p.block_n % 64 == 0 &&
               (staged_epilogue >= 2 || (staged_epilogue == 1 && res != nullptr))) ? 1 : 0;
   p.slab3 = conv_slab3_mode(p);
+  bool force_direct = false;
+  if (p.slab3 == 0 && p.staged && res == nullptr) {
+    // a 256-wide pair tile in slab mode leaves no room for the epilogue ring: without a residual to prefetch the
+    // direct epilogue costs nothing, so prefer the slab (P3, P3_mid)
+    p.staged = 0;
+    p.slab3 = conv_slab3_mode(p);
+    force_direct = p.slab3 != 0;
+    if (!force_direct) p.staged = 1;
+  }
   int rc = conv_encode_tmaps(&op.ta, &op.tb, x->ptr, a_rows, a_cols, a_ld, l.w, l.cout_pad, l.k_total,
                              p.pair ? p.block_n / 2 : p.block_n, p.slab3 ? kConvSlabRows : kConvBlockM);
   if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled failed for layer '%s' (%d)", l.name.c_str(), rc);
   memset(&op.to, 0, sizeof(op.to));
   memset(&op.tr, 0, sizeof(op.tr));
-  p.staged = (l.cout % 64 == 0 && p.block_n % 64 == 0 &&
+  p.staged = (!force_direct && l.cout % 64 == 0 && p.block_n % 64 == 0 &&
               (staged_epilogue >= 2 || (staged_epilogue == 1 && res != nullptr))) ? 1 : 0;
   if (p.staged) {
     rc = conv_encode_rows_tmap(&op.to, y->ptr, y->rows(batch), y->C, y->C);
