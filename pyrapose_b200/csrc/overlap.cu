@@ -4,7 +4,7 @@
 // separately, exactly as the x86-64 build of the reference does.
 //
 //  * overlap_matrix_kernel  — materialises the (N, K) matrix (drop-in compute_overlap API).
-//    Store-bound: N*K*8 bytes; consecutive threads write consecutive k (16-byte stores when K is even).
+//    Store-bound: N*K*8 bytes; anchor-per-lane compute (warp-uniform branches), shared-memory transpose, 16-byte stores.
 //  * gt_assign_kernel       — fused compute_gt_annotations: argmax / max / positive / ignore per anchor
 //    without ever writing the matrix; query boxes staged in shared memory.
 #include "../../include/pyrapose_b200.h"
@@ -14,21 +14,7 @@
 namespace ppb {
 namespace {
 
-__device__ __forceinline__ double iou_plus1(const double b0, const double b1, const double b2, const double b3,
-                                            const double q0, const double q1, const double q2, const double q3,
-                                            const double q_area) {
-  const double iw = (b2 < q2 ? b2 : q2) - (b0 > q0 ? b0 : q0) + 1;  // pyx:37-40
-  if (iw > 0) {
-    const double ih = (b3 < q3 ? b3 : q3) - (b1 > q1 ? b1 : q1) + 1;  // pyx:42-45
-    if (ih > 0) {
-      const double ua = (b2 - b0 + 1) * (b3 - b1 + 1) + q_area - iw * ih;  // pyx:47-51
-      return iw * ih / ua;                                                // pyx:52
-    }
-  }
-  return 0.0;
-}
-
-constexpr int kQChunk = 512;  // query boxes staged per pass (512 * 5 doubles = 20 KiB)
+constexpr int kQChunk = 512;  // query boxes staged per pass of gt_assign_kernel (512 * 40 B = 20 KiB)
 
 // grid: (ceil(N / 32), batch), 256 threads = 8 warps. A block owns 32 consecutive anchors = one contiguous slab of the
 // output. Compute phase: lane = anchor (its box and area live in registers), warp w takes query boxes w, w+8, ... of the
@@ -101,7 +87,12 @@ __global__ void __launch_bounds__(256) overlap_matrix_kernel(const double* __res
   }
 }
 
-// grid: (ceil(N/256), batch). One anchor per thread, all K queries of the image looped from smem.
+// grid: (ceil(N / (256 * kGtPerThread)), batch). Every thread owns kGtPerThread anchors 256 apart (coalesced box
+// loads) and walks all K queries of the image from shared memory: one query fetch (two 16-byte and one 8-byte
+// broadcast load) now serves kGtPerThread pairs — with one anchor per thread the kernel was bound by the shared-memory
+// pipe (5 loads per pair), not by the fp64 units.
+constexpr int kGtPerThread = 4;
+
 __global__ void __launch_bounds__(256) gt_assign_kernel(const double* __restrict__ boxes,
                                                         const double* __restrict__ query,
                                                         const int* __restrict__ query_count, int n, int k_max,
@@ -110,48 +101,75 @@ __global__ void __launch_bounds__(256) gt_assign_kernel(const double* __restrict
                                                         unsigned char* __restrict__ positive,
                                                         unsigned char* __restrict__ ignore,
                                                         double* __restrict__ max_overlap) {
-  __shared__ double sq[kQChunk * 5];
+  __shared__ double2 sq01[kQChunk];
+  __shared__ double2 sq23[kQChunk];
+  __shared__ double sqa[kQChunk];
   const int b = blockIdx.y;
   const int k = query_count != nullptr ? query_count[b] : k_max;
   const double* qx = query + static_cast<long long>(b) * k_max * 4;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  double b0 = 0, b1 = 0, b2 = 0, b3 = 0;
-  if (i < n) {
-    const double* bp = boxes + b * boxes_bstride + static_cast<long long>(i) * 4;
-    const double2 b01 = *reinterpret_cast<const double2*>(bp);
-    const double2 b23 = *reinterpret_cast<const double2*>(bp + 2);
-    b0 = b01.x; b1 = b01.y; b2 = b23.x; b3 = b23.y;
+  const int i0 = blockIdx.x * (256 * kGtPerThread) + threadIdx.x;
+  double b0[kGtPerThread], b1[kGtPerThread], b2[kGtPerThread], b3[kGtPerThread], barea[kGtPerThread];
+  double best[kGtPerThread];
+  int best_k[kGtPerThread];
+#pragma unroll
+  for (int r = 0; r < kGtPerThread; ++r) {
+    const int i = i0 + r * 256;
+    b0[r] = b1[r] = b2[r] = b3[r] = 0.0;
+    if (i < n) {
+      const double* bp = boxes + b * boxes_bstride + static_cast<long long>(i) * 4;
+      const double2 b01 = __ldg(reinterpret_cast<const double2*>(bp));
+      const double2 b23 = __ldg(reinterpret_cast<const double2*>(bp + 2));
+      b0[r] = b01.x; b1[r] = b01.y; b2[r] = b23.x; b3[r] = b23.y;
+    }
+    barea[r] = (b2[r] - b0[r] + 1) * (b3[r] - b1[r] + 1);  // first product of pyx:47-49, same operands for every k
+    best[r] = -1.0;  // numpy.argmax: first maximum wins; an all-zero row gives index 0
+    best_k[r] = 0;
   }
-  double best = -1.0;  // numpy.argmax: first maximum wins; an all-zero row gives index 0
-  long long best_k = 0;
   for (int base = 0; base < k; base += kQChunk) {
     const int chunk = min(kQChunk, k - base);
     __syncthreads();
     for (int t = threadIdx.x; t < chunk; t += blockDim.x) {
-      const double q0 = qx[(base + t) * 4 + 0], q1 = qx[(base + t) * 4 + 1];
-      const double q2 = qx[(base + t) * 4 + 2], q3 = qx[(base + t) * 4 + 3];
-      sq[t * 5 + 0] = q0; sq[t * 5 + 1] = q1; sq[t * 5 + 2] = q2; sq[t * 5 + 3] = q3;
-      sq[t * 5 + 4] = (q2 - q0 + 1) * (q3 - q1 + 1);
+      const double2 q01 = __ldg(reinterpret_cast<const double2*>(qx + (base + t) * 4));
+      const double2 q23 = __ldg(reinterpret_cast<const double2*>(qx + (base + t) * 4 + 2));
+      sq01[t] = q01;
+      sq23[t] = q23;
+      sqa[t] = (q23.x - q01.x + 1) * (q23.y - q01.y + 1);  // pyx:32-35
     }
     __syncthreads();
-    if (i < n) {
-      for (int t = 0; t < chunk; ++t) {
-        const double ov = iou_plus1(b0, b1, b2, b3, sq[t * 5], sq[t * 5 + 1], sq[t * 5 + 2], sq[t * 5 + 3], sq[t * 5 + 4]);
-        if (ov > best) {
-          best = ov;
-          best_k = base + t;
+    for (int t = 0; t < chunk; ++t) {
+      const double2 q01 = sq01[t];
+      const double2 q23 = sq23[t];
+      const double qa = sqa[t];
+#pragma unroll
+      for (int r = 0; r < kGtPerThread; ++r) {
+        double ov = 0.0;
+        const double iw = (b2[r] < q23.x ? b2[r] : q23.x) - (b0[r] > q01.x ? b0[r] : q01.x) + 1;  // pyx:37-40
+        if (iw > 0) {
+          const double ih = (b3[r] < q23.y ? b3[r] : q23.y) - (b1[r] > q01.y ? b1[r] : q01.y) + 1;  // pyx:42-45
+          if (ih > 0) {
+            const double ua = barea[r] + qa - iw * ih;  // pyx:47-51
+            ov = iw * ih / ua;                          // pyx:52
+          }
+        }
+        if (ov > best[r]) {
+          best[r] = ov;
+          best_k[r] = base + t;
         }
       }
     }
   }
-  if (i < n) {
+#pragma unroll
+  for (int r = 0; r < kGtPerThread; ++r) {
+    const int i = i0 + r * 256;
+    if (i >= n) continue;
     const long long o = static_cast<long long>(b) * n + i;
-    if (k == 0) best = 0.0;
-    argmax[o] = best_k;
-    const bool pos = best >= pos_thr;                 // anchors.py:315
+    double bv = best[r];
+    if (k == 0) bv = 0.0;
+    argmax[o] = best_k[r];
+    const bool pos = bv >= pos_thr;                 // anchors.py:315
     positive[o] = pos;
-    ignore[o] = (best > neg_thr) && !pos;             // anchors.py:316
-    if (max_overlap != nullptr) max_overlap[o] = best;
+    ignore[o] = (bv > neg_thr) && !pos;             // anchors.py:316
+    if (max_overlap != nullptr) max_overlap[o] = bv;
   }
 }
 
@@ -283,7 +301,8 @@ int ppb_gt_assign_f64(const double* boxes, const double* query, const int* query
               "ppb_gt_assign_f64: null buffer");
   PPB_REQUIRE(k_max == 0 || query != nullptr, "ppb_gt_assign_f64: null query");
   const long long bs = boxes_shared ? 0 : static_cast<long long>(n) * 4;
-  gt_assign_kernel<<<dim3((n + 255) / 256, batch), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  gt_assign_kernel<<<dim3((n + 256 * kGtPerThread - 1) / (256 * kGtPerThread), batch), 256, 0,
+                     static_cast<cudaStream_t>(stream)>>>(
       boxes, query, query_count, n, k_max, bs, negative_overlap, positive_overlap, argmax, positive, ignore,
       max_overlap);
   PPB_CUDA(cudaGetLastError());
