@@ -398,7 +398,14 @@ __device__ __forceinline__ bool iou_exceeds(const NBox& i, const NBox& j, float 
   const float y0 = fmaxf(i.a0, j.a0), x0 = fmaxf(i.a1, j.a1);
   const float y1 = fminf(i.a2, j.a2), x1 = fminf(i.a3, j.a3);
   const float inter = fmaxf(y1 - y0, 0.0f) * fmaxf(x1 - x0, 0.0f);
-  return inter / (i.area + j.area - inter) > thr;
+  const float uni = i.area + j.area - inter;
+  // The IEEE division costs as much as the rest of the test and nearly every pair is far from the threshold: decide by
+  // multiplication when inter is outside thr * uni * (1 +- 1e-6) — a margin 16x the rounding error of the quotient and
+  // of the product, so the answer is the one the division gives — and divide only inside that band.
+  const float t = thr * uni;
+  if (inter > t * 1.000001f) return true;
+  if (inter < t * 0.999999f) return false;
+  return inter / uni > thr;
 }
 
 // grid (C, B), 1024 threads = 256 candidates x 4 helpers. Reads the sorted keys of (b,c); writes up to max_det anchor
@@ -406,10 +413,12 @@ __device__ __forceinline__ bool iou_exceeds(const NBox& i, const NBox& j, float 
 // Per 256-candidate chunk (descending score): (1) every candidate is tested against the boxes selected so far, the
 // list split four ways over its helpers; (2) the candidate-vs-earlier-candidate suppression bit matrix is built, two
 // 32-bit words per helper; (3) ONE warp resolves the greedy order 32 candidates at a time with ballots/shuffles.
-constexpr int kNmsThreads = 1024;
 constexpr int kNmsWords = kNmsChunk / 32;
 
-__global__ void __launch_bounds__(kNmsThreads) nms_kernel(const uint64_t* __restrict__ keys,
+// NT threads = NT / 256 helper threads per candidate of the 256-wide chunk (PPB_NMS_THREADS=256|512|1024; smaller
+// blocks let several share an SM but measured slightly slower, so 1024 stays the default).
+template <int NT>
+__global__ void __launch_bounds__(NT) nms_kernel(const uint64_t* __restrict__ keys,
                                                           const int* __restrict__ counts, int cap,
                                                           const float* __restrict__ boxes, int N, int C, int do_nms,
                                                           float thr, int max_det, int* __restrict__ sel_idx,
@@ -433,7 +442,9 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const uint64_t* __rest
     return;
   }
   const int cand = tid & (kNmsChunk - 1);
-  const int sub = tid >> 8;  // warp-uniform helper index 0..3
+  constexpr int kNmsSubs = NT / kNmsChunk;
+  static_assert(kNmsSubs >= 1 && kNmsWords % kNmsSubs == 0, "helpers must divide the 8 suppression words");
+  const int sub = tid >> 8;  // warp-uniform helper index 0..kNmsSubs-1
   if (tid == 0) n_sel_s = 0;
   __syncthreads();
   for (int cs = 0; cs < n; cs += kNmsChunk) {
@@ -457,15 +468,15 @@ __global__ void __launch_bounds__(kNmsThreads) nms_kernel(const uint64_t* __rest
     // phase 1: against boxes selected in earlier chunks (helper `sub` takes every fourth one)
     if (valid) {
       bool dead = false;
-      for (int s = sub; s < n_sel && !dead; s += 4) dead = iou_exceeds(me, sel_box[s], thr);
+      for (int s = sub; s < n_sel && !dead; s += kNmsSubs) dead = iou_exceeds(me, sel_box[s], thr);
       if (dead) alive_s[cand] = 0;  // benign race: every writer stores 0
     }
     __syncthreads();
     // phase 2: which earlier (higher-scored) alive members of this chunk would suppress me
     const bool alive = alive_s[cand] != 0;
 #pragma unroll
-    for (int wi = 0; wi < 2; ++wi) {
-      const int w = sub + wi * 4;
+    for (int wi = 0; wi < kNmsWords / kNmsSubs; ++wi) {
+      const int w = sub + wi * kNmsSubs;
       uint32_t bits = 0u;
       if (alive && w * 32 < cand) {
         const int jend = min(32, cand - w * 32);
@@ -533,6 +544,7 @@ __global__ void __launch_bounds__(1024) topk_pad_kernel(const int* __restrict__ 
                                                         uint64_t* __restrict__ scratch, int np2) {
   extern __shared__ uint64_t skeys[];
   __shared__ int total_s;
+  __shared__ int order_s[kMaxDetCap];  // slot index of the r-th detection
   const int b = blockIdx.x;
   uint64_t* a = np2 <= kTopkSmemKeys ? skeys : scratch + static_cast<long long>(b) * np2;
   const int slots = Ceff * max_det;
@@ -556,13 +568,36 @@ __global__ void __launch_bounds__(1024) topk_pad_kernel(const int* __restrict__ 
     a[p] = key;
   }
   __syncthreads();
-  bitonic_sort_block(a, np2);
+  // top_k over the concatenation (filter_detections.py:81-90) without sorting it: every per-class list is already in
+  // ascending key order (NMS selects in descending score, ties by position), so the rank of an element is its position
+  // in its own list plus, for every other class, the number of that list's keys below it (binary search). Keys are
+  // unique (the slot index is their low word). ~9 shared-memory probes per (element, class) instead of a 91-stage
+  // bitonic sort of 8192 keys.
   const int k = min(max_det, total_s);  // filter_detections.py:90
+  for (int p = threadIdx.x; p < slots; p += blockDim.x) {
+    const uint64_t key = a[p];
+    if (key == ~0ull) continue;
+    const int c = p / max_det;
+    int rank = p - c * max_det;
+    for (int c2 = 0; c2 < Ceff && rank < k; ++c2) {
+      if (c2 == c) continue;
+      const uint64_t* lst = a + c2 * max_det;
+      int lo = 0, hi = __ldg(sel_cnt + b * Ceff + c2);
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (lst[mid] < key) lo = mid + 1;
+        else hi = mid;
+      }
+      rank += lo;
+    }
+    if (rank < k) order_s[rank] = p;
+  }
+  __syncthreads();
   for (int t = threadIdx.x; t < max_det * 16; t += blockDim.x) {
     const int r = t >> 4, j = t & 15;
     float v3 = -1.0f;
     if (r < k) {
-      const int p = static_cast<int>(a[r] & 0xffffffffu);
+      const int p = order_s[r];
       const int c = p / max_det;
       const int idx = sel_idx[(static_cast<long long>(b) * Ceff + c) * max_det + (p - c * max_det)];
       const long long row = static_cast<long long>(b) * N + idx;
@@ -737,7 +772,16 @@ int ppb_filter_detections(const float* boxes, const float* boxes3D, const float*
   }
   sort_keys_kernel<<<Ceff * batch, 1024, kSortSmemKeys * 8, st>>>(w.keys, w.counts, cap);
   PPB_CUDA(cudaGetLastError());
-  nms_kernel<<<dim3(Ceff, batch), kNmsThreads, 0, st>>>(w.keys, w.counts, cap, boxes, n, Ceff, nms, nms_threshold,
+  static const int nms_threads = [] {
+    const char* e = getenv("PPB_NMS_THREADS");
+    const int v = e != nullptr ? atoi(e) : 1024;  // measured at B=32, 15 classes: 0.468 ms (1024), 0.503 (512), 0.506 (256)
+    return (v == 256 || v == 512) ? v : 1024;
+  }();
+  if (nms_threads == 256) nms_kernel<256><<<dim3(Ceff, batch), 256, 0, st>>>(w.keys, w.counts, cap, boxes, n, Ceff, nms, nms_threshold,
+                                                      max_detections, w.sel_idx, w.sel_cnt);
+  else if (nms_threads == 512) nms_kernel<512><<<dim3(Ceff, batch), 512, 0, st>>>(w.keys, w.counts, cap, boxes, n, Ceff, nms, nms_threshold,
+                                                      max_detections, w.sel_idx, w.sel_cnt);
+  else nms_kernel<1024><<<dim3(Ceff, batch), 1024, 0, st>>>(w.keys, w.counts, cap, boxes, n, Ceff, nms, nms_threshold,
                                                       max_detections, w.sel_idx, w.sel_cnt);
   PPB_CUDA(cudaGetLastError());
   const int np2 = next_pow2(Ceff * max_detections);

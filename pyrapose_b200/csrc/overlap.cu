@@ -88,10 +88,11 @@ __global__ void __launch_bounds__(256) overlap_matrix_kernel(const double* __res
 }
 
 // grid: (ceil(N / (256 * kGtPerThread)), batch). Every thread owns kGtPerThread anchors 256 apart (coalesced box
-// loads) and walks all K queries of the image from shared memory: one query fetch (two 16-byte and one 8-byte
-// broadcast load) now serves kGtPerThread pairs — with one anchor per thread the kernel was bound by the shared-memory
-// pipe (5 loads per pair), not by the fp64 units.
-constexpr int kGtPerThread = 4;
+// loads) and walks all K queries of the image from shared memory (two 16-byte and one 8-byte broadcast load per query).
+// The kernel is bound by the fp64 pipe (compare / select / add chains per pair, the IEEE division where boxes overlap),
+// not by shared memory: four anchors per thread measured SLOWER (0.456 vs 0.400 ms at B=64, N=56700, K=100), so the
+// blocking factor stays 1.
+constexpr int kGtPerThread = 1;
 
 __global__ void __launch_bounds__(256) gt_assign_kernel(const double* __restrict__ boxes,
                                                         const double* __restrict__ query,
