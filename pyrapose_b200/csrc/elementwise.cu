@@ -65,15 +65,18 @@ __device__ __forceinline__ uint4 max8(uint4 a, uint4 b) {
 __global__ void __launch_bounds__(256) maxpool_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int B,
                                                       int Hi, int Wi, int in_hs, int in_ws, int C8, int Ho, int Wo,
                                                       int pad_top, int pad_left) {
-  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const int Hp = Ho + 2, Wp = Wo + 2;
-  const long long total = static_cast<long long>(B) * Hp * Wp * C8;
+  // 32-bit index arithmetic (the launchers reject tensors with 2^31 or more vectors): the 64-bit divisions and
+  // modulos were most of this kernel's instructions
+  const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned Hp = Ho + 2, Wp = Wo + 2;
+  const unsigned total = static_cast<unsigned>(B) * Hp * Wp * C8;
   if (t >= total) return;
-  const int c = static_cast<int>(t % C8);
-  const long long pix = t / C8;
-  const int wx = static_cast<int>(pix % Wp);
-  const int hy = static_cast<int>((pix / Wp) % Hp);
-  const int b = static_cast<int>(pix / (static_cast<long long>(Wp) * Hp));
+  const unsigned pix = t / static_cast<unsigned>(C8);
+  const int c = static_cast<int>(t - pix * C8);
+  const unsigned rowi = pix / Wp;
+  const int wx = static_cast<int>(pix - rowi * Wp);
+  const int b = static_cast<int>(rowi / Hp);
+  const int hy = static_cast<int>(rowi - b * Hp);
   uint4 r = make_uint4(0, 0, 0, 0);
   if (hy >= 1 && hy <= Ho && wx >= 1 && wx <= Wo) {
     const int oy = hy - 1, ox = wx - 1;
@@ -95,17 +98,18 @@ __global__ void __launch_bounds__(256) maxpool_kernel(const uint4* __restrict__ 
 
 __global__ void __launch_bounds__(256) parity_planes_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int B,
                                                             int H, int W, int C8, int Ho, int Wo, int n_planes) {
-  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const int Hp = Ho + 2, Wp = Wo + 2;
-  const long long plane_elems = static_cast<long long>(B) * Hp * Wp * C8;
+  const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned Hp = Ho + 2, Wp = Wo + 2;
+  const unsigned plane_elems = static_cast<unsigned>(B) * Hp * Wp * C8;
   if (t >= plane_elems * n_planes) return;
   const int plane = static_cast<int>(t / plane_elems);
-  const long long u = t - plane * plane_elems;
-  const int c = static_cast<int>(u % C8);
-  const long long pix = u / C8;
-  const int wx = static_cast<int>(pix % Wp);
-  const int hy = static_cast<int>((pix / Wp) % Hp);
-  const int b = static_cast<int>(pix / (static_cast<long long>(Wp) * Hp));
+  const unsigned u = t - plane * plane_elems;
+  const unsigned pix = u / static_cast<unsigned>(C8);
+  const int c = static_cast<int>(u - pix * C8);
+  const unsigned rowi = pix / Wp;
+  const int wx = static_cast<int>(pix - rowi * Wp);
+  const int b = static_cast<int>(rowi / Hp);
+  const int hy = static_cast<int>(rowi - b * Hp);
   uint4 r = make_uint4(0, 0, 0, 0);
   if (hy >= 1 && hy <= Ho && wx >= 1 && wx <= Wo) {
     const int iy = 2 * (hy - 1) + (plane >> 1), ix = 2 * (wx - 1) + (plane & 1);
@@ -122,9 +126,9 @@ __device__ __forceinline__ void acc8(float (&f)[8], uint4 v) {
 __global__ void __launch_bounds__(256) add_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b,
                                                   const uint4* __restrict__ c, const uint4* __restrict__ u, int uH,
                                                   int uW, uint4* __restrict__ out, int B, int H, int W, int C8) {
-  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const int Hp = H + 2, Wp = W + 2;
-  const long long total = static_cast<long long>(B) * Hp * Wp * C8;
+  const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned Hp = H + 2, Wp = W + 2;
+  const unsigned total = static_cast<unsigned>(B) * Hp * Wp * C8;
   if (t >= total) return;
   float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   // Keras Add sums its inputs left to right in fp32; the operands here are bf16 so the fp32 sums are exact
@@ -133,11 +137,12 @@ __global__ void __launch_bounds__(256) add_kernel(const uint4* __restrict__ a, c
   if (b != nullptr) acc8(f, __ldg(b + t));
   if (c != nullptr) acc8(f, __ldg(c + t));
   if (u != nullptr) {
-    const int ch = static_cast<int>(t % C8);
-    const long long pix = t / C8;
-    const int wx = static_cast<int>(pix % Wp);
-    const int hy = static_cast<int>((pix / Wp) % Hp);
-    const int bi = static_cast<int>(pix / (static_cast<long long>(Wp) * Hp));
+    const unsigned pix = t / static_cast<unsigned>(C8);
+    const int ch = static_cast<int>(t - pix * C8);
+    const unsigned rowi = pix / Wp;
+    const int wx = static_cast<int>(pix - rowi * Wp);
+    const int bi = static_cast<int>(rowi / Hp);
+    const int hy = static_cast<int>(rowi - bi * Hp);
     if (hy >= 1 && hy <= H && wx >= 1 && wx <= W) {
       // tf.image.resize NEAREST, half_pixel_centers: src = min(floor((dst + 0.5) * in / out), in - 1)
       int sy = static_cast<int>(floorf((static_cast<float>(hy - 1) + 0.5f) * (static_cast<float>(uH) / H)));
@@ -156,6 +161,11 @@ __global__ void __launch_bounds__(256) add_kernel(const uint4* __restrict__ a, c
 }
 
 inline unsigned blocks_for(long long total) { return static_cast<unsigned>((total + 255) / 256); }
+// the kernels index with 32 bits
+#define PPB_EW_CHECK(total) \
+  do {                      \
+    if ((total) >= (1ll << 31)) return cudaErrorInvalidValue; \
+  } while (0)
 
 }  // namespace
 
@@ -180,6 +190,7 @@ cudaError_t launch_maxpool3x3s2(const __nv_bfloat16* in, __nv_bfloat16* out, int
   const int pt = ((Ho - 1) * 2 + 3 - Hi) > 0 ? ((Ho - 1) * 2 + 3 - Hi) / 2 : 0;
   const int pl = ((Wo - 1) * 2 + 3 - Wi) > 0 ? ((Wo - 1) * 2 + 3 - Wi) / 2 : 0;
   const long long total = static_cast<long long>(B) * (Ho + 2) * (Wo + 2) * (C / 8);
+  PPB_EW_CHECK(total);
   maxpool_kernel<<<blocks_for(total), 256, 0, st>>>(reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(out), B,
                                                     Hi, Wi, in_hs, in_ws, C / 8, Ho, Wo, pt, pl);
   return cudaGetLastError();
@@ -188,6 +199,7 @@ cudaError_t launch_maxpool3x3s2(const __nv_bfloat16* in, __nv_bfloat16* out, int
 cudaError_t launch_parity_planes(const __nv_bfloat16* in, __nv_bfloat16* out, int B, int H, int W, int C, int Ho,
                                  int Wo, int n_planes, cudaStream_t st) {
   const long long total = static_cast<long long>(B) * (Ho + 2) * (Wo + 2) * (C / 8) * n_planes;
+  PPB_EW_CHECK(total);
   parity_planes_kernel<<<blocks_for(total), 256, 0, st>>>(reinterpret_cast<const uint4*>(in),
                                                           reinterpret_cast<uint4*>(out), B, H, W, C / 8, Ho, Wo,
                                                           n_planes);
@@ -198,6 +210,7 @@ cudaError_t launch_add(const __nv_bfloat16* a, const __nv_bfloat16* b, const __n
                        const __nv_bfloat16* u, int uH, int uW, __nv_bfloat16* out, int B, int H, int W, int C,
                        cudaStream_t st) {
   const long long total = static_cast<long long>(B) * (H + 2) * (W + 2) * (C / 8);
+  PPB_EW_CHECK(total);
   add_kernel<<<blocks_for(total), 256, 0, st>>>(reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b),
                                                 reinterpret_cast<const uint4*>(c), reinterpret_cast<const uint4*>(u),
                                                 uH, uW, reinterpret_cast<uint4*>(out), B, H, W, C / 8);
