@@ -28,7 +28,10 @@ constexpr int kSlabBytes = kConvSlabRows * kConvBlockK * 2;  // 17 KiB: 136 rows
 constexpr int kTmemCols = 512;
 constexpr int kAccCols = 256;
 constexpr int kCtrlWarps = 4;
-constexpr int kEpiWarps = 8;  // two groups of four: a TMEM lane quadrant is only visible to warp (id % 4)
+// two groups of four: a TMEM lane quadrant is only visible to warp (id % 4). Three groups (12 epilogue warps, ring of
+// >= 6 slots) were measured: the residual 2c layers gained 7-12 %, most other layers lost 5-13 % (fewer pipeline stages
+// beside the larger ring, more warps per scheduler) — net zero, so two it stays.
+constexpr int kEpiWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kThreads = (kCtrlWarps + kEpiWarps) * 32;
 // Shared memory map (after 1024-B alignment), all sizes per launch (ConvParams::n_stages / ring_slots / block_n):
@@ -721,7 +724,14 @@ int conv_plan_smem(ConvParams& p) {
     ring_min = ring_max = (need + kChunkBytes - 1) / kChunkBytes;
     if (ring_min > kMaxRing) return -1;
   }
-  int stages = k_iters < 2 ? 2 : (k_iters > kMaxStages ? kMaxStages : k_iters);
+  // The producer runs ahead across tiles, so a 1-2 iteration K loop (the K = 64 / 128 layers of stage 2) still wants
+  // several stages: with two, only two tiles' operands are in flight and the TMA latency is exposed on every tile.
+  static const int min_stages = [] {
+    const char* e = getenv("PPB_MIN_STAGES");
+    const int v = e != nullptr ? atoi(e) : 2;
+    return v < 2 ? 2 : (v > kMaxStages ? kMaxStages : v);
+  }();
+  int stages = k_iters < min_stages ? min_stages : (k_iters > kMaxStages ? kMaxStages : k_iters);
   // Shallow-K layers that add a residual (the bottleneck 2c convolutions) are bound by the epilogue ring, not by the
   // main loop: every tile waits for its residual chunks, and a slot only frees once its TMA store has drained. Three
   // pipeline stages are enough to hide the operand latency of <= 8 k-iterations; the rest of shared memory goes to the
