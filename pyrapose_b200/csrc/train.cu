@@ -432,7 +432,11 @@ int create_state(Engine& e) {
     }
   }
   for (size_t di = 0; di < t.descs.size(); ++di) {
-    const long long chunks = (t.descs[di].count + kOptChunk - 1) / kOptChunk;
+    // kernels: one chunk per 64 x 64 (cout, k) tile so that adam_update_kernel can write the transposed dgrad copy in
+    // coalesced runs (never fewer chunks than the contiguous split grad_prepare_kernel uses; its extra ones are empty)
+    const ParamDesc& pd = t.descs[di];
+    const long long chunks = pd.kind == 0 ? static_cast<long long>((pd.cout + 63) / 64) * ((pd.k_total + 63) / 64)
+                                          : (pd.count + kOptChunk - 1) / kOptChunk;
     for (long long c = 0; c < chunks; ++c) {
       chunk_desc.push_back(static_cast<int>(di));
       chunk_index.push_back(static_cast<int>(c));

@@ -291,7 +291,8 @@ grad_prepare_kernel(const ParamDesc* __restrict__ descs, const int* __restrict__
   double sq = 0.0, l2 = 0.0;
   for (long long i = begin + threadIdx.x; i < end; i += blockDim.x) {
     float gv = grads[d.offset + i] * grad_scale;
-    const int co = static_cast<int>(i / k);
+    // 32-bit division: a tensor has far fewer than 2^31 elements (the 64-bit one was a third of this loop)
+    const int co = static_cast<int>(static_cast<unsigned>(i) / static_cast<unsigned>(k));
     if (d.scale != nullptr) gv *= __ldg(d.scale + co);  // chain rule through the folded BatchNorm scale
     if (d.l2 > 0.0f) {
       const float w = master[d.offset + i];
@@ -311,13 +312,10 @@ adam_update_kernel(const ParamDesc* __restrict__ descs, const int* __restrict__ 
                    float* __restrict__ m, float* __restrict__ v, float lr_t, float beta1, float beta2, float eps,
                    float clipnorm, const double* __restrict__ loss) {
   const ParamDesc d = descs[chunk_desc[blockIdx.x]];
-  const long long begin = static_cast<long long>(chunk_index[blockIdx.x]) * kOptChunk;
-  const long long end = min(d.count, begin + kOptChunk);
   // keras.optimizers.clip_norm: g * c / norm when norm >= c (global norm over all gradients, Keras 2.3.1)
   const float norm = static_cast<float>(sqrt(loss[kGradSumSq]));
   const float clip = (clipnorm > 0.0f && norm >= clipnorm) ? clipnorm / norm : 1.0f;
-  for (long long i = begin + threadIdx.x; i < end; i += blockDim.x) {
-    const long long gi = d.offset + i;
+  auto step = [&](long long gi) {
     const float gv = grads[gi] * clip;
     const float mt = beta1 * m[gi] + (1.0f - beta1) * gv;
     const float vt = beta2 * v[gi] + (1.0f - beta2) * gv * gv;
@@ -325,25 +323,57 @@ adam_update_kernel(const ParamDesc* __restrict__ descs, const int* __restrict__ 
     m[gi] = mt;
     v[gi] = vt;
     master[gi] = w;
-    if (d.kind == 1) {
-      d.bias_fwd[i] = w;
-    } else {
-      const int co = static_cast<int>(i / d.k_total);
-      const int kk = static_cast<int>(i - static_cast<long long>(co) * d.k_total);
+    return w;
+  };
+  if (d.kind == 1) {
+    const long long begin = static_cast<long long>(chunk_index[blockIdx.x]) * kOptChunk;
+    const long long end = min(d.count, begin + kOptChunk);
+    for (long long i = begin + threadIdx.x; i < end; i += blockDim.x) d.bias_fwd[i] = step(d.offset + i);
+    return;
+  }
+  // kernel tensor: this block owns the 64 x 64 tile (co0.., kk0..) of the [cout][k_total] matrix. Thread = one column
+  // kk (its tap / input channel are fixed) and every fourth row: loads and the forward bf16 store run along kk
+  // (coalesced); the transposed dgrad copy [ci][tap_pos * g_ld + co] goes through a shared tile and leaves as 128-byte
+  // runs along co (it used to be 2-byte stores a whole matrix row apart — most of the optimizer's time).
+  __shared__ __nv_bfloat16 tile[64][66];
+  const int tiles_k = (d.k_total + 63) >> 6;
+  const int tile_co = chunk_index[blockIdx.x] / tiles_k;
+  const int co0 = tile_co << 6, kk0 = (chunk_index[blockIdx.x] - tile_co * tiles_k) << 6;
+  const int kl = threadIdx.x & 63, r0 = threadIdx.x >> 6;
+  const int kk = kk0 + kl;
+  if (kk < d.k_total) {
+    for (int rl = r0; rl < 64; rl += 4) {
+      const int co = co0 + rl;
+      if (co >= d.cout) break;
+      const long long i = static_cast<long long>(co) * d.k_total + kk;
+      const float w = step(d.offset + i);
       const float wf = d.scale != nullptr ? w * __ldg(d.scale + co) : w;
       const __nv_bfloat16 wb = __float2bfloat16(wf);
       d.w_fwd[i] = wb;
-      if (d.w_dgrad != nullptr) {
-        const int tap = kk / d.cin, ci = kk - tap * d.cin;
-        d.w_dgrad[static_cast<long long>(ci) * (d.n_taps * d.g_ld) + d.tap_pos[tap] * d.g_ld + co] = wb;
-      }
+      tile[kl][rl] = wb;
+    }
+  }
+  if (d.w_dgrad == nullptr) return;
+  __syncthreads();
+  const int n_co = min(64, d.cout - co0);
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+  for (int c = wp; c < 64; c += 8) {  // one warp per kk column of the tile = one row segment of the dgrad matrix
+    const int k2 = kk0 + c;
+    if (k2 >= d.k_total) break;
+    const int tap = k2 / d.cin, ci = k2 - tap * d.cin;
+    __nv_bfloat16* dst = d.w_dgrad + static_cast<long long>(ci) * (d.n_taps * d.g_ld) + d.tap_pos[tap] * d.g_ld + co0;
+    if (n_co == 64) {
+      reinterpret_cast<uint32_t*>(dst)[lane] = *reinterpret_cast<const uint32_t*>(&tile[c][2 * lane]);
+    } else {
+      for (int r = lane; r < n_co; r += 32) dst[r] = tile[c][r];
     }
   }
 }
 
-inline unsigned blocks_for(long long total, int per = 256) { return static_cast<unsigned>((total + per - 1) / per); }
 
 }  // namespace
+
+inline unsigned blocks_for(long long total, int per = 256) { return static_cast<unsigned>((total + per - 1) / per); }
 
 cudaError_t launch_count_positive(const float* y_true, long long rows, int width, int* counts, int slot,
                                   cudaStream_t st) {
