@@ -28,12 +28,11 @@ constexpr int kSlabBytes = kConvSlabRows * kConvBlockK * 2;  // 17 KiB: 136 rows
 constexpr int kTmemCols = 512;
 constexpr int kAccCols = 256;
 constexpr int kCtrlWarps = 4;
-// two groups of four: a TMEM lane quadrant is only visible to warp (id % 4). Three groups (12 epilogue warps, ring of
-// >= 6 slots) were measured: the residual 2c layers gained 7-12 %, most other layers lost 5-13 % (fewer pipeline stages
-// beside the larger ring, more warps per scheduler) — net zero, so two it stays.
-constexpr int kEpiWarps = 8;
-constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kThreads = (kCtrlWarps + kEpiWarps) * 32;
+// Epilogue warps come in groups of four (a TMEM lane quadrant is only visible to warp id % 4). Two groups are the
+// default; the residual 2c layers (1x1, K <= 512, staged epilogue with a residual to add) are bound by the latency of
+// the epilogue's own instruction stream with two warps per scheduler and run with three groups (7-12 % faster).
+// Three groups everywhere measured net zero: most layers lose 5-13 % to the larger ring / fewer pipeline stages.
+constexpr int kMaxEpiGroups = 3;
 // Shared memory map (after 1024-B alignment), all sizes per launch (ConvParams::n_stages / ring_slots / block_n):
 //   [0, n_stages * stage_bytes)      TMA->MMA pipeline, stage = {A 128x64 bf16 | B block_n x 64 bf16}
 //   [ring_off, + ring_slots * 16 KiB) epilogue ring. kEpiBf16 staged: 128x64 bf16 chunks in the 128B-swizzled TMA
@@ -225,11 +224,14 @@ __device__ __forceinline__ void epi_head16(const ConvParams& p, const float* __r
     if (n0 + j < p.n_valid) srow[n0 - tile_n0 + j] = f[j];
 }
 
-template <bool kPair>
-__global__ void __launch_bounds__(kThreads, 1)
+template <bool kPair, int kGroups>
+__global__ void __launch_bounds__((kCtrlWarps + 4 * kGroups) * 32, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                   const __grid_constant__ ConvParams p) {
+  constexpr int kEpiWarps = 4 * kGroups;
+  constexpr int kEpiThreads = kEpiWarps * 32;
+  constexpr int kThreads = (kCtrlWarps + kEpiWarps) * 32;
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment by OFFSET from the declared array, so the compiler still knows every derived pointer is
   // shared memory (round-tripping through uintptr_t turned all of them into generic LD.E / ST.E accesses)
@@ -456,7 +458,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         // ---- staged bf16 epilogue: accumulators (+bias, +residual, ReLU) -> ring slot -> TMA store
         for (int c = 0; c < n_chunks; ++c) {
           const uint32_t k = chunk_base + c;
-          if ((k & 1u) != static_cast<uint32_t>(g)) continue;
+          if (k % kGroups != static_cast<uint32_t>(g)) continue;
           const uint32_t s = k % R;
           const uint32_t ph = (k / R) & 1u;
           if (has_res) mbar_wait(&slot_full_bar[s], ph, kFaultSlotFull);
@@ -530,7 +532,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         // ---- direct bf16 epilogue: 32-column pieces alternate between the two groups
         int piece = 0;
         for (int c0 = 0; c0 < p.block_n; c0 += 32, ++piece) {
-          if ((piece & 1) != g) continue;
+          if (piece % kGroups != g) continue;
           if (p.block_n - c0 >= 32) {
             uint32_t v[32];
             tmem_ld_32x32(taddr + c0, v);
@@ -554,7 +556,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         float* srow = stile + static_cast<size_t>(row) * sstride;
         int piece = 0;
         for (int c0 = 0; c0 < p.block_n; c0 += 32, ++piece) {
-          if ((piece & 1) != g) continue;
+          if (piece % kGroups != g) continue;
           if (p.block_n - c0 >= 32) {
             uint32_t v[32];
             tmem_ld_32x32(taddr + c0, v);
@@ -683,7 +685,7 @@ int stage_bytes_of(const ConvParams& p) {
   return p.slab3 != 0 ? kSlabBytes + 3 * b_tile : kABytes + b_tile;
 }
 int ring_min_of(const ConvParams& p) {
-  if (p.epi == kEpiBf16) return p.staged ? 4 : 0;
+  if (p.epi == kEpiBf16) return p.staged ? 2 * (p.epi_groups == 3 ? 3 : 2) : 0;  // a group holds two slots
   return (kConvBlockM * (p.block_n | 1) * 4 + kConvBlockM * 8 + kChunkBytes - 1) / kChunkBytes;
 }
 }  // namespace
@@ -713,10 +715,16 @@ int conv_slab3_mode(const ConvParams& p) {
 int conv_plan_smem(ConvParams& p) {
   const int stage_bytes = stage_bytes_of(p);
   const int k_iters = (p.slab3 != 0 ? 3 : p.n_taps) * p.cin_blocks;
+  static const int groups_env = [] {
+    const char* e = getenv("PPB_EPI_GROUPS");  // 2: never three groups; 3: default rule
+    return e != nullptr ? atoi(e) : 3;
+  }();
+  p.epi_groups = (groups_env >= 3 && p.epi == kEpiBf16 && p.staged && p.residual != nullptr && k_iters <= 8 && !p.pair)
+                     ? 3 : 2;
   int ring_min = 0, ring_max = 0;
   if (p.epi == kEpiBf16) {
     if (p.staged) {
-      ring_min = 4;
+      ring_min = ring_min_of(p);
       ring_max = kMaxRing;
     }
   } else {
@@ -755,16 +763,19 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(conv_igemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    attr_err = cudaFuncSetAttribute(conv_igemm_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     if (attr_err == cudaSuccess)
-      attr_err = cudaFuncSetAttribute(conv_igemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+      attr_err = cudaFuncSetAttribute(conv_igemm_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(conv_igemm_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
   });
   if (attr_err != cudaSuccess) return attr_err;
   const int total = p.n_mtiles * p.n_ntiles;
   if (total <= 0) return cudaSuccess;
   ConvParams q = p;
   const int smem_bytes = conv_plan_smem(q);
-  if (smem_bytes < 0 || q.n_stages != p.n_stages || q.ring_slots != p.ring_slots) return cudaErrorInvalidConfiguration;
+  if (smem_bytes < 0 || q.n_stages != p.n_stages || q.ring_slots != p.ring_slots || q.epi_groups != p.epi_groups)
+    return cudaErrorInvalidConfiguration;
   int ctas = max_ctas > 0 ? max_ctas : conv_num_sms();
   if (ctas > total) ctas = total;
   if (p.pair) {
@@ -779,7 +790,7 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
   }();
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(ctas);
-  cfg.blockDim = dim3(kThreads);
+  cfg.blockDim = dim3((kCtrlWarps + 4 * p.epi_groups) * 32);
   cfg.dynamicSmemBytes = static_cast<size_t>(smem_bytes);
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
@@ -812,7 +823,7 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
         cudaLaunchConfig_t probe = cfg;
         probe.gridDim = dim3(conv_num_sms() & ~1);
         int n = 0;
-        if (cudaOccupancyMaxActiveClusters(&n, conv_igemm_kernel<true>, &probe) != cudaSuccess || n <= 0) {
+        if (cudaOccupancyMaxActiveClusters(&n, conv_igemm_kernel<true, 2>, &probe) != cudaSuccess || n <= 0) {
           cudaGetLastError();
           n = conv_num_sms() / 2;
         }
@@ -825,8 +836,10 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
     }
     if (ctas > 2 * max_clusters) cfg.gridDim = dim3(2 * max_clusters);
   }
-  const cudaError_t err = p.pair ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<true>, tmap_a, tmap_b, tmap_out, tmap_res, p)
-                                 : cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false>, tmap_a, tmap_b, tmap_out, tmap_res, p);
+  const cudaError_t err =
+      p.pair ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<true, 2>, tmap_a, tmap_b, tmap_out, tmap_res, p)
+             : (p.epi_groups == 3 ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false, 3>, tmap_a, tmap_b, tmap_out, tmap_res, p)
+                                  : cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false, 2>, tmap_a, tmap_b, tmap_out, tmap_res, p));
   if (err != cudaSuccess)
     fprintf(stderr, "conv_launch failed: %s (grid %u, smem %d, pair %d, attrs %d, block_n %d, m tiles %d, n tiles %d)\n",
             cudaGetErrorString(err), cfg.gridDim.x, smem_bytes, p.pair, na, p.block_n, p.n_mtiles, p.n_ntiles);

@@ -60,6 +60,7 @@ struct ConvParams {
                     // shared-memory address, so a row-shifted start reads the right data (tools/probe_shift.py). Cuts
                     // the A bytes an SM pulls from L2 by 3x. +1 / -1: the taps of a row ascend / descend (dgrad) in
                     // row offset; 0: off. Set by conv_slab3_mode().
+  int epi_groups;   // epilogue warp groups (2 or 3)     }
   int n_stages;     // TMA->MMA pipeline depth (2..8)   } filled by conv_plan_smem()
   int ring_slots;   // 16 KiB epilogue ring slots        }
   const float* bias;              // [n_valid] fp32, BatchNorm folded in; may be null

@@ -63,15 +63,16 @@ focal_loss_grad_kernel(const float* __restrict__ prob, const float* __restrict__
                        float gamma, const int* __restrict__ counts, int slot, double* __restrict__ loss) {
   const int vals = A * C;
   const int pairs = (vals + 1) >> 1;
-  const long long total = static_cast<long long>(batch) * g.locs * pairs;
+  // 32-bit index arithmetic (the launcher rejects 2^31 or more column pairs): four 64-bit divisions per thread were a
+  // large share of this kernel
+  const unsigned total = static_cast<unsigned>(batch) * static_cast<unsigned>(g.locs) * static_cast<unsigned>(pairs);
   const float inv_norm = 1.0f / fmaxf(1.0f, static_cast<float>(__ldg(counts + slot)));
   double local = 0.0;
-  for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total;
-       t += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int pr = static_cast<int>(t % pairs);
-    const long long bl = t / pairs;
-    const int loc = static_cast<int>(bl % g.locs);
-    const int b = static_cast<int>(bl / g.locs);
+  for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+    const unsigned bl = t / static_cast<unsigned>(pairs);
+    const int pr = static_cast<int>(t - bl * pairs);
+    const int b = static_cast<int>(bl / static_cast<unsigned>(g.locs));
+    const int loc = static_cast<int>(bl - static_cast<unsigned>(b) * g.locs);
     float gz[2] = {0.0f, 0.0f};
 #pragma unroll
     for (int e = 0; e < 2; ++e) {
@@ -386,6 +387,7 @@ cudaError_t launch_focal_loss_grad(const float* prob, const float* y_true, __nv_
                                    int batch, int A, int C, float alpha, float gamma, const int* counts, int slot,
                                    double* loss, cudaStream_t st) {
   const long long total = static_cast<long long>(batch) * g.locs * ((A * C + 1) / 2);
+  if (total >= (1ll << 31)) return cudaErrorInvalidValue;
   const unsigned blocks = static_cast<unsigned>(min(static_cast<long long>(148 * 16), (total + 255) / 256));
   focal_loss_grad_kernel<<<blocks, 256, 0, st>>>(prob, y_true, grad, ld, g, batch, A, C, alpha, gamma, counts, slot,
                                                  loss);
