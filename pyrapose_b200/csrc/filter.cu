@@ -101,9 +101,10 @@ __global__ void __launch_bounds__(256) class_max_kernel(const float* __restrict_
 // One warp, one slab row per lane: one LDS + compare + ballot per class (row stride C words: conflict-free for odd
 // C); lane c keeps the word of class c so that the C words leave in one store instruction. (Building a per-row bit
 // field first and transposing it afterwards measured slower: 30.0 vs 24.3 us at B=32, N=56700, C=15.)
+// cnt != nullptr: the population count of each class word is added to cnt[class] (shared or global memory).
 template <int CT>
 __device__ __forceinline__ void ballot_rows(const float* __restrict__ my, bool in_rows, int C, float thr,
-                                            uint32_t* __restrict__ dst, int W, int lane) {
+                                            uint32_t* __restrict__ dst, int W, int lane, int* cnt) {
   if constexpr (CT > 0) {  // class count known at compile time (15 / 21 / 30: LineMOD, YCB-V, T-LESS): the loop unrolls fully and
                  // the CT shared-memory loads are all in flight before the first ballot
     float v[CT];
@@ -115,7 +116,10 @@ __device__ __forceinline__ void ballot_rows(const float* __restrict__ my, bool i
       const uint32_t word = __ballot_sync(0xffffffffu, in_rows && v[c] > thr);
       if (lane == c) mine = word;
     }
-    if (lane < CT) dst[static_cast<long long>(lane) * W] = mine;
+    if (lane < CT) {
+      dst[static_cast<long long>(lane) * W] = mine;
+      if (cnt != nullptr && mine != 0u) atomicAdd(cnt + lane, __popc(mine));
+    }
   } else {
     for (int c0 = 0; c0 < C; c0 += 32) {
       uint32_t mine = 0u;
@@ -124,7 +128,10 @@ __device__ __forceinline__ void ballot_rows(const float* __restrict__ my, bool i
         const uint32_t word = __ballot_sync(0xffffffffu, in_rows && my[c0 + c] > thr);
         if (lane == c) mine = word;
       }
-      if (lane < cn) dst[static_cast<long long>(c0 + lane) * W] = mine;
+      if (lane < cn) {
+        dst[static_cast<long long>(c0 + lane) * W] = mine;
+        if (cnt != nullptr && mine != 0u) atomicAdd(cnt + c0 + lane, __popc(mine));
+      }
     }
   }
 }
@@ -139,9 +146,14 @@ __device__ __forceinline__ void ballot_rows(const float* __restrict__ my, bool i
 // one store instruction.
 template <int TILE, int CT>
 __global__ void __launch_bounds__(TILE) score_mask_kernel(const float* __restrict__ scores, int N, int C, float thr,
-                                                          uint32_t* __restrict__ mask, int W) {
+                                                          uint32_t* __restrict__ mask, int W,
+                                                          int* __restrict__ counts) {
   extern __shared__ __align__(128) float tile[];  // [TILE][C]
   __shared__ __align__(8) uint64_t bar;
+  // vote path: per-class hit counts of this block, flushed with one global atomic per class (counts is zeroed by the
+  // launcher); TILE = 32 blocks are a single warp and add straight to global memory
+  __shared__ int scnt[TILE > 32 ? 64 : 1];
+  if (TILE > 32 && counts != nullptr && threadIdx.x < 64) scnt[threadIdx.x] = 0;
   const int b = blockIdx.y;
   const int n0 = blockIdx.x * TILE;
   const int rows = min(TILE, N - n0);
@@ -181,10 +193,17 @@ __global__ void __launch_bounds__(TILE) score_mask_kernel(const float* __restric
   const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
   const int r = g * 32 + lane;
   const int widx = (n0 >> 5) + g;
-  if (widx >= W) return;
-  const bool in_rows = r < rows;
-  const float* my = tile + (in_rows ? r : 0) * C;
-  ballot_rows<CT>(my, in_rows, C, thr, mask + static_cast<long long>(b) * C * W + widx, W, lane);
+  int* cnt = counts == nullptr ? nullptr : (TILE > 32 ? scnt : counts + static_cast<long long>(b) * C);
+  if (widx < W) {
+    const bool in_rows = r < rows;
+    const float* my = tile + (in_rows ? r : 0) * C;
+    ballot_rows<CT>(my, in_rows, C, thr, mask + static_cast<long long>(b) * C * W + widx, W, lane, cnt);
+  }
+  if (TILE > 32 && counts != nullptr) {
+    __syncthreads();
+    if (threadIdx.x < C && scnt[threadIdx.x] != 0)
+      atomicAdd(counts + static_cast<long long>(b) * C + threadIdx.x, scnt[threadIdx.x]);
+  }
 }
 
 // Persistent form of the same pass for 16-byte aligned score tensors (every slab a legal bulk-copy source):
@@ -232,7 +251,7 @@ __global__ void __launch_bounds__(256) score_mask_stream_kernel(const float* __r
     if (widx < W) {
       const bool in_rows = r < rows;
       const float* my = ring + stage * stage_elems + (in_rows ? r : 0) * C;
-      ballot_rows<0>(my, in_rows, C, thr, mask + static_cast<long long>(b) * C * W + widx, W, lane);
+      ballot_rows<0>(my, in_rows, C, thr, mask + static_cast<long long>(b) * C * W + widx, W, lane, nullptr);
     }
     __syncthreads();  // every warp has finished reading this stage
     if (threadIdx.x == 0) {
@@ -244,18 +263,6 @@ __global__ void __launch_bounds__(256) score_mask_stream_kernel(const float* __r
       phase ^= 1u;
     }
   }
-}
-
-// ------------------------------------------------------------------ mask -> counts (vote path)
-__global__ void __launch_bounds__(256) mask_count_kernel(const uint32_t* __restrict__ mask, int W,
-                                                         int* __restrict__ counts) {
-  __shared__ int warp_sums[32];
-  const uint32_t* words = mask + static_cast<long long>(blockIdx.x) * W;
-  int c = 0;
-  for (int i = threadIdx.x; i < W; i += 256) c += __popc(words[i]);
-  int total;
-  block_exclusive_scan(c, warp_sums, total);
-  if (threadIdx.x == 0) counts[blockIdx.x] = total;
 }
 
 // ------------------------------------------------------------------ mask -> sorted-key candidates
@@ -673,13 +680,16 @@ FilterWorkspace carve(void* base, int B, int N, int C, int class_specific, int m
   return w;
 }
 
-int launch_score_mask(const float* scores, int B, int N, int C, float thr, uint32_t* mask, cudaStream_t st) {
+// counts != nullptr (vote path): int [B][C] hit counts, produced by the same pass (zeroed here first).
+int launch_score_mask(const float* scores, int B, int N, int C, float thr, uint32_t* mask, int* counts,
+                      cudaStream_t st) {
   const int W = (N + 31) / 32;
+  if (counts != nullptr) PPB_CUDA(cudaMemsetAsync(counts, 0, static_cast<size_t>(B) * C * sizeof(int), st));
   static const int stream_mode = [] {
     const char* e = getenv("PPB_MASK_STREAM");  // 0: one block per tile; N > 0: persistent, N blocks per SM
     return e != nullptr ? atoi(e) : 0;
   }();
-  if (stream_mode > 0 && C <= 44 && (reinterpret_cast<uintptr_t>(scores) & 15) == 0 &&
+  if (stream_mode > 0 && counts == nullptr && C <= 44 && (reinterpret_cast<uintptr_t>(scores) & 15) == 0 &&
       ((static_cast<long long>(N) * C) & 3) == 0) {
     static int sms = 0;
     if (sms == 0) {
@@ -701,13 +711,13 @@ int launch_score_mask(const float* scores, int B, int N, int C, float thr, uint3
   } else if (C <= 44) {
     const dim3 grid((N + 255) / 256, B);
     const size_t smem = 256 * static_cast<size_t>(C) * 4;
-    if (C == 15) score_mask_kernel<256, 15><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W);
-    else if (C == 21) score_mask_kernel<256, 21><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W);
-    else if (C == 30) score_mask_kernel<256, 30><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W);
-    else score_mask_kernel<256, 0><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W);
+    if (C == 15) score_mask_kernel<256, 15><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W, counts);
+    else if (C == 21) score_mask_kernel<256, 21><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W, counts);
+    else if (C == 30) score_mask_kernel<256, 30><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W, counts);
+    else score_mask_kernel<256, 0><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W, counts);
   } else {
     PPB_REQUIRE(C <= 352, "score mask: at most 352 classes are supported, got %d", C);
-    score_mask_kernel<32, 0><<<dim3((N + 31) / 32, B), 32, 32 * C * 4, st>>>(scores, N, C, thr, mask, W);
+    score_mask_kernel<32, 0><<<dim3((N + 31) / 32, B), 32, 32 * C * 4, st>>>(scores, N, C, thr, mask, W, counts);
   }
   PPB_CUDA(cudaGetLastError());
   count_launch();
@@ -760,7 +770,7 @@ int ppb_filter_detections(const float* boxes, const float* boxes3D, const float*
     score_src = w.smax;
     score_stride = 1;
   }
-  int rc = launch_score_mask(score_src, batch, n, Ceff, score_threshold, w.mask, st);
+  int rc = launch_score_mask(score_src, batch, n, Ceff, score_threshold, w.mask, nullptr, st);
   if (rc != kOk) return rc;
   compact_keys_kernel<<<dim3(Ceff, batch), 256, 0, st>>>(w.mask, score_src, n, Ceff, W, score_stride, cap, w.keys,
                                                          w.counts);
@@ -820,14 +830,7 @@ int ppb_score_mask(const float* scores, int batch, int n, int num_classes, float
   if (batch == 0) return kOk;
   PPB_REQUIRE(scores != nullptr && mask != nullptr, "ppb_score_mask: null buffer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  int rc = launch_score_mask(scores, batch, n, num_classes, threshold, mask, st);
-  if (rc != kOk) return rc;
-  if (counts != nullptr) {
-    mask_count_kernel<<<batch * num_classes, 256, 0, st>>>(mask, (n + 31) / 32, counts);
-    PPB_CUDA(cudaGetLastError());
-    count_launch();
-  }
-  return kOk;
+  return launch_score_mask(scores, batch, n, num_classes, threshold, mask, counts, st);
 }
 
 /* Vote filter, step 2: ascending hit indices and their 16-vectors in CSR order given by `offsets`

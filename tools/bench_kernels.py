@@ -115,7 +115,7 @@ for tag, mu in (("sparse 2%", -6.0), ("dense 13%", -4.6)):
           note="GB/s counts only the score read; NMS/top-k are latency-bound")
     sc05 = sc
     timed("vote filter thr=0.5 [%s]" % tag, lambda: _kernels.score_mask(sc05, 0.5), B * N * C * 4,
-          note="mask + per-class counts (2 launches)", peak=PEAK_READ,
+          note="mask + per-class counts in one pass (memset + 1 launch)", peak=PEAK_READ,
           train=[(lambda x=x: _kernels.score_mask(x, 0.5)) for x in sc_set])
     del sc_set
 # ---- IoU (config 3): B=64 images, K=100 GT boxes, float64
