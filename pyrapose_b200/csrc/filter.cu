@@ -206,65 +206,6 @@ __global__ void __launch_bounds__(TILE) score_mask_kernel(const float* __restric
   }
 }
 
-// Persistent form of the same pass for 16-byte aligned score tensors (every slab a legal bulk-copy source):
-// grid = SMs x resident blocks, each block walks tiles blockIdx.x, +gridDim.x, ... with a kMaskStages-deep ring of
-// slabs in shared memory. One thread keeps kMaskStages bulk copies in flight (completion on one mbarrier per stage),
-// so the HBM stream never drains between tiles and no block launch / teardown sits on the critical path.
-constexpr int kMaskStages = 4;
-
-__global__ void __launch_bounds__(256) score_mask_stream_kernel(const float* __restrict__ scores, int N, int C,
-                                                                float thr, uint32_t* __restrict__ mask, int W,
-                                                                int tiles_per_image, int total_tiles) {
-  extern __shared__ __align__(128) float ring[];  // [kMaskStages][256][C]
-  __shared__ __align__(8) uint64_t full[kMaskStages];
-  const int stage_elems = 256 * C;
-  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
-  auto issue = [&](int tile, int stage) {
-    const int b = tile / tiles_per_image;
-    const int n0 = (tile - b * tiles_per_image) * 256;
-    const uint32_t bytes = static_cast<uint32_t>(min(256, N - n0) * C) * 4u;
-    const float* src = scores + (static_cast<long long>(b) * N + n0) * C;
-    mbar_arrive_expect_tx(&full[stage], bytes);
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(ring + stage * stage_elems)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(&full[stage]))
-                 : "memory");
-  };
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < kMaskStages; ++i) mbar_init(&full[i], 1);
-    fence_mbar_init();
-    for (int i = 0; i < kMaskStages; ++i) {
-      const int tile = blockIdx.x + i * gridDim.x;
-      if (tile < total_tiles) issue(tile, i);
-    }
-  }
-  __syncthreads();
-  int stage = 0;
-  uint32_t phase = 0;
-  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-    const int b = tile / tiles_per_image;
-    const int n0 = (tile - b * tiles_per_image) * 256;
-    const int rows = min(256, N - n0);
-    mbar_wait(&full[stage], phase, 0x52u);
-    const int r = g * 32 + lane;
-    const int widx = (n0 >> 5) + g;
-    if (widx < W) {
-      const bool in_rows = r < rows;
-      const float* my = ring + stage * stage_elems + (in_rows ? r : 0) * C;
-      ballot_rows<0>(my, in_rows, C, thr, mask + static_cast<long long>(b) * C * W + widx, W, lane, nullptr);
-    }
-    __syncthreads();  // every warp has finished reading this stage
-    if (threadIdx.x == 0) {
-      const int next = tile + kMaskStages * gridDim.x;
-      if (next < total_tiles) issue(next, stage);
-    }
-    if (++stage == kMaskStages) {
-      stage = 0;
-      phase ^= 1u;
-    }
-  }
-}
-
 // ------------------------------------------------------------------ mask -> sorted-key candidates
 // grid (C, B). keys segment of (b,c) starts at (b*C+c)*cap. scores index: (b*N + n)*score_stride + c*class_step.
 __global__ void __launch_bounds__(256) compact_keys_kernel(const uint32_t* __restrict__ mask,
@@ -513,11 +454,15 @@ __global__ void __launch_bounds__(NT) nms_kernel(const uint64_t* __restrict__ ke
           const uint32_t intra = supp[cd][sb];
           uint32_t rem = __ballot_sync(0xffffffffu, a);
           uint32_t kept = 0u;
-          while (rem) {  // warp-uniform loop over the still-alive candidates in score order
-            const int li = __ffs(rem) - 1;
-            rem &= rem - 1;
-            const uint32_t wsup = __shfl_sync(0xffffffffu, intra, li);
-            if ((wsup & kept) == 0u) kept |= 1u << li;
+          if (!__any_sync(0xffffffffu, a && (intra & rem) != 0u)) {
+            kept = rem;  // no alive member of this group overlaps an alive earlier one: all of them are kept
+          } else {
+            while (rem) {  // warp-uniform loop over the still-alive candidates in score order
+              const int li = __ffs(rem) - 1;
+              rem &= rem - 1;
+              const uint32_t wsup = __shfl_sync(0xffffffffu, intra, li);
+              if ((wsup & kept) == 0u) kept |= 1u << li;
+            }
           }
           kept_w[sb] = kept;
           if ((kept >> lane) & 1u) {
@@ -685,30 +630,7 @@ int launch_score_mask(const float* scores, int B, int N, int C, float thr, uint3
                       cudaStream_t st) {
   const int W = (N + 31) / 32;
   if (counts != nullptr) PPB_CUDA(cudaMemsetAsync(counts, 0, static_cast<size_t>(B) * C * sizeof(int), st));
-  static const int stream_mode = [] {
-    const char* e = getenv("PPB_MASK_STREAM");  // 0: one block per tile; N > 0: persistent, N blocks per SM
-    return e != nullptr ? atoi(e) : 0;
-  }();
-  if (stream_mode > 0 && counts == nullptr && C <= 44 && (reinterpret_cast<uintptr_t>(scores) & 15) == 0 &&
-      ((static_cast<long long>(N) * C) & 3) == 0) {
-    static int sms = 0;
-    if (sms == 0) {
-      int dev = 0;
-      PPB_CUDA(cudaGetDevice(&dev));
-      PPB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    }
-    // per device and idempotent; not a stream operation, so it is legal during graph capture
-    PPB_CUDA(cudaFuncSetAttribute(score_mask_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  kMaskStages * 256 * 44 * 4));
-    const int smem = kMaskStages * 256 * C * 4;
-    const int per_sm = max(1, min(stream_mode, (200 * 1024) / smem));
-    const int tiles_per_image = (N + 255) / 256;
-    const long long total = static_cast<long long>(tiles_per_image) * B;
-    PPB_REQUIRE(total < (1ll << 31), "score mask: too many tiles");
-    const int grid = static_cast<int>(min(static_cast<long long>(sms) * per_sm, total));
-    score_mask_stream_kernel<<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W, tiles_per_image,
-                                                      static_cast<int>(total));
-  } else if (C <= 44) {
+  if (C <= 44) {
     const dim3 grid((N + 255) / 256, B);
     const size_t smem = 256 * static_cast<size_t>(C) * 4;
     if (C == 15) score_mask_kernel<256, 15><<<grid, 256, smem, st>>>(scores, N, C, thr, mask, W, counts);
