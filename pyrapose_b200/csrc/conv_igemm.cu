@@ -25,6 +25,8 @@ constexpr int kMaxStages = 8;
 constexpr int kMaxRing = 8;
 constexpr int kABytes = kConvBlockM * kConvBlockK * 2;  // 16 KiB
 constexpr int kSlabBytes = kConvSlabRows * kConvBlockK * 2;  // 17 KiB: 136 rows x 128 B
+constexpr int kStemSlabTx = kConvSlabRows * 32;               // stem slab: 136 pixels x 32 B actually transferred ...
+constexpr int kStemSlabBytes = 5 * 1024;                      // ... in a 5 KiB slot so the B tiles stay 1024-B aligned
 constexpr int kTmemCols = 512;
 constexpr int kAccCols = 256;
 constexpr int kCtrlWarps = 4;
@@ -245,10 +247,15 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const int b_rows = pair ? (p.block_n >> 1) : p.block_n;
   // slab mode (ConvParams::slab3): a stage holds one 136-row A slab and the B tiles of the three taps of a filter row
   const int taps_per_stage = p.slab3 != 0 ? 3 : 1;
-  const int a_bytes = p.slab3 != 0 ? kSlabBytes : kABytes;
-  const int b_tile_bytes = b_rows * (kConvBlockK * 2);
-  const int stage_bytes = a_bytes + taps_per_stage * b_tile_bytes;
-  uint8_t* ring = smem + n_stages * stage_bytes;
+  const bool stem16 = p.stem16 != 0;  // see ConvParams::stem16: four K = 16 column taps per stage, 32-byte rows
+  const int a_bytes = stem16 ? kStemSlabBytes : (p.slab3 != 0 ? kSlabBytes : kABytes);
+  const int b_tile_bytes = stem16 ? b_rows * 32 : b_rows * (kConvBlockK * 2);
+  const int stage_bytes = stem16 ? a_bytes : a_bytes + taps_per_stage * b_tile_bytes;
+  // stem16: the whole weight matrix (16 (dy, dx) tiles of block_n x 16) is loaded ONCE and stays resident after the
+  // pipeline stages, which then carry A slabs only (one TMA request per k-iteration instead of five)
+  uint8_t* b_res = smem + n_stages * stage_bytes;
+  const int b_res_bytes = stem16 ? 16 * b_tile_bytes : 0;
+  uint8_t* ring = b_res + b_res_bytes;
   float* sbias = reinterpret_cast<float*>(ring + p.ring_slots * kChunkBytes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sbias) + kBiasFloats * 4);
   uint64_t* full_bar = bars;
@@ -258,6 +265,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   uint64_t* slot_full_bar = bars + 2 * kMaxStages + 4;
   uint64_t* slot_empty_bar = slot_full_bar + kMaxRing;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(slot_empty_bar + kMaxRing);
+  uint64_t* bres_bar = slot_empty_bar + kMaxRing + 1;  // stem16: resident weights have landed
   const bool staged = p.staged != 0;
   const bool has_res = p.residual != nullptr;
 
@@ -287,6 +295,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         mbar_init(&slot_full_bar[i], 1);
         mbar_init(&slot_empty_bar[i], 1);
       }
+      mbar_init(bres_bar, 1);
       fence_mbar_init();
     }
   } else if (warp == 2) {
@@ -341,7 +350,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      const uint32_t tx_bytes = static_cast<uint32_t>(pair ? 2 * stage_bytes : stage_bytes);
+      const uint32_t tx_bytes = stem16 ? static_cast<uint32_t>(kStemSlabTx)
+                                       : static_cast<uint32_t>(pair ? 2 * stage_bytes : stage_bytes);
+      if (stem16 && it_begin < it_end) {  // resident weights: tile (dy, dx) = K columns dy*64 + dx*16 .. +16
+        mbar_arrive_expect_tx(bres_bar, static_cast<uint32_t>(b_res_bytes));
+        for (int j = 0; j < 16; ++j)
+          tma_load_2d(b_res + j * b_tile_bytes, &tmap_b, p.b_col_base + j * 16, 0, bres_bar);
+      }
       for (int it = it_begin; it < it_end; it += it_step) {
         const TileCoord tc = tile_coord(p, tile_of(it));
         const ConvSeg& sg = p.seg[tc.seg];
@@ -358,6 +373,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               for (int j = 0; j < taps_per_stage; ++j)
                 tma_load_2d_pair(sa + a_bytes + j * b_tile_bytes, &tmap_b,
                                  p.b_col_base + ((tap + j) * p.cin_blocks + kb) * kConvBlockK, b_row, &full_bar[stage]);
+            } else if (stem16) {
+              mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+              tma_load_2d(sa, &tmap_a, 0, a_row, &full_bar[stage]);
             } else {
               mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
               tma_load_2d(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
@@ -381,6 +399,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       int acc = 0;
       uint32_t acc_phase = 0;
       const uint32_t idesc = umma_idesc_bf16(pair ? 2 * kConvBlockM : kConvBlockM, p.block_n);
+      if (stem16 && it_begin < it_end) mbar_wait(bres_bar, 0, kFaultFull);
       for (int it = it_begin; it < it_end; it += it_step) {
         mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1, kFaultTmemEmpty);
         tc_fence_after();
@@ -390,7 +409,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
           const uint32_t b_addr = a_addr + a_bytes;
-          for (int j = 0; j < taps_per_stage; ++j) {
+          if (stem16) {  // never a pair: four K = 16 MMAs, pixel-shifted A descriptors
+#pragma unroll
+            for (int j = 0; j < 4; ++j)  // ki = filter row dy, j = column tap dx
+              tc_mma_bf16(d_tmem, umma_desc_k32(a_addr + j * 32),
+                          umma_desc_k32(smem_u32(b_res) + (ki * 4 + j) * b_tile_bytes), idesc, (ki | j) != 0 ? 1u : 0u);
+          }
+          for (int j = 0; j < (stem16 ? 0 : taps_per_stage); ++j) {
             // slab mode: tap j of the filter row reads the slab from row j (ascending taps) or 2 - j (descending)
             const uint32_t a_tap = a_addr + (p.slab3 == 0 ? 0u : (p.slab3 > 0 ? j : 2 - j) * 128u);
             const uint32_t b_tap = b_addr + j * b_tile_bytes;
@@ -626,16 +651,17 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-int encode_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems, uint32_t box_rows) {
+int encode_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems, uint32_t box_rows,
+              uint32_t box_cols = kConvBlockK, bool swizzle32 = false) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (fn == nullptr) return -1;
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {ld_elems * 2};
-  cuuint32_t box[2] = {static_cast<cuuint32_t>(kConvBlockK), box_rows};
+  cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? 0 : -static_cast<int>(r) - 1000;
 }
 
@@ -654,6 +680,13 @@ int conv_encode_tmaps(CUtensorMap* tmap_a, CUtensorMap* tmap_b, const void* a, l
   int rc = encode_2d(tmap_a, a, static_cast<uint64_t>(a_rows), a_cols, a_ld, static_cast<uint32_t>(a_box_rows));
   if (rc != 0) return rc;
   return encode_2d(tmap_b, w, w_rows, w_cols, w_cols, block_n);
+}
+
+int conv_encode_stem_tmaps(CUtensorMap* tmap_a, CUtensorMap* tmap_b, const void* a, long a_rows, const void* w,
+                           int w_rows, int w_cols, int block_n) {
+  int rc = encode_2d(tmap_a, a, static_cast<uint64_t>(a_rows), 16, 16, kConvSlabRows, 16, true);
+  if (rc != 0) return rc;
+  return encode_2d(tmap_b, w, w_rows, w_cols, w_cols, static_cast<uint32_t>(block_n), 16, true);
 }
 
 int conv_num_sms() {
@@ -681,6 +714,7 @@ bool conv_pair_ok(const ConvParams& p) {
 
 namespace {
 int stage_bytes_of(const ConvParams& p) {
+  if (p.stem16) return kStemSlabBytes;  // A slab only; the weights are resident (stem_resident_bytes)
   const int b_tile = (p.pair ? p.block_n / 2 : p.block_n) * (kConvBlockK * 2);
   return p.slab3 != 0 ? kSlabBytes + 3 * b_tile : kABytes + b_tile;
 }
@@ -740,17 +774,22 @@ int conv_plan_smem(ConvParams& p) {
   // pipeline stages are enough to hide the operand latency of <= 8 k-iterations; the rest of shared memory goes to the
   // ring (measured: res4*_branch2c 73.8 -> 53.3 us, res3*_branch2c 88 -> 82 us; layers without a residual get slower).
   if (p.epi == kEpiBf16 && p.staged && p.residual != nullptr && k_iters <= 8 && stages > 3) stages = 3;
-  while (stages > 2 && stages * stage_bytes + ring_min * kChunkBytes > kSmemBudget) --stages;
-  if (stages * stage_bytes + ring_min * kChunkBytes > kSmemBudget) return -1;
+  // stem16: the resident weight tiles (16 x block_n x 32 B) sit between the stages and the ring; with 5 KB stages the
+  // producer may as well run two tiles ahead
+  const int resident = p.stem16 ? 16 * p.block_n * 32 : 0;
+  if (p.stem16) stages = kMaxStages;
+  const int budget = kSmemBudget - resident;
+  while (stages > 2 && stages * stage_bytes + ring_min * kChunkBytes > budget) --stages;
+  if (stages * stage_bytes + ring_min * kChunkBytes > budget) return -1;
   // keep at least three pipeline stages for deep K loops, give the rest to the ring
-  int ring = (kSmemBudget - stages * stage_bytes) / kChunkBytes;
+  int ring = (budget - stages * stage_bytes) / kChunkBytes;
   if (ring > ring_max) ring = ring_max;
   if (p.epi == kEpiBf16 && p.staged) ring &= ~1;
   if (ring < ring_min) return -1;
   if (p.n_ntiles * p.block_n > kBiasFloats) return -1;
   p.n_stages = stages;
   p.ring_slots = ring;
-  return stages * stage_bytes + ring * kChunkBytes + kBiasFloats * 4 + kBarBytes + 1024;
+  return stages * stage_bytes + resident + ring * kChunkBytes + kBiasFloats * 4 + kBarBytes + 1024;
 }
 
 cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap& tmap_out,

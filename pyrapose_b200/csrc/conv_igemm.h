@@ -60,6 +60,10 @@ struct ConvParams {
                     // shared-memory address, so a row-shifted start reads the right data (tools/probe_shift.py). Cuts
                     // the A bytes an SM pulls from L2 by 3x. +1 / -1: the taps of a row ascend / descend (dgrad) in
                     // row offset; 0: off. Set by conv_slab3_mode().
+  int stem16;       // stem (7x7/2 over the space-to-depth grid, 16 channels per pixel): a stage = one filter row dy; the A
+                    // operand is ONE slab of 136 pixels x 16 channels (32-byte rows, 32B swizzle) and the four column
+                    // taps dx are four K = 16 MMAs whose descriptors start dx pixels (dx x 32 B) into it, instead of four
+                    // overlapping 128-byte rows per pixel (4x the L2 traffic). Maps from conv_encode_stem_tmaps().
   int epi_groups;   // epilogue warp groups (2 or 3)     }
   int n_stages;     // TMA->MMA pipeline depth (2..8)   } filled by conv_plan_smem()
   int ring_slots;   // 16 KiB epilogue ring slots        }
@@ -84,6 +88,11 @@ struct ConvParams {
 // (bf16, row stride a_ld elements); w is [w_rows, w_cols] bf16 row-major (Cout_pad x taps*Cin).
 int conv_encode_tmaps(CUtensorMap* tmap_a, CUtensorMap* tmap_b, const void* a, long a_rows, int a_cols, int a_ld,
                       const void* w, int w_rows, int w_cols, int block_n, int a_box_rows = kConvBlockM);
+
+// Stem maps: A = the space-to-depth pixel matrix [a_rows][16] (row stride 16 elements), box {16 x 136}; B = the
+// [cout_pad][256] weight matrix, box {16 x block_n}; both 32B-swizzled.
+int conv_encode_stem_tmaps(CUtensorMap* tmap_a, CUtensorMap* tmap_b, const void* a, long a_rows, const void* w,
+                           int w_rows, int w_cols, int block_n);
 
 constexpr int kConvSlabRows = 136;  // 128 + 2 rows of halo, rounded up to whole 8-row swizzle atoms
 

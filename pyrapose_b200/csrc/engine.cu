@@ -174,6 +174,11 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
   p.staged = (l.cout % 64 == 0 && p.block_n % 64 == 0 &&
               (staged_epilogue >= 2 || (staged_epilogue == 1 && res != nullptr))) ? 1 : 0;
   p.slab3 = conv_slab3_mode(p);
+  if (l.ksize == 7 && stem16 && l.k_total == 256 && (p.block_n & 7) == 0) {
+    p.stem16 = 1;
+    p.pair = 0;
+    p.slab3 = 0;
+  }
   bool force_direct = false;
   if (p.slab3 == 0 && p.staged && res == nullptr) {
     // a 256-wide pair tile in slab mode leaves no room for the epilogue ring: without a residual to prefetch the
@@ -183,8 +188,9 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
     force_direct = p.slab3 != 0;
     if (!force_direct) p.staged = 1;
   }
-  int rc = conv_encode_tmaps(&op.ta, &op.tb, x->ptr, a_rows, a_cols, a_ld, l.w, l.cout_pad, l.k_total,
-                             p.pair ? p.block_n / 2 : p.block_n, p.slab3 ? kConvSlabRows : kConvBlockM);
+  int rc = p.stem16 ? conv_encode_stem_tmaps(&op.ta, &op.tb, x->ptr, a_rows, l.w, l.cout_pad, l.k_total, p.block_n)
+                    : conv_encode_tmaps(&op.ta, &op.tb, x->ptr, a_rows, a_cols, a_ld, l.w, l.cout_pad, l.k_total,
+                                        p.pair ? p.block_n / 2 : p.block_n, p.slab3 ? kConvSlabRows : kConvBlockM);
   if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled failed for layer '%s' (%d)", l.name.c_str(), rc);
   memset(&op.to, 0, sizeof(op.to));
   memset(&op.tr, 0, sizeof(op.tr));
@@ -551,6 +557,7 @@ int ppb_engine_create(ppb_engine** out, int device, int max_batch, int height, i
   memset(e.base_anchor, 0, sizeof(e.base_anchor));
   memset(e.stride, 0, sizeof(e.stride));
   if (const char* env = getenv("PPB_STAGED_EPILOGUE")) e.staged_epilogue = atoi(env);
+  if (const char* env = getenv("PPB_STEM16")) e.stem16 = atoi(env) != 0;
   e.define_layers();
   int rc = e.allocate_weights();
   if (rc != kOk) return rc;

@@ -97,6 +97,7 @@ struct Engine {
   // with a residual input; 2 every backbone / PFPN conv (measured best, profiles/r01_per_op_staged_variants.txt);
   // 3 head towers too. Override with PPB_STAGED_EPILOGUE for experiments.
   int staged_epilogue = 2;
+  bool stem16 = true;  // stem convolution in pixel-slab mode (ConvParams::stem16); PPB_STEM16=0 turns it off
   // training step (train.cu): every head-tower activation keeps its own buffer so the backward pass can read it
   // input staging: images bound as raw uint8 BGR with the 'caffe' mean subtraction fused into the stem loader
   bool input_u8 = false;

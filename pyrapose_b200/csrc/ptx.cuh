@@ -257,6 +257,16 @@ __device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr) {
   d |= static_cast<uint64_t>(2) << 61;
   return d;
 }
+// K-major bf16 tile whose rows are 16 elements (32 B) wide, written by TMA with CU_TENSOR_MAP_SWIZZLE_32B: 8-row atoms
+// of 256 B, packed densely (layout type 6 = SWIZZLE_32B, stride-dim offset 256 B).
+__device__ __forceinline__ uint64_t umma_desc_k32(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>(256 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(6) << 61;
+  return d;
+}
 // MN-major operand (the contiguous dimension is M or N, rows of the shared-memory tile are K): tiles written by TMA
 // as [K rows][64 elements = 128 B] boxes with CU_TENSOR_MAP_SWIZZLE_128B. Canonical layout (CUTLASS "MN-major,
 // SW128"): ((8,8,m),(8,k)) : ((1,8,LBO),(64,SBO)) elements, i.e. LBO = byte distance between 64-element MN blocks
