@@ -58,8 +58,13 @@ struct TileCoord {
   int n0;
 };
 
+__device__ __forceinline__ uint32_t fastdiv(uint32_t n, uint32_t mul, uint32_t sh) {
+  const uint32_t t = __umulhi(mul, n);
+  return (t + ((n - t) >> (sh & 255u))) >> (sh >> 8);
+}
+
 __device__ __forceinline__ TileCoord tile_coord(const ConvParams& p, int tile) {
-  const int m_tile = tile / p.n_ntiles;
+  const int m_tile = static_cast<int>(fastdiv(static_cast<uint32_t>(tile), p.nt_mul, p.nt_sh));
   const int n_tile = tile - m_tile * p.n_ntiles;
   int s = 0;
   if (p.n_segs > 1 && m_tile >= p.seg[1].tile_begin) s = 1;
@@ -90,14 +95,109 @@ __device__ __forceinline__ RowInfo row_info(const ConvSeg& sg, int m) {
   const int local = m - sg.row_begin;
   r.in_buf = local < sg.rows;
   const int plane = sg.hp * sg.wp;
-  r.b = local / plane;
+  r.b = static_cast<int>(fastdiv(static_cast<uint32_t>(local), sg.plane_mul, sg.plane_sh));  // local >= 0
   const int rem = local - r.b * plane;
-  const int hy = rem / sg.wp;
+  const int hy = static_cast<int>(fastdiv(static_cast<uint32_t>(rem), sg.wp_mul, sg.wp_sh));
   const int wx = rem - hy * sg.wp;
   r.y = hy - sg.pad_lo;
   r.x = wx - sg.pad_lo;
   r.interior = r.in_buf && hy >= sg.pad_lo && hy < sg.hp - sg.pad_hi && wx >= sg.pad_lo && wx < sg.wp - sg.pad_hi;
   return r;
+}
+
+// Staged epilogue, one row of one 64-column chunk: accumulators + bias (+ residual already sitting in the ring slot)
+// (ReLU) -> bf16 -> the row's 128 bytes of the slot, 128B-swizzled for the TMA store. The layer's switches are template
+// parameters so the 8 x 16-byte pieces carry no uniform branches (they were a third of the epilogue's instructions);
+// border rows compute like any other and select zeros at the end.
+// Two fp32 additions in one instruction (sm_100 packed fp32): (a0, a1) += (b0, b1).
+__device__ __forceinline__ void add2(float& a0, float& a1, float b0, float b1) {
+  asm("{\n\t.reg .b64 ra, rb;\n\tmov.b64 ra, {%0, %1};\n\tmov.b64 rb, {%2, %3};\n\tadd.rn.f32x2 ra, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, ra;\n\t}"
+      : "+f"(a0), "+f"(a1)
+      : "f"(b0), "f"(b1));
+}
+
+template <bool kRes, bool kRelu>
+__device__ __forceinline__ void staged_chunk_row(const uint32_t (&v)[64], const float* __restrict__ bsrc, uint8_t* rowp,
+                                                 int row, bool interior) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    uint4* sp = reinterpret_cast<uint4*>(rowp + ((j ^ (row & 7)) << 4));  // 128B swizzle: 16-B piece j of the row
+    const float4 b0 = *reinterpret_cast<const float4*>(bsrc + j * 8);
+    const float4 b1 = *reinterpret_cast<const float4*>(bsrc + j * 8 + 4);
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j * 8 + e]);
+    add2(f[0], f[1], b0.x, b0.y);
+    add2(f[2], f[3], b0.z, b0.w);
+    add2(f[4], f[5], b1.x, b1.y);
+    add2(f[6], f[7], b1.z, b1.w);
+    if (kRes) {
+      const uint4 r = *sp;
+      add2(f[0], f[1], bf16_lo(r.x), bf16_hi(r.x));
+      add2(f[2], f[3], bf16_lo(r.y), bf16_hi(r.y));
+      add2(f[4], f[5], bf16_lo(r.z), bf16_hi(r.z));
+      add2(f[6], f[7], bf16_lo(r.w), bf16_hi(r.w));
+    }
+    if (kRelu) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.0f);
+    }
+    uint4 o;
+    o.x = interior ? pack_bf16x2(f[0], f[1]) : 0u;
+    o.y = interior ? pack_bf16x2(f[2], f[3]) : 0u;
+    o.z = interior ? pack_bf16x2(f[4], f[5]) : 0u;
+    o.w = interior ? pack_bf16x2(f[6], f[7]) : 0u;
+    *sp = o;  // border rows and rows past the segment end are stored as zeros
+  }
+}
+
+// The same with the ReLU-backward mask (dgrad): the result is zeroed where the forward activation was <= 0.
+__device__ __forceinline__ void staged_chunk_row_masked(const ConvParams& p, const uint32_t (&v)[64],
+                                                        const float* __restrict__ bsrc, uint8_t* rowp, int row,
+                                                        bool interior, bool has_res,
+                                                        const __nv_bfloat16* __restrict__ mask_row) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    uint4* sp = reinterpret_cast<uint4*>(rowp + ((j ^ (row & 7)) << 4));
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (interior) {
+      const float4 b0 = *reinterpret_cast<const float4*>(bsrc + j * 8);
+      const float4 b1 = *reinterpret_cast<const float4*>(bsrc + j * 8 + 4);
+      float f[8];
+      f[0] = __uint_as_float(v[j * 8 + 0]) + b0.x;
+      f[1] = __uint_as_float(v[j * 8 + 1]) + b0.y;
+      f[2] = __uint_as_float(v[j * 8 + 2]) + b0.z;
+      f[3] = __uint_as_float(v[j * 8 + 3]) + b0.w;
+      f[4] = __uint_as_float(v[j * 8 + 4]) + b1.x;
+      f[5] = __uint_as_float(v[j * 8 + 5]) + b1.y;
+      f[6] = __uint_as_float(v[j * 8 + 6]) + b1.z;
+      f[7] = __uint_as_float(v[j * 8 + 7]) + b1.w;
+      if (has_res) {
+        const uint4 r = *sp;
+        f[0] += bf16_lo(r.x); f[1] += bf16_hi(r.x); f[2] += bf16_lo(r.y); f[3] += bf16_hi(r.y);
+        f[4] += bf16_lo(r.z); f[5] += bf16_hi(r.z); f[6] += bf16_lo(r.w); f[7] += bf16_hi(r.w);
+      }
+      if (p.relu) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.0f);
+      }
+      const uint4 r = __ldg(reinterpret_cast<const uint4*>(mask_row + j * 8));
+      if (!(bf16_lo(r.x) > 0.0f)) f[0] = 0.0f;
+      if (!(bf16_hi(r.x) > 0.0f)) f[1] = 0.0f;
+      if (!(bf16_lo(r.y) > 0.0f)) f[2] = 0.0f;
+      if (!(bf16_hi(r.y) > 0.0f)) f[3] = 0.0f;
+      if (!(bf16_lo(r.z) > 0.0f)) f[4] = 0.0f;
+      if (!(bf16_hi(r.z) > 0.0f)) f[5] = 0.0f;
+      if (!(bf16_lo(r.w) > 0.0f)) f[6] = 0.0f;
+      if (!(bf16_hi(r.w) > 0.0f)) f[7] = 0.0f;
+      o.x = pack_bf16x2(f[0], f[1]);
+      o.y = pack_bf16x2(f[2], f[3]);
+      o.z = pack_bf16x2(f[4], f[5]);
+      o.w = pack_bf16x2(f[6], f[7]);
+    }
+    *sp = o;
+  }
 }
 
 // bf16 epilogue for NC (16 or 32) accumulator columns of one row, straight to global memory.
@@ -333,7 +433,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const int it_end = pair ? ((p.n_mtiles + 1) >> 1) * p.n_ntiles : total_tiles;
   auto tile_of = [&](int it) {
     if (!pair) return it;
-    const int mp = it / p.n_ntiles;
+    const int mp = static_cast<int>(fastdiv(static_cast<uint32_t>(it), p.nt_mul, p.nt_sh));
     return ((mp << 1) + static_cast<int>(rank)) * p.n_ntiles + (it - mp * p.n_ntiles);
   };
   const int n_chunks = p.block_n >> 6;  // staged epilogue: 64-column chunks per tile
@@ -444,15 +544,17 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     // Prefetches the residual chunk of every (tile, 64-column chunk) into the ring slot the epilogue will
     // overwrite with the result; runs as far ahead as the ring allows.
     if (staged && has_res && elect_one()) {
-      uint32_t k = 0;
+      uint32_t s = 0, ph = 0;
       for (int it = it_begin; it < it_end; it += it_step) {
         const TileCoord tc = tile_coord(p, tile_of(it));
-        for (int c = 0; c < n_chunks; ++c, ++k) {
-          const uint32_t s = k % R;
-          const uint32_t ph = (k / R) & 1u;
+        for (int c = 0; c < n_chunks; ++c) {
           mbar_wait(&slot_empty_bar[s], ph ^ 1u, kFaultSlotEmpty);
           mbar_arrive_expect_tx(&slot_full_bar[s], kChunkBytes);
           tma_load_2d(ring + s * kChunkBytes, &tmap_res, tc.n0 + c * 64, tc.row0, &slot_full_bar[s]);
+          if (++s == static_cast<uint32_t>(R)) {
+            s = 0;
+            ph ^= 1u;
+          }
         }
       }
     }
@@ -464,7 +566,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int row = q * 32 + lane;
     int acc = 0;
     uint32_t acc_phase = 0;
-    uint32_t chunk_base = 0;
+    uint32_t cur_slot = 0, cur_ph = 0, cur_g = 0;  // staged epilogue: ring slot, its phase and the owning group of the next chunk
     int prev_slot = -1;  // store thread only: slot whose TMA store was committed last
     const bool store_thread = (q == 0 && lane == 0);
     // head epilogues: fp32 staging tile + row table inside the ring area
@@ -482,10 +584,15 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       if (staged) {
         // ---- staged bf16 epilogue: accumulators (+bias, +residual, ReLU) -> ring slot -> TMA store
         for (int c = 0; c < n_chunks; ++c) {
-          const uint32_t k = chunk_base + c;
-          if (k % kGroups != static_cast<uint32_t>(g)) continue;
-          const uint32_t s = k % R;
-          const uint32_t ph = (k / R) & 1u;
+          // chunk number k = tiles done * n_chunks + c: slot k % R, phase (k / R) & 1, group k % kGroups as counters
+          const bool mine = cur_g == static_cast<uint32_t>(g);
+          const uint32_t s = cur_slot, ph = cur_ph;
+          if (++cur_slot == static_cast<uint32_t>(R)) {
+            cur_slot = 0;
+            cur_ph ^= 1u;
+          }
+          if (++cur_g == static_cast<uint32_t>(kGroups)) cur_g = 0;
+          if (!mine) continue;
           if (has_res) mbar_wait(&slot_full_bar[s], ph, kFaultSlotFull);
           else mbar_wait(&slot_empty_bar[s], ph ^ 1u, kFaultSlotEmpty);
           uint32_t v[64];
@@ -494,63 +601,33 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           tmem_ld_wait();
           uint8_t* rowp = ring + s * kChunkBytes + row * 128;
           const float* bsrc = sbias + tc.n0 + c * 64;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            uint4* sp = reinterpret_cast<uint4*>(rowp + ((j ^ (row & 7)) << 4));  // 128B swizzle: 16-B piece j of row
-            uint4 o = make_uint4(0u, 0u, 0u, 0u);
-            if (ri.interior) {
-              const float4 b0 = *reinterpret_cast<const float4*>(bsrc + j * 8);
-              const float4 b1 = *reinterpret_cast<const float4*>(bsrc + j * 8 + 4);
-              float f[8];
-              f[0] = __uint_as_float(v[j * 8 + 0]) + b0.x;
-              f[1] = __uint_as_float(v[j * 8 + 1]) + b0.y;
-              f[2] = __uint_as_float(v[j * 8 + 2]) + b0.z;
-              f[3] = __uint_as_float(v[j * 8 + 3]) + b0.w;
-              f[4] = __uint_as_float(v[j * 8 + 4]) + b1.x;
-              f[5] = __uint_as_float(v[j * 8 + 5]) + b1.y;
-              f[6] = __uint_as_float(v[j * 8 + 6]) + b1.z;
-              f[7] = __uint_as_float(v[j * 8 + 7]) + b1.w;
-              if (has_res) {
-                const uint4 r = *sp;
-                f[0] += bf16_lo(r.x); f[1] += bf16_hi(r.x); f[2] += bf16_lo(r.y); f[3] += bf16_hi(r.y);
-                f[4] += bf16_lo(r.z); f[5] += bf16_hi(r.z); f[6] += bf16_lo(r.w); f[7] += bf16_hi(r.w);
-              }
-              if (p.relu) {
-#pragma unroll
-                for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.0f);
-              }
-              if (p.mask != nullptr) {
-                const uint4 r = __ldg(reinterpret_cast<const uint4*>(p.mask + static_cast<size_t>(m) * p.mask_ld +
-                                                                     tc.n0 + c * 64 + j * 8));
-                if (!(bf16_lo(r.x) > 0.0f)) f[0] = 0.0f;
-                if (!(bf16_hi(r.x) > 0.0f)) f[1] = 0.0f;
-                if (!(bf16_lo(r.y) > 0.0f)) f[2] = 0.0f;
-                if (!(bf16_hi(r.y) > 0.0f)) f[3] = 0.0f;
-                if (!(bf16_lo(r.z) > 0.0f)) f[4] = 0.0f;
-                if (!(bf16_hi(r.z) > 0.0f)) f[5] = 0.0f;
-                if (!(bf16_lo(r.w) > 0.0f)) f[6] = 0.0f;
-                if (!(bf16_hi(r.w) > 0.0f)) f[7] = 0.0f;
-              }
-              o.x = pack_bf16x2(f[0], f[1]);
-              o.y = pack_bf16x2(f[2], f[3]);
-              o.z = pack_bf16x2(f[4], f[5]);
-              o.w = pack_bf16x2(f[6], f[7]);
-            }
-            *sp = o;  // border rows and rows past the segment end are stored as zeros
+          if (p.mask != nullptr) {  // dgrad through a ReLU: the generic form
+            staged_chunk_row_masked(p, v, bsrc, rowp, row, ri.interior, has_res,
+                                    p.mask + static_cast<size_t>(m) * p.mask_ld + tc.n0 + c * 64);
+          } else if (has_res) {
+            if (p.relu) staged_chunk_row<true, true>(v, bsrc, rowp, row, ri.interior);
+            else staged_chunk_row<true, false>(v, bsrc, rowp, row, ri.interior);
+          } else {
+            if (p.relu) staged_chunk_row<false, true>(v, bsrc, rowp, row, ri.interior);
+            else staged_chunk_row<false, false>(v, bsrc, rowp, row, ri.interior);
           }
           fence_proxy_async_smem();  // make the generic-proxy writes visible to the TMA store
           named_bar_sync(1 + g, 128);
           if (store_thread) {  // always the same thread per group: bulk-async groups are per thread
             tma_store_2d(&tmap_out, tc.n0 + c * 64, tc.row0, ring + s * kChunkBytes);
             tma_store_commit();
-            if (prev_slot >= 0) {
-              tma_store_wait_read1();  // every group but the newest has finished reading its slot
-              mbar_arrive(&slot_empty_bar[prev_slot]);
+            if (p.early_free) {
+              tma_store_wait_read();  // ~0.3 us: the slot goes straight back to the residual producer
+              mbar_arrive(&slot_empty_bar[s]);
+            } else {
+              if (prev_slot >= 0) {
+                tma_store_wait_read1();  // every group but the newest has finished reading its slot
+                mbar_arrive(&slot_empty_bar[prev_slot]);
+              }
+              prev_slot = static_cast<int>(s);
             }
-            prev_slot = static_cast<int>(s);
           }
         }
-        chunk_base += n_chunks;
         tc_fence_before();
         tmem_release(&tmem_empty_bar[acc]);  // this thread's share of the accumulator is drained
       } else if (p.epi == kEpiBf16) {
@@ -755,6 +832,13 @@ int conv_plan_smem(ConvParams& p) {
   }();
   p.epi_groups = (groups_env >= 3 && p.epi == kEpiBf16 && p.staged && p.residual != nullptr && k_iters <= 8 && !p.pair)
                      ? 3 : 2;
+  static const int early_env = [] {
+    // Measured neutral at B=32 (graph replay 7.31-7.37 ms either way; res3*_branch2c 0.084 vs 0.085 ms): the ring is
+    // not what bounds the residual layers once the epilogue is lean. Off by default; PPB_EARLY_FREE=1 turns it on.
+    const char* e = getenv("PPB_EARLY_FREE");
+    return e != nullptr ? atoi(e) : 0;
+  }();
+  p.early_free = (early_env != 0 && p.epi == kEpiBf16 && p.staged && p.residual != nullptr) ? 1 : 0;
   int ring_min = 0, ring_max = 0;
   if (p.epi == kEpiBf16) {
     if (p.staged) {
@@ -807,6 +891,11 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
   const int total = p.n_mtiles * p.n_ntiles;
   if (total <= 0) return cudaSuccess;
   ConvParams q = p;
+  conv_fastdiv(static_cast<unsigned>(q.n_ntiles), &q.nt_mul, &q.nt_sh);
+  for (int i = 0; i < q.n_segs; ++i) {
+    conv_fastdiv(static_cast<unsigned>(q.seg[i].hp * q.seg[i].wp), &q.seg[i].plane_mul, &q.seg[i].plane_sh);
+    conv_fastdiv(static_cast<unsigned>(q.seg[i].wp), &q.seg[i].wp_mul, &q.seg[i].wp_sh);
+  }
   const int smem_bytes = conv_plan_smem(q);
   if (smem_bytes < 0 || q.n_stages != p.n_stages || q.ring_slots != p.ring_slots || q.epi_groups != p.epi_groups)
     return cudaErrorInvalidConfiguration;
@@ -871,9 +960,10 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
     if (ctas > 2 * max_clusters) cfg.gridDim = dim3(2 * max_clusters);
   }
   const cudaError_t err =
-      p.pair ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<true, 2>, tmap_a, tmap_b, tmap_out, tmap_res, p)
-             : (p.epi_groups == 3 ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false, 3>, tmap_a, tmap_b, tmap_out, tmap_res, p)
-                                  : cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false, 2>, tmap_a, tmap_b, tmap_out, tmap_res, p));
+      // q = p + the division constants (its plan was checked equal to p's above)
+      p.pair ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<true, 2>, tmap_a, tmap_b, tmap_out, tmap_res, q)
+             : (p.epi_groups == 3 ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false, 3>, tmap_a, tmap_b, tmap_out, tmap_res, q)
+                                  : cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false, 2>, tmap_a, tmap_b, tmap_out, tmap_res, q));
   if (err != cudaSuccess)
     fprintf(stderr, "conv_launch failed: %s (grid %u, smem %d, pair %d, attrs %d, block_n %d, m tiles %d, n tiles %d)\n",
             cudaGetErrorString(err), cfg.gridDim.x, smem_bytes, p.pair, na, p.block_n, p.n_mtiles, p.n_ntiles);

@@ -38,7 +38,19 @@ struct ConvSeg {
   int tile_begin;  // index of this segment's first M tile
   int loc_base;    // head epilogues: first location index of this level inside one image
   int tap_off[kConvMaxTaps];  // signed row offset of each filter tap
+  // exact unsigned division by hp*wp and by wp as multiply-high + shifts (filled by conv_launch, see conv_fastdiv)
+  unsigned plane_mul, plane_sh, wp_mul, wp_sh;
 };
+
+// Division of a 32-bit unsigned n by a fixed d >= 1 without the ~25-instruction emulated divide (Granlund-Montgomery
+// round-up method, exact for every 32-bit n): t = umulhi(mul, n); q = (t + ((n - t) >> (sh & 255))) >> (sh >> 8).
+inline void conv_fastdiv(unsigned d, unsigned* mul, unsigned* sh) {
+  unsigned l = 0;
+  while ((1ull << l) < d) ++l;  // ceil(log2 d)
+  *mul = static_cast<unsigned>(((1ull << 32) * ((1ull << l) - d)) / d + 1);
+  const unsigned sh1 = l < 1 ? l : 1;
+  *sh = sh1 | ((l - sh1) << 8);
+}
 
 struct ConvParams {
   int n_segs;
@@ -64,7 +76,10 @@ struct ConvParams {
                     // operand is ONE slab of 136 pixels x 16 channels (32-byte rows, 32B swizzle) and the four column
                     // taps dx are four K = 16 MMAs whose descriptors start dx pixels (dx x 32 B) into it, instead of four
                     // overlapping 128-byte rows per pixel (4x the L2 traffic). Maps from conv_encode_stem_tmaps().
+  unsigned nt_mul, nt_sh;  // division by n_ntiles (conv_fastdiv), filled by conv_launch
   int epi_groups;   // epilogue warp groups (2 or 3)     }
+  int early_free;   // staged + residual: a ring slot is handed back as soon as ITS store has read it, not when the  }
+                    // group's next store is committed (more residual chunks in flight)                            }
   int n_stages;     // TMA->MMA pipeline depth (2..8)   } filled by conv_plan_smem()
   int ring_slots;   // 16 KiB epilogue ring slots        }
   const float* bias;              // [n_valid] fp32, BatchNorm folded in; may be null
