@@ -1,5 +1,6 @@
-// Bandwidth-bound helpers of the PFPN engine; see elementwise.h. Every thread moves one 16-byte vector
-// (8 bf16 channels), consecutive threads walk consecutive channels -> fully coalesced 128-bit accesses.
+// Bandwidth-bound helpers of the PFPN engine; see elementwise.h. Threads move 16-byte vectors (8 bf16 channels),
+// consecutive threads walk consecutive channels -> fully coalesced 128-bit accesses; the copy-like kernels give every
+// thread several vectors 256 apart and issue all their loads before the first use.
 #include "elementwise.h"
 
 #include <stdint.h>
@@ -53,69 +54,88 @@ __global__ void __launch_bounds__(256) stem_s2d_kernel(const T* __restrict__ ima
   out[t * 2 + 1] = hi;
 }
 
-__device__ __forceinline__ uint4 max8(uint4 a, uint4 b) {
-  uint4 r;
-  r.x = pack2(fmaxf(lo_f(a.x), lo_f(b.x)), fmaxf(hi_f(a.x), hi_f(b.x)));
-  r.y = pack2(fmaxf(lo_f(a.y), lo_f(b.y)), fmaxf(hi_f(a.y), hi_f(b.y)));
-  r.z = pack2(fmaxf(lo_f(a.z), lo_f(b.z)), fmaxf(hi_f(a.z), hi_f(b.z)));
-  r.w = pack2(fmaxf(lo_f(a.w), lo_f(b.w)), fmaxf(hi_f(a.w), hi_f(b.w)));
-  return r;
+// max of 8 bf16 pairs as four packed HMNMX2.BF16 (the maximum of two bf16 values is one of them: no rounding, so this
+// equals the fp32 max the unpacked form computed, at a seventh of the instructions)
+__device__ __forceinline__ uint32_t max2(uint32_t a, uint32_t b) {
+  const __nv_bfloat162 r = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+  return *reinterpret_cast<const uint32_t*>(&r);
 }
+__device__ __forceinline__ uint4 max8(uint4 a, uint4 b) {
+  return make_uint4(max2(a.x, b.x), max2(a.y, b.y), max2(a.z, b.z), max2(a.w, b.w));
+}
+
+// Splits a vector index of a padded [B, Hp, Wp, C8] tensor; 32-bit arithmetic (the launchers reject tensors with 2^31
+// or more vectors): 64-bit divisions and modulos were most of these kernels' instructions.
+struct VecPos {
+  int b, hy, wx, c;
+};
+__device__ __forceinline__ VecPos vec_pos(unsigned t, unsigned Hp, unsigned Wp, unsigned C8) {
+  VecPos v;
+  const unsigned pix = t / C8;
+  v.c = static_cast<int>(t - pix * C8);
+  const unsigned rowi = pix / Wp;
+  v.wx = static_cast<int>(pix - rowi * Wp);
+  v.b = static_cast<int>(rowi / Hp);
+  v.hy = static_cast<int>(rowi - v.b * Hp);
+  return v;
+}
+
+constexpr int kEwVecs = 4;  // vectors per thread of the copy-like kernels, 256 apart: all loads issued before the first use
 
 __global__ void __launch_bounds__(256) maxpool_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int B,
                                                       int Hi, int Wi, int in_hs, int in_ws, int C8, int Ho, int Wo,
                                                       int pad_top, int pad_left) {
-  // 32-bit index arithmetic (the launchers reject tensors with 2^31 or more vectors): the 64-bit divisions and
-  // modulos were most of this kernel's instructions
   const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned Hp = Ho + 2, Wp = Wo + 2;
   const unsigned total = static_cast<unsigned>(B) * Hp * Wp * C8;
   if (t >= total) return;
-  const unsigned pix = t / static_cast<unsigned>(C8);
-  const int c = static_cast<int>(t - pix * C8);
-  const unsigned rowi = pix / Wp;
-  const int wx = static_cast<int>(pix - rowi * Wp);
-  const int b = static_cast<int>(rowi / Hp);
-  const int hy = static_cast<int>(rowi - b * Hp);
+  const VecPos q = vec_pos(t, Hp, Wp, C8);
   uint4 r = make_uint4(0, 0, 0, 0);
-  if (hy >= 1 && hy <= Ho && wx >= 1 && wx <= Wo) {
-    const int oy = hy - 1, ox = wx - 1;
-    bool first = true;
+  if (q.hy >= 1 && q.hy <= Ho && q.wx >= 1 && q.wx <= Wo) {
+    // TF 'same' max-pool ignores padded positions: they enter the maximum as -inf (bf16 0xFF80); the window always
+    // holds at least one real pixel. The nine loads are independent and issued together.
+    const uint4 ninf = make_uint4(0xFF80FF80u, 0xFF80FF80u, 0xFF80FF80u, 0xFF80FF80u);
+    const int iy0 = 2 * (q.hy - 1) - pad_top, ix0 = 2 * (q.wx - 1) - pad_left;
+    uint4 v[9];
+#pragma unroll
     for (int dy = 0; dy < 3; ++dy) {
-      const int iy = 2 * oy + dy - pad_top;
-      if (iy < 0 || iy >= Hi) continue;  // TF 'same' max-pool ignores padded positions
+#pragma unroll
       for (int dx = 0; dx < 3; ++dx) {
-        const int ix = 2 * ox + dx - pad_left;
-        if (ix < 0 || ix >= Wi) continue;
-        const uint4 v = __ldg(in + ((static_cast<long long>(b) * in_hs + iy) * in_ws + ix) * C8 + c);
-        r = first ? v : max8(r, v);
-        first = false;
+        const int iy = iy0 + dy, ix = ix0 + dx;
+        const bool ok = iy >= 0 && iy < Hi && ix >= 0 && ix < Wi;
+        v[dy * 3 + dx] = ok ? __ldg(in + ((static_cast<long long>(q.b) * in_hs + iy) * in_ws + ix) * C8 + q.c) : ninf;
       }
     }
+    r = max8(max8(max8(v[0], v[1]), max8(v[2], v[3])), max8(max8(v[4], v[5]), max8(max8(v[6], v[7]), v[8])));
   }
   out[t] = r;
 }
 
 __global__ void __launch_bounds__(256) parity_planes_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int B,
                                                             int H, int W, int C8, int Ho, int Wo, int n_planes) {
-  const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned t0 = blockIdx.x * (256u * kEwVecs) + threadIdx.x;
   const unsigned Hp = Ho + 2, Wp = Wo + 2;
   const unsigned plane_elems = static_cast<unsigned>(B) * Hp * Wp * C8;
-  if (t >= plane_elems * n_planes) return;
-  const int plane = static_cast<int>(t / plane_elems);
-  const unsigned u = t - plane * plane_elems;
-  const unsigned pix = u / static_cast<unsigned>(C8);
-  const int c = static_cast<int>(u - pix * C8);
-  const unsigned rowi = pix / Wp;
-  const int wx = static_cast<int>(pix - rowi * Wp);
-  const int b = static_cast<int>(rowi / Hp);
-  const int hy = static_cast<int>(rowi - b * Hp);
-  uint4 r = make_uint4(0, 0, 0, 0);
-  if (hy >= 1 && hy <= Ho && wx >= 1 && wx <= Wo) {
-    const int iy = 2 * (hy - 1) + (plane >> 1), ix = 2 * (wx - 1) + (plane & 1);
-    if (iy < H && ix < W) r = __ldg(in + ((static_cast<long long>(b) * (H + 2) + iy + 1) * (W + 2) + ix + 1) * C8 + c);
+  const unsigned total = plane_elems * n_planes;
+  uint4 r[kEwVecs];
+#pragma unroll
+  for (int k = 0; k < kEwVecs; ++k) {
+    const unsigned t = t0 + k * 256u;
+    r[k] = make_uint4(0, 0, 0, 0);
+    if (t >= total) continue;
+    const int plane = static_cast<int>(t / plane_elems);
+    const VecPos q = vec_pos(t - plane * plane_elems, Hp, Wp, C8);
+    if (q.hy >= 1 && q.hy <= Ho && q.wx >= 1 && q.wx <= Wo) {
+      const int iy = 2 * (q.hy - 1) + (plane >> 1), ix = 2 * (q.wx - 1) + (plane & 1);
+      if (iy < H && ix < W)
+        r[k] = __ldg(in + ((static_cast<long long>(q.b) * (H + 2) + iy + 1) * (W + 2) + ix + 1) * C8 + q.c);
+    }
   }
-  out[t] = r;
+#pragma unroll
+  for (int k = 0; k < kEwVecs; ++k) {
+    const unsigned t = t0 + k * 256u;
+    if (t < total) out[t] = r[k];
+  }
 }
 
 __device__ __forceinline__ void acc8(float (&f)[8], uint4 v) {
@@ -126,38 +146,51 @@ __device__ __forceinline__ void acc8(float (&f)[8], uint4 v) {
 __global__ void __launch_bounds__(256) add_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b,
                                                   const uint4* __restrict__ c, const uint4* __restrict__ u, int uH,
                                                   int uW, uint4* __restrict__ out, int B, int H, int W, int C8) {
-  const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+  constexpr int V = 2;
+  const unsigned t0 = blockIdx.x * (256u * V) + threadIdx.x;
   const unsigned Hp = H + 2, Wp = W + 2;
   const unsigned total = static_cast<unsigned>(B) * Hp * Wp * C8;
-  if (t >= total) return;
-  float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  // Keras Add sums its inputs left to right in fp32; the operands here are bf16 so the fp32 sums are exact
-  // up to the final rounding. Borders: all inputs carry zero borders, the sum keeps them zero.
-  acc8(f, __ldg(a + t));
-  if (b != nullptr) acc8(f, __ldg(b + t));
-  if (c != nullptr) acc8(f, __ldg(c + t));
-  if (u != nullptr) {
-    const unsigned pix = t / static_cast<unsigned>(C8);
-    const int ch = static_cast<int>(t - pix * C8);
-    const unsigned rowi = pix / Wp;
-    const int wx = static_cast<int>(pix - rowi * Wp);
-    const int bi = static_cast<int>(rowi / Hp);
-    const int hy = static_cast<int>(rowi - bi * Hp);
-    if (hy >= 1 && hy <= H && wx >= 1 && wx <= W) {
-      // tf.image.resize NEAREST, half_pixel_centers: src = min(floor((dst + 0.5) * in / out), in - 1)
-      int sy = static_cast<int>(floorf((static_cast<float>(hy - 1) + 0.5f) * (static_cast<float>(uH) / H)));
-      int sx = static_cast<int>(floorf((static_cast<float>(wx - 1) + 0.5f) * (static_cast<float>(uW) / W)));
-      sy = min(sy, uH - 1);
-      sx = min(sx, uW - 1);
-      acc8(f, __ldg(u + ((static_cast<long long>(bi) * (uH + 2) + sy + 1) * (uW + 2) + sx + 1) * C8 + ch));
+  const uint4 zero = make_uint4(0, 0, 0, 0);
+  uint4 va[V], vb[V], vc[V], vu[V];
+  // every load of the thread's V vectors is issued before the first sum
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    const unsigned t = t0 + k * 256u;
+    const bool valid = t < total;
+    va[k] = valid ? __ldg(a + t) : zero;
+    vb[k] = (valid && b != nullptr) ? __ldg(b + t) : zero;
+    vc[k] = (valid && c != nullptr) ? __ldg(c + t) : zero;
+    vu[k] = zero;
+    if (valid && u != nullptr) {
+      const VecPos q = vec_pos(t, Hp, Wp, C8);
+      if (q.hy >= 1 && q.hy <= H && q.wx >= 1 && q.wx <= W) {
+        // tf.image.resize NEAREST, half_pixel_centers: src = min(floor((dst + 0.5) * in / out), in - 1)
+        int sy = static_cast<int>(floorf((static_cast<float>(q.hy - 1) + 0.5f) * (static_cast<float>(uH) / H)));
+        int sx = static_cast<int>(floorf((static_cast<float>(q.wx - 1) + 0.5f) * (static_cast<float>(uW) / W)));
+        sy = min(sy, uH - 1);
+        sx = min(sx, uW - 1);
+        vu[k] = __ldg(u + ((static_cast<long long>(q.b) * (uH + 2) + sy + 1) * (uW + 2) + sx + 1) * C8 + q.c);
+      }
     }
   }
-  uint4 o;
-  o.x = pack2(f[0], f[1]);
-  o.y = pack2(f[2], f[3]);
-  o.z = pack2(f[4], f[5]);
-  o.w = pack2(f[6], f[7]);
-  out[t] = o;
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    const unsigned t = t0 + k * 256u;
+    if (t >= total) continue;
+    // Keras Add sums its inputs left to right in fp32; the operands here are bf16 so the fp32 sums are exact up to
+    // the final rounding (adding an absent operand's +0 changes nothing). Borders: all inputs carry zero borders.
+    float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    acc8(f, va[k]);
+    if (b != nullptr) acc8(f, vb[k]);
+    if (c != nullptr) acc8(f, vc[k]);
+    if (u != nullptr) acc8(f, vu[k]);
+    uint4 o;
+    o.x = pack2(f[0], f[1]);
+    o.y = pack2(f[2], f[3]);
+    o.z = pack2(f[4], f[5]);
+    o.w = pack2(f[6], f[7]);
+    out[t] = o;
+  }
 }
 
 inline unsigned blocks_for(long long total) { return static_cast<unsigned>((total + 255) / 256); }
@@ -200,7 +233,7 @@ cudaError_t launch_parity_planes(const __nv_bfloat16* in, __nv_bfloat16* out, in
                                  int Wo, int n_planes, cudaStream_t st) {
   const long long total = static_cast<long long>(B) * (Ho + 2) * (Wo + 2) * (C / 8) * n_planes;
   PPB_EW_CHECK(total);
-  parity_planes_kernel<<<blocks_for(total), 256, 0, st>>>(reinterpret_cast<const uint4*>(in),
+  parity_planes_kernel<<<blocks_for((total + kEwVecs - 1) / kEwVecs), 256, 0, st>>>(reinterpret_cast<const uint4*>(in),
                                                           reinterpret_cast<uint4*>(out), B, H, W, C / 8, Ho, Wo,
                                                           n_planes);
   return cudaGetLastError();
@@ -211,7 +244,7 @@ cudaError_t launch_add(const __nv_bfloat16* a, const __nv_bfloat16* b, const __n
                        cudaStream_t st) {
   const long long total = static_cast<long long>(B) * (H + 2) * (W + 2) * (C / 8);
   PPB_EW_CHECK(total);
-  add_kernel<<<blocks_for(total), 256, 0, st>>>(reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b),
+  add_kernel<<<blocks_for((total + 1) / 2), 256, 0, st>>>(reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b),
                                                 reinterpret_cast<const uint4*>(c), reinterpret_cast<const uint4*>(u),
                                                 uH, uW, reinterpret_cast<uint4*>(out), B, H, W, C / 8);
   return cudaGetLastError();
