@@ -184,7 +184,7 @@ def run_reference(args):
                          "sample": "%d images per step (batch 1 each), forward+decode+filter, torch-CPU fp32" % sample},
         "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    _emit(line)
 
 
 def run_ours(args):
@@ -378,13 +378,26 @@ def run_ours(args):
                              "sample": "%d images (batch 1 each) forward+decode+filter, torch-CPU fp32 oracle, %.1f s"
                                        % (args.cpu_images, cpu_s)} if world == 1 else None,
         }
-        print(json.dumps(line))
+        _emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+def _emit(line):
+    """The ONE JSON line goes to the process's original stdout; everything else written to fd 1 by this process or by
+    the libraries it loads (NCCL prints its version banner to stdout at communicator creation) lands on stderr."""
+    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
+
+
+_JSON_FD = 1
+
+
 def main():
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
