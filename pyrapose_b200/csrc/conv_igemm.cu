@@ -350,11 +350,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const bool stem16 = p.stem16 != 0;  // see ConvParams::stem16: four K = 16 column taps per stage, 32-byte rows
   const int a_bytes = stem16 ? kStemSlabBytes : (p.slab3 != 0 ? kSlabBytes : kABytes);
   const int b_tile_bytes = stem16 ? b_rows * 32 : b_rows * (kConvBlockK * 2);
-  const int stage_bytes = stem16 ? a_bytes : a_bytes + taps_per_stage * b_tile_bytes;
+  const bool bres = p.bres != 0;  // see ConvParams::bres: this CTA's weight tiles are loaded once and stay resident
+  const int stage_bytes = (stem16 || bres) ? a_bytes : a_bytes + taps_per_stage * b_tile_bytes;
   // stem16: the whole weight matrix (16 (dy, dx) tiles of block_n x 16) is loaded ONCE and stays resident after the
   // pipeline stages, which then carry A slabs only (one TMA request per k-iteration instead of five)
   uint8_t* b_res = smem + n_stages * stage_bytes;
-  const int b_res_bytes = stem16 ? 16 * b_tile_bytes : 0;
+  const int b_res_bytes = stem16 ? 16 * b_tile_bytes : (bres ? p.n_taps * p.cin_blocks * b_tile_bytes : 0);
   uint8_t* ring = b_res + b_res_bytes;
   float* sbias = reinterpret_cast<float*>(ring + p.ring_slots * kChunkBytes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sbias) + kBiasFloats * 4);
@@ -452,6 +453,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       uint32_t phase = 0;
       const uint32_t tx_bytes = stem16 ? static_cast<uint32_t>(kStemSlabTx)
                                        : static_cast<uint32_t>(pair ? 2 * stage_bytes : stage_bytes);
+      if (bres && it_begin < it_end) {
+        // resident weights: every tile of this CTA has the same N tile (the grid is a multiple of n_ntiles); K block
+        // (tap, kb) = weight columns (tap * cin_blocks + kb) * 64 .. + 64, in the order the MMA issuer walks them
+        const int n0 = tile_coord(p, tile_of(it_begin)).n0;
+        mbar_arrive_expect_tx(bres_bar, static_cast<uint32_t>(b_res_bytes));
+        for (int j = 0; j < p.n_taps * p.cin_blocks; ++j)
+          tma_load_2d(b_res + j * b_tile_bytes, &tmap_b, p.b_col_base + j * kConvBlockK, n0, bres_bar);
+      }
       if (stem16 && it_begin < it_end) {  // resident weights: tile (dy, dx) = K columns dy*64 + dx*16 .. +16
         mbar_arrive_expect_tx(bres_bar, static_cast<uint32_t>(b_res_bytes));
         for (int j = 0; j < 16; ++j)
@@ -476,6 +485,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             } else if (stem16) {
               mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
               tma_load_2d(sa, &tmap_a, 0, a_row, &full_bar[stage]);
+            } else if (bres) {
+              mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+              tma_load_2d(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
             } else {
               mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
               tma_load_2d(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
@@ -499,11 +511,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       int acc = 0;
       uint32_t acc_phase = 0;
       const uint32_t idesc = umma_idesc_bf16(pair ? 2 * kConvBlockM : kConvBlockM, p.block_n);
-      if (stem16 && it_begin < it_end) mbar_wait(bres_bar, 0, kFaultFull);
+      if ((stem16 || bres) && it_begin < it_end) mbar_wait(bres_bar, 0, kFaultFull);
       for (int it = it_begin; it < it_end; it += it_step) {
         mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1, kFaultTmemEmpty);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kAccCols;
+        int res_tap = 0, res_kb = 0;  // bres: (first tap, channel block) of k-iteration ki, in the producer's order
         for (int ki = 0; ki < k_iters; ++ki) {
           mbar_wait(&full_bar[stage], phase, kFaultFull);
           tc_fence_after();
@@ -518,7 +531,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           for (int j = 0; j < (stem16 ? 0 : taps_per_stage); ++j) {
             // slab mode: tap j of the filter row reads the slab from row j (ascending taps) or 2 - j (descending)
             const uint32_t a_tap = a_addr + (p.slab3 == 0 ? 0u : (p.slab3 > 0 ? j : 2 - j) * 128u);
-            const uint32_t b_tap = b_addr + j * b_tile_bytes;
+            const uint32_t b_tap = bres ? smem_u32(b_res) + ((res_tap + j) * p.cin_blocks + res_kb) * b_tile_bytes
+                                        : b_addr + j * b_tile_bytes;
 #pragma unroll
             for (int k = 0; k < kConvBlockK / 16; ++k) {
               const uint32_t accum = (ki | j | k) != 0 ? 1u : 0u;
@@ -528,6 +542,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           }
           if (pair) tc_commit2(&empty_bar[stage]);  // frees this stage in both CTAs
           else tc_commit(&empty_bar[stage]);
+          if (++res_kb == p.cin_blocks) {
+            res_kb = 0;
+            res_tap += taps_per_stage;
+          }
           if (++stage == n_stages) {
             stage = 0;
             phase ^= 1;
@@ -792,6 +810,7 @@ bool conv_pair_ok(const ConvParams& p) {
 namespace {
 int stage_bytes_of(const ConvParams& p) {
   if (p.stem16) return kStemSlabBytes;  // A slab only; the weights are resident (stem_resident_bytes)
+  if (p.bres) return p.slab3 != 0 ? kSlabBytes : kABytes;
   const int b_tile = (p.pair ? p.block_n / 2 : p.block_n) * (kConvBlockK * 2);
   return p.slab3 != 0 ? kSlabBytes + 3 * b_tile : kABytes + b_tile;
 }
@@ -823,7 +842,22 @@ int conv_slab3_mode(const ConvParams& p) {
   return dir;
 }
 
+// Resident weights (ConvParams::bres): layers whose whole [block_n x K] weight tile is at most 72 KB — the stage-2
+// bottlenecks, res3*_branch2c, mask_out. Each CTA then issues one TMA request per k-iteration instead of two (four in
+// slab mode; a request costs the producer thread ~110 cycles) and stops re-reading the weights from L2 for every tile.
+static bool conv_bres_ok(const ConvParams& p) {
+  static const int mode = [] {
+    const char* e = getenv("PPB_BRES");
+    return e != nullptr ? atoi(e) : 1;
+  }();
+  if (mode == 0 || p.pair || p.stem16) return false;
+  if (p.n_ntiles != 1 && p.n_ntiles != 2 && p.n_ntiles != 4) return false;  // must divide the grid (148 = 4 x 37)
+  if (p.n_mtiles * p.n_ntiles < 2 * conv_num_sms()) return false;           // at least two tiles per CTA to pay back
+  return p.n_taps * p.cin_blocks * p.block_n * (kConvBlockK * 2) <= 72 * 1024;
+}
+
 int conv_plan_smem(ConvParams& p) {
+  p.bres = conv_bres_ok(p) ? 1 : 0;
   const int stage_bytes = stage_bytes_of(p);
   const int k_iters = (p.slab3 != 0 ? 3 : p.n_taps) * p.cin_blocks;
   static const int groups_env = [] {
@@ -860,8 +894,15 @@ int conv_plan_smem(ConvParams& p) {
   if (p.epi == kEpiBf16 && p.staged && p.residual != nullptr && k_iters <= 8 && stages > 3) stages = 3;
   // stem16: the resident weight tiles (16 x block_n x 32 B) sit between the stages and the ring; with 5 KB stages the
   // producer may as well run two tiles ahead
-  const int resident = p.stem16 ? 16 * p.block_n * 32 : 0;
+  const int resident = p.stem16 ? 16 * p.block_n * 32
+                                : (p.bres ? p.n_taps * p.cin_blocks * p.block_n * (kConvBlockK * 2) : 0);
   if (p.stem16) stages = kMaxStages;
+  // A-only stages of 16-17 KB: as many as fit beside the ring's minimum, so the producer runs one to two tiles ahead
+  // (with three slab stages res2*_branch2b could only prefetch ONE tile: ~3700 cycles per tile = the load latency,
+  // against 1700 cycles of MMAs)
+  // Residual layers keep four: there the ring is worth more than deeper prefetch (res2*_branch2c 0.122 ms with a ring
+  // of 8 and 4 stages, 0.133 ms with 6 and 6); res2b/c_branch2a 0.080 -> 0.073 ms with eight stages.
+  if (p.bres) stages = (p.staged && p.residual != nullptr) ? 4 : kMaxStages;
   const int budget = kSmemBudget - resident;
   while (stages > 2 && stages * stage_bytes + ring_min * kChunkBytes > budget) --stages;
   if (stages * stage_bytes + ring_min * kChunkBytes > budget) return -1;
@@ -904,6 +945,10 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
   if (p.pair) {
     ctas &= ~1;
     if (ctas < 2) return cudaErrorInvalidConfiguration;
+  }
+  if (q.bres) {  // a CTA's tiles it, it + grid, ... must all have the N tile whose weights it holds
+    ctas -= ctas % q.n_ntiles;
+    if (ctas < q.n_ntiles) return cudaErrorInvalidConfiguration;
   }
   static const bool pdl = [] {
     // Off by default: inside the engine's CUDA graph the launch gap is already hidden and the prologue is ~1 us, so

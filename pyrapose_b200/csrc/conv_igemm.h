@@ -76,6 +76,7 @@ struct ConvParams {
                     // operand is ONE slab of 136 pixels x 16 channels (32-byte rows, 32B swizzle) and the four column
                     // taps dx are four K = 16 MMAs whose descriptors start dx pixels (dx x 32 B) into it, instead of four
                     // overlapping 128-byte rows per pixel (4x the L2 traffic). Maps from conv_encode_stem_tmaps().
+  int bres;         // weights resident in shared memory (filled by conv_plan_smem, see conv_bres_ok in conv_igemm.cu)
   unsigned nt_mul, nt_sh;  // division by n_ntiles (conv_fastdiv), filled by conv_launch
   int epi_groups;   // epilogue warp groups (2 or 3)     }
   int early_free;   // staged + residual: a ring slot is handed back as soon as ITS store has read it, not when the  }
