@@ -3,13 +3,17 @@
 // sigmoid / RegressBoxes3D nodes that the reference builds in PyraPose/models/retinanet.py:9-131,
 // 180-214 and (via keras-resnet) PyraPose/models/resnet.py:87, and that TensorFlow executes.
 //
-// One persistent CTA per SM, 8 warps:
-//   warp 0   : TMA producer (one elected lane)      global -> smem ring, 4 stages of {A 128x64, B Nx64}
-//   warp 1   : MMA issuer (one elected lane)        4 x tcgen05.mma (K=16) per stage, commit -> empty[stage]
+// One persistent CTA per SM (or one CTA pair per two SMs), 4 control warps + 2 or 3 epilogue groups of 4 warps:
+//   warp 0   : TMA producer (one elected lane)      global -> smem pipeline, 2..8 stages of {A 128x64 | B Nx64}
+//   warp 1   : MMA issuer (one elected lane)        4 x tcgen05.mma (K=16) per tap and stage, commit -> empty[stage]
 //   warp 2   : TMEM allocator (512 columns = two 256-column accumulators, double-buffered)
-//   warps 4-7: epilogue, one TMEM lane (= output row) per thread
+//   warp 3   : residual prefetch into the epilogue ring (staged epilogue)
+//   warps 4+ : epilogue, one TMEM lane (= output row) per thread, groups alternate over 64-column chunks / tiles
 // M tile = 128 consecutive rows of the padded-flat activation matrix (see conv_igemm.h); the K loop
 // runs over filter taps x 64-channel blocks, each tap being a row-shifted 2-D TMA box.
+// Modes (ConvParams, chosen on the host per layer): pair (cta_group::2, M = 256 per MMA),
+// slab3 (one 136-row A slab per 3x3 filter row, three row-shifted descriptors), stem16 (7x7/2 stem, 32-byte pixel rows,
+// weights resident), bres (1x1 / small 3x3 layers: the CTA's weight tiles resident, A-only stages).
 #include "conv_igemm.h"
 #include "ptx.cuh"
 
@@ -37,6 +41,7 @@ constexpr int kCtrlWarps = 4;
 constexpr int kMaxEpiGroups = 3;
 // Shared memory map (after 1024-B alignment), all sizes per launch (ConvParams::n_stages / ring_slots / block_n):
 //   [0, n_stages * stage_bytes)      TMA->MMA pipeline, stage = {A 128x64 bf16 | B block_n x 64 bf16}
+//   [.., + resident bytes)            stem16 / bres: the CTA's weight tiles, loaded once
 //   [ring_off, + ring_slots * 16 KiB) epilogue ring. kEpiBf16 staged: 128x64 bf16 chunks in the 128B-swizzled TMA
 //                                     layout (residual prefetched in, result stored out by TMA). Head epilogues:
 //                                     one fp32 [128][vals|1] tile + the row -> output-location table.
