@@ -856,7 +856,9 @@ static bool conv_bres_ok(const ConvParams& p) {
     return e != nullptr ? atoi(e) : 1;
   }();
   if (mode == 0 || p.pair || p.stem16) return false;
-  if (p.n_ntiles != 1 && p.n_ntiles != 2 && p.n_ntiles != 4) return false;  // must divide the grid (148 = 4 x 37)
+  // the grid is trimmed to a multiple of n_ntiles (conv_launch); 148 = 4 x 37. Eight N tiles on 144 CTAs (res4*_branch2c,
+  // block_n = 128, 64 KB of weights) was measured too: 0.057 ms either way, so those keep all 148 SMs.
+  if (p.n_ntiles != 1 && p.n_ntiles != 2 && p.n_ntiles != 4) return false;
   if (p.n_mtiles * p.n_ntiles < 2 * conv_num_sms()) return false;           // at least two tiles per CTA to pay back
   return p.n_taps * p.cin_blocks * p.block_n * (kConvBlockK * 2) <= 72 * 1024;
 }
