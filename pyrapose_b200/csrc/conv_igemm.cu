@@ -873,6 +873,7 @@ int conv_plan_smem(ConvParams& p) {
   }();
   p.epi_groups = (groups_env >= 3 && p.epi == kEpiBf16 && p.staged && p.residual != nullptr && k_iters <= 8 && !p.pair)
                      ? 3 : 2;
+  // (Three groups on every resident-weight layer, residual or not: res2*_branch2b 0.066 -> 0.079 ms. Not that either.)
   static const int early_env = [] {
     // Measured neutral at B=32 (graph replay 7.31-7.37 ms either way; res3*_branch2c 0.084 vs 0.085 ms): the ring is
     // not what bounds the residual layers once the epilogue is lean. Off by default; PPB_EARLY_FREE=1 turns it on.
