@@ -62,6 +62,12 @@ CASES = [
     (1, 30, 40, 1024, 256, 1, False, False, True),
     (3, 17, 23, 192, 144, 3, False, False, True),
     (2, 60, 80, 256, 512, 3, True, False, True),
+    # >= 2 tiles per SM with a weight tile of at most 72 KB: the resident-weights mode (ConvParams::bres) with one, two
+    # and four N tiles, with and without the slab mode / the residual ring
+    (4, 120, 160, 64, 64, 3, True, False, True),
+    (4, 120, 160, 64, 256, 1, True, True, True),
+    (3, 120, 160, 256, 64, 1, True, False, True),
+    (6, 60, 80, 128, 512, 1, True, True, True),
 ]
 
 
