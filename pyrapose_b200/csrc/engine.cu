@@ -188,6 +188,17 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
     force_direct = p.slab3 != 0;
     if (!force_direct) p.staged = 1;
   }
+  // Without a residual the TMA-store ring only pays for shallow K loops (stem, stage-2 1x1, the 3x3 of stages 2-3).
+  // From 8 pipeline iterations per tile on, its shared memory is worth more as pipeline stages: direct epilogue
+  // (measured per layer at B=32: res4*/res5*_branch2b, res3b-d/res4*_branch2a, P3/P5_lateral, P4_mid, P4 4-10 % faster
+  // direct; conv1, res2a_branch2a, the projection shortcuts and res3*_branch2b 5-40 % faster staged).
+  static const bool direct_deep = [] {
+    const char* e = getenv("PPB_DIRECT_DEEP");
+    return e == nullptr || atoi(e) != 0;
+  }();
+  if (direct_deep && staged_epilogue == 2 && p.staged && res == nullptr && !p.stem16 &&
+      (p.slab3 != 0 ? 3 : p.n_taps) * p.cin_blocks >= 8)
+    force_direct = true;
   int rc = p.stem16 ? conv_encode_stem_tmaps(&op.ta, &op.tb, x->ptr, a_rows, l.w, l.cout_pad, l.k_total, p.block_n)
                     : conv_encode_tmaps(&op.ta, &op.tb, x->ptr, a_rows, a_cols, a_ld, l.w, l.cout_pad, l.k_total,
                                         p.pair ? p.block_n / 2 : p.block_n, p.slab3 ? kConvSlabRows : kConvBlockM);
