@@ -358,7 +358,7 @@ def run_ours(args):
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                          "frac": achieved / peak, "kernel": "conv_igemm_kernel",
                          # dram__bytes_read.sum + dram__bytes_write.sum of the heaviest launch from the committed
-                         # ncu --set full capture (profiles/r01_full_convs.txt, launch 64; B=32): 227.7 + 179.5 MB against
+                         # ncu --set full capture (profiles/r01_full_heads_pair.txt, launch 0; B=32): 227.9 + 184.0 MB against
                          # 2 x 222k rows x 512 ch x 2 B = 455 MB of algorithmic input + output (the tail of the output
                          # is still in L2 when the kernel ends): no wasted re-reads
                          "traffic": 411939840 if (B, H, W, C) == (32, 480, 640, 15) else None,
