@@ -187,6 +187,199 @@ def run_reference(args):
     _emit(line)
 
 
+def _max_over_ranks(value, dev, world):
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([value], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def train_block(args, world, rank, dev, barrier):
+    """BASELINE.json config 4, the one place on the path with a collective: YCB-Video 21 classes, batch 16 per GPU at
+    480x640, forward + focal / orthogonal_l1 losses + backward + bucketed NCCL gradient all-reduce + Adam(clipnorm)
+    through model.train_on_batch. Images and targets are resident (targets built once by anchor_targets_bbox from
+    seeded synthetic pose annotations). Returns the `train` object of the JSON line."""
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from synth import pose_annotations
+    from pyrapose_b200 import models, optimizers
+    from pyrapose_b200.utils.anchors import anchor_targets_bbox, anchors_for_shape
+    TH, TW, TC, TB = 480, 640, 21, args.train_batch
+    anchors = anchors_for_shape((TH, TW, 3))
+    mean = np.array([103.939, 116.779, 123.68], dtype=np.float32)
+
+    def make(batch, seed0):
+        rng = np.random.default_rng(seed0)
+        img = rng.integers(0, 256, (batch, TH, TW, 3)).astype(np.float32) - mean
+        anns = [pose_annotations(seed0 * 1000 + i, TC) for i in range(batch)]
+        y = anchor_targets_bbox(anchors, [np.zeros((TH, TW, 3), np.float32)] * batch, anns, TC)
+        return torch.from_numpy(img).to(dev), [torch.from_numpy(t).to(dev) for t in y]
+
+    x_d, y_d = make(TB, 4 + rank)
+    model = models.backbone("resnet50").retinanet(num_classes=TC, seed=1)   # same initial weights on every rank
+    model.compile(optimizer=optimizers.Adam(lr=1e-5, clipnorm=0.001))
+    steps, warm = args.train_steps, 3
+    for _ in range(warm):
+        model.train_on_batch(x_d, y_d, sync_losses=False)
+    eng = model._train_engine
+    opt = model.optimizer
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        model.train_on_batch(x_d, y_d, sync_losses=False)
+    e1.record()
+    torch.cuda.synchronize()
+    step_ms = _max_over_ranks(e0.elapsed_time(e1) / steps, dev, world)
+    losses = eng.train_losses()
+    barrier()
+    # the same step without the exchange (segments back to back, no NCCL): the difference is the EXPOSED all-reduce
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3 * steps + 1)]
+    n_seg = len(eng.train_segments())
+    ev[0].record()
+    for s_ in range(steps):
+        eng.buffers["images"].copy_(x_d, non_blocking=True)
+        for k_, t_ in zip(("y_reg", "y_cls", "y_mask"), y_d):
+            eng.buffers[k_].copy_(t_, non_blocking=True)
+        ev[3 * s_ + 1].record()
+        eng.train_count()
+        for i in range(n_seg):
+            eng.train_run_segment(i)
+        ev[3 * s_ + 2].record()
+        eng.train_apply(opt.lr, opt.beta_1, opt.beta_2, opt.epsilon, opt.clipnorm, 1.0)
+        ev[3 * s_ + 3].record()
+    torch.cuda.synchronize()
+    local_ms = _max_over_ranks(ev[0].elapsed_time(ev[-1]) / steps, dev, world)
+    parts = [sum(ev[3 * s_ + k_].elapsed_time(ev[3 * s_ + k_ + 1]) for s_ in range(steps)) / steps for k_ in range(3)]
+    n_params = int(eng.grads_tensor().numel())
+    # tcgen05 kernel classes of one step, per-launch CUDA events (forward conv / dgrad / wgrad)
+    groups = {}
+    if rank == 0:
+        for name, fl, ms in eng.train_profile():
+            kind = name.split(":")[0] if ":" in name else ("fwd_conv" if fl > 0 else "fwd_other")
+            g = groups.setdefault(kind, [0.0, 0.0, 0])
+            g[0] += ms
+            g[1] += fl
+            g[2] += 1
+    out = {
+        "metric": "images_per_sec_pfpn_480x640_train_step", "value": TB * world / (step_ms * 1e-3), "unit": "images/s",
+        "ms_per_step": step_ms, "steps": steps, "warmup": warm,
+        "config": {"workload": "PFPN ResNet-50 training step (forward + focal/orthogonal_l1 + backward + NCCL gradient "
+                               "all-reduce + Adam clipnorm), YCB-Video %d classes, batch %d per GPU, %dx%d"
+                               % (TC, TB, TH, TW), "global_batch": TB * world, "parallelism": "dp%d" % world,
+                   "dp_normalizer": model.dp_normalizer},
+        "split_ms": {"copy_inputs": parts[0], "forward_backward": parts[1], "optimizer": parts[2],
+                     "allreduce_exposed": max(step_ms - local_ms, 0.0) if world > 1 else 0.0,
+                     "step_without_exchange": local_ms},
+        "allreduce_bytes": 4 * n_params if world > 1 else 0,
+        "allreduce": ("%d buckets of ~%d MB, each all-reduced (NCCL, async) as soon as its last weight gradient has "
+                      "landed, overlapping the rest of the backward pass" % (sum(1 for _, c, _ in eng.train_segments() if c),
+                                                                              model.bucket_bytes >> 20)) if world > 1 else None,
+        "kernels": {k: {"ms": v[0], "launches": v[2], "tflops": (v[1] / v[0] * 1e-9) if v[0] > 0 and v[1] > 0 else None}
+                    for k, v in groups.items()},
+        "losses": {k: losses[k] for k in ("3Dbox", "cls", "mask", "l2", "grad_norm")},
+        "trainable_params": n_params,
+    }
+    del model, eng
+    torch.cuda.empty_cache()
+    if world > 1:
+        out["dp_check"] = dp_check(world, rank, dev, make)
+    return out
+
+
+def dp_check(world, rank, dev, make):
+    """An N-replica step on shards must equal the 1-replica step on the concatenated batch (what
+    keras.utils.multi_gpu_model computes, PyraPose/bin/train.py:82-86): every rank steps on its own 2 images over
+    NCCL, rank 0 repeats the step alone on all 2N images; compared: global gradient norm and every updated tensor."""
+    import torch
+    import torch.distributed as dist
+    from pyrapose_b200 import models, optimizers
+    TC, b = 21, 2
+    x_d, y_d = make(b, 900 + rank)
+    m = models.backbone("resnet50").retinanet(num_classes=TC, seed=1)
+    m.compile(optimizer=optimizers.Adam(lr=1e-5, clipnorm=0.001))
+    m.train_on_batch(x_d, y_d)
+    g_dp = m.last_step["grad_norm"]
+    w_dp = {k: v.copy() for k, v in m.get_weights_dict().items()}
+    gathered = []
+    for t in [x_d] + y_d:
+        parts = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(parts, t.contiguous())
+        gathered.append(torch.cat(parts, dim=0))
+    res = None
+    if rank == 0:
+        one = models.backbone("resnet50").retinanet(num_classes=TC, seed=1)
+        w0 = {k: v.copy() for k, v in one.weights.items()}
+        one.compile(optimizer=optimizers.Adam(lr=1e-5, clipnorm=0.001), data_parallel=False)
+        one.train_on_batch(gathered[0], gathered[1:])
+        g_one = one.last_step["grad_norm"]
+        w_one = one.get_weights_dict()
+        worst = 0.0
+        for k, v0 in w0.items():
+            d = w_one[k].astype(np.float64) - v0
+            n = np.linalg.norm(d)
+            if n < 1e-12:
+                continue
+            worst = max(worst, float(np.linalg.norm(w_dp[k].astype(np.float64) - v0 - d) / n))
+        rel_norm = abs(g_dp - g_one) / g_one
+        res = {"replicas": world, "images_per_replica": b, "grad_norm_dp": g_dp, "grad_norm_single": g_one,
+               "grad_norm_rel": rel_norm, "max_rel": worst, "tolerance": 1e-3,
+               "ok": bool(worst <= 1e-3 and rel_norm <= 1e-3),
+               "what": "max over trainable tensors of |step_dp - step_single| / |step_single| after one "
+                       "Adam(lr=1e-5, clipnorm=1e-3) step; single = rank 0 alone on the concatenated batch"}
+        del one
+    del m
+    torch.cuda.empty_cache()
+    dist.barrier()
+    return res
+
+
+def config5_block(args, world, rank, dev, barrier):
+    """BASELINE.json config 5: 960x1280, T-LESS 30 classes, GLOBAL batch 64 sharded over the N GPUs (strong scaling:
+    64 / N images per GPU), inference + decode + FilterDetections, images resident."""
+    import torch
+    from pyrapose_b200 import _kernels, models
+    from pyrapose_b200.models import spec
+    h5, w5, c5, gb = 960, 1280, 30, 64
+    per = gb // world
+    w = spec.init_weights(c5, A, seed=1, head_init="spread")
+    w["pyramid_classification/bias"] = np.full_like(w["pyramid_classification/bias"], args.cls_bias)
+    train = models.backbone("resnet50").retinanet(num_classes=c5)
+    train.set_weights_dict(w)
+    model = models.convert_model(train)
+    rng = np.random.default_rng(500 + rank)
+    img = torch.from_numpy(rng.integers(0, 256, (per, h5, w5, 3), dtype=np.uint8)).pin_memory()
+    buf = model.forward_device(img, want_hull=True)
+    eng = model._engines[(h5, w5)]
+
+    def step():
+        eng.run()
+        return _kernels.filter_detections(buf["hull"], buf["boxes3D"], buf["cls"])
+
+    for _ in range(3):
+        step()
+    barrier()
+    steps = 5
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = _max_over_ranks(e0.elapsed_time(e1) / steps, dev, world)
+    flops = conv_flops_per_image(h5, w5, c5, A)
+    out = {"metric": "images_per_sec_pfpn_960x1280_infer_decode_filter", "value": gb / (ms * 1e-3), "unit": "images/s",
+           "ms_per_step": ms, "steps": steps, "scaling": "strong", "global_batch": gb, "batch_per_gpu": per,
+           "classes": c5, "conv_tflops_per_gpu": flops * per / (ms * 1e-3) / 1e12,
+           "device_bytes_per_gpu": eng.device_bytes()}
+    del model, train, eng, buf
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -239,52 +432,94 @@ def run_ours(args):
     torch.cuda.synchronize()
     dev_ms = e0.elapsed_time(e1)
     launches = _native.launch_count() - launches0
-    t = torch.tensor([dev_ms], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms = float(t.item())
+    dev_ms = _max_over_ranks(dev_ms, dev, world)
     barrier()
 
-    # ---- e2e arm: pinned host images in, host detections out, every step, through the public API.
-    # model.detect_stream is the pipelined batch loop (copy of step i+1 overlaps the forward pass of step i); every
-    # step still pays its own H2D of the images and D2H of the detections. The synchronous one-call-per-step
-    # figure (model.detect_on_batch) is reported beside it as e2e_sync.
-    pinned2 = torch.from_numpy(make_images(50 + rank, B)).pin_memory()
-
-    def host_batches(n):
-        for i in range(n):
-            yield pinned if (i & 1) == 0 else pinned2
-
-    for det in model.detect_stream(host_batches(3)):
-        pass
-    barrier()
-    t0 = time.perf_counter()
-    for det in model.detect_stream(host_batches(args.steps)):
-        pass
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    t = torch.tensor([e2e_s], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_s = float(t.item())
-    for _ in range(2):
-        model.detect_on_batch(pinned)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        model.detect_on_batch(pinned)
-    torch.cuda.synchronize()
-    sync_s = time.perf_counter() - t0
-    t = torch.tensor([sync_s], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    sync_s = float(t.item())
+    # ---- sustained: the same step for >= args.sustain_s seconds (the K-step region above is a burst of ~0.2 s; under
+    # back-to-back replay the board sits on its power cap), with its own clock sample
+    sustained = None
+    if args.sustain_s > 0:
+        n_sus = max(int(args.sustain_s * 1e3 / (dev_ms / args.steps)) + 1, args.steps)
+        barrier()
+        e0.record()
+        for _ in range(n_sus):
+            step_device()
+        e1.record()
+        torch.cuda.synchronize()
+        sus_ms = _max_over_ranks(e0.elapsed_time(e1), dev, world)
+        barrier()
+        sustained = {"value": world * B * n_sus / (sus_ms * 1e-3), "unit": "images/s", "steps": n_sus,
+                     "seconds": sus_ms * 1e-3, "ms_per_step": sus_ms / n_sus}
+    # one nvidia-smi sampler (100 ms period) over the K timed steps AND the sustained loop of the same step
     clocks = sampler.stop() if rank == 0 else None
-    h2d = int(pinned.numel() * 4)
+    if clocks is not None:
+        clocks["window"] = "timed steps + sustained loop (same step, %.1f s)" % ((sustained or {}).get("seconds", 0.0))
+
+    # ---- e2e arms: HOST images in, HOST results out, every step, through the public API. The real caller's input is
+    # raw uint8 BGR (cv2.imread -> preprocess_image, PyraPose/utils/linemod_eval.py:283-303): preprocess_image('caffe')
+    # runs fused in the stem loader, so the headline e2e ships uint8 (29.5 MB per batch-32 step); the float32
+    # mean-subtracted form the reference hands to predict_on_batch (118 MB) is timed beside it.
+    #   stream : model.detect_stream — pipelined batch loop (H2D of step i+1 overlaps the forward pass of step i)
+    #   sync   : model.detect_on_batch — one blocking call per step
+    #   predict_on_batch : the reference's own call; returns the three FULL arrays (234 MB D2H per step)
+    rng8 = np.random.default_rng(70 + rank)
+    raw = [torch.from_numpy(rng8.integers(0, 256, (B, H, W, 3), dtype=np.uint8)).pin_memory() for _ in range(2)]
+    f32 = [pinned, torch.from_numpy(make_images(50 + rank, B)).pin_memory()]
+
+    def time_stream(batches):
+        def gen(n):
+            for i in range(n):
+                yield batches[i & 1]
+        det = None
+        for det in model.detect_stream(gen(3)):
+            pass
+        barrier()
+        t0 = time.perf_counter()
+        for det in model.detect_stream(gen(args.steps)):
+            pass
+        torch.cuda.synchronize()
+        return _max_over_ranks(time.perf_counter() - t0, dev, world), det
+
+    def time_calls(fn, x, steps):
+        out = None
+        for _ in range(2):
+            out = fn(x)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            out = fn(x)
+        torch.cuda.synchronize()
+        return _max_over_ranks(time.perf_counter() - t0, dev, world), out
+
+    e2e_s, det = time_stream(raw)
+    e2e_f32_s, _ = time_stream(f32)
+    sync_s, _ = time_calls(model.detect_on_batch, raw[0], args.steps)
+    sync_f32_s, _ = time_calls(model.detect_on_batch, f32[0], args.steps)
+    pob_steps = max(args.steps // 2, 3)
+    pob_s, pob_out = time_calls(model.predict_on_batch, raw[0], pob_steps)
+    pob_f32_s, _ = time_calls(model.predict_on_batch, f32[0], pob_steps)
+    h2d = int(raw[0].numel())
     d2h = int(sum(o.nbytes for o in det))
+    pob_d2h = int(sum(o.nbytes for o in pob_out))
+    del pob_out
+    ips = lambda sec, n=args.steps: world * B * n / sec
+    e2e = {"value": ips(e2e_s), "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+           "api": "model.detect_stream(uint8 host batches) -> host detections [boxes, boxes3D, scores, labels]",
+           "input": "raw uint8 BGR (preprocess_image('caffe') fused into the stem loader)",
+           "e2e_sync": ips(sync_s), "api_sync": "model.detect_on_batch(uint8 host batch)",
+           "fp32_input": {"value": ips(e2e_f32_s), "e2e_sync": ips(sync_f32_s), "h2d_bytes_per_step": int(pinned.numel() * 4)},
+           "predict_on_batch": {"value": ips(pob_s, pob_steps), "fp32_input": ips(pob_f32_s, pob_steps),
+                                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": pob_d2h,
+                                "api": "model.predict_on_batch(host batch) -> [boxes3D, cls, mask] full float32 arrays "
+                                       "(the reference's call, linemod_eval.py:303), pinned buffers + async D2H"}}
+
+    train_out = train_block(args, world, rank, dev, barrier) if args.train_steps > 0 else None
+    cfg5_out = config5_block(args, world, rank, dev, barrier) if (world > 1 and 64 % world == 0 and args.config5) else None
 
     if rank == 0:
         # ---- roofline of the dominant kernel (tcgen05 implicit-GEMM conv), timed per launch with CUDA events
+        buf = model.forward_device(pinned, want_hull=True)   # back to the plan of the timed region
+        eng = model._engines[(H, W)]
         prof = [eng.profile() for _ in range(3)][-1]
         conv_ms = sum(ms for k, ms in prof if k == 0)
         other_ms = sum(ms for k, ms in prof if k != 0)
@@ -292,13 +527,37 @@ def run_ours(args):
         flops_img = conv_flops_per_image(H, W, C, A)
         peaks, peak_src = load_peaks()
         achieved = flops_img * B / (conv_ms * 1e-3) / 1e12
-        peak = float(peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"]))
+        # the K-step region is a ~0.2 s burst and the per-launch profile times every kernel alone: the BURST cuBLAS
+        # figure is the denominator; the sustained one is reported beside it
+        peak = float(peaks["bf16_tflops"])
+        peak_sus = float(peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"]))
         # the single heaviest launch (a 3x3 512->512 regression-tower convolution over the three pyramid levels)
         ops = eng.op_table()
         top_i = max(range(len(prof)), key=lambda i: prof[i][1] if prof[i][0] == 0 else -1.0)
         top = {"name": ops[top_i][0], "ms": prof[top_i][1], "tflops": ops[top_i][1] / (prof[top_i][1] * 1e-3) / 1e12}
         top["frac"] = top["tflops"] / peak
-        top["frac_of_burst"] = top["tflops"] / float(peaks["bf16_tflops"])
+        top["frac_of_sustained"] = top["tflops"] / peak_sus
+        groups = {}
+        for (name, fl), (k, ms) in zip(ops, prof):
+            if k != 0:
+                grp = "elementwise"
+            elif name == "conv1":
+                grp = "stem"
+            elif name.startswith("res"):
+                grp = "stage" + name[3]
+            elif name.startswith("pyramid_regression"):
+                grp = "reg_head"
+            elif name.startswith("pyramid_class"):
+                grp = "cls_head"
+            elif name.startswith("mask"):
+                grp = "mask_head"
+            else:
+                grp = "pfpn"
+            g = groups.setdefault(grp, [0.0, 0.0])
+            g[0] += ms
+            g[1] += fl
+        by_group = {k: {"ms": v[0], "tflops": v[1] / (v[0] * 1e-3) / 1e12 if v[1] > 0 else None}
+                    for k, v in groups.items()}
         # ---- secondary: HBM-bound score pass of the filter (reads B*N*C fp32 once)
         n_boxes = eng.num_boxes
         pass_rate = float((buf["cls"] > 0.05).float().mean())
@@ -348,11 +607,11 @@ def run_ours(args):
                        "global_batch": world * B, "parallelism": "replicas x%d (no collective)" % world,
                        "weights": "random-init (seed 1), he-normal heads, cls bias %.1f: %.1f%% of scores pass 0.05"
                                   % (args.cls_bias, 100 * pass_rate),
+                       "candidates_per_image": pass_rate * n_boxes * C,
                        "l2": "working set per step (activations ~%.1f GB) far exceeds the 126 MB L2; no flush needed"
                              % (eng.device_bytes() / 1e9)},
-            "e2e": {"value": world * B * args.steps / e2e_s, "unit": "images/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "api": "model.detect_stream(host batches) -> host detections",
-                    "e2e_sync": world * B * args.steps / sync_s, "api_sync": "model.detect_on_batch(host batch)"},
+            "e2e": e2e,
+            "sustained": sustained,
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
@@ -364,8 +623,9 @@ def run_ours(args):
                          "traffic": 411939840 if (B, H, W, C) == (32, 480, 640, 15) else None,
                          "traffic_launch": "pyramid_regression3D_1 (CTA-pair + slab mode), profiles/r01_full_heads_pair.txt launch 0", "top_launch": top,
                          "launches_per_step": n_conv, "conv_ms_per_step": conv_ms, "other_ms_per_step": other_ms,
-                         "flops_per_image": flops_img, "peak_source": peak_src + " bf16_tflops_sustained",
-                         "frac_of_burst": achieved / float(peaks["bf16_tflops"])},
+                         "flops_per_image": flops_img, "peak_source": peak_src + " bf16_tflops (burst)",
+                         "frac_of_burst": achieved / peak, "frac_of_sustained": achieved / peak_sus,
+                         "by_group": by_group},
             "roofline_hbm": {"kernel": "score_mask_kernel", "bound": "hbm", "achieved": mask_gbs,
                              "peak": float(peaks["hbm_gbs"]), "unit": "GB/s", "frac": mask_gbs / float(peaks["hbm_gbs"]),
                              "bytes_per_launch": B * n_boxes * C * 4, "ms": mask_ms,
@@ -377,6 +637,8 @@ def run_ours(args):
             "cpu_baseline": {"value": cpu_ips, "unit": "images/s", "cores": threads, "kind": "port",
                              "sample": "%d images (batch 1 each) forward+decode+filter, torch-CPU fp32 oracle, %.1f s"
                                        % (args.cpu_images, cpu_s)} if world == 1 else None,
+            "train": train_out,
+            "config5": cfg5_out,
         }
         _emit(line)
     if world > 1:
@@ -405,6 +667,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--cpu-images", type=int, default=8)
+    ap.add_argument("--sustain-s", type=float, default=5.0, help="seconds of back-to-back steps for the `sustained` figure (0: skip)")
+    ap.add_argument("--train-steps", type=int, default=10, help="timed steps of the `train` block (config 4); 0: skip")
+    ap.add_argument("--train-batch", type=int, default=16)
+    ap.add_argument("--no-config5", dest="config5", action="store_false",
+                    help="skip the `config5` block (960x1280, 30 classes, global batch 64 over N >= 2 GPUs)")
     ap.add_argument("--height", type=int, default=H, help="other BASELINE.json configs, e.g. config 5: 960 x 1280, 30 classes")
     ap.add_argument("--width", type=int, default=W)
     ap.add_argument("--classes", type=int, default=C)

@@ -276,6 +276,24 @@ PPB_API int ppb_engine_train_bind(ppb_engine* engine, int batch, const float* im
                                   const float* y_cls, const float* y_mask, float* out_reg, float* out_cls,
                                   float* out_mask, void* stream);
 PPB_API int ppb_engine_train_forward_backward(ppb_engine* engine, int eager, void* stream);
+/* Data-parallel step (keras.utils.multi_gpu_model, PyraPose/bin/train.py:82-86).
+ * ppb_engine_train_set_bucket_bytes: call before ppb_engine_train_bind. With bucket_bytes > 0 the step is captured
+ *   as ppb_engine_train_num_segments graphs, cut after the launch that completes each ~bucket_bytes slice of the flat
+ *   gradient buffer (the backward pass fills it from the end — heads — to the beginning — res3). Segment i leaves
+ *   [grad_offset, grad_offset + grad_count) final, so the caller starts the NCCL all-reduce of that slice on its
+ *   communication stream and launches segment i + 1 at once (grad_count may be 0 for the trailing segment).
+ * ppb_engine_train_count: the positives of the three outputs (the loss normalisers of losses.py:61-66, 395-397) into
+ *   the device int[4] that ppb_engine_train_counts returns; they depend on the targets only. multi_gpu_model computes
+ *   each loss once over the CONCATENATED replica outputs, i.e. normalises by the positives of the global batch: a
+ *   data-parallel caller sums the counters over the replicas between _count and the first segment, then sums (not
+ *   averages) the gradients. If _count was not called explicitly the first segment / _forward_backward runs it. */
+PPB_API int ppb_engine_train_set_bucket_bytes(ppb_engine* engine, long long bucket_bytes);
+PPB_API int ppb_engine_train_count(ppb_engine* engine, void* stream);
+PPB_API int ppb_engine_train_counts(ppb_engine* engine, int** counts_dev);
+PPB_API int ppb_engine_train_num_segments(const ppb_engine* engine);
+PPB_API int ppb_engine_train_segment_info(const ppb_engine* engine, int segment, long long* grad_offset,
+                                          long long* grad_count, int* n_launches);
+PPB_API int ppb_engine_train_run_segment(ppb_engine* engine, int segment, void* stream);
 PPB_API int ppb_engine_train_grads(ppb_engine* engine, float** grads, long long* count);
 PPB_API int ppb_engine_train_apply(ppb_engine* engine, float lr, float beta1, float beta2, float epsilon,
                                    float clipnorm, float grad_scale, void* stream);

@@ -15,6 +15,7 @@
 // slab3 (one 136-row A slab per 3x3 filter row, three row-shifted descriptors), stem16 (7x7/2 stem, 32-byte pixel rows,
 // weights resident), bres (1x1 / small 3x3 layers: the CTA's weight tiles resident, A-only stages).
 #include "conv_igemm.h"
+#include "launch_count.h"
 #include "ptx.cuh"
 
 #include <cstdio>
@@ -927,16 +928,15 @@ int conv_plan_smem(ConvParams& p) {
 
 cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const CUtensorMap& tmap_out,
                         const CUtensorMap& tmap_res, const ConvParams& p, int max_ctas, cudaStream_t stream) {
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(conv_igemm_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+  static PerDeviceOnce once;  // the opt-in is per device (one process may own engines on several GPUs)
+  if (once.first_on_current_device()) {
+    cudaError_t attr_err = cudaFuncSetAttribute(conv_igemm_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     if (attr_err == cudaSuccess)
       attr_err = cudaFuncSetAttribute(conv_igemm_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     if (attr_err == cudaSuccess)
       attr_err = cudaFuncSetAttribute(conv_igemm_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
-  });
-  if (attr_err != cudaSuccess) return attr_err;
+    if (attr_err != cudaSuccess) return attr_err;
+  }
   const int total = p.n_mtiles * p.n_ntiles;
   if (total <= 0) return cudaSuccess;
   ConvParams q = p;

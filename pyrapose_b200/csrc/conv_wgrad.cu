@@ -5,6 +5,7 @@
 // Replaces the filter-gradient ops TensorFlow runs for keras.layers.Conv2D during model.fit_generator
 // (PyraPose/bin/train.py:381-390).
 #include "conv_wgrad.h"
+#include "launch_count.h"
 #include "ptx.cuh"
 
 #include <cstdlib>
@@ -267,14 +268,13 @@ void wgrad_plan(WgradParams& p) {
 
 cudaError_t wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, const WgradParams& p,
                          cudaStream_t stream) {
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(conv_wgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemLimit);
+  static PerDeviceOnce once;  // per device, see launch_count.h
+  if (once.first_on_current_device()) {
+    cudaError_t attr_err = cudaFuncSetAttribute(conv_wgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemLimit);
     if (attr_err == cudaSuccess)
       attr_err = cudaFuncSetAttribute(conv_wgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemLimit);
-  });
-  if (attr_err != cudaSuccess) return attr_err;
+    if (attr_err != cudaSuccess) return attr_err;
+  }
   const int total = (p.pair ? p.n_mtiles / 2 : p.n_mtiles) * p.n_taps * p.n_ntiles * p.k_splits;
   if (total <= 0 || p.total_k_iters <= 0) return cudaSuccess;
   const int stage_bytes = kWgABytes + (p.pair ? p.block_n >> 7 : p.block_n >> 6) * kWgBoxBytes;

@@ -604,8 +604,10 @@ int ppb_engine_set_layer(ppb_engine* h, const char* name, const float* kernel_hw
                          const float* bn_var_host, float bn_eps) {
   PPB_REQUIRE(h != nullptr && name != nullptr, "ppb_engine_set_layer: null argument");
   PPB_CUDA(cudaSetDevice(h->e.device));
-  return h->e.set_layer(name, kernel_hwio_host, bias_host, bn_gamma_host, bn_beta_host, bn_mean_host, bn_var_host,
-                        bn_eps);
+  const int rc = h->e.set_layer(name, kernel_hwio_host, bias_host, bn_gamma_host, bn_beta_host, bn_mean_host,
+                                bn_var_host, bn_eps);
+  if (rc != kOk) return rc;
+  return train_refresh_layer(h->e, h->e.layer_index.at(name));  // an engine that has trained keeps its master copy in step
 }
 
 int ppb_engine_set_anchors(ppb_engine* h, const float* base_anchors_host, const float* strides_host,

@@ -103,6 +103,7 @@ struct Engine {
   bool input_u8 = false;
   float input_mean[3] = {103.939f, 116.779f, 123.68f};
   bool training_plan = false;
+  long long train_bucket_bytes = 0;  // gradient bucket size of the segmented training step (0 = one graph)
   std::shared_ptr<struct TrainState> train;
 
   ~Engine() {
@@ -175,6 +176,10 @@ struct Engine {
   int launch_all(cudaStream_t st);
   void fill_head_segs(ConvParams& p, int batch, int n_levels) const;
 };
+
+// train.cu: re-seeds the master weights / dgrad matrix of one layer after Engine::set_layer when a training state
+// exists (no-op otherwise).
+int train_refresh_layer(Engine& e, int layer);
 
 }  // namespace ppb
 

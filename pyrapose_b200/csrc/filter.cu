@@ -697,10 +697,10 @@ int ppb_filter_detections(const float* boxes, const float* boxes3D, const float*
   compact_keys_kernel<<<dim3(Ceff, batch), 256, 0, st>>>(w.mask, score_src, n, Ceff, W, score_stride, cap, w.keys,
                                                          w.counts);
   PPB_CUDA(cudaGetLastError());
-  static bool sort_attr_set = false;
-  if (!sort_attr_set) {
+  static PerDeviceOnce filter_attr_once;  // per device, see launch_count.h
+  if (filter_attr_once.first_on_current_device()) {
     PPB_CUDA(cudaFuncSetAttribute(sort_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortSmemKeys * 8));
-    sort_attr_set = true;
+    PPB_CUDA(cudaFuncSetAttribute(topk_pad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTopkSmemKeys * 8));
   }
   sort_keys_kernel<<<Ceff * batch, 1024, kSortSmemKeys * 8, st>>>(w.keys, w.counts, cap);
   PPB_CUDA(cudaGetLastError());
@@ -718,11 +718,6 @@ int ppb_filter_detections(const float* boxes, const float* boxes3D, const float*
   PPB_CUDA(cudaGetLastError());
   const int np2 = next_pow2(Ceff * max_detections);
   const size_t topk_smem = np2 <= kTopkSmemKeys ? static_cast<size_t>(np2) * 8 : 0;
-  static bool attr_set = false;
-  if (!attr_set) {
-    PPB_CUDA(cudaFuncSetAttribute(topk_pad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTopkSmemKeys * 8));
-    attr_set = true;
-  }
   topk_pad_kernel<<<batch, 1024, topk_smem, st>>>(w.sel_idx, w.sel_cnt, Ceff, max_detections, classification,
                                                   class_specific ? nullptr : w.sarg, n, num_classes, boxes, boxes3D,
                                                   out_boxes, out_boxes3D, out_scores, out_labels, out_indices,

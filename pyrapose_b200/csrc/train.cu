@@ -46,6 +46,18 @@ struct TrainLayer {
   int n_taps = 0;
   int tap_pos[9] = {0, 1, 2, 3, 4, 5, 6, 7, 8};
   int plane_tap_begin[5] = {0, 0, 0, 0, 0};  // stride-2 3x3 layers: taps grouped by input parity plane
+  int last_grad_op = -1;  // index in TrainState::bwd of the last op that writes this layer's gradient (wgrad / bgrad)
+};
+
+// One CUDA graph of the step and the slice of the flat gradient buffer that is final when it has run. The step is cut
+// after the op that completes each gradient bucket, so a data-parallel caller can start the NCCL all-reduce of bucket
+// k on its communication stream while segment k + 1 (the rest of the backward pass) runs.
+struct Segment {
+  int op_begin = 0, op_end = 0;  // range of TrainState::bwd ops (segment 0 also holds the memsets + forward pass)
+  long long g_off = 0, g_cnt = 0;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  int kernels = 0;
 };
 
 struct TrainState {
@@ -63,15 +75,22 @@ struct TrainState {
   int* chunk_index = nullptr;
   int n_chunks = 0;
   std::vector<TOp> bwd;
+  std::vector<TOp> count_ops;  // positives per output: depend on the targets only, launched ahead of the graphs
+  std::vector<Segment> segs;
+  long long bucket_bytes = 0;  // 0: one segment = the whole step
+  bool counts_ready = false;   // ppb_engine_train_count ran for this step (the caller may have all-reduced them)
   int bound_batch = 0;
   long long step = 0;
-  cudaGraph_t graph = nullptr;
-  cudaGraphExec_t exec = nullptr;
   int graph_kernels = 0;
-  ~TrainState() {
-    if (exec) cudaGraphExecDestroy(exec);
-    if (graph) cudaGraphDestroy(graph);
+  void drop_graphs() {
+    for (Segment& sg : segs) {
+      if (sg.exec) cudaGraphExecDestroy(sg.exec);
+      if (sg.graph) cudaGraphDestroy(sg.graph);
+      sg.exec = nullptr;
+      sg.graph = nullptr;
+    }
   }
+  ~TrainState() { drop_graphs(); }
 };
 
 namespace {
@@ -238,6 +257,7 @@ struct Builder {
       snprintf(b.name, sizeof(b.name), "bgrad:%s", layer.c_str());
       t.bwd.push_back(b);
     }
+    T(layer).last_grad_op = static_cast<int>(t.bwd.size()) - 1;
     return kOk;
   }
 
@@ -323,6 +343,35 @@ struct Builder {
 
 int round64(int v) { return (v + 63) / 64 * 64; }
 
+// Master weights (+ BatchNorm scale, + the transposed bf16 data-gradient matrix) of one trainable layer from the host
+// copies Engine::set_layer keeps. Also runs when weights are loaded into an engine that has already trained
+// (model.load_weights / set_weights after compile): the Adam moments stay, the master copy follows the new weights.
+int seed_layer(Engine& e, TrainState& t, int i) {
+  const LayerW& l = e.layers[i];
+  TrainLayer& tl = t.tl[i];
+  if (!tl.trainable) return kOk;
+  PPB_CUDA(cudaMemcpy(t.master + tl.off_kernel, l.raw_kernel.data(), l.raw_kernel.size() * sizeof(float),
+                      cudaMemcpyHostToDevice));
+  if (l.has_bias)
+    PPB_CUDA(cudaMemcpy(t.master + tl.off_bias, l.raw_bias.data(), l.raw_bias.size() * sizeof(float),
+                        cudaMemcpyHostToDevice));
+  if (tl.scale != nullptr)
+    PPB_CUDA(cudaMemcpy(tl.scale, l.bn_scale.data(), l.cout * sizeof(float), cudaMemcpyHostToDevice));
+  if (tl.w_dgrad != nullptr) {
+    const size_t cols = static_cast<size_t>(tl.n_taps) * tl.g_ld;
+    std::vector<__nv_bfloat16> wt(static_cast<size_t>(l.cin) * cols, __float2bfloat16(0.0f));
+    for (int co = 0; co < l.cout; ++co) {
+      const float sc = l.bn_scale.empty() ? 1.0f : l.bn_scale[co];
+      for (int tap = 0; tap < tl.n_taps; ++tap)
+        for (int ci = 0; ci < l.cin; ++ci)
+          wt[static_cast<size_t>(ci) * cols + static_cast<size_t>(tl.tap_pos[tap]) * tl.g_ld + co] =
+              __float2bfloat16(l.raw_kernel[static_cast<size_t>(co) * l.k_total + tap * l.cin + ci] * sc);
+    }
+    PPB_CUDA(cudaMemcpy(tl.w_dgrad, wt.data(), wt.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
+  }
+  return kOk;
+}
+
 // Allocates the optimizer state and the dgrad weights, seeds them from the host copies kept by set_layer.
 int create_state(Engine& e) {
   std::shared_ptr<TrainState> st(new TrainState);
@@ -376,32 +425,22 @@ int create_state(Engine& e) {
   PPB_TRY(e.device_alloc(&p, 4 * sizeof(int)));
   t.counts = static_cast<int*>(p);
 
-  std::vector<float> master(off, 0.0f);
   std::vector<int> chunk_desc, chunk_index;
+  PPB_CUDA(cudaMemset(t.master, 0, off * sizeof(float)));
   for (size_t i = 0; i < e.layers.size(); ++i) {
     const LayerW& l = e.layers[i];
     TrainLayer& tl = t.tl[i];
     if (!tl.trainable) continue;
-    std::copy(l.raw_kernel.begin(), l.raw_kernel.end(), master.begin() + tl.off_kernel);
     if (!l.bn_scale.empty()) {
       PPB_TRY(e.device_alloc(&p, l.cout * sizeof(float)));
       tl.scale = static_cast<float*>(p);
-      PPB_CUDA(cudaMemcpy(tl.scale, l.bn_scale.data(), l.cout * sizeof(float), cudaMemcpyHostToDevice));
     }
     if (tl.need_dgrad) {
       const size_t cols = static_cast<size_t>(tl.n_taps) * tl.g_ld;
-      std::vector<__nv_bfloat16> wt(static_cast<size_t>(l.cin) * cols, __float2bfloat16(0.0f));
-      for (int co = 0; co < l.cout; ++co) {
-        const float sc = l.bn_scale.empty() ? 1.0f : l.bn_scale[co];
-        for (int tap = 0; tap < tl.n_taps; ++tap)
-          for (int ci = 0; ci < l.cin; ++ci)
-            wt[static_cast<size_t>(ci) * cols + static_cast<size_t>(tl.tap_pos[tap]) * tl.g_ld + co] =
-                __float2bfloat16(l.raw_kernel[static_cast<size_t>(co) * l.k_total + tap * l.cin + ci] * sc);
-      }
-      PPB_TRY(e.device_alloc(&p, wt.size() * sizeof(__nv_bfloat16)));
+      PPB_TRY(e.device_alloc(&p, static_cast<size_t>(l.cin) * cols * sizeof(__nv_bfloat16)));
       tl.w_dgrad = static_cast<__nv_bfloat16*>(p);
-      PPB_CUDA(cudaMemcpy(tl.w_dgrad, wt.data(), wt.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
     }
+    PPB_TRY(seed_layer(e, t, static_cast<int>(i)));
     ParamDesc d;
     memset(&d, 0, sizeof(d));
     d.offset = tl.off_kernel;
@@ -419,7 +458,6 @@ int create_state(Engine& e) {
     for (int k = 0; k < 9; ++k) d.tap_pos[k] = tl.tap_pos[k];
     t.descs.push_back(d);
     if (l.has_bias) {
-      std::copy(l.raw_bias.begin(), l.raw_bias.end(), master.begin() + tl.off_bias);
       ParamDesc b;
       memset(&b, 0, sizeof(b));
       b.offset = tl.off_bias;
@@ -443,7 +481,6 @@ int create_state(Engine& e) {
     }
   }
   t.n_chunks = static_cast<int>(chunk_desc.size());
-  PPB_CUDA(cudaMemcpy(t.master, master.data(), off * sizeof(float), cudaMemcpyHostToDevice));
   PPB_TRY(e.device_alloc(&p, t.descs.size() * sizeof(ParamDesc)));
   t.descs_dev = static_cast<ParamDesc*>(p);
   PPB_CUDA(cudaMemcpy(t.descs_dev, t.descs.data(), t.descs.size() * sizeof(ParamDesc), cudaMemcpyHostToDevice));
@@ -461,6 +498,8 @@ int build_backward(Engine& e, int batch, const float* y_reg, const float* y_cls,
                    const float* out_reg, const float* out_cls, const float* out_mask) {
   TrainState& t = *e.train;
   t.bwd.clear();
+  t.count_ops.clear();
+  for (TrainLayer& tl : t.tl) tl.last_grad_op = -1;
   Builder B{e, t, batch};
   const int A = e.num_anchors, C = e.num_classes;
   const long long featrows = e.feat_rows_total;
@@ -497,7 +536,7 @@ int build_backward(Engine& e, int batch, const float* y_reg, const float* y_cls,
       op.a[0] = width[i];
       op.a[1] = i;
       snprintf(op.name, sizeof(op.name), "count_positive:%d", i);
-      t.bwd.push_back(op);
+      t.count_ops.push_back(op);
     }
     TOp r;
     r.kind = kTOrth;
@@ -684,9 +723,9 @@ int build_backward(Engine& e, int batch, const float* y_reg, const float* y_cls,
   return kOk;
 }
 
-int launch_backward(Engine& e, cudaStream_t st) {
+int launch_op(Engine& e, const TOp& op, cudaStream_t st) {
   TrainState& t = *e.train;
-  for (const TOp& op : t.bwd) {
+  {
     switch (op.kind) {
       case kTConv:
         PPB_CUDA(conv_launch(op.ta, op.tb, op.to, op.tr, op.p, 0, st));
@@ -724,16 +763,119 @@ int launch_backward(Engine& e, cudaStream_t st) {
   return kOk;
 }
 
-int launch_step(Engine& e, cudaStream_t st) {
+int launch_backward(Engine& e, int op_begin, int op_end, cudaStream_t st) {
   TrainState& t = *e.train;
-  PPB_CUDA(cudaMemsetAsync(t.grads, 0, t.n_params * sizeof(float), st));
-  PPB_CUDA(cudaMemsetAsync(t.loss, 0, 8 * sizeof(double), st));
+  for (int i = op_begin; i < op_end; ++i) PPB_TRY(launch_op(e, t.bwd[i], st));
+  return kOk;
+}
+
+// Positives of the three outputs (the loss normalisers, losses.py:61-66 / 395-397). They depend on the targets only,
+// so they run ahead of the forward pass and a data-parallel caller can sum them over the replicas first — the
+// normaliser of keras.utils.multi_gpu_model, which computes each loss once over the concatenated outputs
+// (PyraPose/bin/train.py:82-86).
+int launch_counts(Engine& e, cudaStream_t st) {
+  TrainState& t = *e.train;
   PPB_CUDA(cudaMemsetAsync(t.counts, 0, 4 * sizeof(int), st));
-  PPB_TRY(e.launch_all(st));
-  return launch_backward(e, st);
+  for (const TOp& op : t.count_ops) PPB_TRY(launch_op(e, op, st));
+  t.counts_ready = true;
+  return kOk;
+}
+
+// Segment `si` as plain launches: segment 0 zeroes the accumulators and runs the forward pass first.
+int launch_segment(Engine& e, int si, cudaStream_t st) {
+  TrainState& t = *e.train;
+  const Segment& sg = t.segs[si];
+  if (si == 0) {
+    PPB_CUDA(cudaMemsetAsync(t.grads, 0, t.n_params * sizeof(float), st));
+    PPB_CUDA(cudaMemsetAsync(t.loss, 0, 8 * sizeof(double), st));
+    PPB_TRY(e.launch_all(st));
+  }
+  return launch_backward(e, sg.op_begin, sg.op_end, st);
+}
+
+// Cuts the backward op list after the op that completes each gradient bucket. Buckets are contiguous slices of the
+// flat buffer of about `bucket_bytes`, cut at layer boundaries; the backward pass runs heads -> PFPN -> res5 -> res3,
+// i.e. roughly from the END of the buffer (layer order) to its beginning.
+void plan_segments(Engine& e) {
+  TrainState& t = *e.train;
+  t.drop_graphs();
+  t.segs.clear();
+  const int n_ops = static_cast<int>(t.bwd.size());
+  struct Bucket {
+    long long lo, hi;
+    int ready;
+  };
+  std::vector<Bucket> buckets;
+  if (t.bucket_bytes > 0) {
+    std::vector<int> order;  // trainable layers by descending offset
+    for (size_t i = 0; i < t.tl.size(); ++i)
+      if (t.tl[i].trainable && t.tl[i].last_grad_op >= 0) order.push_back(static_cast<int>(i));
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return t.tl[a].off_kernel > t.tl[b].off_kernel; });
+    long long hi = t.n_params;
+    Bucket cur{hi, hi, -1};
+    for (size_t k = 0; k < order.size(); ++k) {
+      const TrainLayer& tl = t.tl[order[k]];
+      cur.lo = tl.off_kernel;
+      cur.ready = std::max(cur.ready, tl.last_grad_op);
+      if ((cur.hi - cur.lo) * static_cast<long long>(sizeof(float)) >= t.bucket_bytes || k + 1 == order.size()) {
+        if (k + 1 == order.size()) cur.lo = 0;
+        buckets.push_back(cur);
+        cur = Bucket{cur.lo, cur.lo, -1};
+      }
+    }
+    std::stable_sort(buckets.begin(), buckets.end(), [](const Bucket& a, const Bucket& b) { return a.ready < b.ready; });
+  }
+  int begin = 0;
+  for (const Bucket& b : buckets) {
+    Segment sg;
+    sg.op_begin = begin;
+    sg.op_end = std::max(begin, b.ready + 1);
+    sg.g_off = b.lo;
+    sg.g_cnt = b.hi - b.lo;
+    begin = sg.op_end;
+    t.segs.push_back(sg);
+  }
+  if (begin < n_ops || t.segs.empty()) {  // the rest (data gradients after the last weight gradient), or the whole step
+    Segment sg;
+    sg.op_begin = begin;
+    sg.op_end = n_ops;
+    if (buckets.empty()) {
+      sg.g_off = 0;
+      sg.g_cnt = t.n_params;
+    }
+    t.segs.push_back(sg);
+  }
+}
+
+int capture_segments(Engine& e, cudaStream_t st) {
+  TrainState& t = *e.train;
+  t.graph_kernels = static_cast<int>(e.ops.size() + t.bwd.size());
+  for (size_t si = 0; si < t.segs.size(); ++si) {
+    Segment& sg = t.segs[si];
+    sg.kernels = sg.op_end - sg.op_begin + (si == 0 ? static_cast<int>(e.ops.size()) : 0);
+    if (sg.kernels == 0) continue;  // a bucket that was already complete: nothing to launch
+    PPB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    const int rc = launch_segment(e, static_cast<int>(si), st);
+    cudaGraph_t g = nullptr;
+    const cudaError_t end = cudaStreamEndCapture(st, &g);
+    if (rc != kOk) {
+      if (g) cudaGraphDestroy(g);
+      return rc;
+    }
+    PPB_CUDA(end);
+    sg.graph = g;
+    PPB_CUDA(cudaGraphInstantiate(&sg.exec, sg.graph, 0));
+  }
+  return kOk;
 }
 
 }  // namespace
+
+int train_refresh_layer(Engine& e, int layer) {
+  if (!e.train) return kOk;
+  return seed_layer(e, *e.train, layer);
+}
+
 }  // namespace ppb
 
 using namespace ppb;
@@ -755,41 +897,91 @@ int ppb_engine_train_bind(ppb_engine* h, int batch, const float* images, const f
     rc = create_state(e);
     if (rc != kOk) return rc;
   }
+  e.train->bucket_bytes = e.train_bucket_bytes;
   rc = build_backward(e, batch, y_reg, y_cls, y_mask, out_reg, out_cls, out_mask);
   if (rc != kOk) {
     e.train->bound_batch = 0;
     return rc;
   }
   TrainState& t = *e.train;
-  if (t.exec) {
-    cudaGraphExecDestroy(t.exec);
-    t.exec = nullptr;
-  }
-  if (t.graph) {
-    cudaGraphDestroy(t.graph);
-    t.graph = nullptr;
-  }
+  plan_segments(e);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaStream_t own = nullptr;
   if (st == nullptr) {
     PPB_CUDA(cudaStreamCreateWithFlags(&own, cudaStreamNonBlocking));
     st = own;
   }
-  PPB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-  rc = launch_step(e, st);
-  cudaGraph_t g = nullptr;
-  const cudaError_t end = cudaStreamEndCapture(st, &g);
+  rc = capture_segments(e, st);
   if (own) cudaStreamDestroy(own);
   if (rc != kOk) {
-    if (g) cudaGraphDestroy(g);
     t.bound_batch = 0;
     return rc;
   }
-  PPB_CUDA(end);
-  t.graph = g;
-  PPB_CUDA(cudaGraphInstantiate(&t.exec, t.graph, 0));
-  t.graph_kernels = static_cast<int>(e.ops.size() + t.bwd.size());
+  t.counts_ready = false;
   e.bound_batch = 0;  // the inference graph (if any) no longer matches the plan
+  return kOk;
+}
+
+int ppb_engine_train_set_bucket_bytes(ppb_engine* h, long long bucket_bytes) {
+  PPB_REQUIRE(h != nullptr && bucket_bytes >= 0, "ppb_engine_train_set_bucket_bytes: bad argument");
+  Engine& e = h->e;
+  e.train_bucket_bytes = bucket_bytes;
+  if (e.train && e.train->bucket_bytes != bucket_bytes) {
+    e.train->bucket_bytes = bucket_bytes;
+    e.train->bound_batch = 0;  // the segment graphs no longer match: force a re-bind
+  }
+  return kOk;
+}
+
+int ppb_engine_train_count(ppb_engine* h, void* stream) {
+  PPB_REQUIRE(h != nullptr, "ppb_engine_train_count: null engine");
+  Engine& e = h->e;
+  if (!e.train || e.train->bound_batch == 0) return fail(kErrState, "ppb_engine_train_count: call ppb_engine_train_bind first");
+  PPB_CUDA(cudaSetDevice(e.device));
+  const int rc = launch_counts(e, static_cast<cudaStream_t>(stream));
+  if (rc == kOk) count_launch(static_cast<int>(e.train->count_ops.size()));
+  return rc;
+}
+
+int ppb_engine_train_counts(ppb_engine* h, int** counts_dev) {
+  PPB_REQUIRE(h != nullptr && h->e.train && counts_dev != nullptr, "ppb_engine_train_counts: training state not created");
+  *counts_dev = h->e.train->counts;
+  return kOk;
+}
+
+int ppb_engine_train_num_segments(const ppb_engine* h) {
+  return (h && h->e.train && h->e.train->bound_batch != 0) ? static_cast<int>(h->e.train->segs.size()) : 0;
+}
+
+int ppb_engine_train_segment_info(const ppb_engine* h, int segment, long long* grad_offset, long long* grad_count,
+                                  int* n_launches) {
+  PPB_REQUIRE(h != nullptr && h->e.train && segment >= 0 && segment < static_cast<int>(h->e.train->segs.size()),
+              "ppb_engine_train_segment_info: bad segment %d", segment);
+  const Segment& sg = h->e.train->segs[segment];
+  if (grad_offset) *grad_offset = sg.g_off;
+  if (grad_count) *grad_count = sg.g_cnt;
+  if (n_launches) *n_launches = sg.kernels;
+  return kOk;
+}
+
+int ppb_engine_train_run_segment(ppb_engine* h, int segment, void* stream) {
+  PPB_REQUIRE(h != nullptr, "ppb_engine_train_run_segment: null engine");
+  Engine& e = h->e;
+  if (!e.train || e.train->bound_batch == 0)
+    return fail(kErrState, "ppb_engine_train_run_segment: call ppb_engine_train_bind first");
+  TrainState& t = *e.train;
+  PPB_REQUIRE(segment >= 0 && segment < static_cast<int>(t.segs.size()), "ppb_engine_train_run_segment: bad segment %d",
+              segment);
+  PPB_CUDA(cudaSetDevice(e.device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (segment == 0 && !t.counts_ready) {
+    const int rc = launch_counts(e, st);
+    if (rc != kOk) return rc;
+  }
+  const Segment& sg = t.segs[segment];
+  if (sg.exec != nullptr) PPB_CUDA(cudaGraphLaunch(sg.exec, st));
+  count_launch(sg.kernels);
+  if (segment + 1 == static_cast<int>(t.segs.size())) t.counts_ready = false;
   return kOk;
 }
 
@@ -800,12 +992,20 @@ int ppb_engine_train_forward_backward(ppb_engine* h, int eager, void* stream) {
     return fail(kErrState, "ppb_engine_train_forward_backward: call ppb_engine_train_bind first");
   PPB_CUDA(cudaSetDevice(e.device));
   TrainState& t = *e.train;
-  if (eager) {
-    const int rc = launch_step(e, static_cast<cudaStream_t>(stream));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (!t.counts_ready) {
+    const int rc = launch_counts(e, st);
     if (rc != kOk) return rc;
-  } else {
-    PPB_CUDA(cudaGraphLaunch(t.exec, static_cast<cudaStream_t>(stream)));
   }
+  for (size_t si = 0; si < t.segs.size(); ++si) {
+    if (eager) {
+      const int rc = launch_segment(e, static_cast<int>(si), st);
+      if (rc != kOk) return rc;
+    } else if (t.segs[si].exec != nullptr) {
+      PPB_CUDA(cudaGraphLaunch(t.segs[si].exec, st));
+    }
+  }
+  t.counts_ready = false;
   count_launch(t.graph_kernels);
   return kOk;
 }
@@ -904,11 +1104,10 @@ int ppb_engine_train_profile(ppb_engine* h, void* stream, float* ms_out_host, in
   for (auto& x : ev) PPB_CUDA(cudaEventCreate(&x));
   PPB_CUDA(cudaMemsetAsync(t.grads, 0, t.n_params * sizeof(float), st));
   PPB_CUDA(cudaMemsetAsync(t.loss, 0, 8 * sizeof(double), st));
-  PPB_CUDA(cudaMemsetAsync(t.counts, 0, 4 * sizeof(int), st));
+  PPB_TRY(launch_counts(e, st));
+  t.counts_ready = false;
   std::vector<Op> all_f;
-  std::vector<TOp> all_b;
   all_f.swap(e.ops);
-  all_b.swap(t.bwd);
   int rc = kOk;
   cudaEventRecord(ev[0], st);
   for (int i = 0; i < nf && rc == kOk; ++i) {
@@ -916,14 +1115,11 @@ int ppb_engine_train_profile(ppb_engine* h, void* stream, float* ms_out_host, in
     rc = e.launch_all(st);
     cudaEventRecord(ev[i + 1], st);
   }
-  e.ops.clear();
+  e.ops.swap(all_f);
   for (int i = 0; i < nb && rc == kOk; ++i) {
-    t.bwd.assign(1, all_b[i]);
-    rc = launch_backward(e, st);
+    rc = launch_backward(e, i, i + 1, st);
     cudaEventRecord(ev[nf + i + 1], st);
   }
-  e.ops.swap(all_f);
-  t.bwd.swap(all_b);
   const cudaError_t sync = cudaStreamSynchronize(st);
   if (rc == kOk && sync == cudaSuccess) {
     for (int i = 0; i < nf + nb && i < cap; ++i) cudaEventElapsedTime(&ms_out_host[i], ev[i], ev[i + 1]);

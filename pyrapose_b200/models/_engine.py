@@ -155,10 +155,11 @@ class Engine(object):
         return out
 
     # ------------------------------------------------------------------ training step (ppb_engine_train_*)
-    def train_bind(self, batch, input_u8=False):
+    def train_bind(self, batch, input_u8=False, bucket_bytes=0):
         """Allocates the step's device buffers (inputs, targets, the three model outputs) and captures
-        forward + losses + backward as one CUDA graph. Returns the buffer dict."""
-        key = ("train", int(batch), bool(input_u8))
+        forward + losses + backward as one CUDA graph — or, with bucket_bytes > 0, as one graph per gradient bucket
+        (train_num_segments / train_run_segment) for the overlapped data-parallel exchange. Returns the buffer dict."""
+        key = ("train", int(batch), bool(input_u8), int(bucket_bytes))
         if self._bound == key:
             return self.buffers
         dev = self.device
@@ -178,6 +179,7 @@ class Engine(object):
         with torch.cuda.device(dev):
             torch.cuda.current_stream().synchronize()
             self._set_input(input_u8)
+            nat.check(self.lib.ppb_engine_train_set_bucket_bytes(self._h, ctypes.c_longlong(int(bucket_bytes))))
             nat.check(self.lib.ppb_engine_train_bind(self._h, B, nat.ptr(buf["images"]), nat.ptr(buf["y_reg"]),
                                                      nat.ptr(buf["y_cls"]), nat.ptr(buf["y_mask"]),
                                                      nat.ptr(buf["3Dbox"]), nat.ptr(buf["cls"]), nat.ptr(buf["mask"]),
@@ -185,7 +187,41 @@ class Engine(object):
         self.buffers = buf
         self._bound = key
         self._grads = None
+        self._counts = None
         return buf
+
+    def train_count(self):
+        """Positives of the three outputs -> the device counters (train_counts_tensor); targets only, no forward."""
+        with torch.cuda.device(self.device):
+            nat.check(self.lib.ppb_engine_train_count(self._h, nat.current_stream_ptr()))
+
+    def train_counts_tensor(self):
+        """The engine's int32[4] positive counters as a torch tensor sharing the device memory."""
+        if getattr(self, "_counts", None) is None:
+            p = ctypes.POINTER(ctypes.c_int)()
+            nat.check(self.lib.ppb_engine_train_counts(self._h, ctypes.byref(p)))
+            addr = ctypes.cast(p, ctypes.c_void_p).value
+
+            class _Cnt(object):
+                __cuda_array_interface__ = {"shape": (4,), "typestr": "<i4", "data": (int(addr), False),
+                                            "version": 2, "strides": None}
+            with torch.cuda.device(self.device):
+                self._counts = torch.as_tensor(_Cnt(), device=self.device)
+        return self._counts
+
+    def train_segments(self):
+        """[(grad_offset, grad_count, launches)] per segment graph of the bound step."""
+        out = []
+        off, cnt, nl = ctypes.c_longlong(), ctypes.c_longlong(), ctypes.c_int()
+        for i in range(self.lib.ppb_engine_train_num_segments(self._h)):
+            nat.check(self.lib.ppb_engine_train_segment_info(self._h, i, ctypes.byref(off), ctypes.byref(cnt),
+                                                             ctypes.byref(nl)))
+            out.append((off.value, cnt.value, nl.value))
+        return out
+
+    def train_run_segment(self, i):
+        with torch.cuda.device(self.device):
+            nat.check(self.lib.ppb_engine_train_run_segment(self._h, int(i), nat.current_stream_ptr()))
 
     def train_forward_backward(self, eager=False):
         with torch.cuda.device(self.device):

@@ -36,7 +36,9 @@ class PFPNModel(object):
         self.layers = spec.all_layers(self.num_classes, self.num_anchors)
         self.weights = weights if weights is not None else spec.init_weights(
             self.num_classes, self.num_anchors, seed=1 if seed is None else seed)
-        self._engines = {}
+        self._engines = {}         # (H, W) -> Engine; SHARED with the prediction model convert_model builds
+        self._parent = None        # prediction model: the training model whose layers (engines, weights) it shares
+        self._host_out = {}        # predict_on_batch: persistent pinned output buffers per output shape
         self.regress_mean = None   # RegressBoxes3D(mean, std) defaults: 0 / 0.2 (layers/_misc.py:176-179)
         self.regress_std = None
 
@@ -59,11 +61,15 @@ class PFPNModel(object):
             print_fn("%-28s conv %dx%d/%d  %4d -> %4d  params %d" % (l.name, l.ksize, l.ksize, l.stride, l.cin, l.cout, n))
         print_fn("Total params: {:,}".format(total))
 
+    def _root(self):
+        return self if self._parent is None else self._parent._root()
+
     def get_weights_dict(self):
         self.sync_weights()
         return self.weights
 
     def set_weights_dict(self, weights, skip_mismatch=False):
+        self.sync_weights()   # tensors NOT named in `weights` keep their trained values
         for k, v in weights.items():
             if k not in self.weights:
                 continue  # by_name semantics: unknown names are ignored
@@ -109,15 +115,23 @@ class PFPNModel(object):
         eng = self._engines.get(key)
         if eng is None or eng.max_batch < batch:
             if eng is not None:
+                # a larger batch needs a larger arena: the trained master weights go back into self.weights first so
+                # the new engine starts from them (the Adam moments restart)
+                self._root().sync_weights()
+                if self._root().__dict__.get('_train_engine') is eng:
+                    self._root()._train_engine = None
                 eng.close()
             dev = self.device if self.device is not None else torch.cuda.current_device()
             eng = Engine(dev, batch, height, width, self.num_classes, self.num_anchors)
             eng.load_weights(self.weights, self._bn_names())
+            eng._anchor_owner = None
+            self._engines[key] = eng
+        if getattr(eng, '_anchor_owner', None) is not self:
             p = self.anchor_params
             # Anchors layer: float64 base anchors cast to float32 (layers/_misc.py:52-56)
             base = np.stack([generate_anchors(p.sizes[i], p.ratios, p.scales).astype(np.float32) for i in range(3)])
             eng.set_anchors(base, np.asarray(p.strides[:3], np.float32), self.regress_mean, self.regress_std)
-            self._engines[key] = eng
+            eng._anchor_owner = self
         return eng
 
     @staticmethod
@@ -155,8 +169,23 @@ class PFPNModel(object):
         """ Returns [boxes3D (B,N,16), classification (B,N,C), mask (B,H/8*W/8,C)] float32 numpy for an inference
         model ([3Dbox, cls, mask] for a training model), as the reference's model.predict_on_batch does
         (PyraPose/utils/linemod_eval.py:303)."""
+        import torch
         buf = self.forward_device(x)
-        return [buf["boxes3D"].cpu().numpy(), buf["cls"].cpu().numpy(), buf["mask"].cpu().numpy()]
+        outs = [buf["boxes3D"], buf["cls"], buf["mask"]]
+        key = tuple(tuple(o.shape) for o in outs)
+        host = self._host_out.get(key)
+        if host is None:
+            # persistent pinned buffers: the three device->host copies (234 MB at batch 32) run at PCIe rate as
+            # asynchronous DMAs instead of three blocking pageable copies
+            if len(self._host_out) >= 4:
+                self._host_out.clear()
+            host = self._host_out[key] = [torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs]
+        with torch.cuda.device(outs[0].device):
+            for h, o in zip(host, outs):
+                h.copy_(o, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        # the caller owns what it gets (Keras returns fresh arrays): one host memcpy per output
+        return [h.numpy().copy() for h in host]
 
     def detect_on_batch(self, x, score_threshold=0.05, max_detections=300, nms=True, nms_threshold=0.5,
                         class_specific_filter=True):
@@ -248,10 +277,28 @@ class PFPNModel(object):
         return self._engines[(height, width)].activation(name)
 
     # ------------------------------------------------------------------ training (keras.Model.compile / train_on_batch)
-    def compile(self, loss=None, optimizer=None, **kwargs):
+    def compile(self, loss=None, optimizer=None, dp_normalizer='global', bucket_bytes=25 << 20, data_parallel=True,
+                **kwargs):
         """ Mirror of `training_model.compile(loss={'3Dbox': orthogonal_l1(), 'cls': focal(), 'mask': focal()},
         optimizer=Adam(lr, clipnorm=0.001))` (PyraPose/bin/train.py:95-102). Only that configuration exists in the
-        native step; anything else raises ValueError."""
+        native step; anything else raises ValueError.
+
+        Data parallel (one process per GPU, torch.distributed initialised; the reference's
+        keras.utils.multi_gpu_model, bin/train.py:82-86):
+          dp_normalizer='global'  — the losses are normalised by the positives of the GLOBAL batch and the replica
+                                    gradients are summed: exactly the single-replica step on the concatenated batch,
+                                    which is what multi_gpu_model computes (it concatenates the replica outputs and
+                                    evaluates each loss once);
+          dp_normalizer='replica' — every replica normalises by its own positives (losses.py:61-66 on the local
+                                    batch) and the gradients are averaged.
+          bucket_bytes            — size of the gradient buckets whose NCCL all-reduce overlaps the rest of the
+                                    backward pass (0: one all-reduce after the backward pass);
+          data_parallel=False     — this model steps alone even when torch.distributed is initialised."""
+        if dp_normalizer not in ('global', 'replica'):
+            raise ValueError("dp_normalizer must be 'global' or 'replica'")
+        self.dp_normalizer = dp_normalizer
+        self.bucket_bytes = int(bucket_bytes)
+        self.data_parallel = bool(data_parallel)
         from .. import losses, optimizers
         if self.inference:
             raise ValueError("compile() needs a training model")
@@ -268,17 +315,18 @@ class PFPNModel(object):
         if not isinstance(self.optimizer, optimizers.Adam):
             raise ValueError("optimizer must be pyrapose_b200.optimizers.Adam")
         self._compiled = True
-        self._train_engine = None
+        self._train_engine = getattr(self, '_train_engine', None)
         self.metrics_names = ['loss', '3Dbox_loss', 'cls_loss', 'mask_loss']
 
     def train_on_batch(self, x, y, sync_losses=True):
         """ One optimisation step on a batch, as `fit_generator` runs it for every batch of the reference generator.
 
         x: images (B,H,W,3) float32 (mean-subtracted) or raw uint8 BGR; y: [regression_3D (B,N,17), labels (B,N,C+1), mask (B,H/8*W/8,C+1)] — the three
-        arrays anchor_targets_bbox returns. numpy or CUDA tensors. With torch.distributed initialised the flat
-        gradient buffer is all-reduced (NCCL) and averaged before the Adam step (one replica per GPU).
-        Returns [loss, 3Dbox_loss, cls_loss, mask_loss] (loss includes the l2 regulariser) — of the local replica's
-        batch, like Keras — or None when sync_losses=False (no host synchronisation)."""
+        arrays anchor_targets_bbox returns. numpy or CUDA tensors. With torch.distributed initialised (one replica per
+        GPU) the gradient buckets are all-reduced over NCCL while the rest of the backward pass runs; see compile().
+        Returns [loss, 3Dbox_loss, cls_loss, mask_loss] (loss includes the l2 regulariser) — the local replica's
+        share (with dp_normalizer='global' the shares of all replicas add up to the loss of the global batch) — or
+        None when sync_losses=False (no host synchronisation)."""
         import torch
         if not getattr(self, '_compiled', False):
             raise RuntimeError("You must compile a model before training/testing. Use `model.compile(optimizer, loss)`.")
@@ -286,8 +334,10 @@ class PFPNModel(object):
             raise ValueError("expected y = [regression_3D, labels, mask]")
         x, u8 = self._as_input(x)
         B, H, W = int(x.shape[0]), int(x.shape[1]), int(x.shape[2])
+        dist = torch.distributed
+        world = dist.get_world_size() if (self.data_parallel and dist.is_available() and dist.is_initialized()) else 1
         eng = self._engine(B, H, W)
-        buf = eng.train_bind(B, input_u8=u8)
+        buf = eng.train_bind(B, input_u8=u8, bucket_bytes=self.bucket_bytes if world > 1 else 0)
         self._train_engine = eng
 
         def put(dst, src):
@@ -303,12 +353,24 @@ class PFPNModel(object):
             put(buf["y_reg"], y[0])
             put(buf["y_cls"], y[1])
             put(buf["y_mask"], y[2])
-            eng.train_forward_backward()
             scale = 1.0
-            if torch.distributed.is_available() and torch.distributed.is_initialized() and \
-                    torch.distributed.get_world_size() > 1:
-                torch.distributed.all_reduce(eng.grads_tensor())
-                scale = 1.0 / torch.distributed.get_world_size()
+            if world > 1:
+                # bucketed exchange: the all-reduce of gradient bucket k runs on NCCL's stream while segment k + 1 of
+                # the backward pass runs on this one (async_op=True: NCCL's stream waits for the work queued so far)
+                eng.train_count()
+                if self.dp_normalizer == 'global':
+                    dist.all_reduce(eng.train_counts_tensor())
+                else:
+                    scale = 1.0 / world
+                grads, works = eng.grads_tensor(), []
+                for i, (off, cnt, _) in enumerate(eng.train_segments()):
+                    eng.train_run_segment(i)
+                    if cnt > 0:
+                        works.append(dist.all_reduce(grads[off:off + cnt], async_op=True))
+                for w in works:
+                    w.wait()
+            else:
+                eng.train_forward_backward()
             eng.train_apply(opt.lr, opt.beta_1, opt.beta_2, opt.epsilon, opt.clipnorm, scale)
         self._weights_stale = True
         if not sync_losses:
@@ -319,6 +381,8 @@ class PFPNModel(object):
 
     def sync_weights(self):
         """Copies the trained master weights from the engine back into `self.weights` (Keras HWIO layout)."""
+        if self._parent is not None:
+            return self._parent.sync_weights()   # the prediction model shares the training model's dict
         eng = getattr(self, '_train_engine', None)
         if eng is None or not getattr(self, '_weights_stale', False):
             return
@@ -356,4 +420,10 @@ def retinanet_bbox(model=None, nms=True, class_specific_filter=True, name='retin
         assert_training_model(model)
     out = PFPNModel(model.num_classes, model.num_anchors, name=name, inference=True, anchor_params=anchor_params,
                     weights=model.weights, device=model.device)
+    # Like the reference (bin/train.py:86-92: prediction_model = retinanet_bbox(model=model) is built BEFORE training
+    # and evaluated after every epoch), the prediction model shares the training model's layers: same weight dict,
+    # same engines. The Adam kernel rewrites the bf16 forward matrices in place, so a predict_on_batch after
+    # train_on_batch runs on the trained weights with no copy.
+    out._engines = model._engines
+    out._parent = model
     return out

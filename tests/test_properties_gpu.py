@@ -130,6 +130,10 @@ def test_engine_full_batch_equals_single_image_runs(cuda_device):
     infer = models.convert_model(train)
     rng = np.random.default_rng(3)
     img = rng.integers(0, 256, (B, H, W, 3)).astype(np.float32) - np.array([103.939, 116.779, 123.68], np.float32)
+    # image 0 IS the image (and these are the weights) of tests/test_engine_gpu.py::test_engine_matches_oracle
+    # [480x640_C15]: the batch-32 run is chained directly to the case compared with the fp32 oracle
+    from test_engine_gpu import make_images
+    img[0] = make_images(1, 1, H, W)[0]
     full = [np.array(o, copy=True) for o in infer.predict_on_batch(img)]
     assert full[0].shape == (B, 56700, 16) and full[1].shape == (B, 56700, C) and full[2].shape == (B, 4800, C)
     det_full = [np.array(o, copy=True) for o in infer.detect_on_batch(img)]

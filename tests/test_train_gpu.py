@@ -197,3 +197,44 @@ def test_second_step_decreases_nothing_weird(step):
     b = model.train_on_batch(img, y)
     assert all(np.isfinite(a)) and all(np.isfinite(b))
     assert b[0] < a[0] * 1.05
+
+
+def test_prediction_model_follows_training(cuda_device, tmp_path):
+    """The reference builds prediction_model = retinanet_bbox(model) BEFORE training and evaluates through it after
+    every epoch (PyraPose/bin/train.py:86-92, 119-129): the two share their layers. Here they share the engine: a
+    predict_on_batch after train_on_batch must run on the TRAINED weights, convert_model() after training too, and
+    save -> load_model must reproduce them."""
+    from pyrapose_b200 import models, optimizers
+    from pyrapose_b200.models import spec
+    from pyrapose_b200.utils.anchors import anchor_targets_bbox, anchors_for_shape
+    weights = spec.init_weights(C, seed=9, head_init="spread", randomize_bn=True)
+    rng = np.random.default_rng(17)
+    img = rng.integers(0, 256, (B, H, W, 3)).astype(np.float32) - np.array([103.939, 116.779, 123.68], np.float32)
+    y = _targets(anchors_for_shape, anchor_targets_bbox)
+    train = models.backbone("resnet50").retinanet(num_classes=C)
+    train.set_weights_dict({k: v.copy() for k, v in weights.items()})
+    pred = models.convert_model(train)                      # built before training, like train.py:92
+    before = pred.predict_on_batch(img)
+    train.compile(optimizer=optimizers.Adam(lr=1e-2, clipnorm=0.001))
+    for _ in range(3):
+        train.train_on_batch(img, y)
+    after = pred.predict_on_batch(img)
+    assert np.abs(after[1] - before[1]).max() > 1e-3, "the prediction model still runs the initial weights"
+    t_out = train.predict_on_batch(img)                     # training model: [3Dbox raw, cls, mask]
+    assert np.array_equal(after[1], t_out[1]) and np.array_equal(after[2], t_out[2])
+    late = models.convert_model(train)                      # built after training
+    assert np.array_equal(late.predict_on_batch(img)[1], after[1])
+    # another training step after the inference binds: the engine goes back to the training plan with its state
+    l1 = train.train_on_batch(img, y)
+    assert all(np.isfinite(l1))
+    path = str(tmp_path / "snapshot.npz")
+    pred.save(path)                                         # syncs the trained master weights into the shared dict
+    again = models.load_model(path, backbone_name="resnet50")
+    a, b = again.predict_on_batch(img), pred.predict_on_batch(img)
+    # fp32 master -> bf16 on load vs the Adam kernel's own bf16 rewrite: the same rounding of the same fp32 values
+    assert np.array_equal(a[1], b[1]) and np.array_equal(a[0], b[0])
+    # loading weights into a model that has trained refreshes the training master copy as well
+    train.set_weights_dict({k: v.copy() for k, v in weights.items()})
+    assert np.array_equal(pred.predict_on_batch(img)[1], before[1])
+    new = train.get_weights_dict()
+    assert all(np.array_equal(new[k], weights[k]) for k in weights)
