@@ -253,6 +253,19 @@ PPB_API int ppb_engine_activation(ppb_engine* engine, const char* name, float* o
 PPB_API int ppb_engine_op_info(const ppb_engine* engine, int index, char* name, int name_cap, double* flops);
 PPB_API int ppb_engine_profile(ppb_engine* engine, void* stream, float* ms_out_host, int* kind_out_host, int cap);
 
+/* ------------------------------------------------------------------ input staging
+ * preprocess_image('caffe') + resize_image + compute_inputs of ONE image in one kernel
+ * (PyraPose/utils/image.py:35-62, 281-323; PyraPose/preprocessing/generator.py:320-336):
+ *   src  DEVICE raw pixels [src_h,src_w,3], uint8 (src_is_u8) or float32, BGR
+ *   dst  DEVICE f32 [pad_h,pad_w,3]: the image's slot of the zero-padded batch tensor; rows < dst_h / cols < dst_w
+ *        receive the bilinearly resized (cv2.resize(img, None, fx, fy), OpenCV's float32 INTER_LINEAR arithmetic),
+ *        mean-subtracted pixels, everything else zeros
+ *   dst_h = cvRound(src_h * fy), dst_w = cvRound(src_w * fx) (the caller computes them, like cv::resize does)
+ *   mean3_host: HOST float[3] subtracted per channel, or NULL for none. */
+PPB_API int ppb_resize_preprocess_f32(const void* src, int src_is_u8, int src_h, int src_w, float* dst, int dst_h,
+                                      int dst_w, int pad_h, int pad_w, double fx, double fy, const float* mean3_host,
+                                      void* stream);
+
 /* ------------------------------------------------------------------ training step (BASELINE.json config 4)
  * Replaces one batch of `training_model.fit_generator(...)` (PyraPose/bin/train.py:381-390) for the model compiled at
  * train.py:95-102: loss = {'3Dbox': orthogonal_l1(), 'cls': focal(), 'mask': focal()} (PyraPose/losses.py:22-68,

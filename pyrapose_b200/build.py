@@ -30,6 +30,7 @@ def _optional_sources():
         ("overlap.cu", True),
         ("anchors.cu", True),
         ("decode.cu", True),
+        ("image.cu", True),
         ("filter.cu", True),
         ("elementwise.cu", False),
         ("engine.cu", False),

@@ -45,8 +45,9 @@ def backbone(backbone_name):
 
 
 def load_model(filepath, backbone_name='resnet50'):
-    """ Loads a model saved with `model.save(filepath)` (npz container keyed by Keras layer names, HWIO kernels;
-    HDF5 needs h5py, which this image does not have)."""
+    """ Loads a model saved with `model.save(filepath)`: a Keras HDF5 snapshot (this package's or the reference's
+    ModelCheckpoint files, read by utils/hdf5.py and mapped by models/keras_io.py) or an npz container keyed by Keras
+    layer names (HWIO kernels)."""
     from .retinanet import PFPNModel
     backbone(backbone_name)  # validates the name like the reference does
     return PFPNModel.load(filepath)

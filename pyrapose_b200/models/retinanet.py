@@ -83,22 +83,59 @@ class PFPNModel(object):
             e.load_weights(self.weights, self._bn_names())
 
     def load_weights(self, filepath, by_name=True, skip_mismatch=False):
-        """npz container keyed '<keras layer name>/<param>' (HWIO kernels). by_name=True semantics."""
+        """`model.load_weights(path, by_name=True, skip_mismatch=...)` (PyraPose/bin/train.py:65-68).
+        Keras HDF5 files (what the reference writes and what keras-resnet's ImageNet checkpoint is,
+        PyraPose/models/resnet.py:89-98) are read by the pure-Python reader in utils/hdf5.py and mapped to this model's
+        layers by name where the reference names them and by graph order where it does not (models/keras_io.py);
+        .npz containers keyed '<layer>/<param>' are accepted as well. Layers the file does not hold keep their values
+        (by_name semantics); a shape mismatch raises unless skip_mismatch."""
+        from . import keras_io
+        if keras_io.is_hdf5(filepath):
+            w, _unused = keras_io.load_h5(filepath, self.weights.keys())
+            return self.set_weights_dict(w, skip_mismatch=skip_mismatch)
         with np.load(filepath) as z:
             self.set_weights_dict({k: z[k] for k in z.files if not k.startswith("__")}, skip_mismatch=skip_mismatch)
 
+    @staticmethod
+    def _wants_h5(filepath):
+        return str(filepath).lower().endswith((".h5", ".hdf5", ".keras.h5"))
+
     def save_weights(self, filepath):
+        """Keras HDF5 layout with the reference's layer names for *.h5 / *.hdf5 (loadable by the reference's
+        model.load_weights(by_name=True)); npz otherwise."""
         self.sync_weights()
+        if self._wants_h5(filepath):
+            from . import keras_io
+            return keras_io.save_h5(filepath, self.weights, self.layers)
         np.savez(filepath, **self.weights)
 
     def save(self, filepath):
+        """ModelCheckpoint's full-model save (bin/train.py:131-142): *.h5 gets Keras' 'model_weights' group; the
+        architecture travels as (num_classes, num_anchors, inference) instead of Keras' model_config JSON."""
         self.sync_weights()
         meta = np.array([self.num_classes, self.num_anchors, int(self.inference)], dtype=np.int64)
+        if self._wants_h5(filepath):
+            from . import keras_io
+            return keras_io.save_h5(filepath, self.weights, self.layers, meta=meta, full_model=True)
         with open(filepath, "wb") as f:
             np.savez(f, __meta__=meta, **self.weights)
 
     @classmethod
     def load(cls, filepath):
+        from . import keras_io
+        if keras_io.is_hdf5(filepath):
+            layers, attrs = keras_io.read_layers(filepath)
+            if "pyrapose_b200_meta" in attrs:
+                meta = [int(v) for v in np.atleast_1d(attrs["pyrapose_b200_meta"])]
+            else:   # a snapshot written by the reference: classes from the head shapes, inference model
+                meta = [keras_io.infer_classes(layers), 9, 1]
+            model = cls(meta[0], meta[1], inference=bool(meta[2]))
+            w, _unused = keras_io.to_engine_weights(layers, model.weights.keys())
+            missing = [k for k in model.weights if k not in w]
+            if missing:
+                raise ValueError("%s: %d tensors of the model are missing, e.g. %s" % (filepath, len(missing), missing[:3]))
+            model.set_weights_dict(w)
+            return model
         with np.load(filepath) as z:
             meta = z["__meta__"]
             weights = {k: z[k] for k in z.files if not k.startswith("__")}
@@ -170,22 +207,51 @@ class PFPNModel(object):
         model ([3Dbox, cls, mask] for a training model), as the reference's model.predict_on_batch does
         (PyraPose/utils/linemod_eval.py:303)."""
         import torch
+        import weakref
         buf = self.forward_device(x)
         outs = [buf["boxes3D"], buf["cls"], buf["mask"]]
         key = tuple(tuple(o.shape) for o in outs)
-        host = self._host_out.get(key)
-        if host is None:
-            # persistent pinned buffers: the three device->host copies (234 MB at batch 32) run at PCIe rate as
-            # asynchronous DMAs instead of three blocking pageable copies
-            if len(self._host_out) >= 4:
-                self._host_out.clear()
-            host = self._host_out[key] = [torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs]
+        # Output buffers are persistent PINNED host tensors, so the three device->host copies (234 MB at batch 32) are
+        # asynchronous DMAs at PCIe rate, and the arrays handed to the caller are views of them: no host memcpy, no
+        # page faults on 234 MB of fresh memory per call (that alone was 45 ms of a 60 ms call). The caller still OWNS
+        # what it gets, like the fresh arrays Keras returns: a buffer set is only reused once every array handed out
+        # from it (and every view derived from one) has been dropped — tracked with weak references; while the caller
+        # holds on to results, new sets are allocated (up to 4 per output shape, then plain copies).
+        pool = self._host_out.setdefault(key, [])
+        if len(self._host_out) > 4:
+            self._host_out = {key: pool}
+        slot = None
+        for s in pool:
+            if all(r() is None for r in s["refs"]):
+                slot = s
+                break
+        if slot is None and len(pool) < 4:
+            slot = {"host": [torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs], "refs": []}
+            pool.append(slot)
         with torch.cuda.device(outs[0].device):
-            for h, o in zip(host, outs):
+            if slot is None:   # every set is still referenced by the caller: private pageable copies
+                return [o.cpu().numpy() for o in outs]
+            for h, o in zip(slot["host"], outs):
                 h.copy_(o, non_blocking=True)
             torch.cuda.current_stream().synchronize()
-        # the caller owns what it gets (Keras returns fresh arrays): one host memcpy per output
-        return [h.numpy().copy() for h in host]
+        arrays = [h.numpy() for h in slot["host"]]
+        slot["refs"] = [weakref.ref(a) for a in arrays]
+        return arrays
+
+    def predict_on_images(self, raw_images, min_side=480, max_side=640):
+        """ The evaluators' per-image sequence read_image_bgr -> preprocess_image -> resize_image -> predict_on_batch
+        (PyraPose/utils/linemod_eval.py:283-303) for a list of RAW uint8 BGR images of any sizes: preprocessing,
+        bilinear resize and zero padding run on the device straight into the engine's input tensor
+        (utils.image.stage_batch). Returns (predict_on_batch outputs, scales)."""
+        from ..utils import image as ui
+        scales = [ui.compute_resize_scale(im.shape, min_side, max_side) for im in raw_images]
+        shapes = [ui._resized_shape(im.shape, s) for im, s in zip(raw_images, scales)]
+        B, H, W = len(raw_images), max(s[0] for s in shapes), max(s[1] for s in shapes)
+        eng = self._engine(B, H, W)
+        buf = eng.bind(B, decode=self.inference, want_mask=True, want_hull=False, input_u8=False)
+        ui.stage_batch(raw_images, min_side, max_side, out=buf["images"])
+        eng.run()
+        return [buf[k].cpu().numpy() for k in ("boxes3D", "cls", "mask")], scales
 
     def detect_on_batch(self, x, score_threshold=0.05, max_detections=300, nms=True, nms_threshold=0.5,
                         class_specific_filter=True):
