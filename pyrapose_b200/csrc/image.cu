@@ -8,7 +8,7 @@
 // tensor the engine is bound to: resized, mean-subtracted, zero-padded.
 //
 // Arithmetic = OpenCV's float32 INTER_LINEAR path (resize.cpp: hresize then vresize, coefficients computed in float
-// from the double scale): fx = float((dx + 0.5) * scale_x - 0.5); sx = floor(fx); a1 = fx - sx (a1 = 0 and the edge
+// from the double scale): fx = (dx + 0.5) * scale_x - 0.5 in double; sx = floor(fx); a1 = float(fx - sx) (a1 = 0 and the edge
 // pixel when sx falls outside), row value = S[sx] * a0 + S[sx + 1] * a1, pixel = row0 * b0 + row1 * b1. Compiled with
 // -fmad=false, every product and sum rounded separately; OpenCV's SIMD kernels may fuse them, so parity with
 // cv2.resize is stated as <= 2 ulp of the result (tests/test_image_gpu.py), not bit-exact.
@@ -42,9 +42,11 @@ resize_preprocess_kernel(const T* __restrict__ src, int sh, int sw, float* __res
     for (int c = 0; c < 3; ++c) o[c] = static_cast<float>(s[c]) - mean[c];
     return;
   }
-  float fx = static_cast<float>((x + 0.5) * scale_x - 0.5);
-  int sx = static_cast<int>(floorf(fx));
-  fx -= static_cast<float>(sx);
+  // OpenCV 4.13 keeps the source coordinate in double until the integer part is removed (a float32 coordinate near
+  // 1240 would quantise the weight to 1.2e-4); measured against cv2.resize with an alternating 0/1 image.
+  const double fxd = (x + 0.5) * scale_x - 0.5;
+  int sx = static_cast<int>(floor(fxd));
+  float fx = static_cast<float>(fxd - sx);
   if (sx < 0) {
     fx = 0.0f;
     sx = 0;
@@ -53,9 +55,9 @@ resize_preprocess_kernel(const T* __restrict__ src, int sh, int sw, float* __res
     fx = 0.0f;
     sx = sw - 1;
   }
-  float fy = static_cast<float>((y + 0.5) * scale_y - 0.5);
-  int sy = static_cast<int>(floorf(fy));
-  fy -= static_cast<float>(sy);
+  const double fyd = (y + 0.5) * scale_y - 0.5;
+  int sy = static_cast<int>(floor(fyd));
+  float fy = static_cast<float>(fyd - sy);
   if (sy < 0) {
     fy = 0.0f;
     sy = 0;

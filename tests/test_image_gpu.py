@@ -4,7 +4,7 @@ PyraPose/preprocessing/generator.py:320-336.
 
 Tolerance: OpenCV's float32 INTER_LINEAR kernels and the CUDA kernel evaluate the same expression
 (p00*a0 + p01*a1)*b0 + (p10*a0 + p11*a1)*b1 with float coefficients; OpenCV's SIMD code may fuse multiply-adds, so
-results may differ in the last bits: |diff| <= 2e-5 on pixel values of magnitude <= 152 (2 ulp), most pixels identical.
+results may differ in the last bits: |diff| <= 3.1e-5 on pixel values of magnitude <= 152 (2 ulp = 2 x 1.53e-5), most pixels identical.
 Sizes, scales and the padding are exact."""
 import numpy as np
 import pytest
@@ -37,7 +37,7 @@ def test_resize_image_matches_cv2(cuda_device, shape):
     assert scale == ref_scale and got.shape == ref.shape and got.dtype == np.float32
     d = np.abs(got - ref)
     print("resize %s -> %s: max |diff| %.2e, identical %.2f%%" % (shape, got.shape[:2], d.max(), 100 * (d == 0).mean()))
-    assert d.max() <= 2e-5
+    assert d.max() <= 3.1e-5
     assert min(got.shape[:2]) <= 480 and max(got.shape[:2]) <= 640
     with pytest.raises(ValueError):
         ui.resize_image(raw)
@@ -53,10 +53,12 @@ def test_stage_batch_equals_host_pipeline(cuda_device):
     got, scales = ui.stage_batch(raws)
     got = got.cpu().numpy()
     assert scales == ref_scales and got.shape == ref.shape
-    assert np.abs(got - ref).max() <= 2e-5
+    assert np.abs(got - ref).max() <= 3.1e-5
     # padding is exactly zero and the unscaled 480x640 image is bit-identical to preprocess_image
-    assert np.array_equal(got[3, :, 320:], np.zeros_like(got[3, :, 320:]))
-    assert np.array_equal(got[1], ui.preprocess_image(raws[1]))
+    assert got.shape[1:3] == (640, 640) and scales[3] == 1.28          # (500, 333) -> (640, 426)
+    assert np.array_equal(got[3, :, 426:], np.zeros_like(got[3, :, 426:])) and np.abs(got[3, :, 425]).min() > 0
+    assert np.array_equal(got[1, 480:], np.zeros_like(got[1, 480:]))
+    assert np.array_equal(got[1, :480], ui.preprocess_image(raws[1]))
 
 
 def test_predict_on_images_runs_the_staged_batch(cuda_device):

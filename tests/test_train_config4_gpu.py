@@ -203,15 +203,17 @@ def test_data_parallel_global_normaliser_equals_concatenated_batch(cfg4):
         assert abs(l[0][k] + l[1][k] - cfg4["out"][i]) <= 1e-5 * abs(cfg4["out"][i])
     # the exchanged gradient itself (after train_apply the buffer holds the prepared gradient: fold undone, l2 added)
     eng1, engr = one._train_engine, reps[0][1]
-    worst_g = 0.0
+    worst_g, table = 0.0, []
     for lyr in one.layers:
         for bias in (False, True):
             a = eng1.train_layer_tensor("grads", lyr.name, lyr.ksize, lyr.cin, lyr.cout, bias=bias)
             if a is None or np.linalg.norm(a) < 1e-4 * g1:
                 continue
             b = engr.train_layer_tensor("grads", lyr.name, lyr.ksize, lyr.cin, lyr.cout, bias=bias)
-            worst_g = max(worst_g, _rel(b, a.astype(np.float64)))
-    print("DP(global) vs concatenated batch: worst relative gradient-tensor difference %.2e" % worst_g)
+            table.append((_rel(b, a.astype(np.float64)), lyr.name, bias, float(np.linalg.norm(a))))
+            worst_g = max(worst_g, table[-1][0])
+    table.sort(reverse=True)
+    print("DP(global) vs concatenated batch: worst relative gradient-tensor difference %.2e" % worst_g, table[:8])
     assert worst_g <= 1e-3
     w_one = one.get_weights_dict()
     w_a, w_b = reps[0][0].get_weights_dict(), reps[1][0].get_weights_dict()
