@@ -212,6 +212,15 @@ typedef struct ppb_engine ppb_engine;
 
 PPB_API int ppb_engine_create(ppb_engine** out, int device, int max_batch, int height, int width, int num_classes,
                               int num_anchors);
+/* precision 0: the production path (bf16 operands, fp32 accumulation; feature maps / scores / corners within rel.
+ * 1e-2 of the fp32 reference). precision 1: the "fp32 path" of BASELINE.json north_star (tolerance 1e-4): every
+ * activation and weight is carried as three bf16 parts (24 significant bits) and every product is the six tcgen05
+ * MMAs whose terms reach 2^-16 of it, summed in the fp32 accumulator; the stem, Add / UpsampleLike, MaxPool and the
+ * sigmoid run in IEEE fp32. Inference only (ppb_engine_train_bind returns PPB_ERR_STATE); about 6x the tensor work and
+ * 3x the activation bytes. Replaces running the reference's float32 Keras graph
+ * (PyraPose/models/retinanet.py:260-335) where parity tighter than bf16 matters. */
+PPB_API int ppb_engine_create_ex(ppb_engine** out, int device, int max_batch, int height, int width, int num_classes,
+                                 int num_anchors, int precision);
 PPB_API void ppb_engine_destroy(ppb_engine* engine);
 
 /* Layer table (Keras layer names; keras-resnet 0.1.0 for the backbone). */
@@ -251,6 +260,12 @@ PPB_API int ppb_engine_activation(ppb_engine* engine, const char* name, float* o
  * 3 parity planes, 4 add. Fills min(cap, kernels_per_run) entries of the HOST arrays. */
 /* Name (layer name for convolutions) and algorithmic FLOPs of launch `index` of the bound plan. */
 PPB_API int ppb_engine_op_info(const ppb_engine* engine, int index, char* name, int name_cap, double* flops);
+/* Diagnostic (tools/trace_conv.py): cycle-stamped trace of CTA `cta` of convolution launch `index` of the bound plan —
+ * every barrier hand-off of its TMA producer, MMA issuer, residual producer and epilogue groups. trace_dev: DEVICE
+ * buffer of 8 * cap 8-byte entries; info_out_host: 12 ints (M tiles, N tiles, block_n, taps, cin blocks, stages, ring
+ * slots, pair, slab3, bres, staged, epilogue groups) or NULL. No reference counterpart (TensorFlow's profiler). */
+PPB_API int ppb_engine_trace_op(ppb_engine* engine, int index, int cta, void* trace_dev, int cap, int* info_out_host,
+                                void* stream);
 PPB_API int ppb_engine_profile(ppb_engine* engine, void* stream, float* ms_out_host, int* kind_out_host, int cap);
 
 /* ------------------------------------------------------------------ input staging

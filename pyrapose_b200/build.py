@@ -33,6 +33,7 @@ def _optional_sources():
         ("image.cu", True),
         ("filter.cu", True),
         ("elementwise.cu", False),
+        ("split_ops.cu", False),
         ("engine.cu", False),
         ("conv_wgrad.cu", False),
         ("pnp.cu", False),

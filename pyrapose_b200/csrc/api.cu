@@ -42,7 +42,12 @@ void conv_fill_single_seg(ConvParams& p, int batch, int h, int w, int ksize) {
 // the tile shape -- K-deep (tensor-bound) layers prefer N = 256 (N = 64 MMAs are shared-memory-bandwidth bound),
 // shallow-K (HBM / epilogue-bound) layers prefer N = 128 so that the epilogue ring holds several tiles of
 // residual / output chunks in flight.
-int conv_pick_block_n(int cout_pad, int k_iters, long m_tiles, bool bf16_out) {
+int conv_pick_block_n(int cout_pad, int k_iters, long m_tiles, bool bf16_out, int max_n) {
+  if (max_n < kConvMaxBlockN) {  // fp32 path: two accumulators share a 256-column buffer (conv_igemm.cu kSideCol)
+    if (bf16_out && cout_pad % 64 == 0) return cout_pad % max_n == 0 ? max_n : 64;
+    const int nt = (cout_pad + max_n - 1) / max_n;
+    return ((cout_pad + nt - 1) / nt + 15) / 16 * 16;
+  }
   if (!bf16_out && cout_pad > kConvMaxBlockN) {  // wide head output (e.g. 30 classes x 9 anchors): equal N tiles
     const int nt = (cout_pad + kConvMaxBlockN - 1) / kConvMaxBlockN;
     return ((cout_pad + nt - 1) / nt + 15) / 16 * 16;

@@ -34,6 +34,12 @@ constexpr int kStemSlabTx = kConvSlabRows * 32;               // stem slab: 136 
 constexpr int kStemSlabBytes = 5 * 1024;                      // ... in a 5 KiB slot so the B tiles stay 1024-B aligned
 constexpr int kTmemCols = 512;
 constexpr int kAccCols = 256;
+// fp32 path (ConvParams::split, block_n <= 128): the products of the leading parts (segment 0) accumulate in columns
+// [0, block_n) of an accumulator buffer, every smaller term in [kSideCol, kSideCol + block_n); the epilogue adds the two
+// in IEEE fp32. The tensor core's fp32 accumulation truncates, an error that grows with the LENGTH of the accumulation
+// chain relative to the accumulator's magnitude (measured: three segments in one accumulator 5e-5 at P5, six segments
+// 1.1e-4): keeping the five small-term chains out of the main accumulator leaves K/16 steps in it instead of 6 K/16.
+constexpr int kSideCol = 128;
 constexpr int kCtrlWarps = 4;
 // Epilogue warps come in groups of four (a TMEM lane quadrant is only visible to warp id % 4). Two groups are the
 // default; the residual 2c layers (1x1, K <= 512, staged epilogue with a residual to add) are bound by the latency of
@@ -216,6 +222,11 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __res
     const uint4 z = make_uint4(0, 0, 0, 0);
 #pragma unroll
     for (int i = 0; i < NC / 8; ++i) reinterpret_cast<uint4*>(dst)[i] = z;
+    if (p.split) {
+      for (int part = 1; part < p.parts; ++part)
+#pragma unroll
+        for (int i = 0; i < NC / 8; ++i) reinterpret_cast<uint4*>(dst + part * p.out_part_off)[i] = z;
+    }
     return;
   }
   float f[NC];
@@ -241,6 +252,50 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __res
       f[i * 8 + 6] += bf16_lo(r.w);
       f[i * 8 + 7] += bf16_hi(r.w);
     }
+  }
+  if (p.split) {  // fp32 path: the residual's remaining parts, then the parts of the result
+    if (p.residual != nullptr) {
+      for (int part = 1; part < p.parts; ++part) {
+        const uint4* rp = reinterpret_cast<const uint4*>(p.residual + static_cast<size_t>(m) * p.res_ld +
+                                                         part * p.res_part_off + n0);
+#pragma unroll
+        for (int i = 0; i < NC / 8; ++i) {
+          const uint4 r = __ldg(rp + i);
+          f[i * 8 + 0] += bf16_lo(r.x);
+          f[i * 8 + 1] += bf16_hi(r.x);
+          f[i * 8 + 2] += bf16_lo(r.y);
+          f[i * 8 + 3] += bf16_hi(r.y);
+          f[i * 8 + 4] += bf16_lo(r.z);
+          f[i * 8 + 5] += bf16_hi(r.z);
+          f[i * 8 + 6] += bf16_lo(r.w);
+          f[i * 8 + 7] += bf16_hi(r.w);
+        }
+      }
+    }
+    if (p.relu) {
+#pragma unroll
+      for (int j = 0; j < NC; ++j) f[j] = fmaxf(f[j], 0.0f);
+    }
+    for (int part = 0; part < p.parts; ++part) {
+#pragma unroll
+      for (int i = 0; i < NC / 8; ++i) {
+        uint4 o;
+        o.x = pack_bf16x2(f[i * 8 + 0], f[i * 8 + 1]);
+        o.y = pack_bf16x2(f[i * 8 + 2], f[i * 8 + 3]);
+        o.z = pack_bf16x2(f[i * 8 + 4], f[i * 8 + 5]);
+        o.w = pack_bf16x2(f[i * 8 + 6], f[i * 8 + 7]);
+        f[i * 8 + 0] -= bf16_lo(o.x);  // exact: the remainder of an fp32 value after its leading bf16 part
+        f[i * 8 + 1] -= bf16_hi(o.x);
+        f[i * 8 + 2] -= bf16_lo(o.y);
+        f[i * 8 + 3] -= bf16_hi(o.y);
+        f[i * 8 + 4] -= bf16_lo(o.z);
+        f[i * 8 + 5] -= bf16_hi(o.z);
+        f[i * 8 + 6] -= bf16_lo(o.w);
+        f[i * 8 + 7] -= bf16_hi(o.w);
+        reinterpret_cast<uint4*>(dst + part * p.out_part_off)[i] = o;
+      }
+    }
+    return;
   }
   if (p.relu) {
 #pragma unroll
@@ -293,7 +348,8 @@ __device__ __forceinline__ void epi_head16(const ConvParams& p, const float* __r
     // ex2 + rcp on the SFU (relative error ~1e-6, far inside the 1e-2 score tolerance of the bf16 path): the
     // IEEE expf + division pair was a third of this epilogue's instructions with two warps per scheduler to hide them
 #pragma unroll
-    for (int j = 0; j < 16; ++j) f[j] = __fdividef(1.0f, 1.0f + __expf(-f[j]));
+    for (int j = 0; j < 16; ++j)
+      f[j] = p.split ? 1.0f / (1.0f + expf(-f[j])) : __fdividef(1.0f, 1.0f + __expf(-f[j]));  // fp32 path: IEEE forms
   } else if (p.epi == kEpiHeadDecode) {
     // box3D_transform_inv (PyraPose/backend/common.py:25-56) against the Anchors layer's boxes
     // (PyraPose/layers/_misc.py:52-69, backend/common.py:93-116): fp32 base anchor + fp32 shift.
@@ -332,7 +388,24 @@ __device__ __forceinline__ void epi_head16(const ConvParams& p, const float* __r
     if (n0 + j < p.n_valid) srow[n0 - tile_n0 + j] = f[j];
 }
 
-template <bool kPair, int kGroups>
+// fp32 path: v += the side accumulator's NC columns (IEEE fp32 add), see kSideCol.
+template <int NC>
+__device__ __forceinline__ void add_side(uint32_t taddr_side, uint32_t (&v)[NC]) {
+  uint32_t w[NC];
+  if constexpr (NC == 32) tmem_ld_32x32(taddr_side, w);
+  else tmem_ld_32x16(taddr_side, w);
+  tmem_ld_wait();
+#pragma unroll
+  for (int i = 0; i < NC; ++i) v[i] = __float_as_uint(__fadd_rn(__uint_as_float(v[i]), __uint_as_float(w[i])));
+}
+
+// Trace events (ConvParams::trace): producer 1 = stage free, 2 = loads issued; MMA issuer 3 = accumulator free (tile
+// start), 4 = stage full, 5 = MMAs + commit issued, 6 = tile committed; residual producer 7 = slot free, 8 = issued;
+// epilogue group leader 9 = accumulator full, 10 = ring slot ready, 11 = tcgen05.ld done, 12 = chunk computed (group
+// barrier passed), 13 = TMA store issued, 14 = accumulator released.
+enum TraceRole : int { kTrProducer = 0, kTrMma = 1, kTrResidual = 2, kTrEpilogue = 3 };
+
+template <bool kPair, int kGroups, bool kTrace = false>
 __global__ void __launch_bounds__((kCtrlWarps + 4 * kGroups) * 32, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
@@ -378,6 +451,23 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  uint32_t tr_n = 0;  // trace: events this thread has written (kTrace instantiations only)
+  const bool tr_on = kTrace && p.trace != nullptr && static_cast<int>(blockIdx.x) == p.trace_cta;
+  auto tr = [&](int role, uint32_t ev, int seq, int sub) {
+    if constexpr (kTrace) {
+      if (tr_on && static_cast<int>(tr_n) + 1 < p.trace_cap) {
+        p.trace[static_cast<size_t>(role) * p.trace_cap + 1 + tr_n] =
+            make_uint2((ev << 24) | ((static_cast<uint32_t>(seq) & 0xffffu) << 8) | (static_cast<uint32_t>(sub) & 0xffu),
+                       static_cast<uint32_t>(clock64()));
+        ++tr_n;
+      }
+    }
+  };
+  auto tr_end = [&](int role) {
+    if constexpr (kTrace) {
+      if (tr_on) p.trace[static_cast<size_t>(role) * p.trace_cap] = make_uint2(tr_n, static_cast<uint32_t>(clock64()));
+    }
+  };
 
   if (warp == 0) {
     if (elect_one()) {
@@ -472,7 +562,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         for (int j = 0; j < 16; ++j)
           tma_load_2d(b_res + j * b_tile_bytes, &tmap_b, p.b_col_base + j * 16, 0, bres_bar);
       }
-      for (int it = it_begin; it < it_end; it += it_step) {
+      // fp32-path layers: K-loop segment -> activation part (ConvParams::split)
+      auto a_col = [&](int kb) {
+        if (p.split == 0) return kb * kConvBlockK;
+        const int sgm = kb / p.a_cb;
+        return (p.a_seg[sgm] * p.a_cb + kb - sgm * p.a_cb) * kConvBlockK;
+      };
+      int tseq = 0, kseq = 0;
+      for (int it = it_begin; it < it_end; it += it_step, ++tseq, kseq = 0) {
         const TileCoord tc = tile_coord(p, tile_of(it));
         const ConvSeg& sg = p.seg[tc.seg];
         const int b_row = tc.n0 + static_cast<int>(rank) * b_rows;
@@ -481,10 +578,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           const int a_row = tc.row0 + sg.tap_off[p.slab3 < 0 ? tap + 2 : tap];
           for (int kb = 0; kb < p.cin_blocks; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1, kFaultEmpty);
+            tr(kTrProducer, 1, tseq, kseq);
             uint8_t* sa = smem + stage * stage_bytes;
             if (pair) {  // both CTAs' bytes are counted on rank 0's barrier, armed by rank 0 for the two stages
               if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-              tma_load_2d_pair(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
+              tma_load_2d_pair(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage]);
               for (int j = 0; j < taps_per_stage; ++j)
                 tma_load_2d_pair(sa + a_bytes + j * b_tile_bytes, &tmap_b,
                                  p.b_col_base + ((tap + j) * p.cin_blocks + kb) * kConvBlockK, b_row, &full_bar[stage]);
@@ -493,14 +591,15 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               tma_load_2d(sa, &tmap_a, 0, a_row, &full_bar[stage]);
             } else if (bres) {
               mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-              tma_load_2d(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
+              tma_load_2d(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage]);
             } else {
               mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-              tma_load_2d(sa, &tmap_a, kb * kConvBlockK, a_row, &full_bar[stage]);
+              tma_load_2d(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage]);
               for (int j = 0; j < taps_per_stage; ++j)
                 tma_load_2d(sa + a_bytes + j * b_tile_bytes, &tmap_b,
                             p.b_col_base + ((tap + j) * p.cin_blocks + kb) * kConvBlockK, tc.n0, &full_bar[stage]);
             }
+            tr(kTrProducer, 2, tseq, kseq++);
             if (++stage == n_stages) {
               stage = 0;
               phase ^= 1;
@@ -508,6 +607,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           }
         }
       }
+      tr_end(kTrProducer);
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
@@ -518,13 +618,17 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       uint32_t acc_phase = 0;
       const uint32_t idesc = umma_idesc_bf16(pair ? 2 * kConvBlockM : kConvBlockM, p.block_n);
       if ((stem16 || bres) && it_begin < it_end) mbar_wait(bres_bar, 0, kFaultFull);
-      for (int it = it_begin; it < it_end; it += it_step) {
+      int tseq = 0;
+      for (int it = it_begin; it < it_end; it += it_step, ++tseq) {
         mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1, kFaultTmemEmpty);
+        tr(kTrMma, 3, tseq, 0);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kAccCols;
         int res_tap = 0, res_kb = 0;  // bres: (first tap, channel block) of k-iteration ki, in the producer's order
+        bool started[2] = {false, false};  // fp32 path: main / side accumulator already written in this tile
         for (int ki = 0; ki < k_iters; ++ki) {
           mbar_wait(&full_bar[stage], phase, kFaultFull);
+          tr(kTrMma, 4, tseq, ki);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
           const uint32_t b_addr = a_addr + a_bytes;
@@ -539,15 +643,19 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const uint32_t a_tap = a_addr + (p.slab3 == 0 ? 0u : (p.slab3 > 0 ? j : 2 - j) * 128u);
             const uint32_t b_tap = bres ? smem_u32(b_res) + ((res_tap + j) * p.cin_blocks + res_kb) * b_tile_bytes
                                         : b_addr + j * b_tile_bytes;
+            const int side = (p.split != 0 && res_kb >= p.a_cb) ? 1 : 0;  // segments 1.. -> the side accumulator
+            const uint32_t d_acc = d_tmem + side * kSideCol;
 #pragma unroll
             for (int k = 0; k < kConvBlockK / 16; ++k) {
-              const uint32_t accum = (ki | j | k) != 0 ? 1u : 0u;
-              if (pair) tc_mma_bf16_2cta(d_tmem, umma_desc_k128(a_tap + k * 32), umma_desc_k128(b_tap + k * 32), idesc, accum);
-              else tc_mma_bf16(d_tmem, umma_desc_k128(a_tap + k * 32), umma_desc_k128(b_tap + k * 32), idesc, accum);
+              const uint32_t accum = p.split != 0 ? ((started[side] || (j | k) != 0) ? 1u : 0u) : ((ki | j | k) != 0 ? 1u : 0u);
+              if (pair) tc_mma_bf16_2cta(d_acc, umma_desc_k128(a_tap + k * 32), umma_desc_k128(b_tap + k * 32), idesc, accum);
+              else tc_mma_bf16(d_acc, umma_desc_k128(a_tap + k * 32), umma_desc_k128(b_tap + k * 32), idesc, accum);
             }
+            if (j == taps_per_stage - 1) started[side] = true;
           }
           if (pair) tc_commit2(&empty_bar[stage]);  // frees this stage in both CTAs
           else tc_commit(&empty_bar[stage]);
+          tr(kTrMma, 5, tseq, ki);
           if (++res_kb == p.cin_blocks) {
             res_kb = 0;
             res_tap += taps_per_stage;
@@ -559,9 +667,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         if (pair) tc_commit2(&tmem_full_bar[acc]);
         else tc_commit(&tmem_full_bar[acc]);
+        tr(kTrMma, 6, tseq, 0);
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
+      tr_end(kTrMma);
     }
   } else if (warp == 3) {
     // ------------------------------------------------------------ residual producer (staged epilogue only)
@@ -569,18 +679,22 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     // overwrite with the result; runs as far ahead as the ring allows.
     if (staged && has_res && elect_one()) {
       uint32_t s = 0, ph = 0;
-      for (int it = it_begin; it < it_end; it += it_step) {
+      int tseq = 0;
+      for (int it = it_begin; it < it_end; it += it_step, ++tseq) {
         const TileCoord tc = tile_coord(p, tile_of(it));
         for (int c = 0; c < n_chunks; ++c) {
           mbar_wait(&slot_empty_bar[s], ph ^ 1u, kFaultSlotEmpty);
+          tr(kTrResidual, 7, tseq, c);
           mbar_arrive_expect_tx(&slot_full_bar[s], kChunkBytes);
           tma_load_2d(ring + s * kChunkBytes, &tmap_res, tc.n0 + c * 64, tc.row0, &slot_full_bar[s]);
+          tr(kTrResidual, 8, tseq, c);
           if (++s == static_cast<uint32_t>(R)) {
             s = 0;
             ph ^= 1u;
           }
         }
       }
+      tr_end(kTrResidual);
     }
   } else if (warp >= kCtrlWarps) {
     // ------------------------------------------------------------ epilogue: 2 groups x 4 lane quadrants
@@ -597,12 +711,15 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int sstride = p.block_n | 1;  // odd stride: conflict-free column writes
     float* stile = reinterpret_cast<float*>(ring);
     long long* srow_loc = reinterpret_cast<long long*>(ring + static_cast<size_t>(kConvBlockM) * sstride * 4);
-    for (int it = it_begin; it < it_end; it += it_step) {
+    const bool tr_lead = store_thread;  // one trace writer per epilogue group
+    int tseq = 0;
+    for (int it = it_begin; it < it_end; it += it_step, ++tseq) {
       const TileCoord tc = tile_coord(p, tile_of(it));
       const ConvSeg& sg = p.seg[tc.seg];
       const int m = tc.row0 + row;
       const RowInfo ri = row_info(sg, m);
       mbar_wait(&tmem_full_bar[acc], acc_phase, kFaultTmemFull);
+      if (tr_lead) tr(kTrEpilogue + g, 9, tseq, 0);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * kAccCols;
       if (staged) {
@@ -619,10 +736,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           if (!mine) continue;
           if (has_res) mbar_wait(&slot_full_bar[s], ph, kFaultSlotFull);
           else mbar_wait(&slot_empty_bar[s], ph ^ 1u, kFaultSlotEmpty);
+          if (tr_lead) tr(kTrEpilogue + g, 10, tseq, c);
           uint32_t v[64];
           tmem_ld_32x32(taddr + c * 64, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
           tmem_ld_32x32(taddr + c * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
           tmem_ld_wait();
+          if (tr_lead) tr(kTrEpilogue + g, 11, tseq, c);
           uint8_t* rowp = ring + s * kChunkBytes + row * 128;
           const float* bsrc = sbias + tc.n0 + c * 64;
           if (p.mask != nullptr) {  // dgrad through a ReLU: the generic form
@@ -638,8 +757,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           fence_proxy_async_smem();  // make the generic-proxy writes visible to the TMA store
           named_bar_sync(1 + g, 128);
           if (store_thread) {  // always the same thread per group: bulk-async groups are per thread
+            tr(kTrEpilogue + g, 12, tseq, c);
             tma_store_2d(&tmap_out, tc.n0 + c * 64, tc.row0, ring + s * kChunkBytes);
             tma_store_commit();
+            tr(kTrEpilogue + g, 13, tseq, c);
             if (p.early_free) {
               tma_store_wait_read();  // ~0.3 us: the slot goes straight back to the residual producer
               mbar_arrive(&slot_empty_bar[s]);
@@ -654,6 +775,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         tc_fence_before();
         tmem_release(&tmem_empty_bar[acc]);  // this thread's share of the accumulator is drained
+        if (tr_lead) tr(kTrEpilogue + g, 14, tseq, 0);
       } else if (p.epi == kEpiBf16) {
         // ---- direct bf16 epilogue: 32-column pieces alternate between the two groups
         int piece = 0;
@@ -663,16 +785,19 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             uint32_t v[32];
             tmem_ld_32x32(taddr + c0, v);
             tmem_ld_wait();
+            if (p.split) add_side<32>(taddr + kSideCol + c0, v);
             epi_bf16<32>(p, sbias, ri, m, tc.n0 + c0, v);
           } else {
             uint32_t v[16];
             tmem_ld_32x16(taddr + c0, v);
             tmem_ld_wait();
+            if (p.split) add_side<16>(taddr + kSideCol + c0, v);
             epi_bf16<16>(p, sbias, ri, m, tc.n0 + c0, v);
           }
         }
         tc_fence_before();
         tmem_release(&tmem_empty_bar[acc]);
+        if (tr_lead) tr(kTrEpilogue + g, 14, tseq, 0);
       } else {
         // ---- head epilogues: fp32 tile staged in shared memory, then written out coalesced
         const int w = sg.wp - sg.pad_lo - sg.pad_hi;
@@ -687,12 +812,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             uint32_t v[32];
             tmem_ld_32x32(taddr + c0, v);
             tmem_ld_wait();
+            if (p.split) add_side<32>(taddr + kSideCol + c0, v);
             epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0, tc.n0, v, srow);
             epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0 + 16, tc.n0, v + 16, srow);
           } else {
             uint32_t v[16];
             tmem_ld_32x16(taddr + c0, v);
             tmem_ld_wait();
+            if (p.split) add_side<16>(taddr + kSideCol + c0, v);
             epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0, tc.n0, v, srow);
           }
         }
@@ -721,6 +848,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       if (acc == 0) acc_phase ^= 1;
     }
     if (staged && store_thread) tma_store_wait_all();
+    if (tr_lead) tr_end(kTrEpilogue + g);
   }
 
   tc_fence_before();
@@ -865,6 +993,7 @@ static bool conv_bres_ok(const ConvParams& p) {
 }
 
 int conv_plan_smem(ConvParams& p) {
+  if (p.split != 0 && (p.block_n > kSideCol || p.staged)) return -1;  // two accumulators per buffer, direct epilogue only
   p.bres = conv_bres_ok(p) ? 1 : 0;
   const int stage_bytes = stage_bytes_of(p);
   const int k_iters = (p.slab3 != 0 ? 3 : p.n_taps) * p.cin_blocks;
@@ -935,6 +1064,12 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
       attr_err = cudaFuncSetAttribute(conv_igemm_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     if (attr_err == cudaSuccess)
       attr_err = cudaFuncSetAttribute(conv_igemm_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(conv_igemm_kernel<false, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(conv_igemm_kernel<true, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(conv_igemm_kernel<false, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     if (attr_err != cudaSuccess) return attr_err;
   }
   const int total = p.n_mtiles * p.n_ntiles;
@@ -1014,7 +1149,12 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
   }
   const cudaError_t err =
       // q = p + the division constants (its plan was checked equal to p's above)
-      p.pair ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<true, 2>, tmap_a, tmap_b, tmap_out, tmap_res, q)
+      p.trace != nullptr
+          ? (p.pair ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<true, 2, true>, tmap_a, tmap_b, tmap_out, tmap_res, q)
+                    : (p.epi_groups == 3
+                           ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false, 3, true>, tmap_a, tmap_b, tmap_out, tmap_res, q)
+                           : cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false, 2, true>, tmap_a, tmap_b, tmap_out, tmap_res, q)))
+      : p.pair ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<true, 2>, tmap_a, tmap_b, tmap_out, tmap_res, q)
              : (p.epi_groups == 3 ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false, 3>, tmap_a, tmap_b, tmap_out, tmap_res, q)
                                   : cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false, 2>, tmap_a, tmap_b, tmap_out, tmap_res, q));
   if (err != cudaSuccess)

@@ -77,12 +77,30 @@ struct ConvParams {
                     // taps dx are four K = 16 MMAs whose descriptors start dx pixels (dx x 32 B) into it, instead of four
                     // overlapping 128-byte rows per pixel (4x the L2 traffic). Maps from conv_encode_stem_tmaps().
   int bres;         // weights resident in shared memory (filled by conv_plan_smem, see conv_bres_ok in conv_igemm.cu)
+  int split;        // fp32-path layers (Engine precision 1): number of K segments per tap, 0 = off. Every
+                    // activation value v is stored as `parts` bf16 numbers p0 = bf16(v), p1 = bf16(v - p0), p2 = bf16(v
+                    // - p0 - p1) in columns [0, C), [C, 2C), [2C, 3C) of its row (24 significant bits), weights likewise
+                    // as w0, w1, w2. A product is the six MMAs whose terms are >= 2^-16 of it, accumulated in the fp32
+                    // TMEM accumulator: (a0,w0) (a1,w0) (a0,w1) (a2,w0) (a1,w1) (a0,w2). The weight matrix holds per tap
+                    // the column blocks [w0 | w0 | w1 | w0 | w1 | w2]; K-loop channel block kb belongs to segment
+                    // s = kb / a_cb and reads A columns (a_seg[s] * a_cb + kb - s * a_cb) * 64. The bf16 epilogue (direct
+                    // only) writes part i at column n + i * out_part_off; the residual is the sum of its parts.
+  int parts;        // 3 on the fp32 path
+  int a_cb;         // channel blocks per segment (C / 64)
+  int a_seg[6];     // which activation part each segment reads
+  int out_part_off, res_part_off;
   unsigned nt_mul, nt_sh;  // division by n_ntiles (conv_fastdiv), filled by conv_launch
   int epi_groups;   // epilogue warp groups (2 or 3)     }
   int early_free;   // staged + residual: a ring slot is handed back as soon as ITS store has read it, not when the  }
                     // group's next store is committed (more residual chunks in flight)                            }
   int n_stages;     // TMA->MMA pipeline depth (2..8)   } filled by conv_plan_smem()
   int ring_slots;   // 16 KiB epilogue ring slots        }
+  // Cycle-stamped trace of ONE CTA (tools/trace_conv.py; the kTrace instantiations of the kernel): when non-null, CTA
+  // trace_cta writes (tag, clock64 low word) pairs at every barrier hand-off of its producer / MMA / residual /
+  // epilogue-group threads into trace[role * trace_cap + 1 ...]; entry 0 of a role's region holds its event count.
+  // tag = event << 24 | (tile sequence number & 0xffff) << 8 | (k-iteration or chunk & 0xff); events in conv_igemm.cu.
+  uint2* trace;
+  int trace_cap, trace_cta;
   const float* bias;              // [n_valid] fp32, BatchNorm folded in; may be null
   const __nv_bfloat16* residual;  // kEpiBf16: added before ReLU; row stride res_ld; may be null
   int res_ld;
@@ -135,6 +153,9 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
 void conv_read_fault(unsigned int out[4]);
 
 int conv_num_sms();
+
+// UMMA N of one tile (api.cu). max_n < 256: the fp32 path's limit (two accumulators per buffer).
+int conv_pick_block_n(int cout_pad, int k_iters, long m_tiles, bool bf16_out, int max_n = kConvMaxBlockN);
 
 // CTA-pair mode is usable for this shape (N tile a multiple of 16: each CTA stages N/2 rows = whole 8-row swizzle atoms, K loop
 // deep enough to be operand-feed bound) and enabled (PPB_PAIR: 0 off, 1 default, 2 every eligible shape).

@@ -36,3 +36,22 @@ cudaError_t launch_add(const __nv_bfloat16* a, const __nv_bfloat16* b, const __n
                        cudaStream_t st);
 
 }  // namespace ppb
+
+// ---- fp32 path (Engine precision 1, ConvParams::split): every activation row holds 3*C bf16 values, the three parts
+// p0 = bf16(v), p1 = bf16(v - p0), p2 = bf16(v - p0 - p1) of each channel in columns [0, C), [C, 2C), [2C, 3C). The
+// copy-like kernel (parity planes) runs unchanged on 3*C channels; the arithmetic ones have split forms that compute on
+// the fp32 sum of the parts and split the result again.
+namespace ppb {
+
+// Stem in full fp32 on the CUDA cores (1.45 GFLOP per image, not a tensor-core job at K = 147):
+// ZeroPadding2D(3) + 7x7/2 VALID + folded BatchNorm + ReLU from the fp32 (or raw uint8 - mean) image into the stem's
+// pixel grid [B, Ho+3, Wo+3, 3*64]. w = [7][7][3][64] fp32 (BatchNorm scale folded in), bias = [64].
+cudaError_t launch_stem_conv_split(const void* image, int is_u8, const float mean[3], const float* w, const float* bias,
+                                   __nv_bfloat16* out, int B, int H, int W, int Ho, int Wo, cudaStream_t st);
+cudaError_t launch_maxpool3x3s2_split(const __nv_bfloat16* in, __nv_bfloat16* out, int B, int Hi, int Wi, int in_hs,
+                                      int in_ws, int C, int Ho, int Wo, cudaStream_t st);
+cudaError_t launch_add_split(const __nv_bfloat16* a, const __nv_bfloat16* b, const __nv_bfloat16* c,
+                             const __nv_bfloat16* u, int uH, int uW, __nv_bfloat16* out, int B, int H, int W, int C,
+                             cudaStream_t st);
+
+}  // namespace ppb

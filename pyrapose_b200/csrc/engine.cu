@@ -55,7 +55,14 @@ void Engine::define_layers() {
 int Engine::allocate_weights() {
   for (LayerW& l : layers) {
     void* p = nullptr;
-    int rc = device_alloc(&p, static_cast<size_t>(l.cout_pad) * l.k_total * sizeof(__nv_bfloat16));
+    l.k_dev = split() ? kSplitSegs * l.k_total : l.k_total;
+    int rc = kOk;
+    if (split() && l.ksize == 7) {  // fp32 path: the stem is a plain fp32 convolution (launch_stem_conv_split)
+      rc = device_alloc(&p, static_cast<size_t>(7 * 7 * 3) * l.cout * sizeof(float));
+      if (rc != kOk) return rc;
+      l.w_f32 = static_cast<float*>(p);
+    }
+    rc = device_alloc(&p, static_cast<size_t>(l.cout_pad) * l.k_dev * sizeof(__nv_bfloat16));
     if (rc != kOk) return rc;
     l.w = static_cast<__nv_bfloat16*>(p);
     rc = device_alloc(&p, static_cast<size_t>(l.cout_pad) * sizeof(float));
@@ -74,7 +81,9 @@ int Engine::set_layer(const char* name, const float* kernel, const float* bias, 
   PPB_REQUIRE(kernel != nullptr, "ppb_engine_set_layer: null kernel for '%s'", name);
   PPB_REQUIRE(!l.has_bn || (gamma && beta && mean && var), "ppb_engine_set_layer: '%s' needs BatchNorm parameters", name);
   const int k = l.ksize, cin = l.cin, cout = l.cout;
-  std::vector<__nv_bfloat16> w(static_cast<size_t>(l.cout_pad) * l.k_total, __float2bfloat16(0.0f));
+  std::vector<__nv_bfloat16> w(static_cast<size_t>(l.cout_pad) * l.k_dev, __float2bfloat16(0.0f));
+  std::vector<float> w32;  // fp32 path, stem: [7][7][3][cout]
+  if (split() && k == 7) w32.assign(static_cast<size_t>(7 * 7 * 3) * cout, 0.0f);
   std::vector<float> b(l.cout_pad, 0.0f);
   l.raw_kernel.assign(static_cast<size_t>(cout) * l.k_total, 0.0f);
   l.raw_bias.assign(cout, 0.0f);
@@ -101,11 +110,25 @@ int Engine::set_layer(const char* name, const float* kernel, const float* bias, 
             const int ry = r + 1, rx = s + 1;
             col = static_cast<size_t>(ry >> 1) * 64 + (rx >> 1) * 16 + ((ry & 1) * 2 + (rx & 1)) * 3 + c;
           }
-          w[static_cast<size_t>(o) * l.k_total + col] = __float2bfloat16(v);
+          if (!split()) {
+            w[static_cast<size_t>(o) * l.k_total + col] = __float2bfloat16(v);
+          } else if (k == 7) {
+            w32[(static_cast<size_t>(r * k + s) * cin + c) * cout + o] = v;
+          } else {  // per tap the column blocks [w0 | w0 | w1 | w0 | w1 | w2] (ConvParams::split)
+            __nv_bfloat16 part[3];
+            float rem = v;
+            for (int i = 0; i < 3; ++i) {
+              part[i] = __float2bfloat16(rem);
+              rem -= __bfloat162float(part[i]);
+            }
+            __nv_bfloat16* row = w.data() + static_cast<size_t>(o) * l.k_dev + static_cast<size_t>(r * k + s) * kSplitSegs * cin;
+            for (int sg = 0; sg < kSplitSegs; ++sg) row[sg * cin + c] = part[kSplitWPart[sg]];
+          }
           l.raw_kernel[static_cast<size_t>(o) * l.k_total + col] = kernel[((static_cast<size_t>(r) * k + s) * cin + c) * cout + o];
         }
   }
   PPB_CUDA(cudaMemcpy(l.w, w.data(), w.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
+  if (!w32.empty()) PPB_CUDA(cudaMemcpy(l.w_f32, w32.data(), w32.size() * sizeof(float), cudaMemcpyHostToDevice));
   PPB_CUDA(cudaMemcpy(l.bias, b.data(), b.size() * sizeof(float), cudaMemcpyHostToDevice));
   l.loaded = true;
   return kOk;
@@ -125,8 +148,9 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
   op.kind = kOpConv;
   ConvParams& p = op.p;
   memset(&p, 0, sizeof(p));
-  int a_cols = x->C, a_ld = x->C;
-  if (l.ksize == 7) {  // stem over the space-to-depth grid: 4 row taps, A rows overlap (stride 16 < extent 64)
+  int a_cols = x->ld, a_ld = x->ld;
+  if (l.ksize == 7) {
+    if (split()) return fail(kErrState, "internal: the fp32 path runs the stem as launch_stem_conv_split");  // stem over the space-to-depth grid: 4 row taps, A rows overlap (stride 16 < extent 64)
     p.n_segs = 1;
     ConvSeg& s = p.seg[0];
     s.row_begin = 0;
@@ -159,19 +183,20 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
     }
   }
   p.cin_blocks = a_cols / kConvBlockK;
+  if (split()) conv_set_split(p, x->C, y->C, res ? res->C : 0);
   p.n_valid = l.cout;
-  p.block_n = conv_pick_block_n(l.cout_pad, p.n_taps * p.cin_blocks, p.n_mtiles, true);
+  p.block_n = conv_pick_block_n(l.cout_pad, p.n_taps * p.cin_blocks, p.n_mtiles, true, split() ? 128 : kConvMaxBlockN);
   p.n_ntiles = (l.cout_pad + p.block_n - 1) / p.block_n;
   p.epi = kEpiBf16;
   p.relu = relu;
   p.bias = l.bias;
   p.residual = res ? res->ptr : nullptr;
-  p.res_ld = res ? res->C : 0;
+  p.res_ld = res ? res->ld : 0;
   p.out = y->ptr;
-  p.out_ld = y->C;
+  p.out_ld = y->ld;
   const long long a_rows = x->rows(batch) * (x_planes > 0 ? x_planes : 1);
   p.pair = conv_pair_ok(p) ? 1 : 0;
-  p.staged = (l.cout % 64 == 0 && p.block_n % 64 == 0 &&
+  p.staged = (!split() && l.cout % 64 == 0 && p.block_n % 64 == 0 &&
               (staged_epilogue >= 2 || (staged_epilogue == 1 && res != nullptr))) ? 1 : 0;
   p.slab3 = conv_slab3_mode(p);
   if (l.ksize == 7 && stem16 && l.k_total == 256 && (p.block_n & 7) == 0) {
@@ -200,16 +225,16 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
       (p.slab3 != 0 ? 3 : p.n_taps) * p.cin_blocks >= 8)
     force_direct = true;
   int rc = p.stem16 ? conv_encode_stem_tmaps(&op.ta, &op.tb, x->ptr, a_rows, l.w, l.cout_pad, l.k_total, p.block_n)
-                    : conv_encode_tmaps(&op.ta, &op.tb, x->ptr, a_rows, a_cols, a_ld, l.w, l.cout_pad, l.k_total,
+                    : conv_encode_tmaps(&op.ta, &op.tb, x->ptr, a_rows, a_cols, a_ld, l.w, l.cout_pad, l.k_dev,
                                         p.pair ? p.block_n / 2 : p.block_n, p.slab3 ? kConvSlabRows : kConvBlockM);
   if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled failed for layer '%s' (%d)", l.name.c_str(), rc);
   memset(&op.to, 0, sizeof(op.to));
   memset(&op.tr, 0, sizeof(op.tr));
-  p.staged = (!force_direct && l.cout % 64 == 0 && p.block_n % 64 == 0 &&
+  p.staged = (!force_direct && !split() && l.cout % 64 == 0 && p.block_n % 64 == 0 &&
               (staged_epilogue >= 2 || (staged_epilogue == 1 && res != nullptr))) ? 1 : 0;
   if (p.staged) {
-    rc = conv_encode_rows_tmap(&op.to, y->ptr, y->rows(batch), y->C, y->C);
-    if (rc == 0 && res != nullptr) rc = conv_encode_rows_tmap(&op.tr, res->ptr, res->rows(batch), res->C, res->C);
+    rc = conv_encode_rows_tmap(&op.to, y->ptr, y->rows(batch), y->C, y->ld);
+    if (rc == 0 && res != nullptr) rc = conv_encode_rows_tmap(&op.tr, res->ptr, res->rows(batch), res->C, res->ld);
     if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled (output) failed for layer '%s' (%d)", l.name.c_str(), rc);
   }
   if (conv_plan_smem(p) < 0) return fail(kErrInvalid, "layer '%s' does not fit the shared-memory plan", l.name.c_str());
@@ -217,6 +242,18 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
   op.flops = 2.0 * batch * y->H * y->W * static_cast<double>(l.cout) * l.ksize * l.ksize * l.cin;
   ops.push_back(op);
   return kOk;
+}
+
+// fp32 path: six channel-block passes per tap (activation part x weight part, every term >= 2^-16 of the product),
+// three-part output (ConvParams::split).
+void Engine::conv_set_split(ConvParams& p, int cin, int out_c, int res_c) const {
+  p.split = kSplitSegs;
+  p.parts = kSplitParts;
+  p.a_cb = cin / kConvBlockK;
+  for (int sg = 0; sg < kSplitSegs; ++sg) p.a_seg[sg] = kSplitAPart[sg];
+  p.cin_blocks = kSplitSegs * p.a_cb;
+  p.out_part_off = out_c;
+  p.res_part_off = res_c;
 }
 
 // Row segments of the multi-level feature matrix (one per pyramid level) with the 3x3 'same' tap offsets.
@@ -254,14 +291,16 @@ int Engine::head_conv_op(const __nv_bfloat16* x, int cin, const std::string& lay
   fill_head_segs(p, batch, n_levels);
   const long long last_row = p.seg[n_levels - 1].row_begin + p.seg[n_levels - 1].rows;
   p.cin_blocks = cin / kConvBlockK;
+  if (split()) conv_set_split(p, cin, l.cout, 0);
   p.n_valid = l.cout;
-  p.block_n = conv_pick_block_n(l.cout_pad, p.n_taps * p.cin_blocks, p.n_mtiles, epi == kEpiBf16);
+  p.block_n = conv_pick_block_n(l.cout_pad, p.n_taps * p.cin_blocks, p.n_mtiles, epi == kEpiBf16,
+                                split() ? 128 : kConvMaxBlockN);
   p.n_ntiles = (l.cout_pad + p.block_n - 1) / p.block_n;
   p.epi = epi;
   p.relu = relu;
   p.bias = l.bias;
   p.out = y;
-  p.out_ld = l.cout;
+  p.out_ld = split() ? kSplitParts * l.cout : l.cout;
   p.out_f32 = out_f32;
   p.out_hull = out_hull;
   int locs = 0;
@@ -273,14 +312,15 @@ int Engine::head_conv_op(const __nv_bfloat16* x, int cin, const std::string& lay
   memcpy(p.dec_mean, dec_mean, sizeof(dec_mean));
   memcpy(p.dec_std, dec_std, sizeof(dec_std));
   p.pair = conv_pair_ok(p) ? 1 : 0;
-  p.staged = (epi == kEpiBf16 && l.cout % 64 == 0 && p.block_n % 64 == 0 && staged_epilogue >= 3) ? 1 : 0;
+  p.staged = (!split() && epi == kEpiBf16 && l.cout % 64 == 0 && p.block_n % 64 == 0 && staged_epilogue >= 3) ? 1 : 0;
   p.slab3 = conv_slab3_mode(p);
-  int rc = conv_encode_tmaps(&op.ta, &op.tb, x, last_row, cin, cin, l.w, l.cout_pad, l.k_total,
+  const int a_ld = split() ? kSplitParts * cin : cin;
+  int rc = conv_encode_tmaps(&op.ta, &op.tb, x, last_row, a_ld, a_ld, l.w, l.cout_pad, l.k_dev,
                              p.pair ? p.block_n / 2 : p.block_n, p.slab3 ? kConvSlabRows : kConvBlockM);
   if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled failed for layer '%s' (%d)", l.name.c_str(), rc);
   memset(&op.to, 0, sizeof(op.to));
   memset(&op.tr, 0, sizeof(op.tr));
-  p.staged = (epi == kEpiBf16 && l.cout % 64 == 0 && p.block_n % 64 == 0 && staged_epilogue >= 3) ? 1 : 0;
+  p.staged = (!split() && epi == kEpiBf16 && l.cout % 64 == 0 && p.block_n % 64 == 0 && staged_epilogue >= 3) ? 1 : 0;
   if (p.staged) {
     rc = conv_encode_rows_tmap(&op.to, y, last_row, l.cout, l.cout);
     if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled (output) failed for layer '%s' (%d)", l.name.c_str(), rc);
@@ -319,7 +359,7 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
     op.out = out;
     int k = 0;
     for (int v : args) op.a[k++] = v;
-    static const char* kNames[] = {"conv", "stem_s2d", "maxpool", "parity_planes", "add"};
+    static const char* kNames[] = {"conv", "stem_s2d", "maxpool", "parity_planes", "add", "stem_conv_fp32"};
     snprintf(op.name, sizeof(op.name), "%s", kNames[kind]);
     ops.push_back(op);
   };
@@ -333,13 +373,19 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
   const int h1 = (H + 1) / 2, w1 = (W + 1) / 2;
   const int h2 = (h1 + 1) / 2, w2 = (w1 + 1) / 2;
   Tensor *s2d, *stem, *x;
-  s2d = tensor("conv1_s2d");
-  if (s2d == nullptr) PPB_TRY(new_tensor(&s2d, "conv1_s2d", h1, w1, 16, 0, 1, 0, 3));
   stem = tensor("conv1_relu");
   if (stem == nullptr) PPB_TRY(new_tensor(&stem, "conv1_relu", h1, w1, 64, 0, 1, 0, 3));
   PPB_TRY(get(&x, "pool1", h2, w2, 64, 1));
-  elementwise(kOpStemS2d, images, nullptr, nullptr, nullptr, s2d->ptr, {batch, H, W, h1, w1, input_u8 ? 1 : 0});
-  PPB_TRY(conv_op(s2d, 1, "conv1", nullptr, stem, 1, batch));
+  if (split()) {  // fp32 path: the stem is one fp32 CUDA-core convolution straight from the image
+    const LayerW& l1 = layers[layer_index.at("conv1")];
+    if (!l1.loaded) return fail(kErrState, "layer 'conv1' has no weights (call ppb_engine_set_layer first)");
+    elementwise(kOpStemSplit, images, l1.w_f32, l1.bias, nullptr, stem->ptr, {batch, H, W, h1, w1, input_u8 ? 1 : 0});
+  } else {
+    s2d = tensor("conv1_s2d");
+    if (s2d == nullptr) PPB_TRY(new_tensor(&s2d, "conv1_s2d", h1, w1, 16, 0, 1, 0, 3));
+    elementwise(kOpStemS2d, images, nullptr, nullptr, nullptr, s2d->ptr, {batch, H, W, h1, w1, input_u8 ? 1 : 0});
+    PPB_TRY(conv_op(s2d, 1, "conv1", nullptr, stem, 1, batch));
+  }
   elementwise(kOpMaxpool, stem->ptr, nullptr, nullptr, nullptr, x->ptr, {batch, h1, w1, stem->hp(), stem->wp(), 64, h2, w2});
 
   // ---- bottleneck stages
@@ -357,7 +403,7 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
         const int nh = (ch + 1) / 2, nw = (cw + 1) / 2;
         Tensor* sub;
         PPB_TRY(get(&sub, "res" + tag + "_sub", nh, nw, x->C, 1));
-        elementwise(kOpPlanes, x->ptr, nullptr, nullptr, nullptr, sub->ptr, {batch, ch, cw, x->C, nh, nw, 1});
+        elementwise(kOpPlanes, x->ptr, nullptr, nullptr, nullptr, sub->ptr, {batch, ch, cw, x->ld, nh, nw, 1});
         xin = sub;
         ch = nh;
         cw = nw;
@@ -400,7 +446,7 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
   PPB_TRY(conv_op(t3, 1, "P3_mid", nullptr, P3m, 0, batch));                                       // :201
   PPB_TRY(get(&s3, "P3_mid_planes", C4->H, C4->W, 256, 1, 4));
   PPB_TRY(get(&P3d, "P3_down", C4->H, C4->W, 256, 1));
-  elementwise(kOpPlanes, P3m->ptr, nullptr, nullptr, nullptr, s3->ptr, {batch, C3->H, C3->W, 256, C4->H, C4->W, 4});
+  elementwise(kOpPlanes, P3m->ptr, nullptr, nullptr, nullptr, s3->ptr, {batch, C3->H, C3->W, P3m->ld, C4->H, C4->W, 4});
   PPB_TRY(conv_op(s3, 4, "P3_down", nullptr, P3d, 0, batch, C3->H, C3->W));                        // :202
   PPB_TRY(get(&t3f, "P3_fin", C3->H, C3->W, 256, 1));
   elementwise(kOpAdd, P3m->ptr, P3l->ptr, nullptr, nullptr, t3f->ptr, {batch, C3->H, C3->W, 256, 0, 0});  // :203
@@ -408,7 +454,7 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
   elementwise(kOpAdd, P3d->ptr, P4m->ptr, P4l->ptr, nullptr, t4f->ptr, {batch, C4->H, C4->W, 256, 0, 0});  // :206,208
   PPB_TRY(get(&s4, "P4_mid_planes", C5->H, C5->W, 256, 1, 4));
   PPB_TRY(get(&P4d, "P4_down", C5->H, C5->W, 256, 1));
-  elementwise(kOpPlanes, P4m->ptr, nullptr, nullptr, nullptr, s4->ptr, {batch, C4->H, C4->W, 256, C5->H, C5->W, 4});
+  elementwise(kOpPlanes, P4m->ptr, nullptr, nullptr, nullptr, s4->ptr, {batch, C4->H, C4->W, P4m->ld, C5->H, C5->W, 4});
   PPB_TRY(conv_op(s4, 4, "P4_down", nullptr, P4d, 0, batch, C4->H, C4->W));                        // :207
   PPB_TRY(get(&t5f, "P5_fin", C5->H, C5->W, 256, 1));
   elementwise(kOpAdd, P4d->ptr, P5l->ptr, nullptr, nullptr, t5f->ptr, {batch, C5->H, C5->W, 256, 0, 0});  // :211
@@ -420,10 +466,11 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
   Tensor* fin[3] = {t3f, t4f, t5f};
   const char* pname[3] = {"P3", "P4", "P5"};
   for (int i = 0; i < 3; ++i) {
-    fview[i].ptr = feat->ptr + static_cast<size_t>(seg_row_begin[i]) * 256;
+    fview[i].ptr = feat->ptr + static_cast<size_t>(seg_row_begin[i]) * feat->ld;
     fview[i].H = lvl_h[i];
     fview[i].W = lvl_w[i];
     fview[i].C = 256;
+    fview[i].ld = feat->ld;
     PPB_TRY(conv_op(fin[i], 1, pname[i], nullptr, &fview[i], 0, batch));                           // :204,209,212
   }
 
@@ -481,7 +528,17 @@ int Engine::launch_all(cudaStream_t st) {
           PPB_CUDA(launch_stem_s2d(static_cast<const float*>(op.in0), static_cast<__nv_bfloat16*>(op.out), op.a[0],
                                    op.a[1], op.a[2], op.a[3], op.a[4], st));
         break;
+      case kOpStemSplit:
+        PPB_CUDA(launch_stem_conv_split(op.in0, op.a[5], input_mean, static_cast<const float*>(op.in1),
+                                        static_cast<const float*>(op.in2), static_cast<__nv_bfloat16*>(op.out), op.a[0],
+                                        op.a[1], op.a[2], op.a[3], op.a[4], st));
+        break;
       case kOpMaxpool:
+        if (split()) {
+          PPB_CUDA(launch_maxpool3x3s2_split(static_cast<const __nv_bfloat16*>(op.in0), static_cast<__nv_bfloat16*>(op.out),
+                                             op.a[0], op.a[1], op.a[2], op.a[3], op.a[4], op.a[5], op.a[6], op.a[7], st));
+          break;
+        }
         PPB_CUDA(launch_maxpool3x3s2(static_cast<const __nv_bfloat16*>(op.in0), static_cast<__nv_bfloat16*>(op.out),
                                      op.a[0], op.a[1], op.a[2], op.a[3], op.a[4], op.a[5], op.a[6], op.a[7], st));
         break;
@@ -490,6 +547,13 @@ int Engine::launch_all(cudaStream_t st) {
                                       op.a[0], op.a[1], op.a[2], op.a[3], op.a[4], op.a[5], op.a[6], st));
         break;
       case kOpAdd:
+        if (split()) {
+          PPB_CUDA(launch_add_split(static_cast<const __nv_bfloat16*>(op.in0), static_cast<const __nv_bfloat16*>(op.in1),
+                                    static_cast<const __nv_bfloat16*>(op.in2), static_cast<const __nv_bfloat16*>(op.in3),
+                                    op.a[4], op.a[5], static_cast<__nv_bfloat16*>(op.out), op.a[0], op.a[1], op.a[2],
+                                    op.a[3], st));
+          break;
+        }
         PPB_CUDA(launch_add(static_cast<const __nv_bfloat16*>(op.in0), static_cast<const __nv_bfloat16*>(op.in1),
                             static_cast<const __nv_bfloat16*>(op.in2), static_cast<const __nv_bfloat16*>(op.in3),
                             op.a[4], op.a[5], static_cast<__nv_bfloat16*>(op.out), op.a[0], op.a[1], op.a[2], op.a[3],
@@ -532,7 +596,14 @@ extern "C" {
 
 int ppb_engine_create(ppb_engine** out, int device, int max_batch, int height, int width, int num_classes,
                       int num_anchors) {
+  return ppb_engine_create_ex(out, device, max_batch, height, width, num_classes, num_anchors, 0);
+}
+
+int ppb_engine_create_ex(ppb_engine** out, int device, int max_batch, int height, int width, int num_classes,
+                         int num_anchors, int precision) {
   PPB_REQUIRE(out != nullptr, "ppb_engine_create: null out");
+  PPB_REQUIRE(precision == 0 || precision == 1, "ppb_engine_create_ex: precision must be 0 (bf16) or 1 (fp32 path), got %d",
+              precision);
   PPB_REQUIRE(max_batch > 0 && height >= 32 && width >= 32, "ppb_engine_create: bad shape batch=%d h=%d w=%d",
               max_batch, height, width);
   PPB_REQUIRE(num_classes > 0 && num_classes * num_anchors <= 2000 && num_anchors > 0 && num_anchors <= 9,
@@ -547,6 +618,7 @@ int ppb_engine_create(ppb_engine** out, int device, int max_batch, int height, i
   e.W = width;
   e.num_classes = num_classes;
   e.num_anchors = num_anchors;
+  e.precision = precision;
   int rows = 0, tiles = 0;
   for (int i = 0; i < 3; ++i) {  // guess_shapes (PyraPose/utils/anchors.py:357-369): (dim + 2^l - 1) // 2^l
     const int s = 8 << i;
@@ -702,20 +774,22 @@ int ppb_engine_activation(ppb_engine* h, const char* name, float* out_host, int*
     Tensor* base = e.tensor(nm.substr(0, at));
     const int i = atoi(nm.c_str() + at + 1);
     PPB_REQUIRE(base != nullptr && i >= 0 && i < 3, "ppb_engine_activation: unknown tensor '%s'", name);
-    view.ptr = base->ptr + static_cast<size_t>(e.seg_row_begin[i]) * base->C;
+    view.ptr = base->ptr + static_cast<size_t>(e.seg_row_begin[i]) * base->ld;
     view.H = e.lvl_h[i];
     view.W = e.lvl_w[i];
     view.C = base->C;
+    view.ld = base->ld;
     t = &view;
   }
   if (t == nullptr && (nm == "P3" || nm == "P4" || nm == "P5")) {
     Tensor* feat = e.tensor("features");
     PPB_REQUIRE(feat != nullptr, "ppb_engine_activation: features not allocated");
     const int i = nm[1] - '3';
-    view.ptr = feat->ptr + static_cast<size_t>(e.seg_row_begin[i]) * 256;
+    view.ptr = feat->ptr + static_cast<size_t>(e.seg_row_begin[i]) * feat->ld;
     view.H = e.lvl_h[i];
     view.W = e.lvl_w[i];
     view.C = 256;
+    view.ld = feat->ld;
     t = &view;
   }
   PPB_REQUIRE(t != nullptr && t->H > 0, "ppb_engine_activation: unknown tensor '%s'", name);
@@ -729,16 +803,20 @@ int ppb_engine_activation(ppb_engine* h, const char* name, float* out_host, int*
   if (out_host == nullptr) return kOk;
   PPB_CUDA(cudaSetDevice(e.device));
   PPB_CUDA(cudaDeviceSynchronize());
-  const size_t n = static_cast<size_t>(t->rows(B)) * t->C;
+  const size_t n = static_cast<size_t>(t->rows(B)) * t->ld;
   std::vector<__nv_bfloat16> host(n);
   PPB_CUDA(cudaMemcpy(host.data(), t->ptr, n * sizeof(__nv_bfloat16), cudaMemcpyDeviceToHost));
   const int hp = t->hp(), wp = t->wp();
   for (int b = 0; b < B; ++b)
     for (int y = 0; y < t->H; ++y)
       for (int x = 0; x < t->W; ++x) {
-        const __nv_bfloat16* src = host.data() + ((static_cast<size_t>(b) * hp + y + t->pad_lo) * wp + x + t->pad_lo) * t->C;
+        const __nv_bfloat16* src = host.data() + ((static_cast<size_t>(b) * hp + y + t->pad_lo) * wp + x + t->pad_lo) * t->ld;
         float* dst = out_host + ((static_cast<size_t>(b) * t->H + y) * t->W + x) * t->C;
-        for (int c = 0; c < t->C; ++c) dst[c] = __bfloat162float(src[c]);
+        for (int c = 0; c < t->C; ++c) {  // fp32 path: value = sum of the parts, smallest first
+          float v = 0.0f;
+          for (int part = t->ld / t->C - 1; part >= 0; --part) v += __bfloat162float(src[part * t->C + c]);
+          dst[c] = v;
+        }
       }
   return kOk;
 }
@@ -776,6 +854,34 @@ int ppb_engine_profile(ppb_engine* h, void* stream, float* ms_out_host, int* kin
   for (auto& x : ev) cudaEventDestroy(x);
   if (rc != kOk) return rc;
   PPB_CUDA(sync);
+  return kOk;
+}
+
+/* Cycle-stamped trace of one CTA of one convolution launch (ConvParams::trace): runs op `index` of the bound plan
+ * eagerly with the tracing instantiation of the kernel. trace_dev: device buffer of 8 * cap uint2 entries (zeroed by
+ * the call); role r (0 producer, 1 MMA issuer, 2 residual producer, 3.. epilogue groups) owns entries [r*cap, (r+1)*cap):
+ * entry 0 = {event count, end clock}, then {tag, clock64 low word} pairs. grid_out receives the CTA count. */
+int ppb_engine_trace_op(ppb_engine* h, int index, int cta, void* trace_dev, int cap, int* info_out_host, void* stream) {
+  PPB_REQUIRE(h != nullptr && trace_dev != nullptr && cap >= 16, "ppb_engine_trace_op: bad argument");
+  Engine& e = h->e;
+  PPB_REQUIRE(e.bound_batch != 0 || e.plan_batch != 0, "ppb_engine_trace_op: nothing bound");
+  PPB_REQUIRE(index >= 0 && index < static_cast<int>(e.ops.size()) && e.ops[index].kind == kOpConv,
+              "ppb_engine_trace_op: op %d is not a convolution", index);
+  PPB_CUDA(cudaSetDevice(e.device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  PPB_CUDA(cudaMemsetAsync(trace_dev, 0, static_cast<size_t>(8) * cap * sizeof(uint2), st));
+  Op op = e.ops[index];
+  op.p.trace = static_cast<uint2*>(trace_dev);
+  op.p.trace_cap = cap;
+  op.p.trace_cta = cta;
+  PPB_CUDA(conv_launch(op.ta, op.tb, op.to, op.tr, op.p, 0, st));
+  count_launch();
+  if (info_out_host != nullptr) {  // the launch shape, for the tool's header
+    const ConvParams& p = op.p;
+    const int v[12] = {p.n_mtiles, p.n_ntiles, p.block_n, p.n_taps, p.cin_blocks, p.n_stages, p.ring_slots, p.pair,
+                       p.slab3, p.bres, p.staged, p.epi_groups};
+    memcpy(info_out_host, v, sizeof(v));
+  }
   return kOk;
 }
 

@@ -16,8 +16,14 @@
 
 namespace ppb {
 
+// fp32 path (Engine::precision 1, ConvParams::split): parts per value and the (activation part, weight part) of the
+// six K segments, largest terms first.
+constexpr int kSplitParts = 3;
+constexpr int kSplitSegs = 6;
+constexpr int kSplitAPart[kSplitSegs] = {0, 1, 0, 2, 1, 0};
+constexpr int kSplitWPart[kSplitSegs] = {0, 0, 1, 0, 1, 2};
+
 void conv_fill_single_seg(ConvParams& p, int batch, int h, int w, int ksize);
-int conv_pick_block_n(int cout_pad, int k_iters, long m_tiles, bool bf16_out);
 
 struct LayerW {
   std::string name;
@@ -25,7 +31,9 @@ struct LayerW {
   bool has_bn, has_bias;
   int k_total;   // columns of the device weight matrix (ksize*ksize*cin, stem: 192)
   int cout_pad;  // rows, multiple of 16
+  int k_dev = 0;  // columns of the device matrix: k_total, or 6 * k_total on the fp32 path (six part blocks per tap)
   __nv_bfloat16* w = nullptr;
+  float* w_f32 = nullptr;  // fp32 path, stem only: [7][7][3][64] with the BatchNorm scale folded in (launch_stem_conv_split)
   float* bias = nullptr;
   bool loaded = false;
   // host copies kept for the training step (master weights start from them): raw Keras kernel as [cout][k_total]
@@ -37,12 +45,13 @@ struct Tensor {  // bf16 activation on a pixel grid with pad_lo border pixels be
   std::string name;
   __nv_bfloat16* ptr = nullptr;
   int H = 0, W = 0, C = 0, pad_lo = 1, pad_hi = 1;  // padded-flat: 1/1; stem grid: 0/3
+  int ld = 0;  // elements per row: C, or 3 * C on the fp32 path (three bf16 parts per value, ConvParams::split)
   int hp() const { return H + pad_lo + pad_hi; }
   int wp() const { return W + pad_lo + pad_hi; }
   long long rows(int B) const { return static_cast<long long>(B) * hp() * wp(); }
 };
 
-enum OpKind { kOpConv, kOpStemS2d, kOpMaxpool, kOpPlanes, kOpAdd };
+enum OpKind { kOpConv, kOpStemS2d, kOpMaxpool, kOpPlanes, kOpAdd, kOpStemSplit };
 
 struct Op {
   OpKind kind;
@@ -102,6 +111,12 @@ struct Engine {
   // input staging: images bound as raw uint8 BGR with the 'caffe' mean subtraction fused into the stem loader
   bool input_u8 = false;
   float input_mean[3] = {103.939f, 116.779f, 123.68f};
+  // 0: bf16 activations and weights, fp32 accumulation (the production path, tolerance 1e-2).
+  // 1: the fp32 path of BASELINE.json north_star (tolerance 1e-4): activations and weights as three bf16 parts each
+  //    (24 significant bits), six tcgen05 MMAs per product (ConvParams::split), stem / Add / MaxPool in fp32
+  //    (split_ops.cu). Inference only.
+  int precision = 0;
+  bool split() const { return precision == 1; }
   bool training_plan = false;
   long long train_bucket_bytes = 0;  // gradient bucket size of the segmented training step (0 = one graph)
   std::shared_ptr<struct TrainState> train;
@@ -150,10 +165,11 @@ struct Engine {
     t->C = c;
     t->pad_lo = pad;
     t->pad_hi = pad_hi >= 0 ? pad_hi : pad;
+    t->ld = split() ? kSplitParts * c : c;
     long long rows = rows_override ? rows_override : t->rows(max_batch) * planes;
     rows = (rows + kConvBlockM - 1) / kConvBlockM * kConvBlockM + kConvBlockM;  // slack: TMA rows may overlap the end
     void* p = nullptr;
-    int rc = device_alloc(&p, static_cast<size_t>(rows) * c * sizeof(__nv_bfloat16));
+    int rc = device_alloc(&p, static_cast<size_t>(rows) * t->ld * sizeof(__nv_bfloat16));
     if (rc != kOk) return rc;
     t->ptr = static_cast<__nv_bfloat16*>(p);
     *out = t.get();
@@ -172,6 +188,7 @@ struct Engine {
               int src_h = 0, int src_w = 0);
   int head_conv_op(const __nv_bfloat16* x, int cin, const std::string& layer, __nv_bfloat16* y, int relu, int batch,
                    int n_levels, int epi, float* out_f32, float* out_hull);
+  void conv_set_split(ConvParams& p, int cin, int out_c, int res_c) const;
   int capture(cudaStream_t st);
   int launch_all(cudaStream_t st);
   void fill_head_segs(ConvParams& p, int batch, int n_levels) const;

@@ -889,6 +889,7 @@ int ppb_engine_train_bind(ppb_engine* h, int batch, const float* images, const f
   PPB_REQUIRE(batch > 0 && batch <= e.max_batch, "ppb_engine_train_bind: batch %d outside [1, %d]", batch, e.max_batch);
   PPB_REQUIRE(images && y_reg && y_cls && y_mask && out_reg && out_cls && out_mask, "ppb_engine_train_bind: null buffer");
   PPB_REQUIRE((reinterpret_cast<uintptr_t>(out_reg) & 15) == 0, "ppb_engine_train_bind: outputs must be 16-byte aligned");
+  if (e.split()) return fail(kErrState, "ppb_engine_train_bind: the fp32 path (precision 1) is inference only");
   PPB_CUDA(cudaSetDevice(e.device));
   e.training_plan = true;
   int rc = e.build_plan(batch, images, out_reg, out_cls, out_mask, nullptr, 0);

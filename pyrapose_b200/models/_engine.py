@@ -20,7 +20,7 @@ def _fp(a):
 
 
 class Engine(object):
-    def __init__(self, device, max_batch, height, width, num_classes, num_anchors):
+    def __init__(self, device, max_batch, height, width, num_classes, num_anchors, precision=0):
         self.lib = nat.load()
         self.lib.ppb_engine_device_bytes.restype = ctypes.c_size_t
         self.device = torch.device("cuda", device if device is not None else torch.cuda.current_device())
@@ -28,8 +28,9 @@ class Engine(object):
         self.height, self.width = int(height), int(width)
         self.num_classes, self.num_anchors = int(num_classes), int(num_anchors)
         self._h = ctypes.c_void_p()
-        nat.check(self.lib.ppb_engine_create(ctypes.byref(self._h), self.device.index, self.max_batch, self.height,
-                                             self.width, self.num_classes, self.num_anchors))
+        self.precision = int(precision)   # 0: bf16 production path; 1: fp32 path (three bf16 parts, six MMAs)
+        nat.check(self.lib.ppb_engine_create_ex(ctypes.byref(self._h), self.device.index, self.max_batch, self.height,
+                                                self.width, self.num_classes, self.num_anchors, self.precision))
         self.levels = [((self.height + (8 << i) - 1) // (8 << i), (self.width + (8 << i) - 1) // (8 << i))
                        for i in range(3)]
         self.num_locations = sum(h * w for h, w in self.levels)
@@ -143,6 +144,28 @@ class Engine(object):
         with torch.cuda.device(self.device):
             nat.check(self.lib.ppb_engine_profile(self._h, nat.current_stream_ptr(), ms, kinds, n))
         return [(int(kinds[i]), float(ms[i])) for i in range(n)]
+
+    def trace_op(self, index, cta=0, cap=4096):
+        """Cycle-stamped trace of CTA `cta` of convolution launch `index` (ppb_engine_trace_op). Returns (info dict,
+        {role: int64 array [n, 4] of (event, tile, sub, clock)})."""
+        buf = torch.zeros(8 * cap, 2, dtype=torch.int32, device=self.device)
+        info = (ctypes.c_int * 12)()
+        with torch.cuda.device(self.device):
+            nat.check(self.lib.ppb_engine_trace_op(self._h, int(index), int(cta), nat.ptr(buf), int(cap), info,
+                                                   nat.current_stream_ptr()))
+            torch.cuda.synchronize()
+        raw = buf.cpu().numpy().astype(np.int64) & 0xFFFFFFFF
+        keys = ("m_tiles", "n_tiles", "block_n", "taps", "cin_blocks", "stages", "ring_slots", "pair", "slab3", "bres",
+                "staged", "epi_groups")
+        roles = {}
+        for r, name in enumerate(("producer", "mma", "residual", "epi0", "epi1", "epi2")):
+            reg = raw[r * cap:(r + 1) * cap]
+            n = int(reg[0, 0])
+            if n == 0:
+                continue
+            tag, clk = reg[1:1 + n, 0], reg[1:1 + n, 1]
+            roles[name] = np.stack([tag >> 24, (tag >> 8) & 0xFFFF, tag & 0xFF, clk], axis=1)
+        return dict(zip(keys, [int(v) for v in info])), roles
 
     def op_table(self):
         """[(name, algorithmic flops)] per launch of the bound plan."""

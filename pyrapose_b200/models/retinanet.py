@@ -26,7 +26,11 @@ class _LayerView(object):
 
 class PFPNModel(object):
     def __init__(self, num_classes, num_anchors=None, name='retinanet', inference=False, anchor_params=None,
-                 weights=None, seed=None, device=None):
+                 weights=None, seed=None, device=None, precision='bf16'):
+        if precision not in ('bf16', 'fp32'):
+            raise ValueError("precision must be 'bf16' (production path, tolerance 1e-2) or 'fp32' (three-part bf16 "
+                             "split, six MMAs per product, tolerance 1e-4; inference only), got %r" % (precision,))
+        self.precision = precision
         self.num_classes = int(num_classes)
         self.num_anchors = int(num_anchors if num_anchors is not None else AnchorParameters.default.num_anchors())
         self.name = name
@@ -148,7 +152,8 @@ class PFPNModel(object):
     def _engine(self, batch, height, width):
         import torch
         from ._engine import Engine
-        key = (height, width)
+        fp32 = self.precision == 'fp32'
+        key = (height, width, 'fp32') if fp32 else (height, width)
         eng = self._engines.get(key)
         if eng is None or eng.max_batch < batch:
             if eng is not None:
@@ -159,7 +164,9 @@ class PFPNModel(object):
                     self._root()._train_engine = None
                 eng.close()
             dev = self.device if self.device is not None else torch.cuda.current_device()
-            eng = Engine(dev, batch, height, width, self.num_classes, self.num_anchors)
+            if fp32:
+                self._root().sync_weights()   # a trained parent's master weights first
+            eng = Engine(dev, batch, height, width, self.num_classes, self.num_anchors, precision=1 if fp32 else 0)
             eng.load_weights(self.weights, self._bn_names())
             eng._anchor_owner = None
             self._engines[key] = eng
@@ -340,7 +347,8 @@ class PFPNModel(object):
             yield finish(pending.pop(0))
 
     def activation(self, name, height, width):
-        return self._engines[(height, width)].activation(name)
+        key = (height, width, 'fp32') if self.precision == 'fp32' else (height, width)
+        return self._engines[key].activation(name)
 
     # ------------------------------------------------------------------ training (keras.Model.compile / train_on_batch)
     def compile(self, loss=None, optimizer=None, dp_normalizer='global', bucket_bytes=25 << 20, data_parallel=True,
@@ -398,6 +406,8 @@ class PFPNModel(object):
             raise RuntimeError("You must compile a model before training/testing. Use `model.compile(optimizer, loss)`.")
         if not isinstance(y, (list, tuple)) or len(y) != 3:
             raise ValueError("expected y = [regression_3D, labels, mask]")
+        if self.precision == 'fp32':
+            raise RuntimeError("the fp32 path (precision='fp32') is inference only; train with precision='bf16'")
         x, u8 = self._as_input(x)
         B, H, W = int(x.shape[0]), int(x.shape[1]), int(x.shape[2])
         dist = torch.distributed
@@ -463,18 +473,18 @@ class PFPNModel(object):
 
 
 def retinanet(inputs=None, backbone_layers=None, num_classes=None, num_anchors=None, create_pyramid_features=None,
-              submodels=None, name='retinanet', seed=None, device=None):
+              submodels=None, name='retinanet', seed=None, device=None, precision='bf16'):
     """ Construct a PFPN training model (outputs '3Dbox', 'cls', 'mask'). `inputs`/`backbone_layers` are accepted for
     signature compatibility; the ResNet-50 backbone and __create_sparceFPN are built into the engine."""
     if num_classes is None:
         raise ValueError("num_classes is required")
     if create_pyramid_features is not None or submodels is not None:
         raise NotImplementedError("custom pyramid builders / submodels are not part of the hot path")
-    return PFPNModel(num_classes, num_anchors, name=name, seed=seed, device=device)
+    return PFPNModel(num_classes, num_anchors, name=name, seed=seed, device=device, precision=precision)
 
 
 def retinanet_bbox(model=None, nms=True, class_specific_filter=True, name='retinanet-bbox', anchor_params=None,
-                   **kwargs):
+                   precision=None, **kwargs):
     """ Inference model: training model + Anchors + RegressBoxes3D. Like the reference (:302-335), `nms` and
     `class_specific_filter` are accepted and not wired into the graph; use layers.FilterDetections or
     model.detect_on_batch for filtering."""
@@ -485,7 +495,8 @@ def retinanet_bbox(model=None, nms=True, class_specific_filter=True, name='retin
     else:
         assert_training_model(model)
     out = PFPNModel(model.num_classes, model.num_anchors, name=name, inference=True, anchor_params=anchor_params,
-                    weights=model.weights, device=model.device)
+                    weights=model.weights, device=model.device,
+                    precision=precision if precision is not None else model.precision)
     # Like the reference (bin/train.py:86-92: prediction_model = retinanet_bbox(model=model) is built BEFORE training
     # and evaluated after every epoch), the prediction model shares the training model's layers: same weight dict,
     # same engines. The Adam kernel rewrites the bf16 forward matrices in place, so a predict_on_batch after
