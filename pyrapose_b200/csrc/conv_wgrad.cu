@@ -29,17 +29,38 @@ struct Task {
   int m_tile, tap, n_tile, k_begin, k_end;
 };
 
-__device__ __forceinline__ Task decode_task(const WgradParams& p, int t) {
-  Task k;
-  const int split = t % p.k_splits;
-  t /= p.k_splits;
-  k.n_tile = t % p.n_ntiles;
-  t /= p.n_ntiles;
-  k.tap = t % p.n_taps;
-  k.m_tile = t / p.n_taps;
-  k.k_begin = static_cast<int>(static_cast<long long>(p.total_k_iters) * split / p.k_splits);
-  k.k_end = static_cast<int>(static_cast<long long>(p.total_k_iters) * (split + 1) / p.k_splits);
-  return k;
+// Work distribution: tasks = K splits x output tiles, task t = split * tiles + tile (tile = (m, tap, n), n fastest), worker
+// w of G (a CTA, or a CTA pair) runs tasks w, w + G, ... . Concurrently running workers therefore sit in the SAME few
+// row ranges of g and x (all tiles of one split move in lockstep), so every 64-row block comes from HBM once and is an
+// L2 hit for the other tiles. (A stream-K walk that gives every worker an equal contiguous share of tiles x k-iterations
+// was measured first: perfectly balanced, but the workers' row positions spread over the whole matrix, nothing is
+// shared in L2 and the 512 -> 512 head layers went from 0.37 to 0.45 ms.) The balance comes from the choice of the
+// split count instead: wgrad_plan() picks it so that tasks fill whole waves of G.
+struct TaskWalk {
+  int t, t_step, t_end, tiles;
+  __device__ __forceinline__ bool next(const WgradParams& p, bool pair, uint32_t rank, Task& k) {
+    if (t >= t_end) return false;
+    const int split = t / tiles;
+    int tile = t - split * tiles;
+    t += t_step;
+    k.k_begin = static_cast<int>(static_cast<long long>(p.total_k_iters) * split / p.k_splits);
+    k.k_end = static_cast<int>(static_cast<long long>(p.total_k_iters) * (split + 1) / p.k_splits);
+    k.n_tile = tile % p.n_ntiles;
+    tile /= p.n_ntiles;
+    k.tap = tile % p.n_taps;
+    k.m_tile = tile / p.n_taps;
+    if (pair) k.m_tile = (k.m_tile << 1) + static_cast<int>(rank);
+    return true;
+  }
+};
+
+__device__ __forceinline__ TaskWalk make_walk(const WgradParams& p, bool pair) {
+  TaskWalk t;
+  t.tiles = (pair ? p.n_mtiles >> 1 : p.n_mtiles) * p.n_taps * p.n_ntiles;
+  t.t = pair ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  t.t_step = pair ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  t.t_end = t.tiles * p.k_splits;
+  return t;
 }
 
 template <bool kPair>
@@ -96,23 +117,16 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
   if (pair) cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  // pair: tasks enumerate (Cout-tile PAIR, tap, n tile, split); this CTA's Cout tile is 2 * pair + rank
-  const int total_tasks = (pair ? p.n_mtiles >> 1 : p.n_mtiles) * p.n_taps * p.n_ntiles * p.k_splits;
-  const int t_begin = pair ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
-  const int t_step = pair ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
-  auto my_task = [&](int t) {
-    Task k = decode_task(p, t);
-    if (pair) k.m_tile = (k.m_tile << 1) + static_cast<int>(rank);
-    return k;
-  };
+  // pair: tiles enumerate (Cout-tile PAIR, tap, n tile); this CTA's Cout tile is 2 * pair + rank
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = t_begin; t < total_tasks; t += t_step) {
-        const Task k = my_task(t);
+      TaskWalk walk = make_walk(p, pair);
+      Task k;
+      while (walk.next(p, pair, rank, k)) {
         // locate k_begin inside the segment list
         int seg = 0, local = k.k_begin;
         while (seg < p.n_segs - 1 && local >= p.seg[seg].k_iters) {
@@ -158,9 +172,9 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
       int acc = 0;
       uint32_t acc_phase = 0;
       const uint32_t idesc = umma_idesc_bf16_mn(pair ? 256 : 128, p.block_n);
-      for (int t = t_begin; t < total_tasks; t += t_step) {
-        const Task k = my_task(t);
-        if (k.k_end <= k.k_begin) continue;
+      TaskWalk walk = make_walk(p, pair);
+      Task k;
+      while (walk.next(p, pair, rank, k)) {
         mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1, kWgFaultTmemEmpty);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kWgAccCols;
@@ -195,9 +209,9 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
     const int q = warp - 4;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int t = t_begin; t < total_tasks; t += t_step) {
-      const Task k = my_task(t);
-      if (k.k_end <= k.k_begin) continue;
+    TaskWalk walk = make_walk(p, pair);
+    Task k;
+    while (walk.next(p, pair, rank, k)) {
       mbar_wait(&tmem_full_bar[acc], acc_phase, kWgFaultTmemFull);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * kWgAccCols;
@@ -244,26 +258,75 @@ int wgrad_encode_tmaps(CUtensorMap* tmap_g, CUtensorMap* tmap_x, const void* g, 
   return conv_encode_box_tmap(tmap_x, x, x_rows, x_cols, x_ld, 64);
 }
 
+// Tile shape and split count, by a small cost model over (pair, block_n, splits):
+//   cycles ~ MMA cycles / (shape efficiency x wave efficiency) + flushed bytes / atomic throughput.
+// Every task ends in a 128 x block_n fp32 flush into dW with 128-bit atomics, which the L2 retires at ~1 TB/s
+// (measured r02: 25-38 MB of flushes <-> 35-40 us on the stage-4/5 and PFPN layers, whose MMAs need ~5 us), so small
+// layers want narrow tiles and few splits while large ones want the 256 x 256 CTA-pair tile (92 % tensor-pipe activity
+// in the head layers) and a split count whose tasks fill whole waves (tiles x splits a multiple of the workers: the old
+// fixed rule ran 36 x 5 = 180 tasks on 74 pairs, 3 waves for 2.43 waves of work).
+// PPB_WGRAD_BN / PPB_WGRAD_PAIR / PPB_WGRAD_SPLITS force a choice for A/B runs.
 void wgrad_plan(WgradParams& p) {
-  p.block_n = (p.cin % 256 == 0) ? 256 : ((p.cin % 128 == 0) ? 128 : 64);
-  p.n_mtiles = (p.cout + 127) / 128;
-  p.n_ntiles = p.cin / p.block_n;
   static const int pair_mode = [] {
     const char* e = getenv("PPB_PAIR");
     return e != nullptr ? atoi(e) : 1;
   }();
-  p.pair = (pair_mode != 0 && p.cout % 256 == 0 && p.block_n >= 128) ? 1 : 0;
+  static const int force_bn = [] {
+    const char* e = getenv("PPB_WGRAD_BN");
+    return e != nullptr ? atoi(e) : 0;
+  }();
+  static const int force_pair = [] {
+    const char* e = getenv("PPB_WGRAD_PAIR");
+    return e != nullptr ? atoi(e) : -1;
+  }();
+  static const int force_splits = [] {
+    const char* e = getenv("PPB_WGRAD_SPLITS");
+    return e != nullptr ? atoi(e) : 0;
+  }();
+  const int sms = conv_num_sms() > 0 ? conv_num_sms() : 148;
+  p.n_mtiles = (p.cout + 127) / 128;
+  // per-SM MMA cycles of the whole layer at full rate: a k-iteration (64 rows) of a 128 x 64 tile is 4 MMAs x 32 clk
+  const double mma_clk = static_cast<double>(p.n_mtiles) * p.n_taps * (p.cin / 64.0) * p.total_k_iters * 128.0 / sms;
+  const int max_splits = p.total_k_iters / 8 > 0 ? p.total_k_iters / 8 : 1;
+  double best_cost = 0.0;
+  int best_bn = 0, best_pair = 0, best_splits = 1;
+  for (int pr = 1; pr >= 0; --pr)
+    for (int bn = 256; bn >= 64; bn >>= 1) {
+      if (p.cin % bn != 0) continue;
+      if (pr && (pair_mode == 0 || p.cout % 256 != 0 || bn < 128)) continue;
+      if (force_bn != 0 && bn != force_bn && p.cin % force_bn == 0) continue;
+      if (force_pair >= 0 && pr != force_pair && !(force_pair == 1 && (p.cout % 256 != 0 || bn < 128))) continue;
+      // relative MMA efficiency: narrow tiles are bound by the shared-memory reads of the A operand, single-CTA wide
+      // tiles by the L2 -> SM operand feed
+      const double shape_eff = bn == 64 ? 0.67 : (bn == 128 ? (pr ? 0.95 : 0.9) : (pr ? 1.0 : 0.87));
+      const int tiles = (pr ? p.n_mtiles / 2 : p.n_mtiles) * p.n_taps * (p.cin / bn);
+      const int workers = pr ? sms / 2 : sms;
+      const int s_hi = (4 * workers + tiles - 1) / tiles < max_splits ? (4 * workers + tiles - 1) / tiles : max_splits;
+      for (int sp = 1; sp <= s_hi; ++sp) {
+        if (force_splits != 0 && sp != (force_splits < s_hi ? force_splits : s_hi)) continue;
+        const int tasks = tiles * sp;
+        const int waves = (tasks + workers - 1) / workers;
+        const double wave_eff = static_cast<double>(tasks) / (static_cast<double>(waves) * workers);
+        const double flush_bytes = static_cast<double>(tasks) * (pr ? 2 : 1) * 128.0 * bn * 4.0;
+        // the flushes of all but the last wave overlap the next task's MMAs (double-buffered accumulators)
+        const double exposed = flush_bytes / waves;
+        const double cost = mma_clk / (shape_eff * wave_eff) + exposed / 550.0 + 0.1 * (flush_bytes - exposed) / 550.0;
+        if (best_bn == 0 || cost < best_cost) {
+          best_cost = cost;
+          best_bn = bn;
+          best_pair = pr;
+          best_splits = sp;
+        }
+      }
+    }
+  p.block_n = best_bn;
+  p.pair = best_pair;
+  p.k_splits = best_splits;
+  p.n_ntiles = p.cin / p.block_n;
   const int stage_bytes = kWgABytes + (p.pair ? p.block_n >> 7 : p.block_n >> 6) * kWgBoxBytes;
   int stages = (kWgSmemLimit - 1024 - kWgBarBytes) / stage_bytes;
   if (stages > kWgMaxStages) stages = kWgMaxStages;
   p.n_stages = stages;
-  const int tiles = (p.pair ? p.n_mtiles / 2 : p.n_mtiles) * p.n_taps * p.n_ntiles;
-  const int sms = (conv_num_sms() > 0 ? conv_num_sms() : 148) / (p.pair ? 2 : 1);
-  int splits = (2 * sms + tiles - 1) / tiles;
-  const int max_splits = p.total_k_iters / 8 > 0 ? p.total_k_iters / 8 : 1;
-  if (splits > max_splits) splits = max_splits;
-  if (splits < 1) splits = 1;
-  p.k_splits = splits;
 }
 
 cudaError_t wgrad_launch(const CUtensorMap& tmap_g, const CUtensorMap& tmap_x, const WgradParams& p,

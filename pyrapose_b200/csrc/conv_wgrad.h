@@ -23,7 +23,7 @@ struct WgradParams {
   int block_n;        // Cin columns per tile: 64, 128 or 256
   int n_mtiles;       // ceil(cout / 128)
   int n_ntiles;       // cin / block_n
-  int k_splits;       // CTAs sharing one (m, tap, n) tile along K
+  int k_splits;       // tasks sharing one (m, tap, n) tile along K (chosen by wgrad_plan so that tasks fill whole waves)
   int n_stages;
   int pair;           // 1: CTA pairs over two Cout tiles (tcgen05 cta_group::2), set by wgrad_plan() when cout % 256 == 0,
                       // cin tile >= 128 and PPB_PAIR != 0
