@@ -252,6 +252,11 @@ PPB_API int ppb_engine_set_input_u8(ppb_engine* engine, int enable, const float*
 PPB_API int ppb_engine_bind(ppb_engine* engine, int batch, const float* images, float* out_box3d, float* out_cls,
                             float* out_mask, float* out_hull, int decode, void* stream);
 PPB_API int ppb_engine_run(ppb_engine* engine, void* stream);
+/* The forward pass in three parts cut where an output is complete (0: through the classification head -> 'cls';
+ * 1: regression head -> 'boxes3D' / '3Dbox'; 2: mask head -> 'mask'). Parts 0, 1, 2 in order on one stream equal
+ * ppb_engine_run; model.predict_on_batch (PyraPose/utils/linemod_eval.py:303 returns all three arrays on the host)
+ * uses the cuts to copy each output to the host while the remaining heads compute. */
+PPB_API int ppb_engine_run_part(ppb_engine* engine, int part, void* stream);
 PPB_API int ppb_engine_run_eager(ppb_engine* engine, void* stream);
 PPB_API int ppb_engine_kernels_per_run(const ppb_engine* engine);
 PPB_API size_t ppb_engine_device_bytes(const ppb_engine* engine);

@@ -489,17 +489,22 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
     PPB_TRY(tower_buf(&mt[i], "mask_tower" + sfx, 256));
   }
   const int kRaw = decode ? kEpiHeadDecode : kEpiHeadRaw;
+  // Head order: classification, regression, mask. The two large outputs are complete as early as possible, so a
+  // caller that wants them on the host (predict_on_batch: 234 MB per batch of 32) can copy 'cls' while the regression
+  // head computes and 'boxes3D' while the mask head does (part_end / ppb_engine_run_part).
+  PPB_TRY(head_conv_op(feat->ptr, 256, "pyramid_classification_0", ct[0]->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
+  for (int i = 1; i < 4; ++i)
+    PPB_TRY(head_conv_op(ct[i - 1]->ptr, 256, "pyramid_classification_" + std::to_string(i), ct[i]->ptr, 1, batch, 3,
+                         kEpiBf16, nullptr, nullptr));
+  PPB_TRY(head_conv_op(ct[3]->ptr, 256, "pyramid_classification", nullptr, 0, batch, 3, kEpiHeadSigmoid, out_cls, nullptr));
+  part_end[0] = static_cast<int>(ops.size());
   PPB_TRY(head_conv_op(feat->ptr, 256, "pyramid_regression3D_0", rt[0]->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
   for (int i = 1; i < 4; ++i)
     PPB_TRY(head_conv_op(rt[i - 1]->ptr, 512, "pyramid_regression3D_" + std::to_string(i), rt[i]->ptr, 1, batch, 3,
                          kEpiBf16, nullptr, nullptr));
   PPB_TRY(head_conv_op(rt[3]->ptr, 512, "pyramid_regression3D", nullptr, 0, batch, 3, kRaw, out_reg,
                        decode ? out_hull : nullptr));
-  PPB_TRY(head_conv_op(feat->ptr, 256, "pyramid_classification_0", ct[0]->ptr, 1, batch, 3, kEpiBf16, nullptr, nullptr));
-  for (int i = 1; i < 4; ++i)
-    PPB_TRY(head_conv_op(ct[i - 1]->ptr, 256, "pyramid_classification_" + std::to_string(i), ct[i]->ptr, 1, batch, 3,
-                         kEpiBf16, nullptr, nullptr));
-  PPB_TRY(head_conv_op(ct[3]->ptr, 256, "pyramid_classification", nullptr, 0, batch, 3, kEpiHeadSigmoid, out_cls, nullptr));
+  part_end[1] = static_cast<int>(ops.size());
   if (out_mask != nullptr) {  // mask head on P3 only (retinanet.py:296-297)
     PPB_TRY(head_conv_op(feat->ptr, 256, "mask_0", mt[0]->ptr, 1, batch, 1, kEpiBf16, nullptr, nullptr));
     for (int i = 1; i < 4; ++i)
@@ -507,14 +512,17 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
                            nullptr));
     PPB_TRY(head_conv_op(mt[3]->ptr, 256, "mask_out", nullptr, 0, batch, 1, kEpiHeadSigmoid, out_mask, nullptr));
   }
+  part_end[2] = static_cast<int>(ops.size());
+  drop_parts();
 #undef PPB_TRY
   bound_batch = batch;
   plan_batch = batch;
   return kOk;
 }
 
-int Engine::launch_all(cudaStream_t st) {
-  for (const Op& op : ops) {
+int Engine::launch_range(int begin, int end, cudaStream_t st) {
+  for (int oi = begin; oi < end; ++oi) {
+    const Op& op = ops[oi];
     switch (op.kind) {
       case kOpConv:
         PPB_CUDA(conv_launch(op.ta, op.tb, op.to, op.tr, op.p, 0, st));
@@ -585,6 +593,26 @@ int Engine::capture(cudaStream_t st) {
   graph = g;
   PPB_CUDA(cudaGraphInstantiate(&graph_exec, graph, 0));
   graph_kernels = static_cast<int>(ops.size());
+  return kOk;
+}
+
+int Engine::capture_parts(cudaStream_t st) {
+  drop_parts();
+  int begin = 0;
+  for (int i = 0; i < 3; ++i) {
+    PPB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    const int rc = launch_range(begin, part_end[i], st);
+    cudaGraph_t g = nullptr;
+    const cudaError_t end = cudaStreamEndCapture(st, &g);
+    if (rc != kOk) {
+      if (g) cudaGraphDestroy(g);
+      return rc;
+    }
+    PPB_CUDA(end);
+    part_graph[i] = g;
+    PPB_CUDA(cudaGraphInstantiate(&part_exec[i], g, 0));
+    begin = part_end[i];
+  }
   return kOk;
 }
 
@@ -742,6 +770,26 @@ int ppb_engine_run(ppb_engine* h, void* stream) {
   if (e.bound_batch == 0 || e.graph_exec == nullptr) return fail(kErrState, "ppb_engine_run: call ppb_engine_bind first");
   PPB_CUDA(cudaGraphLaunch(e.graph_exec, static_cast<cudaStream_t>(stream)));
   count_launch(e.graph_kernels);
+  return kOk;
+}
+
+/* One of the three parts of the forward pass (0: everything up to and including the classification head — 'cls' is
+ * complete afterwards; 1: regression head — 'boxes3D' / '3Dbox' complete; 2: mask head). Running parts 0, 1, 2 in order
+ * on one stream equals ppb_engine_run; between them the caller may record events and start copying finished outputs. */
+int ppb_engine_run_part(ppb_engine* h, int part, void* stream) {
+  PPB_REQUIRE(h != nullptr && part >= 0 && part < 3, "ppb_engine_run_part: bad argument (part %d)", part);
+  Engine& e = h->e;
+  if (e.bound_batch == 0 || e.graph_exec == nullptr) return fail(kErrState, "ppb_engine_run_part: call ppb_engine_bind first");
+  PPB_CUDA(cudaSetDevice(e.device));
+  if (e.part_exec[0] == nullptr) {
+    cudaStream_t own = nullptr;
+    PPB_CUDA(cudaStreamCreateWithFlags(&own, cudaStreamNonBlocking));
+    const int rc = e.capture_parts(own);
+    cudaStreamDestroy(own);
+    if (rc != kOk) return rc;
+  }
+  PPB_CUDA(cudaGraphLaunch(e.part_exec[part], static_cast<cudaStream_t>(stream)));
+  count_launch((part == 0 ? e.part_end[0] : e.part_end[part] - e.part_end[part - 1]));
   return kOk;
 }
 

@@ -101,6 +101,21 @@ struct Engine {
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t graph_exec = nullptr;
   int graph_kernels = 0;
+  // The same plan cut into three graphs at the points where an output tensor is complete — after the classification
+  // head ('cls'), after the regression head ('boxes3D' / '3Dbox'), after the mask head — so that predict_on_batch can
+  // start the device->host copy of each output while the remaining heads still compute (ppb_engine_run_part).
+  // Captured lazily on the first ppb_engine_run_part; the single graph above stays the path of ppb_engine_run.
+  int part_end[3] = {0, 0, 0};
+  cudaGraph_t part_graph[3] = {nullptr, nullptr, nullptr};
+  cudaGraphExec_t part_exec[3] = {nullptr, nullptr, nullptr};
+  void drop_parts() {
+    for (int i = 0; i < 3; ++i) {
+      if (part_exec[i]) cudaGraphExecDestroy(part_exec[i]);
+      if (part_graph[i]) cudaGraphDestroy(part_graph[i]);
+      part_exec[i] = nullptr;
+      part_graph[i] = nullptr;
+    }
+  }
   size_t arena_bytes = 0;
   // TMA-store epilogue through the shared-memory chunk ring (residual chunks prefetched by TMA): 0 never; 1 only convs
   // with a residual input; 2 every backbone / PFPN conv (measured best, profiles/r01_per_op_staged_variants.txt);
@@ -122,6 +137,7 @@ struct Engine {
   std::shared_ptr<struct TrainState> train;
 
   ~Engine() {
+    drop_parts();
     if (graph_exec) cudaGraphExecDestroy(graph_exec);
     if (graph) cudaGraphDestroy(graph);
     for (void* p : allocations) cudaFree(p);
@@ -190,7 +206,9 @@ struct Engine {
                    int n_levels, int epi, float* out_f32, float* out_hull);
   void conv_set_split(ConvParams& p, int cin, int out_c, int res_c) const;
   int capture(cudaStream_t st);
-  int launch_all(cudaStream_t st);
+  int capture_parts(cudaStream_t st);
+  int launch_all(cudaStream_t st) { return launch_range(0, static_cast<int>(ops.size()), st); }
+  int launch_range(int begin, int end, cudaStream_t st);
   void fill_head_segs(ConvParams& p, int batch, int n_levels) const;
 };
 

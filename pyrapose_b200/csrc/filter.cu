@@ -457,11 +457,20 @@ __global__ void __launch_bounds__(NT) nms_kernel(const uint64_t* __restrict__ ke
           if (!__any_sync(0xffffffffu, a && (intra & rem) != 0u)) {
             kept = rem;  // no alive member of this group overlaps an alive earlier one: all of them are kept
           } else {
-            while (rem) {  // warp-uniform loop over the still-alive candidates in score order
-              const int li = __ffs(rem) - 1;
-              rem &= rem - 1;
-              const uint32_t wsup = __shfl_sync(0xffffffffu, intra, li);
-              if ((wsup & kept) == 0u) kept |= 1u << li;
+            // Greedy order without walking the lanes one by one: a lane is dead as soon as a kept lane suppresses
+            // it, and kept once none of its (lower-lane) suppressors is kept or still undecided. The lowest undecided
+            // lane is always decided, so this ends in at most 32 rounds — in practice the depth of the longest
+            // suppression chain, 2-4 — and gives exactly the serial result (r02 capture: 47 % of this kernel's warp
+            // samples sat at the barrier behind the one-lane-per-step loop this replaces).
+            uint32_t und = rem;
+            while (und) {  // warp-uniform
+              const bool u = (und >> lane) & 1u;
+              const bool dead = u && (intra & kept) != 0u;
+              const bool keep = u && !dead && (intra & und) == 0u;
+              const uint32_t kb = __ballot_sync(0xffffffffu, keep);
+              const uint32_t db = __ballot_sync(0xffffffffu, dead);
+              kept |= kb;
+              und &= ~(kb | db);
             }
           }
           kept_w[sb] = kept;

@@ -123,6 +123,12 @@ class Engine(object):
             fn = self.lib.ppb_engine_run_eager if eager else self.lib.ppb_engine_run
             nat.check(fn(self._h, nat.current_stream_ptr()))
 
+    def run_part(self, part):
+        """Part 0 / 1 / 2 of the forward pass (through the classification head / regression head / mask head); the
+        three in order equal run(). See ppb_engine_run_part."""
+        with torch.cuda.device(self.device):
+            nat.check(self.lib.ppb_engine_run_part(self._h, int(part), nat.current_stream_ptr()))
+
     def kernels_per_run(self):
         return int(self.lib.ppb_engine_kernels_per_run(self._h))
 

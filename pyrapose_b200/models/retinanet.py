@@ -215,7 +215,10 @@ class PFPNModel(object):
         (PyraPose/utils/linemod_eval.py:303)."""
         import torch
         import weakref
-        buf = self.forward_device(x)
+        src, u8 = self._as_input(x)
+        B, H, W = int(src.shape[0]), int(src.shape[1]), int(src.shape[2])
+        eng = self._engine(B, H, W)
+        buf = eng.bind(B, decode=self.inference, want_mask=True, want_hull=False, input_u8=u8)
         outs = [buf["boxes3D"], buf["cls"], buf["mask"]]
         key = tuple(tuple(o.shape) for o in outs)
         # Output buffers are persistent PINNED host tensors, so the three device->host copies (234 MB at batch 32) are
@@ -236,11 +239,26 @@ class PFPNModel(object):
             slot = {"host": [torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs], "refs": []}
             pool.append(slot)
         with torch.cuda.device(outs[0].device):
+            main = torch.cuda.current_stream()
+            buf["images"].copy_(src, non_blocking=True)
             if slot is None:   # every set is still referenced by the caller: private pageable copies
+                eng.run()
                 return [o.cpu().numpy() for o in outs]
-            for h, o in zip(slot["host"], outs):
-                h.copy_(o, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+            # The forward pass runs as three graphs cut where an output is complete (classification head, regression
+            # head, mask head: ppb_engine_run_part), and each output's device->host DMA starts on a copy stream as soon
+            # as its part is done: the 109 MB of 'cls' travel while the regression head computes, the 116 MB of
+            # 'boxes3D' while the mask head does.
+            copy = self.__dict__.get('_copy_stream')
+            if copy is None or copy.device != outs[0].device:
+                copy = self._copy_stream = torch.cuda.Stream(device=outs[0].device)
+            for part, oi in ((0, 1), (1, 0), (2, 2)):
+                eng.run_part(part)
+                ev = torch.cuda.Event()
+                ev.record(main)
+                copy.wait_event(ev)
+                with torch.cuda.stream(copy):
+                    slot["host"][oi].copy_(outs[oi], non_blocking=True)
+            copy.synchronize()
         arrays = [h.numpy() for h in slot["host"]]
         slot["refs"] = [weakref.ref(a) for a in arrays]
         return arrays

@@ -4,10 +4,13 @@ rep, kid = sys.argv[1], sys.argv[2]
 n = int(sys.argv[3]) if len(sys.argv) > 3 else 25
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-id", ":::" + kid], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
-hdr = rows[1]
+heads = [i for i, r in enumerate(rows) if r and r[0] in ("Address", "#")]
+hdr = rows[heads[0]]
+end = heads[1] - 1 if len(heads) > 1 else len(rows)
+print(rows[0][:2])
 i_src, i_s, i_ex = hdr.index("Source"), hdr.index("# Samples"), hdr.index("Instructions Executed")
 stalls = [(i, h) for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
-data = rows[2:]
+data = [r for r in rows[heads[0] + 1:end] if len(r) == len(hdr) and r[i_s].isdigit()]
 tot = sum(int(r[i_s]) for r in data)
 print("total samples", tot, " instructions", sum(int(r[i_ex]) for r in data))
 agg = sorted(((sum(int(r[i] or 0) for r in data), h) for i, h in stalls), reverse=True)[:8]
