@@ -345,7 +345,11 @@ __device__ __forceinline__ bool iou_exceeds(const NBox& i, const NBox& j, float 
   if (i.area <= 0.0f || j.area <= 0.0f) return 0.0f > thr;
   const float y0 = fmaxf(i.a0, j.a0), x0 = fmaxf(i.a1, j.a1);
   const float y1 = fminf(i.a2, j.a2), x1 = fminf(i.a3, j.a3);
-  const float inter = fmaxf(y1 - y0, 0.0f) * fmaxf(x1 - x0, 0.0f);
+  const float dy = y1 - y0, dx = x1 - x0;
+  // Disjoint boxes — nearly every pair — have intersection 0 and IoU 0, which exceeds no threshold >= 0: leave before
+  // the union / threshold arithmetic (a third of the instructions of a test; the NMS kernel is issue-bound).
+  if (thr >= 0.0f && (dy <= 0.0f || dx <= 0.0f)) return false;
+  const float inter = fmaxf(dy, 0.0f) * fmaxf(dx, 0.0f);
   const float uni = i.area + j.area - inter;
   // The IEEE division costs as much as the rest of the test and nearly every pair is far from the threshold: decide by
   // multiplication when inter is outside thr * uni * (1 +- 1e-6) — a margin 16x the rounding error of the quotient and
