@@ -215,13 +215,17 @@ __device__ __forceinline__ void staged_chunk_row_masked(const ConvParams& p, con
 // bf16 epilogue for NC (16 or 32) accumulator columns of one row, straight to global memory.
 template <int NC>
 __device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __restrict__ sbias, const RowInfo& ri, int m,
-                                         int n0, uint32_t (&v)[NC]) {
+                                         int n0, uint32_t (&v)[NC], long long row2 = 0) {
   if (!ri.in_buf || n0 >= p.n_valid) return;
   __nv_bfloat16* dst = p.out + static_cast<size_t>(m) * p.out_ld + n0;
   if (!ri.interior) {
     const uint4 z = make_uint4(0, 0, 0, 0);
 #pragma unroll
     for (int i = 0; i < NC / 8; ++i) reinterpret_cast<uint4*>(dst)[i] = z;
+    if (p.out2 != nullptr) {
+#pragma unroll
+      for (int i = 0; i < NC / 8; ++i) reinterpret_cast<uint4*>(p.out2 + static_cast<size_t>(m) * p.out2_ld + n0)[i] = z;
+    }
     if (p.split) {
       for (int part = 1; part < p.parts; ++part)
 #pragma unroll
@@ -316,6 +320,9 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __res
       if (!(bf16_hi(r.w) > 0.0f)) f[i * 8 + 7] = 0.0f;
     }
   }
+  const uint4* r2p = p.out2 != nullptr
+                         ? reinterpret_cast<const uint4*>(p.res2 + static_cast<size_t>(row2) * p.res2_ld + n0) : nullptr;
+  uint4* d2p = p.out2 != nullptr ? reinterpret_cast<uint4*>(p.out2 + static_cast<size_t>(m) * p.out2_ld + n0) : nullptr;
 #pragma unroll
   for (int i = 0; i < NC / 8; ++i) {
     uint4 o;
@@ -324,7 +331,28 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __res
     o.z = pack_bf16x2(f[i * 8 + 4], f[i * 8 + 5]);
     o.w = pack_bf16x2(f[i * 8 + 6], f[i * 8 + 7]);
     reinterpret_cast<uint4*>(dst)[i] = o;
+    if (p.out2 != nullptr) {  // fused Add: the ROUNDED output + the second operand, rounded once more
+      const uint4 r = __ldg(r2p + i);
+      uint4 o2;
+      o2.x = pack_bf16x2(bf16_lo(o.x) + bf16_lo(r.x), bf16_hi(o.x) + bf16_hi(r.x));
+      o2.y = pack_bf16x2(bf16_lo(o.y) + bf16_lo(r.y), bf16_hi(o.y) + bf16_hi(r.y));
+      o2.z = pack_bf16x2(bf16_lo(o.z) + bf16_lo(r.z), bf16_hi(o.z) + bf16_hi(r.z));
+      o2.w = pack_bf16x2(bf16_lo(o.w) + bf16_lo(r.w), bf16_hi(o.w) + bf16_hi(r.w));
+      d2p[i] = o2;
+    }
   }
+}
+
+// Row of the second operand of a fused Add for output row m: identity, or the nearest-resized source pixel (the float
+// arithmetic of elementwise.cu's add_kernel, so both give the same row).
+__device__ __forceinline__ long long fused_add_row(const ConvParams& p, const ConvSeg& sg, const RowInfo& ri, int m) {
+  if (p.res2_uh == 0 || !ri.interior) return m;
+  const int H = sg.hp - sg.pad_lo - sg.pad_hi, W = sg.wp - sg.pad_lo - sg.pad_hi;
+  int sy = static_cast<int>(floorf((static_cast<float>(ri.y) + 0.5f) * (static_cast<float>(p.res2_uh) / H)));
+  int sx = static_cast<int>(floorf((static_cast<float>(ri.x) + 0.5f) * (static_cast<float>(p.res2_uw) / W)));
+  sy = min(sy, p.res2_uh - 1);
+  sx = min(sx, p.res2_uw - 1);
+  return (static_cast<long long>(ri.b) * (p.res2_uh + 2) + sy + 1) * (p.res2_uw + 2) + sx + 1;
 }
 
 // fp32 head epilogue for 16 accumulator columns of one row (= the 16 regression values of one anchor when
@@ -778,6 +806,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         if (tr_lead) tr(kTrEpilogue + g, 14, tseq, 0);
       } else if (p.epi == kEpiBf16) {
         // ---- direct bf16 epilogue: 32-column pieces alternate between the two groups
+        const long long row2 = p.out2 != nullptr ? fused_add_row(p, sg, ri, m) : 0;
         int piece = 0;
         for (int c0 = 0; c0 < p.block_n; c0 += 32, ++piece) {
           if (piece % kGroups != g) continue;
@@ -786,13 +815,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             tmem_ld_32x32(taddr + c0, v);
             tmem_ld_wait();
             if (p.split) add_side<32>(taddr + kSideCol + c0, v);
-            epi_bf16<32>(p, sbias, ri, m, tc.n0 + c0, v);
+            epi_bf16<32>(p, sbias, ri, m, tc.n0 + c0, v, row2);
           } else {
             uint32_t v[16];
             tmem_ld_32x16(taddr + c0, v);
             tmem_ld_wait();
             if (p.split) add_side<16>(taddr + kSideCol + c0, v);
-            epi_bf16<16>(p, sbias, ri, m, tc.n0 + c0, v);
+            epi_bf16<16>(p, sbias, ri, m, tc.n0 + c0, v, row2);
           }
         }
         tc_fence_before();
@@ -994,6 +1023,7 @@ static bool conv_bres_ok(const ConvParams& p) {
 
 int conv_plan_smem(ConvParams& p) {
   if (p.split != 0 && (p.block_n > kSideCol || p.staged)) return -1;  // two accumulators per buffer, direct epilogue only
+  if (p.out2 != nullptr && (p.staged || p.epi != kEpiBf16 || p.split != 0)) return -1;  // fused Add: direct bf16 epilogue
   p.bres = conv_bres_ok(p) ? 1 : 0;
   const int stage_bytes = stage_bytes_of(p);
   const int k_iters = (p.slab3 != 0 ? 3 : p.n_taps) * p.cin_blocks;

@@ -109,6 +109,15 @@ struct ConvParams {
   int b_col_base;                 // first column of this launch's taps inside the weight matrix (multiple of 64)
   __nv_bfloat16* out;             // kEpiBf16
   int out_ld;
+  // Second output of the DIRECT bf16 epilogue: the Keras Add (+ UpsampleLike) that follows the convolution in
+  // __create_sparceFPN (PyraPose/models/retinanet.py:196-211) fused into it:
+  //   out2[m] = bf16(float(out[m]) + res2[src(m)])    (out already rounded to bf16: bit-identical to a separate add)
+  // src(m) = m when res2_uh == 0, else the row of the nearest-resized pixel of a [B, res2_uh + 2, res2_uw + 2] plane
+  // (tf.image.resize NEAREST, half-pixel centres: layers/_misc.py:96-115). Border rows of out2 are written as zeros.
+  __nv_bfloat16* out2;
+  int out2_ld;
+  const __nv_bfloat16* res2;
+  int res2_ld, res2_uh, res2_uw;
   float* out_f32;                 // head epilogues
   float* out_hull;                // kEpiHeadDecode: optional [B, locs*A, 4] axis-aligned hull of the 8 corners
   int locs_per_image;             // sum over levels of H*W

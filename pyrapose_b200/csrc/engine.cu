@@ -141,7 +141,7 @@ namespace ppb {
 // One convolution over a single padded-flat plane set. `x` has the OUTPUT geometry (for stride-2 layers it is the
 // parity-plane tensor produced by launch_parity_planes from a src_h x src_w input).
 int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, const Tensor* res, Tensor* y, int relu,
-                    int batch, int src_h, int src_w) {
+                    int batch, int src_h, int src_w, Tensor* out2, const Tensor* res2, bool res2_up) {
   const LayerW& l = layers[layer_index.at(layer)];
   if (!l.loaded) return fail(kErrState, "layer '%s' has no weights (call ppb_engine_set_layer first)", l.name.c_str());
   Op op;
@@ -195,8 +195,17 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
   p.out = y->ptr;
   p.out_ld = y->ld;
   const long long a_rows = x->rows(batch) * (x_planes > 0 ? x_planes : 1);
+  if (out2 != nullptr) {  // fused Add: direct epilogue only
+    if (split() || res != nullptr) return fail(kErrState, "internal: fused Add needs the bf16 path and no residual");
+    p.out2 = out2->ptr;
+    p.out2_ld = out2->ld;
+    p.res2 = res2->ptr;
+    p.res2_ld = res2->ld;
+    p.res2_uh = res2_up ? res2->H : 0;
+    p.res2_uw = res2_up ? res2->W : 0;
+  }
   p.pair = conv_pair_ok(p) ? 1 : 0;
-  p.staged = (!split() && l.cout % 64 == 0 && p.block_n % 64 == 0 &&
+  p.staged = (!split() && out2 == nullptr && l.cout % 64 == 0 && p.block_n % 64 == 0 &&
               (staged_epilogue >= 2 || (staged_epilogue == 1 && res != nullptr))) ? 1 : 0;
   p.slab3 = conv_slab3_mode(p);
   if (l.ksize == 7 && stem16 && l.k_total == 256 && (p.block_n & 7) == 0) {
@@ -204,7 +213,7 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
     p.pair = 0;
     p.slab3 = 0;
   }
-  bool force_direct = false;
+  bool force_direct = out2 != nullptr;
   if (p.slab3 == 0 && p.staged && res == nullptr) {
     // a 256-wide pair tile in slab mode leaves no room for the epilogue ring: without a residual to prefetch the
     // direct epilogue costs nothing, so prefer the slab (P3, P3_mid)
@@ -433,31 +442,47 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
   PPB_TRY(get(&P3l, "P3_lateral", C3->H, C3->W, 256, 1));
   PPB_TRY(get(&P4l, "P4_lateral", C4->H, C4->W, 256, 1));
   PPB_TRY(get(&P5l, "P5_lateral", C5->H, C5->W, 256, 1));
-  PPB_TRY(conv_op(C3, 1, "P3_lateral", nullptr, P3l, 0, batch));                                   // :192
-  PPB_TRY(conv_op(C4, 1, "P4_lateral", nullptr, P4l, 0, batch));                                   // :193
-  PPB_TRY(conv_op(C5, 1, "P5_lateral", nullptr, P5l, 0, batch));                                   // :194
   PPB_TRY(get(&t4, "P4_mid_in", C4->H, C4->W, 256, 1));
   PPB_TRY(get(&t3, "P3_mid_in", C3->H, C3->W, 256, 1));
   PPB_TRY(get(&P4m, "P4_mid", C4->H, C4->W, 256, 1));
   PPB_TRY(get(&P3m, "P3_mid", C3->H, C3->W, 256, 1));
-  elementwise(kOpAdd, P4l->ptr, nullptr, nullptr, P5l->ptr, t4->ptr, {batch, C4->H, C4->W, 256, C5->H, C5->W});  // :196,198
-  PPB_TRY(conv_op(t4, 1, "P4_mid", nullptr, P4m, 0, batch));                                       // :199
-  elementwise(kOpAdd, P3l->ptr, nullptr, nullptr, P4l->ptr, t3->ptr, {batch, C3->H, C3->W, 256, C4->H, C4->W});  // :197,200
-  PPB_TRY(conv_op(t3, 1, "P3_mid", nullptr, P3m, 0, batch));                                       // :201
   PPB_TRY(get(&s3, "P3_mid_planes", C4->H, C4->W, 256, 1, 4));
   PPB_TRY(get(&P3d, "P3_down", C4->H, C4->W, 256, 1));
-  elementwise(kOpPlanes, P3m->ptr, nullptr, nullptr, nullptr, s3->ptr, {batch, C3->H, C3->W, P3m->ld, C4->H, C4->W, 4});
-  PPB_TRY(conv_op(s3, 4, "P3_down", nullptr, P3d, 0, batch, C3->H, C3->W));                        // :202
   PPB_TRY(get(&t3f, "P3_fin", C3->H, C3->W, 256, 1));
-  elementwise(kOpAdd, P3m->ptr, P3l->ptr, nullptr, nullptr, t3f->ptr, {batch, C3->H, C3->W, 256, 0, 0});  // :203
   PPB_TRY(get(&t4f, "P4_fin", C4->H, C4->W, 256, 1));
-  elementwise(kOpAdd, P3d->ptr, P4m->ptr, P4l->ptr, nullptr, t4f->ptr, {batch, C4->H, C4->W, 256, 0, 0});  // :206,208
   PPB_TRY(get(&s4, "P4_mid_planes", C5->H, C5->W, 256, 1, 4));
   PPB_TRY(get(&P4d, "P4_down", C5->H, C5->W, 256, 1));
-  elementwise(kOpPlanes, P4m->ptr, nullptr, nullptr, nullptr, s4->ptr, {batch, C4->H, C4->W, P4m->ld, C5->H, C5->W, 4});
-  PPB_TRY(conv_op(s4, 4, "P4_down", nullptr, P4d, 0, batch, C4->H, C4->W));                        // :207
   PPB_TRY(get(&t5f, "P5_fin", C5->H, C5->W, 256, 1));
-  elementwise(kOpAdd, P4d->ptr, P5l->ptr, nullptr, nullptr, t5f->ptr, {batch, C5->H, C5->W, 256, 0, 0});  // :211
+  if (fuse_adds && !split()) {
+    // Every Add / UpsampleLike of the pyramid leaves with the convolution that produces its first operand
+    // (ConvParams::out2): no elementwise launch, and the operand is never re-read from HBM.
+    Tensor* P4ml;  // P4_mid + P4_lateral, the part of P4_fin (:206, 208) that does not wait for P3_down
+    PPB_TRY(get(&P4ml, "P4_mid_plus_lateral", C4->H, C4->W, 256, 1));
+    PPB_TRY(conv_op(C5, 1, "P5_lateral", nullptr, P5l, 0, batch));                                   // :194
+    PPB_TRY(conv_op(C4, 1, "P4_lateral", nullptr, P4l, 0, batch, 0, 0, t4, P5l, true));              // :193 + :196, 198
+    PPB_TRY(conv_op(C3, 1, "P3_lateral", nullptr, P3l, 0, batch, 0, 0, t3, P4l, true));              // :192 + :197, 200
+    PPB_TRY(conv_op(t4, 1, "P4_mid", nullptr, P4m, 0, batch, 0, 0, P4ml, P4l, false));               // :199 (+ P4l of :208)
+    PPB_TRY(conv_op(t3, 1, "P3_mid", nullptr, P3m, 0, batch, 0, 0, t3f, P3l, false));                // :201 + :203
+    elementwise(kOpPlanes, P3m->ptr, nullptr, nullptr, nullptr, s3->ptr, {batch, C3->H, C3->W, P3m->ld, C4->H, C4->W, 4});
+    PPB_TRY(conv_op(s3, 4, "P3_down", nullptr, P3d, 0, batch, C3->H, C3->W, t4f, P4ml, false));      // :202 + :206, 208
+    elementwise(kOpPlanes, P4m->ptr, nullptr, nullptr, nullptr, s4->ptr, {batch, C4->H, C4->W, P4m->ld, C5->H, C5->W, 4});
+    PPB_TRY(conv_op(s4, 4, "P4_down", nullptr, P4d, 0, batch, C4->H, C4->W, t5f, P5l, false));       // :207 + :211
+  } else {
+    PPB_TRY(conv_op(C3, 1, "P3_lateral", nullptr, P3l, 0, batch));                                   // :192
+    PPB_TRY(conv_op(C4, 1, "P4_lateral", nullptr, P4l, 0, batch));                                   // :193
+    PPB_TRY(conv_op(C5, 1, "P5_lateral", nullptr, P5l, 0, batch));                                   // :194
+    elementwise(kOpAdd, P4l->ptr, nullptr, nullptr, P5l->ptr, t4->ptr, {batch, C4->H, C4->W, 256, C5->H, C5->W});  // :196,198
+    PPB_TRY(conv_op(t4, 1, "P4_mid", nullptr, P4m, 0, batch));                                       // :199
+    elementwise(kOpAdd, P3l->ptr, nullptr, nullptr, P4l->ptr, t3->ptr, {batch, C3->H, C3->W, 256, C4->H, C4->W});  // :197,200
+    PPB_TRY(conv_op(t3, 1, "P3_mid", nullptr, P3m, 0, batch));                                       // :201
+    elementwise(kOpPlanes, P3m->ptr, nullptr, nullptr, nullptr, s3->ptr, {batch, C3->H, C3->W, P3m->ld, C4->H, C4->W, 4});
+    PPB_TRY(conv_op(s3, 4, "P3_down", nullptr, P3d, 0, batch, C3->H, C3->W));                        // :202
+    elementwise(kOpAdd, P3m->ptr, P3l->ptr, nullptr, nullptr, t3f->ptr, {batch, C3->H, C3->W, 256, 0, 0});  // :203
+    elementwise(kOpAdd, P3d->ptr, P4m->ptr, P4l->ptr, nullptr, t4f->ptr, {batch, C4->H, C4->W, 256, 0, 0});  // :206,208
+    elementwise(kOpPlanes, P4m->ptr, nullptr, nullptr, nullptr, s4->ptr, {batch, C4->H, C4->W, P4m->ld, C5->H, C5->W, 4});
+    PPB_TRY(conv_op(s4, 4, "P4_down", nullptr, P4d, 0, batch, C4->H, C4->W));                        // :207
+    elementwise(kOpAdd, P4d->ptr, P5l->ptr, nullptr, nullptr, t5f->ptr, {batch, C5->H, C5->W, 256, 0, 0});  // :211
+  }
 
   // ---- pyramid outputs P3, P4, P5 written into ONE multi-segment feature matrix
   Tensor* feat = tensor("features");
@@ -669,6 +694,7 @@ int ppb_engine_create_ex(ppb_engine** out, int device, int max_batch, int height
   memset(e.stride, 0, sizeof(e.stride));
   if (const char* env = getenv("PPB_STAGED_EPILOGUE")) e.staged_epilogue = atoi(env);
   if (const char* env = getenv("PPB_STEM16")) e.stem16 = atoi(env) != 0;
+  if (const char* env = getenv("PPB_FUSE_ADD")) e.fuse_adds = atoi(env) != 0;
   e.define_layers();
   int rc = e.allocate_weights();
   if (rc != kOk) return rc;

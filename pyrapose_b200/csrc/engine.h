@@ -200,8 +200,16 @@ struct Engine {
                 const float* mean, const float* var, float eps);
   int build_plan(int batch, const float* images, float* out_reg, float* out_cls, float* out_mask, float* out_hull,
                  int decode);
+  // out2 / res2: the Add (+ UpsampleLike when res2_up) that follows the layer, fused into its epilogue
+  // (ConvParams::out2): out2 = y + res2, or y + nearest-resize(res2) to y's size.
   int conv_op(const Tensor* x, int x_planes, const std::string& layer, const Tensor* res, Tensor* y, int relu, int batch,
-              int src_h = 0, int src_w = 0);
+              int src_h = 0, int src_w = 0, Tensor* out2 = nullptr, const Tensor* res2 = nullptr, bool res2_up = false);
+  // PPB_FUSE_ADD=1: the five PFPN Add / UpsampleLike ops leave with the convolution that produces their first operand
+  // instead of as elementwise launches. Off by default — measured neutral at B=32 (r02, same box, graph replay 7.40-7.49
+  // ms unfused vs 7.46-7.48 fused): the direct epilogue's per-thread 64-byte row accesses cost the convolution about
+  // what the coalesced add kernel costs (P3_lateral 0.079 -> 0.138 ms for a 0.048 ms add, P3_mid 0.142 -> 0.185 for
+  // 0.046), so only bytes are saved, not time.
+  bool fuse_adds = false;
   int head_conv_op(const __nv_bfloat16* x, int cin, const std::string& layer, __nv_bfloat16* y, int relu, int batch,
                    int n_levels, int epi, float* out_f32, float* out_hull);
   void conv_set_split(ConvParams& p, int cin, int out_c, int res_c) const;

@@ -199,3 +199,33 @@ def test_predict_on_batch_results_are_owned_by_the_caller(cuda_device):
     del a, b, held, view
     c = infer.predict_on_batch(x2)        # recycled buffers, correct content
     assert not np.array_equal(c[1], a_copy[1])
+
+
+def test_fused_pfpn_adds_match_separate_launches(cuda_device, monkeypatch):
+    """PPB_FUSE_ADD=1 (ConvParams::out2: the pyramid's Add / UpsampleLike ops in the producing convolution's epilogue)
+    gives the same feature maps as the separate elementwise launches: identical where the add has two operands
+    (the epilogue adds to the ROUNDED output), within one bf16 rounding for P4_fin, whose three-operand sum is
+    split in two."""
+    from pyrapose_b200 import models
+    from pyrapose_b200.models import spec
+    C, H, W = 4, 136, 200
+    weights = spec.init_weights(C, seed=3, head_init="spread", randomize_bn=True)
+    img = make_images(2, 2, H, W)
+
+    def run(fuse):
+        monkeypatch.setenv("PPB_FUSE_ADD", "1" if fuse else "0")
+        train = models.backbone("resnet50").retinanet(C)
+        train.set_weights_dict(weights)
+        m = models.convert_model(train)
+        outs = m.predict_on_batch(img)
+        taps = {n: m.activation(n, H, W) for n in ("P4_mid_in", "P3_mid_in", "P3_fin", "P4_fin", "P5_fin", "P3", "P4", "P5")}
+        return [o.copy() for o in outs], taps, m._engines[(H, W)].kernels_per_run()
+
+    o0, t0, k0 = run(False)
+    o1, t1, k1 = run(True)
+    assert k1 == k0 - 5
+    for n in ("P4_mid_in", "P3_mid_in", "P3_fin", "P5_fin"):
+        assert np.array_equal(t0[n], t1[n]), n
+    assert rel_l2(t1["P4_fin"], t0["P4_fin"]) < 4e-3
+    for a, b in zip(o0, o1):
+        assert rel_l2(b, a) < 1e-2
