@@ -236,6 +236,13 @@ PPB_API int ppb_engine_set_layer(ppb_engine* engine, const char* name, const flo
  * float32 as keras.backend.variable does, strides f32 [3]; RegressBoxes3D mean/std f32 [16] or NULL (0 / 0.2). */
 PPB_API int ppb_engine_set_anchors(ppb_engine* engine, const float* base_anchors_host, const float* strides_host,
                                    const float* mean16_host, const float* std16_host);
+/* Production arena: the backbone's bottleneck intermediates share a handful of buffers (every branch2a / branch2b
+ * output one buffer each, block outputs ping-pong between two, one projection-shortcut and one subsample buffer)
+ * instead of one buffer per layer; 6.4 -> 3.7 GB at batch 32, 480x640. Call before the first ppb_engine_bind.
+ * Inference plans only (a training plan needs every activation and ignores it); ppb_engine_activation then returns
+ * only tensors that still hold their value when the pass ends. No reference counterpart (TensorFlow's allocator). */
+PPB_API int ppb_engine_set_arena_alias(ppb_engine* engine, int enable);
+
 /* Input staging (the step before the path: read_image_bgr -> preprocess_image, PyraPose/utils/image.py:35-62;
  * call sites utils/linemod_eval.py:265-267, preprocessing/generator.py:320-336): with enable=1 the `images` pointer of
  * the next ppb_engine_bind / ppb_engine_train_bind is read as RAW uint8 BGR pixels [batch,H,W,3] and

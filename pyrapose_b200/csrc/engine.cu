@@ -357,6 +357,13 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
     if (*t != nullptr) return kOk;
     return new_tensor(t, name, h, w, c, pad, planes);
   };
+  // backbone intermediates: their own buffer, or (production arena) a view of a shared one
+  const bool alias = alias_arena && !training_plan;
+  auto get_bb = [&](Tensor** t, const std::string& name, const char* pool, int h, int w, int c) -> int {
+    *t = tensor(name);
+    if (*t != nullptr) return kOk;
+    return alias ? alias_tensor(t, name, pool, h, w, c) : new_tensor(t, name, h, w, c, 1);
+  };
   auto elementwise = [&](OpKind kind, const void* i0, const void* i1, const void* i2, const void* i3, void* out,
                          std::initializer_list<int> args) {
     Op op;
@@ -399,7 +406,7 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
 
   // ---- bottleneck stages
   const int blocks[4] = {3, 4, 6, 3};
-  int features = 64, ch = h2, cw = w2;
+  int features = 64, ch = h2, cw = w2, n_block = 0;
   Tensor* c_out[4] = {nullptr, nullptr, nullptr, nullptr};
   for (int stage = 0; stage < 4; ++stage) {
     for (int b = 0; b < blocks[stage]; ++b) {
@@ -411,20 +418,24 @@ int Engine::build_plan(int batch, const float* images, float* out_reg, float* ou
       if (down) {  // 1x1 stride-2 VALID: out(i,j) = in(2i,2j)
         const int nh = (ch + 1) / 2, nw = (cw + 1) / 2;
         Tensor* sub;
-        PPB_TRY(get(&sub, "res" + tag + "_sub", nh, nw, x->C, 1));
+        PPB_TRY(get_bb(&sub, "res" + tag + "_sub", "bb_sub", nh, nw, x->C));
         elementwise(kOpPlanes, x->ptr, nullptr, nullptr, nullptr, sub->ptr, {batch, ch, cw, x->ld, nh, nw, 1});
         xin = sub;
         ch = nh;
         cw = nw;
       }
       Tensor *y1, *y2, *y3, *sc = x;
-      PPB_TRY(get(&y1, "res" + tag + "_branch2a_relu", ch, cw, features, 1));
-      PPB_TRY(get(&y2, "res" + tag + "_branch2b_relu", ch, cw, features, 1));
-      PPB_TRY(get(&y3, "res" + tag + "_relu", ch, cw, features * 4, 1));
+      PPB_TRY(get_bb(&y1, "res" + tag + "_branch2a_relu", "bb_y1", ch, cw, features));
+      PPB_TRY(get_bb(&y2, "res" + tag + "_branch2b_relu", "bb_y2", ch, cw, features));
+      // block outputs ping-pong (a block reads its input as the residual while it writes its output); C3, C4, C5 —
+      // the last block of stages 3-5 — feed the pyramid much later and keep their own buffer
+      if (stage > 0 && b == blocks[stage] - 1) PPB_TRY(get(&y3, "res" + tag + "_relu", ch, cw, features * 4, 1));
+      else PPB_TRY(get_bb(&y3, "res" + tag + "_relu", (n_block & 1) ? "bb_x1" : "bb_x0", ch, cw, features * 4));
+      ++n_block;
       PPB_TRY(conv_op(xin, 1, "res" + tag + "_branch2a", nullptr, y1, 1, batch));
       PPB_TRY(conv_op(y1, 1, "res" + tag + "_branch2b", nullptr, y2, 1, batch));
       if (b == 0) {
-        PPB_TRY(get(&sc, "res" + tag + "_branch1_bn", ch, cw, features * 4, 1));
+        PPB_TRY(get_bb(&sc, "res" + tag + "_branch1_bn", "bb_sc", ch, cw, features * 4));
         PPB_TRY(conv_op(xin, 1, "res" + tag + "_branch1", nullptr, sc, 0, batch));
       }
       PPB_TRY(conv_op(y2, 1, "res" + tag + "_branch2c", sc, y3, 1, batch));
@@ -750,6 +761,15 @@ int ppb_engine_set_anchors(ppb_engine* h, const float* base_anchors_host, const 
   if (std16_host) memcpy(e.dec_std, std16_host, sizeof(e.dec_std));
   e.anchors_set = true;
   e.bound_batch = 0;  // parameters are baked into the plan: force a re-bind
+  return kOk;
+}
+
+int ppb_engine_set_arena_alias(ppb_engine* h, int enable) {
+  PPB_REQUIRE(h != nullptr, "ppb_engine_set_arena_alias: null engine");
+  Engine& e = h->e;
+  if (!e.tensors.empty() && (enable != 0) != e.alias_arena)
+    return fail(kErrState, "ppb_engine_set_arena_alias: call before the first ppb_engine_bind (the arena is already laid out)");
+  e.alias_arena = enable != 0;
   return kOk;
 }
 

@@ -132,6 +132,13 @@ struct Engine {
   //    (split_ops.cu). Inference only.
   int precision = 0;
   bool split() const { return precision == 1; }
+  // Production arena (ppb_engine_set_arena_alias, inference plans only): the bottleneck intermediates of the backbone
+  // share a handful of buffers instead of one per layer — all branch2a / branch2b outputs one buffer each, block
+  // outputs ping-pong between two, one projection-shortcut and one subsample buffer — sized by their first (largest,
+  // stage 2) use; C3 / C4 / C5, the pyramid and the head towers keep their own. ppb_engine_activation then only
+  // returns tensors that still hold their value at the end of the pass; the parity tests run without it.
+  bool alias_arena = false;
+  std::map<std::string, __nv_bfloat16*> alias_pool;
   bool training_plan = false;
   long long train_bucket_bytes = 0;  // gradient bucket size of the segmented training step (0 = one graph)
   std::shared_ptr<struct TrainState> train;
@@ -170,6 +177,30 @@ struct Engine {
   Tensor* tensor(const std::string& name) {
     auto it = tensor_index.find(name);
     return it == tensor_index.end() ? nullptr : it->second;
+  }
+
+  // A tensor that lives in the shared buffer `pool` (allocated by its first user, which is the largest).
+  int alias_tensor(Tensor** out, const std::string& name, const std::string& pool, int h, int w, int c) {
+    auto it = alias_pool.find(pool);
+    if (it == alias_pool.end()) {
+      Tensor* first = nullptr;
+      const int rc = new_tensor(&first, name, h, w, c, 1);
+      if (rc != kOk) return rc;
+      alias_pool[pool] = first->ptr;
+      *out = first;
+      return kOk;
+    }
+    std::unique_ptr<Tensor> t(new Tensor);
+    t->name = name;
+    t->H = h;
+    t->W = w;
+    t->C = c;
+    t->ld = split() ? kSplitParts * c : c;
+    t->ptr = it->second;
+    *out = t.get();
+    tensor_index[name] = t.get();
+    tensors.push_back(std::move(t));
+    return kOk;
   }
 
   int new_tensor(Tensor** out, const std::string& name, int h, int w, int c, int pad, int planes = 1,

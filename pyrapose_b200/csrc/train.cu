@@ -849,6 +849,12 @@ void plan_segments(Engine& e) {
     std::stable_sort(buckets.begin(), buckets.end(), [](const Bucket& a, const Bucket& b) { return a.ready < b.ready; });
   }
   int begin = 0;
+  if (!buckets.empty()) {
+    // Segment 0 = memsets + forward pass only (no backward op, no gradient slice): the data-parallel caller's
+    // all-reduce of the loss normalisers (ppb_engine_train_counts, a few bytes but a full NCCL latency) runs while the
+    // forward pass computes and is awaited only before segment 1, whose first launches are the loss kernels.
+    t.segs.push_back(Segment());
+  }
   for (const Bucket& b : buckets) {
     Segment sg;
     sg.op_begin = begin;
@@ -913,6 +919,7 @@ int ppb_engine_train_bind(ppb_engine* h, int batch, const float* images, const f
   PPB_REQUIRE(images && y_reg && y_cls && y_mask && out_reg && out_cls && out_mask, "ppb_engine_train_bind: null buffer");
   PPB_REQUIRE((reinterpret_cast<uintptr_t>(out_reg) & 15) == 0, "ppb_engine_train_bind: outputs must be 16-byte aligned");
   if (e.split()) return fail(kErrState, "ppb_engine_train_bind: the fp32 path (precision 1) is inference only");
+  if (e.alias_arena) return fail(kErrState, "ppb_engine_train_bind: the production arena (ppb_engine_set_arena_alias) is inference only");
   PPB_CUDA(cudaSetDevice(e.device));
   e.training_plan = true;
   int rc = e.build_plan(batch, images, out_reg, out_cls, out_mask, nullptr, 0);

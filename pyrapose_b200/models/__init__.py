@@ -53,12 +53,12 @@ def load_model(filepath, backbone_name='resnet50'):
     return PFPNModel.load(filepath)
 
 
-def convert_model(model, nms=True, class_specific_filter=True, anchor_params=None, precision=None):
+def convert_model(model, nms=True, class_specific_filter=True, anchor_params=None, precision=None, alias_arena=False):
     """ Converts a training model to an inference model (adds anchors + RegressBoxes3D). precision=None keeps the
     training model's ('bf16'); 'fp32' builds the 1e-4 path (six MMAs over three-part bf16 splits) on the same weights."""
     from .retinanet import retinanet_bbox
     return retinanet_bbox(model=model, nms=nms, class_specific_filter=class_specific_filter,
-                          anchor_params=anchor_params, precision=precision)
+                          anchor_params=anchor_params, precision=precision, alias_arena=alias_arena)
 
 
 def assert_training_model(model):

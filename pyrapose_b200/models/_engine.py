@@ -20,7 +20,7 @@ def _fp(a):
 
 
 class Engine(object):
-    def __init__(self, device, max_batch, height, width, num_classes, num_anchors, precision=0):
+    def __init__(self, device, max_batch, height, width, num_classes, num_anchors, precision=0, alias_arena=False):
         self.lib = nat.load()
         self.lib.ppb_engine_device_bytes.restype = ctypes.c_size_t
         self.device = torch.device("cuda", device if device is not None else torch.cuda.current_device())
@@ -31,6 +31,9 @@ class Engine(object):
         self.precision = int(precision)   # 0: bf16 production path; 1: fp32 path (three bf16 parts, six MMAs)
         nat.check(self.lib.ppb_engine_create_ex(ctypes.byref(self._h), self.device.index, self.max_batch, self.height,
                                                 self.width, self.num_classes, self.num_anchors, self.precision))
+        self.alias_arena = bool(alias_arena)
+        if self.alias_arena:   # production arena: backbone intermediates share buffers (ppb_engine_set_arena_alias)
+            nat.check(self.lib.ppb_engine_set_arena_alias(self._h, 1))
         self.levels = [((self.height + (8 << i) - 1) // (8 << i), (self.width + (8 << i) - 1) // (8 << i))
                        for i in range(3)]
         self.num_locations = sum(h * w for h, w in self.levels)

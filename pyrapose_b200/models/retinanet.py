@@ -26,11 +26,14 @@ class _LayerView(object):
 
 class PFPNModel(object):
     def __init__(self, num_classes, num_anchors=None, name='retinanet', inference=False, anchor_params=None,
-                 weights=None, seed=None, device=None, precision='bf16'):
+                 weights=None, seed=None, device=None, precision='bf16', alias_arena=False):
         if precision not in ('bf16', 'fp32'):
             raise ValueError("precision must be 'bf16' (production path, tolerance 1e-2) or 'fp32' (three-part bf16 "
                              "split, six MMAs per product, tolerance 1e-4; inference only), got %r" % (precision,))
         self.precision = precision
+        # production arena: backbone intermediates share buffers (6.4 -> 3.7 GB at batch 32); inference models only,
+        # and model.activation() can then only return tensors that survive the pass (outputs, C3-C5, the pyramid)
+        self.alias_arena = bool(alias_arena)
         self.num_classes = int(num_classes)
         self.num_anchors = int(num_anchors if num_anchors is not None else AnchorParameters.default.num_anchors())
         self.name = name
@@ -85,6 +88,7 @@ class PFPNModel(object):
             self.weights[k] = v
         for e in self._engines.values():
             e.load_weights(self.weights, self._bn_names())
+            e._wver = self._root().__dict__.get('_wver', 0)
 
     def load_weights(self, filepath, by_name=True, skip_mismatch=False):
         """`model.load_weights(path, by_name=True, skip_mismatch=...)` (PyraPose/bin/train.py:65-68).
@@ -154,6 +158,8 @@ class PFPNModel(object):
         from ._engine import Engine
         fp32 = self.precision == 'fp32'
         key = (height, width, 'fp32') if fp32 else (height, width)
+        if self.alias_arena:
+            key = key + ('alias',)
         eng = self._engines.get(key)
         if eng is None or eng.max_batch < batch:
             if eng is not None:
@@ -166,10 +172,20 @@ class PFPNModel(object):
             dev = self.device if self.device is not None else torch.cuda.current_device()
             if fp32:
                 self._root().sync_weights()   # a trained parent's master weights first
-            eng = Engine(dev, batch, height, width, self.num_classes, self.num_anchors, precision=1 if fp32 else 0)
+            if self.alias_arena:
+                self._root().sync_weights()
+            eng = Engine(dev, batch, height, width, self.num_classes, self.num_anchors, precision=1 if fp32 else 0,
+                         alias_arena=self.alias_arena)
             eng.load_weights(self.weights, self._bn_names())
             eng._anchor_owner = None
+            eng._wver = self._root().__dict__.get('_wver', 0)
             self._engines[key] = eng
+        elif (fp32 or self.alias_arena) and eng._wver != self._root().__dict__.get('_wver', 0):
+            # engines of the fp32 path / the production arena are not the one the training step updates in place:
+            # reload them when the model has stepped since they were filled
+            self._root().sync_weights()
+            eng.load_weights(self.weights, self._bn_names())
+            eng._wver = self._root().__dict__.get('_wver', 0)
         if getattr(eng, '_anchor_owner', None) is not self:
             p = self.anchor_params
             # Anchors layer: float64 base anchors cast to float32 (layers/_misc.py:52-56)
@@ -366,6 +382,8 @@ class PFPNModel(object):
 
     def activation(self, name, height, width):
         key = (height, width, 'fp32') if self.precision == 'fp32' else (height, width)
+        if self.alias_arena:
+            key = key + ('alias',)
         return self._engines[key].activation(name)
 
     # ------------------------------------------------------------------ training (keras.Model.compile / train_on_batch)
@@ -452,13 +470,18 @@ class PFPNModel(object):
                 # bucketed exchange: the all-reduce of gradient bucket k runs on NCCL's stream while segment k + 1 of
                 # the backward pass runs on this one (async_op=True: NCCL's stream waits for the work queued so far)
                 eng.train_count()
+                counts_work = None
                 if self.dp_normalizer == 'global':
-                    dist.all_reduce(eng.train_counts_tensor())
+                    # a few bytes, but a full NCCL latency: in flight during the forward pass (segment 0), awaited
+                    # before the loss kernels (the first launches of segment 1)
+                    counts_work = dist.all_reduce(eng.train_counts_tensor(), async_op=True)
                 else:
                     scale = 1.0 / world
                 grads, works = eng.grads_tensor(), []
                 for i, (off, cnt, _) in enumerate(eng.train_segments()):
                     eng.train_run_segment(i)
+                    if i == 0 and counts_work is not None:
+                        counts_work.wait()
                     if cnt > 0:
                         works.append(dist.all_reduce(grads[off:off + cnt], async_op=True))
                 for w in works:
@@ -467,6 +490,7 @@ class PFPNModel(object):
                 eng.train_forward_backward()
             eng.train_apply(opt.lr, opt.beta_1, opt.beta_2, opt.epsilon, opt.clipnorm, scale)
         self._weights_stale = True
+        self._wver = self.__dict__.get('_wver', 0) + 1
         if not sync_losses:
             return None
         l = eng.train_losses()
@@ -502,7 +526,7 @@ def retinanet(inputs=None, backbone_layers=None, num_classes=None, num_anchors=N
 
 
 def retinanet_bbox(model=None, nms=True, class_specific_filter=True, name='retinanet-bbox', anchor_params=None,
-                   precision=None, **kwargs):
+                   precision=None, alias_arena=False, **kwargs):
     """ Inference model: training model + Anchors + RegressBoxes3D. Like the reference (:302-335), `nms` and
     `class_specific_filter` are accepted and not wired into the graph; use layers.FilterDetections or
     model.detect_on_batch for filtering."""
@@ -514,7 +538,7 @@ def retinanet_bbox(model=None, nms=True, class_specific_filter=True, name='retin
         assert_training_model(model)
     out = PFPNModel(model.num_classes, model.num_anchors, name=name, inference=True, anchor_params=anchor_params,
                     weights=model.weights, device=model.device,
-                    precision=precision if precision is not None else model.precision)
+                    precision=precision if precision is not None else model.precision, alias_arena=alias_arena)
     # Like the reference (bin/train.py:86-92: prediction_model = retinanet_bbox(model=model) is built BEFORE training
     # and evaluated after every epoch), the prediction model shares the training model's layers: same weight dict,
     # same engines. The Adam kernel rewrites the bf16 forward matrices in place, so a predict_on_batch after

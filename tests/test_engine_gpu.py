@@ -229,3 +229,35 @@ def test_fused_pfpn_adds_match_separate_launches(cuda_device, monkeypatch):
     assert rel_l2(t1["P4_fin"], t0["P4_fin"]) < 4e-3
     for a, b in zip(o0, o1):
         assert rel_l2(b, a) < 1e-2
+
+
+def test_production_arena_gives_identical_outputs_with_less_memory(cuda_device):
+    """alias_arena=True (ppb_engine_set_arena_alias): the backbone's bottleneck intermediates share buffers. Outputs,
+    detections and the tensors that survive the pass (C3-C5, the pyramid) are bit-identical to the one-buffer-per-layer
+    arena; the arena is smaller; the training step refuses such an engine."""
+    from pyrapose_b200 import models
+    from pyrapose_b200.models import spec
+    C, H, W = 4, 136, 200
+    weights = spec.init_weights(C, seed=3, head_init="spread", randomize_bn=True)
+    train = models.backbone("resnet50").retinanet(C)
+    train.set_weights_dict(weights)
+    plain = models.convert_model(train)
+    prod = models.convert_model(train, alias_arena=True)
+    img = make_images(4, 3, H, W)
+    a = [o.copy() for o in plain.predict_on_batch(img)]
+    b = [o.copy() for o in prod.predict_on_batch(img)]
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+    for name in ("res3d_relu", "res4f_relu", "res5c_relu", "P3", "P4", "P5"):
+        assert np.array_equal(plain.activation(name, H, W), prod.activation(name, H, W)), name
+    for x, y in zip(plain.detect_on_batch(img), prod.detect_on_batch(img)):
+        assert np.array_equal(x, y)
+    e0, e1 = plain._engines[(H, W)], prod._engines[(H, W, 'alias')]
+    print("arena bytes: %d (one buffer per layer) vs %d (production arena)" % (e0.device_bytes(), e1.device_bytes()))
+    assert e1.device_bytes() < 0.85 * e0.device_bytes()   # weights included; at batch 32, 480x640: 6.41 -> 3.67 GB
+    # a second batch through the same aliased arena (stale contents of the shared buffers must not leak)
+    img2 = make_images(5, 2, H, W)
+    for x, y in zip(plain.predict_on_batch(img2), prod.predict_on_batch(img2)):
+        assert np.array_equal(x, y)
+    with pytest.raises(RuntimeError):
+        e1.train_bind(1)
