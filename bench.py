@@ -135,26 +135,24 @@ def load_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
-CPU_BATCH = 4  # images per oracle call: the CPU arm batches too (oneDNN gains ~2x from batch 1 to 4 on 8 cores and
-                # nothing beyond); a bounded sample of the batch-32 step
-
-
-def cpu_step(weights, n_images, seed):
-    """One bounded CPU sample: oracle forward + decode + filter over n_images, in batches of CPU_BATCH."""
+def cpu_step(weights, n_images, seed, batch=1):
+    """One bounded CPU sample: oracle forward + decode + filter over n_images, `batch` images per oracle call. Both
+    batch 1 and batch 4 are measured and reported (batch 4 is ~2x faster per image on an 8-core host, slower on the
+    16-core GPU box); larger batches gain nothing."""
     from oracle import decode as od, filter as of, pfpn
-    for i in range(0, n_images, CPU_BATCH):
-        img = np.concatenate([make_images(seed + i + j, 1) for j in range(min(CPU_BATCH, n_images - i))], axis=0)
+    for i in range(0, n_images, batch):
+        img = np.concatenate([make_images(seed + i + j, 1) for j in range(min(batch, n_images - i))], axis=0)
         b3, cls, _ = pfpn.forward_inference(img, weights, C)
         of.filter_detections_batch(od.hull_boxes(b3), b3, cls)
 
 
-def cpu_reference(weights, n_images, threads, seed=100):
+def cpu_reference(weights, n_images, threads, seed=100, batch=1):
     """Oracle forward + decode + filter on the host cores. Returns (images/s, seconds)."""
     import torch
     torch.set_num_threads(threads)
-    cpu_step(weights, CPU_BATCH, seed)  # warm-up (oneDNN primitive creation)
+    cpu_step(weights, batch, seed, batch)  # warm-up (oneDNN primitive creation)
     t0 = time.perf_counter()
-    cpu_step(weights, n_images, seed + 1)
+    cpu_step(weights, n_images, seed + 1, batch)
     dt = time.perf_counter() - t0
     return n_images / dt, dt
 
@@ -169,12 +167,16 @@ def run_reference(args):
     weights = bench_weights(args)
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
-    sample = CPU_BATCH
+    # both batchings once, then the timed steps in the faster one
+    b1, _ = cpu_reference(weights, 4, threads, seed=900, batch=1)
+    b4, _ = cpu_reference(weights, 4, threads, seed=950, batch=4)
+    sample = 4 if b4 > b1 else 2
+    cb = 4 if b4 > b1 else 1
     for i in range(max(args.warmup, 1)):
-        cpu_step(weights, sample, 1000 + 10 * i)
+        cpu_step(weights, sample, 1000 + 10 * i, cb)
     t0 = time.perf_counter()
     for i in range(args.steps):
-        cpu_step(weights, sample, 2000 + 10 * i)
+        cpu_step(weights, sample, 2000 + 10 * i, cb)
     dt = time.perf_counter() - t0
     ips = args.steps * sample / dt
     line = {
@@ -185,8 +187,10 @@ def run_reference(args):
                                "max 300), 480x640, 15 classes",
                    "note": "reference TF/Keras path unavailable on this box; this is the cited CPU restatement (oracle/)"},
         "cpu_baseline": {"value": ips, "unit": "images/s", "cores": threads, "kind": "port",
-                         "sample": "%d images per step as one batch (a bounded sample of the batch-32 step), "
-                                   "forward+decode+filter, torch-CPU fp32" % sample},
+                         "sample": "%d images per step, %d per oracle call (the faster of batch 1: %.2f and batch 4: %.2f "
+                                   "images/s on this host; a bounded sample of the batch-32 step), forward+decode+filter, "
+                                   "torch-CPU fp32" % (sample, cb, b1, b4),
+                         "batch1_images_per_s": b1, "batch4_images_per_s": b4},
         "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     _emit(line)
@@ -380,11 +384,11 @@ def config5_block(args, world, rank, dev, barrier):
     w["pyramid_classification/bias"] = np.full_like(w["pyramid_classification/bias"], args.cls_bias)
     train = models.backbone("resnet50").retinanet(num_classes=c5)
     train.set_weights_dict(w)
-    model = models.convert_model(train)
+    model = models.convert_model(train, alias_arena=True)   # production arena (shared backbone buffers)
     rng = np.random.default_rng(500 + rank)
     img = torch.from_numpy(rng.integers(0, 256, (per, h5, w5, 3), dtype=np.uint8)).pin_memory()
     buf = model.forward_device(img, want_hull=True)
-    eng = model._engines[(h5, w5)]
+    eng = model._engines[(h5, w5, 'alias')]
 
     def step():
         eng.run()
@@ -434,13 +438,13 @@ def run_ours(args):
     weights = bench_weights(args)
     train = models.backbone("resnet50").retinanet(num_classes=C)
     train.set_weights_dict(weights)
-    model = models.convert_model(train)
+    model = models.convert_model(train, alias_arena=True)   # production arena: backbone intermediates share buffers
 
     # ---- device-resident arm: images already in HBM
     host_img = make_images(10 + rank, B)
     pinned = torch.from_numpy(host_img).pin_memory()
     buf = model.forward_device(pinned, want_hull=True)        # builds the engine, binds, first run
-    eng = model._engines[(H, W)]
+    eng = model._engines[(H, W, 'alias')]
     torch.cuda.synchronize()
 
     def step_device():
@@ -550,7 +554,7 @@ def run_ours(args):
     if rank == 0:
         # ---- roofline of the dominant kernel (tcgen05 implicit-GEMM conv), timed per launch with CUDA events
         buf = model.forward_device(pinned, want_hull=True)   # back to the plan of the timed region
-        eng = model._engines[(H, W)]
+        eng = model._engines[(H, W, 'alias')]
         prof = [eng.profile() for _ in range(3)][-1]
         conv_ms = sum(ms for k, ms in prof if k == 0)
         other_ms = sum(ms for k, ms in prof if k != 0)
@@ -625,9 +629,11 @@ def run_ours(args):
         # ---- CPU baseline on this box's host cores (bounded sample)
         threads = os.cpu_count() or 1
         if world == 1:
-            cpu_ips, cpu_s = cpu_reference(weights, args.cpu_images, threads)
+            cpu_b1, cpu_s1 = cpu_reference(weights, args.cpu_images, threads, batch=1)
+            cpu_b4, cpu_s4 = cpu_reference(weights, args.cpu_images, threads, batch=4)
+            cpu_ips, cpu_s = max(cpu_b1, cpu_b4), cpu_s1 + cpu_s4
         else:  # the CPU baseline is an N=1 leg: at N>1 the other ranks' barrier spinning would share its cores
-            cpu_ips, cpu_s = None, 0.0
+            cpu_ips, cpu_s, cpu_b1, cpu_b4 = None, 0.0, None, None
         value = world * B * args.steps / (dev_ms * 1e-3)
         line = {
             "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
@@ -666,8 +672,10 @@ def run_ours(args):
                              "frac_single_launch": B * n_boxes * C * 4 / (mask_ms_single * 1e-3) / 1e9
                                                    / float(peaks["hbm_gbs"])},
             "cpu_baseline": {"value": cpu_ips, "unit": "images/s", "cores": threads, "kind": "port",
-                             "sample": "%d images (batches of 4: a bounded sample of the batch-32 step) forward+decode+filter, torch-CPU fp32 oracle, %.1f s"
-                                       % (args.cpu_images, cpu_s)} if world == 1 else None,
+                             "sample": "%d images forward+decode+filter at batch 1 and again at batch 4 (value = the faster; "
+                                       "a bounded sample of the batch-32 step), torch-CPU fp32 oracle, %.1f s"
+                                       % (args.cpu_images, cpu_s),
+                             "batch1_images_per_s": cpu_b1, "batch4_images_per_s": cpu_b4} if world == 1 else None,
             "train": train_out,
             "config5": cfg5_out,
         }
