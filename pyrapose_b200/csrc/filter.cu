@@ -10,7 +10,8 @@
 //                      shared memory, and emits one bit per score (warp ballot) -> mask[B][C][ceil(N/32)]
 //   compact_keys_kernel  per (image, class): popc scan over the mask words -> ascending candidate list,
 //                      emitted directly as 64-bit sort keys  (~orderable(score) << 32 | anchor index)
-//   sort_keys_kernel   per (image, class) bitonic sort (shared memory up to 4096 keys, global beyond)
+//   sort_keys_kernel   per (image, class) bitonic sort (registers + warp shuffles + shared memory up to 8192 keys,
+//                      global memory beyond)
 //   nms_kernel         greedy NMS in score order, TensorFlow semantics (IoU > thr suppresses, no "+1",
 //                      min/max-normalised corners, area <= 0 -> 0, stop at max_detections), float32, no FMA
 //   topk_pad_kernel    per image: merge the per-class survivors, top-k by score (ties -> lower position),
@@ -304,6 +305,81 @@ __device__ __forceinline__ void bitonic_sort_block(uint64_t* a, int n_pow2) {
   }
 }
 
+// Bitonic sort of np2 = 1024 * E keys held in REGISTERS, E consecutive keys per thread (key index i = tid * E + e):
+// compare distances below E stay inside the thread, distances up to 16 E are warp shuffles, only the rest go through
+// shared memory (two buffers alternate, so one barrier per such pass). For 2048 keys that is 15 shared-memory passes out
+// of 66; the all-shared-memory form was issue-bound at ~47 instructions per warp and pass (r02 capture: 73 us for 480
+// lists of ~1200 keys, no dominant stall reason).
+template <int E>
+__device__ __forceinline__ void bitonic_sort_regs(uint64_t (&v)[E], int np2, uint64_t* buf0, uint64_t* buf1) {
+  const int tid = threadIdx.x;
+  int flip = 0;
+  for (int k = 2; k <= np2; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      if (j < E) {
+        // partner inside the thread; J is a compile-time constant in every copy so v[] stays in registers (indexing it
+        // with the runtime j sent it to local memory: 8192 keys 0.29 ms slower than the shared-memory sort)
+#pragma unroll
+        for (int J = 1; J < E; J <<= 1) {
+          if (j == J) {
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+              if ((e & J) == 0) {
+                const int i = tid * E + e;
+                const bool up = (i & k) == 0;
+                const uint64_t a = v[e], b = v[e | J];
+                const bool sw = (a > b) == up;
+                v[e] = sw ? b : a;
+                v[e | J] = sw ? a : b;
+              }
+            }
+          }
+        }
+      } else if (j < 32 * E) {
+        const int lane_xor = j / E;
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+          const int i = tid * E + e;
+          const uint64_t other = __shfl_xor_sync(0xffffffffu, v[e], lane_xor);
+          const bool lower = (i & j) == 0, up = (i & k) == 0;
+          const bool take_min = lower == up;
+          v[e] = (v[e] < other) == take_min ? v[e] : other;
+        }
+      } else {
+        uint64_t* w = flip ? buf1 : buf0;
+        flip ^= 1;
+#pragma unroll
+        for (int e = 0; e < E; ++e) w[tid * E + e] = v[e];
+        __syncthreads();
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+          const int i = tid * E + e;
+          const uint64_t other = w[i ^ j];
+          const bool lower = (i & j) == 0, up = (i & k) == 0;
+          const bool take_min = lower == up;
+          v[e] = (v[e] < other) == take_min ? v[e] : other;
+        }
+      }
+    }
+  }
+}
+
+template <int E>
+__device__ __forceinline__ void sort_segment_regs(uint64_t* seg, int n, int np2, uint64_t* smem) {
+  uint64_t v[E];
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    const int i = threadIdx.x * E + e;
+    v[e] = i < n ? seg[i] : ~0ull;
+  }
+  bitonic_sort_regs<E>(v, np2, smem, smem + 1024 * E);
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    const int i = threadIdx.x * E + e;
+    if (i < n) seg[i] = v[e];
+  }
+}
+
 // grid (segments), 1024 threads, dynamic smem kSortSmemKeys * 8. Segment s holds counts[s] keys at keys + s*cap;
 // cap is a power of two, so the global fallback can pad in place.
 __global__ void __launch_bounds__(1024) sort_keys_kernel(uint64_t* __restrict__ keys, const int* __restrict__ counts,
@@ -313,12 +389,20 @@ __global__ void __launch_bounds__(1024) sort_keys_kernel(uint64_t* __restrict__ 
   if (n <= 1) return;
   uint64_t* seg = keys + static_cast<long long>(blockIdx.x) * cap;
   const int np2 = next_pow2(n);
-  if (np2 <= kSortSmemKeys) {
+  if (np2 <= 1024) {
+    sort_segment_regs<1>(seg, n, np2, skeys);
+  } else if (np2 == 2048) {
+    sort_segment_regs<2>(seg, n, np2, skeys);
+  } else if (np2 == 4096) {
+    sort_segment_regs<4>(seg, n, np2, skeys);
+  } else if (np2 <= kSortSmemKeys) {
+    // 8192 keys: all passes through shared memory (eight keys per thread in registers need the whole 64 KB for ONE
+    // exchange buffer and a second barrier per pass: measured 0.59 vs 0.56 ms on the dense set)
     for (int i = threadIdx.x; i < np2; i += blockDim.x) skeys[i] = i < n ? seg[i] : ~0ull;
     __syncthreads();
     bitonic_sort_block(skeys, np2);
     for (int i = threadIdx.x; i < n; i += blockDim.x) seg[i] = skeys[i];
-  } else {
+  } else {  // more than kSortSmemKeys = 8192 candidates in one (image, class) list: in place in global memory
     for (int i = n + threadIdx.x; i < np2; i += blockDim.x) seg[i] = ~0ull;
     __syncthreads();
     bitonic_sort_block(seg, np2);
@@ -365,6 +449,9 @@ __device__ __forceinline__ bool iou_exceeds(const NBox& i, const NBox& j, float 
 // Per 256-candidate chunk (descending score): (1) every candidate is tested against the boxes selected so far, the
 // list split four ways over its helpers; (2) the candidate-vs-earlier-candidate suppression bit matrix is built, two
 // 32-bit words per helper; (3) ONE warp resolves the greedy order 32 candidates at a time with ballots/shuffles.
+// (Building the bit matrix one chunk AHEAD, on the other 31 warps while warp 0 resolves, was measured in r02 and lost:
+// the matrix can then no longer skip the candidates phase 1 has killed, and that pruning is worth more than the overlap
+// — 0.267 -> 0.296 ms per step on the sparse set, 0.564 -> 0.879 on the dense one.)
 constexpr int kNmsWords = kNmsChunk / 32;
 
 // NT threads = NT / 256 helper threads per candidate of the 256-wide chunk (PPB_NMS_THREADS=256|512|1024; smaller
