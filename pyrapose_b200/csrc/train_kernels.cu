@@ -290,18 +290,31 @@ grad_prepare_kernel(const ParamDesc* __restrict__ descs, const int* __restrict__
   const long long end = min(d.count, begin + kOptChunk);
   const int k = d.kind == 0 ? d.k_total : 1;
   double sq = 0.0, l2 = 0.0;
-  for (long long i = begin + threadIdx.x; i < end; i += blockDim.x) {
-    float gv = grads[d.offset + i] * grad_scale;
-    // 32-bit division: a tensor has far fewer than 2^31 elements (the 64-bit one was a third of this loop)
-    const int co = static_cast<int>(static_cast<unsigned>(i) / static_cast<unsigned>(k));
-    if (d.scale != nullptr) gv *= __ldg(d.scale + co);  // chain rule through the folded BatchNorm scale
-    if (d.l2 > 0.0f) {
-      const float w = master[d.offset + i];
-      gv += 2.0f * d.l2 * w;
-      l2 += static_cast<double>(d.l2 * w * w);
+  // four elements per round, loads first (the store to grads[] would otherwise order the next load behind it)
+  for (long long i0 = begin + threadIdx.x; i0 < end; i0 += 4ll * blockDim.x) {
+    float gq[4], wq[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + static_cast<long long>(u) * blockDim.x;
+      gq[u] = i < end ? grads[d.offset + i] : 0.0f;
+      wq[u] = (i < end && d.l2 > 0.0f) ? master[d.offset + i] : 0.0f;
     }
-    grads[d.offset + i] = gv;
-    sq += static_cast<double>(gv) * gv;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + static_cast<long long>(u) * blockDim.x;
+      if (i >= end) continue;
+      float gv = gq[u] * grad_scale;
+      // 32-bit division: a tensor has far fewer than 2^31 elements (the 64-bit one was a third of this loop)
+      const int co = static_cast<int>(static_cast<unsigned>(i) / static_cast<unsigned>(k));
+      if (d.scale != nullptr) gv *= __ldg(d.scale + co);  // chain rule through the folded BatchNorm scale
+      if (d.l2 > 0.0f) {
+        const float w = wq[u];
+        gv += 2.0f * d.l2 * w;
+        l2 += static_cast<double>(d.l2 * w * w);
+      }
+      grads[d.offset + i] = gv;
+      sq += static_cast<double>(gv) * gv;
+    }
   }
   block_accumulate(sq, loss + kGradSumSq);
   if (d.l2 > 0.0f) block_accumulate(l2, loss + kLossL2);
@@ -343,15 +356,41 @@ adam_update_kernel(const ParamDesc* __restrict__ descs, const int* __restrict__ 
   const int kl = threadIdx.x & 63, r0 = threadIdx.x >> 6;
   const int kk = kk0 + kl;
   if (kk < d.k_total) {
-    for (int rl = r0; rl < 64; rl += 4) {
-      const int co = co0 + rl;
-      if (co >= d.cout) break;
-      const long long i = static_cast<long long>(co) * d.k_total + kk;
-      const float w = step(d.offset + i);
-      const float wf = d.scale != nullptr ? w * __ldg(d.scale + co) : w;
-      const __nv_bfloat16 wb = __float2bfloat16(wf);
-      d.w_fwd[i] = wb;
-      tile[kl][rl] = wb;
+    // four rows per round with all sixteen loads (g, m, v, w of each row) issued before the first store: the one-row
+    // loop waited out a full memory latency per row (stores to m / v / w may alias the next row's loads as far as the
+    // compiler knows), 0.52 ms for 1.7 GB
+    for (int rb = r0; rb < 64; rb += 16) {
+      float gq[4], mq[4], vq[4], wq[4];
+      long long iq[4];
+      bool ok[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int co = co0 + rb + 4 * u;
+        ok[u] = co < d.cout;
+        iq[u] = static_cast<long long>(ok[u] ? co : co0) * d.k_total + kk;
+        const long long gi = d.offset + iq[u];
+        gq[u] = grads[gi];
+        mq[u] = m[gi];
+        vq[u] = v[gi];
+        wq[u] = master[gi];
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (!ok[u]) continue;
+        const int rl = rb + 4 * u, co = co0 + rl;
+        const long long gi = d.offset + iq[u];
+        const float gv = gq[u] * clip;
+        const float mt = beta1 * mq[u] + (1.0f - beta1) * gv;
+        const float vt = beta2 * vq[u] + (1.0f - beta2) * gv * gv;
+        const float w = wq[u] - lr_t * mt / (sqrtf(vt) + eps);
+        m[gi] = mt;
+        v[gi] = vt;
+        master[gi] = w;
+        const float wf = d.scale != nullptr ? w * __ldg(d.scale + co) : w;
+        const __nv_bfloat16 wb = __float2bfloat16(wf);
+        d.w_fwd[iq[u]] = wb;
+        tile[kl][rl] = wb;
+      }
     }
   }
   if (d.w_dgrad == nullptr) return;
