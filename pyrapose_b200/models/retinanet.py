@@ -7,6 +7,8 @@ The returned PFPNModel answers the calls the reference's callers make on a keras
 predict_on_batch, output_names, load_weights(by_name=True), save / save_weights, summary, get_layer(name).weights.
 The graph itself runs in the native engine (tcgen05 implicit-GEMM convolutions, one CUDA graph per batch size).
 """
+import os
+
 import numpy as np
 
 from . import assert_training_model, spec
@@ -408,6 +410,8 @@ class PFPNModel(object):
             raise ValueError("dp_normalizer must be 'global' or 'replica'")
         self.dp_normalizer = dp_normalizer
         self.bucket_bytes = int(bucket_bytes)
+        if os.environ.get("PPB_BUCKET_MB"):   # A/B runs of the bucket size without touching the caller
+            self.bucket_bytes = int(float(os.environ["PPB_BUCKET_MB"]) * (1 << 20))
         self.data_parallel = bool(data_parallel)
         from .. import losses, optimizers
         if self.inference:
