@@ -276,17 +276,21 @@ def train_block(args, world, rank, dev, barrier):
     out = {
         "metric": "images_per_sec_pfpn_480x640_train_step", "value": TB * world / (step_ms * 1e-3), "unit": "images/s",
         "ms_per_step": step_ms, "steps": steps, "warmup": warm,
-        "config": {"workload": "PFPN ResNet-50 training step (forward + focal/orthogonal_l1 + backward + NCCL gradient "
-                               "all-reduce + Adam clipnorm), YCB-Video %d classes, batch %d per GPU, %dx%d"
+        "config": {"workload": "PFPN ResNet-50 training step (forward + focal/orthogonal_l1 + backward + gradient "
+                               "exchange over NVLink + Adam clipnorm), YCB-Video %d classes, batch %d per GPU, %dx%d"
                                % (TC, TB, TH, TW), "global_batch": TB * world, "parallelism": "dp%d" % world,
                    "dp_normalizer": model.dp_normalizer},
         "split_ms": {"copy_inputs": parts[0], "forward_backward": parts[1], "optimizer": parts[2],
                      "allreduce_exposed": max(step_ms - local_ms, 0.0) if world > 1 else 0.0,
                      "step_without_exchange": local_ms},
         "allreduce_bytes": 4 * n_params if world > 1 else 0,
-        "allreduce": ("%d buckets of ~%d MB, each all-reduced (NCCL, async) as soon as its last weight gradient has "
-                      "landed, overlapping the rest of the backward pass" % (sum(1 for _, c, _ in eng.train_segments() if c),
-                                                                              model.bucket_bytes >> 20)) if world > 1 else None,
+        "allreduce": (("%d buckets of ~%d MB; " % (sum(1 for _, c, _ in eng.train_segments() if c), model.bucket_bytes >> 20)) +
+                      ("peer-to-peer exchange: every finished bucket is pushed into the peers' staging memory by copy "
+                       "engines over NVLink while the backward pass runs (no SM taken), one kernel sums the replicas' "
+                       "slices afterwards (utils/exchange.py, ppb_p2p_*)" if eng.__dict__.get("_p2p") else
+                       "each all-reduced (NCCL, async) as soon as its last weight gradient has landed, overlapping the "
+                       "rest of the backward pass")) if world > 1 else None,
+        "exchange": ("p2p" if eng.__dict__.get("_p2p") else "nccl") if world > 1 else None,
         "kernels": {k: {"ms": v[0], "launches": v[2], "tflops": (v[1] / v[0] * 1e-9) if v[0] > 0 and v[1] > 0 else None}
                     for k, v in groups.items()},
         "losses": {k: losses[k] for k in ("3Dbox", "cls", "mask", "l2", "grad_norm")},

@@ -348,6 +348,26 @@ PPB_API int ppb_engine_train_op_info(const ppb_engine* engine, int index, char* 
 /* Per-launch device times (ms) of one eager training step, in op order; synchronises `stream`. */
 PPB_API int ppb_engine_train_profile(ppb_engine* engine, void* stream, float* ms_out_host, int cap);
 
+/* ------------------------------------------------------------------ peer-to-peer gradient exchange
+ * Data-parallel training step (the reference: keras.utils.multi_gpu_model + fit_generator, PyraPose/bin/train.py:82-102,
+ * 381-390). One process per GPU on one node. Every replica owns a staging buffer with one slot
+ * per peer; a finished gradient bucket is pushed into the peers' slots with asynchronous copies (copy engines over
+ * NVLink: no SM is taken from the backward pass, unlike an overlapped NCCL all-reduce), and after the backward pass
+ * ppb_p2p_sum_f32 adds the slices in rank order (bit-identical on every replica).
+ *   ppb_p2p_alloc / _free      device memory that can be exported (plain cudaMalloc on the current device, zeroed)
+ *   ppb_p2p_export             64-byte CUDA IPC handle of such a buffer, to be sent to the peers (any host channel)
+ *   ppb_p2p_import / _release  map / unmap a peer's buffer from its handle (enables peer access lazily)
+ *   ppb_p2p_copy               asynchronous copy between local and peer-mapped device memory on `stream`
+ *   ppb_p2p_sum_f32            out[i] = srcs[0][i] + srcs[1][i] + ... (srcs_host: HOST array of n_srcs device pointers,
+ *                              16-byte aligned; out may be one of them) */
+PPB_API int ppb_p2p_alloc(size_t bytes, void** dev_ptr);
+PPB_API int ppb_p2p_free(void* dev_ptr);
+PPB_API int ppb_p2p_export(const void* dev_ptr, unsigned char* handle64);
+PPB_API int ppb_p2p_import(const unsigned char* handle64, void** peer_ptr);
+PPB_API int ppb_p2p_release(void* peer_ptr);
+PPB_API int ppb_p2p_copy(void* dst, const void* src, size_t bytes, void* stream);
+PPB_API int ppb_p2p_sum_f32(float* out, const float* const* srcs_host, int n_srcs, long long count, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

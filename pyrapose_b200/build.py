@@ -39,6 +39,7 @@ def _optional_sources():
         ("pnp.cu", False),
         ("train_kernels.cu", False),
         ("train.cu", False),
+        ("exchange.cu", True),
     ]
     return [(s, e) for s, e in extra if os.path.exists(os.path.join(CSRC, s))]
 

@@ -390,7 +390,7 @@ class PFPNModel(object):
 
     # ------------------------------------------------------------------ training (keras.Model.compile / train_on_batch)
     def compile(self, loss=None, optimizer=None, dp_normalizer='global', bucket_bytes=25 << 20, data_parallel=True,
-                **kwargs):
+                exchange='auto', **kwargs):
         """ Mirror of `training_model.compile(loss={'3Dbox': orthogonal_l1(), 'cls': focal(), 'mask': focal()},
         optimizer=Adam(lr, clipnorm=0.001))` (PyraPose/bin/train.py:95-102). Only that configuration exists in the
         native step; anything else raises ValueError.
@@ -405,7 +405,15 @@ class PFPNModel(object):
                                     batch) and the gradients are averaged.
           bucket_bytes            — size of the gradient buckets whose NCCL all-reduce overlaps the rest of the
                                     backward pass (0: one all-reduce after the backward pass);
-          data_parallel=False     — this model steps alone even when torch.distributed is initialised."""
+          data_parallel=False     — this model steps alone even when torch.distributed is initialised;
+          exchange                — how the replica gradients are summed: 'p2p' pushes every finished bucket into the
+                                    peers' memory with copy engines over NVLink and adds the slices in one kernel after
+                                    the backward pass (utils/exchange.py; no SM is taken from the backward pass);
+                                    'nccl' all-reduces the buckets on NCCL's stream; 'auto' = 'p2p' when all replicas
+                                    are on this node, else 'nccl'."""
+        if exchange not in ('auto', 'p2p', 'nccl'):
+            raise ValueError("exchange must be 'auto', 'p2p' or 'nccl'")
+        self.exchange = os.environ.get("PPB_EXCHANGE", exchange)
         if dp_normalizer not in ('global', 'replica'):
             raise ValueError("dp_normalizer must be 'global' or 'replica'")
         self.dp_normalizer = dp_normalizer
@@ -482,12 +490,18 @@ class PFPNModel(object):
                 else:
                     scale = 1.0 / world
                 grads, works = eng.grads_tensor(), []
+                p2p = self._p2p_exchange(eng, grads)
                 for i, (off, cnt, _) in enumerate(eng.train_segments()):
                     eng.train_run_segment(i)
                     if i == 0 and counts_work is not None:
                         counts_work.wait()
                     if cnt > 0:
-                        works.append(dist.all_reduce(grads[off:off + cnt], async_op=True))
+                        if p2p is not None:
+                            p2p.push(grads, off, cnt)      # copy engines, no SM
+                        else:
+                            works.append(dist.all_reduce(grads[off:off + cnt], async_op=True))
+                if p2p is not None:
+                    p2p.finish(grads)                      # "all pushes landed" signal + one sum kernel
                 for w in works:
                     w.wait()
             else:
@@ -500,6 +514,34 @@ class PFPNModel(object):
         l = eng.train_losses()
         self.last_step = l
         return [l["3Dbox"] + l["cls"] + l["mask"] + l["l2"], l["3Dbox"], l["cls"], l["mask"]]
+
+    def _p2p_exchange(self, eng, grads):
+        """The engine's P2PExchange (created collectively on the first data-parallel step), or None for NCCL."""
+        import torch
+        import torch.distributed as dist
+        ex = eng.__dict__.get('_p2p', False)
+        if ex is not False:
+            return ex
+        from ..utils import exchange as xch
+        want = getattr(self, 'exchange', 'auto')
+        ex = None
+        if want != 'nccl' and xch.available():
+            ex = xch.P2PExchange(grads.numel(), grads.device)   # collective; never raises on one replica alone
+            # every replica must take the same path (this all-reduce is also the barrier before the first push)
+            ok = torch.tensor([1.0 if ex.ok else 0.0], device=grads.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if float(ok.item()) < 1.0:
+                err = ex.error
+                ex.close()
+                ex = None
+                if want == 'p2p':
+                    raise RuntimeError("exchange='p2p': peer-to-peer staging could not be set up (%r)" % (err,))
+                import sys
+                sys.stderr.write("pyrapose_b200: peer-to-peer gradient exchange unavailable (%r): using NCCL\n" % (err,))
+        elif want == 'p2p':
+            raise RuntimeError("exchange='p2p' needs torch.distributed with all replicas on this node")
+        eng._p2p = ex
+        return ex
 
     def sync_weights(self):
         """Copies the trained master weights from the engine back into `self.weights` (Keras HWIO layout)."""
