@@ -1,13 +1,15 @@
 // Peer-to-peer gradient exchange for the data-parallel training step (the reference's
 // keras.utils.multi_gpu_model / fit_generator step, PyraPose/bin/train.py:82-102, 381-390).
 //
-// Why not only NCCL: every kernel of the step is a persistent grid of one CTA per SM that owns the SM's whole shared
-// memory, and NCCL's channels are CTAs too — an all-reduce that overlaps the backward pass takes SMs away and the conv
-// / wgrad launch that coincides with it runs a second wave (measured r02: the overlap hides 0.35 ms and costs 0.25 ms).
-// Here the exchange needs no SM while the backward pass runs: as soon as a gradient bucket is complete, every replica
-// pushes it into a staging slot in EACH peer's memory with plain asynchronous copies (copy engines, NVLink / NVSwitch,
-// peer mappings from CUDA IPC handles), and after the backward pass one bandwidth-bound kernel sums the N slices in
-// rank order — the same order on every replica, so the replicas stay bit-identical.
+// An alternative to the overlapped NCCL all-reduce that needs no SM while the backward pass runs (NCCL's channels are
+// CTAs, and every kernel of the step is a persistent grid of one CTA per SM): as soon as a gradient bucket is complete,
+// every replica pushes it into a staging slot in EACH peer's memory with plain asynchronous copies (copy engines,
+// NVLink / NVSwitch, peer mappings from CUDA IPC handles), and after the backward pass one bandwidth-bound kernel sums
+// the N slices in rank order — the same order on every replica, so the replicas stay bit-identical.
+// Measured r02 (config 4): the same step time as NCCL at 2 GPUs (13.30-13.42 vs 13.31 ms), slower at 8 (15.08 vs 13.63
+// ms) — an all-gather by copies moves N-1 times the gradient (1.19 GB out and in per replica and step at N = 8), which
+// the copy engines do not finish inside the backward pass. It is therefore an option (compile(exchange='p2p')), not the
+// default.
 #include "../../include/pyrapose_b200.h"
 #include "errors.h"
 #include "launch_count.h"

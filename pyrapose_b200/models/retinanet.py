@@ -406,11 +406,12 @@ class PFPNModel(object):
           bucket_bytes            — size of the gradient buckets whose NCCL all-reduce overlaps the rest of the
                                     backward pass (0: one all-reduce after the backward pass);
           data_parallel=False     — this model steps alone even when torch.distributed is initialised;
-          exchange                — how the replica gradients are summed: 'p2p' pushes every finished bucket into the
-                                    peers' memory with copy engines over NVLink and adds the slices in one kernel after
-                                    the backward pass (utils/exchange.py; no SM is taken from the backward pass);
-                                    'nccl' all-reduces the buckets on NCCL's stream; 'auto' = 'p2p' when all replicas
-                                    are on this node, else 'nccl'."""
+          exchange                — how the replica gradients are summed: 'nccl' (= 'auto') all-reduces the buckets
+                                    on NCCL's stream while the backward pass runs; 'p2p' pushes every finished bucket
+                                    into the peers' memory with copy engines over NVLink and adds the slices in one
+                                    kernel after the backward pass (utils/exchange.py; single node). Measured r02:
+                                    equal at 2 GPUs (13.30-13.42 vs 13.31 ms per step), slower at 8 (15.08 vs 13.63 ms:
+                                    an all-gather by copies moves N-1 times the gradient), hence not the default."""
         if exchange not in ('auto', 'p2p', 'nccl'):
             raise ValueError("exchange must be 'auto', 'p2p' or 'nccl'")
         self.exchange = os.environ.get("PPB_EXCHANGE", exchange)
@@ -525,7 +526,7 @@ class PFPNModel(object):
         from ..utils import exchange as xch
         want = getattr(self, 'exchange', 'auto')
         ex = None
-        if want != 'nccl' and xch.available():
+        if want == 'p2p' and xch.available():
             ex = xch.P2PExchange(grads.numel(), grads.device)   # collective; never raises on one replica alone
             # every replica must take the same path (this all-reduce is also the barrier before the first push)
             ok = torch.tensor([1.0 if ex.ok else 0.0], device=grads.device)

@@ -2,9 +2,9 @@
 
 The reference trains data-parallel with keras.utils.multi_gpu_model (PyraPose/bin/train.py:82-86): replica outputs are
 concatenated and one gradient is applied. Here every replica is a process with its own GPU and
-the replica gradients have to be summed. An NCCL all-reduce overlapped with the backward pass takes SMs away from it
-(NCCL's channels are CTAs; every kernel of the step is a persistent grid of one CTA per SM), so this exchange uses none
-while the backward pass runs:
+the replica gradients have to be summed. The default is NCCL's all-reduce, bucket by bucket, overlapped with the
+backward pass; this module is the alternative that uses no SM while the backward pass runs (compile(exchange='p2p');
+measured equal to NCCL at 2 GPUs and slower at 8, see csrc/exchange.cu):
 
   * every replica owns a staging buffer [2 parities][world][n] float32 and maps its peers' buffers (CUDA IPC handles
     exchanged once over torch.distributed);

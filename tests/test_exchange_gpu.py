@@ -1,5 +1,5 @@
-"""Peer-to-peer gradient exchange (ppb_p2p_*, utils/exchange.py): the data-parallel step's replacement for the
-overlapped NCCL all-reduce. The sum kernel runs on one GPU; the exchange itself needs two (skipped otherwise — the
+"""Peer-to-peer gradient exchange (ppb_p2p_*, utils/exchange.py): the data-parallel step's alternative to the
+overlapped NCCL all-reduce (compile(exchange='p2p')). The sum kernel runs on one GPU; the exchange itself needs two (skipped otherwise — the
 driver-run bench covers it at N > 1 through train.dp_check)."""
 import ctypes
 import os
