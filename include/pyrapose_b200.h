@@ -146,6 +146,12 @@ PPB_API int ppb_bbox_transform_inv_f32(const float* anchors, const float* deltas
 /* ClipBoxes (PyraPose/layers/_misc.py:259-280): x to [0,width], y to [0,height]. boxes f32 [total_boxes,4]. */
 PPB_API int ppb_clip_boxes_f32(const float* boxes, float* out, long long total_boxes, float width, float height,
                                void* stream);
+/* UpsampleLike (PyraPose/layers/_misc.py:96-115 -> backend.resize_images(..., method='nearest'),
+ * backend/tf_backend.py:28-35): source f32 [batch, src_h, src_w, channels] -> out [batch, dst_h, dst_w, channels],
+ * out[y, x] = source[min(floor((y + 0.5) src_h / dst_h), src_h - 1), ...]. (Inside the engine the same resize is
+ * fused into the pyramid's add kernel; this is the stand-alone layer.) */
+PPB_API int ppb_upsample_like_f32(const float* source, float* out, int batch, int src_h, int src_w, int dst_h,
+                                  int dst_w, int channels, void* stream);
 
 /* ------------------------------------------------------------------ FilterDetections
  * Replaces FilterDetections.call / filter_detections (PyraPose/layers/filter_detections.py:21-118, 153-191).

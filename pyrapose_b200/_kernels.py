@@ -182,6 +182,19 @@ def clip_boxes(boxes, width, height):
     return out
 
 
+def upsample_like(source, dst_h, dst_w):
+    """UpsampleLike: nearest resize of an NHWC float32 tensor to (dst_h, dst_w)."""
+    source = _dev(source, torch.float32, "source")
+    if source.dim() != 4:
+        raise ValueError("expected source of shape (B, H, W, C), got %s" % (tuple(source.shape),))
+    B, ih, iw, C = (int(v) for v in source.shape)
+    out = torch.empty((B, int(dst_h), int(dst_w), C), dtype=torch.float32, device=source.device)
+    with torch.cuda.device(source.device):
+        nat.check(nat.load().ppb_upsample_like_f32(nat.ptr(source), nat.ptr(out), B, ih, iw, int(dst_h), int(dst_w), C,
+                                                   _stream()))
+    return out
+
+
 # --------------------------------------------------------------------------- filter
 _workspaces = {}
 

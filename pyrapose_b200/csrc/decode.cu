@@ -108,6 +108,25 @@ Vec16 load16(const float* p, float fill, int n) {
   return v;
 }
 
+// UpsampleLike (PyraPose/layers/_misc.py:96-115 -> tf.image.resize NEAREST, half-pixel centres): fp32 NHWC,
+// out[b, y, x, :] = in[b, min(floor((y + 0.5) * ih / oh), ih - 1), min(floor((x + 0.5) * iw / ow), iw - 1), :].
+// One thread per float4 of the output (C % 4 == 0) or per float; consecutive threads on consecutive channels.
+template <typename V>
+__global__ void __launch_bounds__(256) upsample_like_kernel(const V* __restrict__ in, V* __restrict__ out, int B, int ih,
+                                                            int iw, int oh, int ow, int cv) {
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long total = static_cast<long long>(B) * oh * ow * cv;
+  if (t >= total) return;
+  const int c = static_cast<int>(t % cv);
+  const long long pix = t / cv;
+  const int x = static_cast<int>(pix % ow), y = static_cast<int>((pix / ow) % oh), b = static_cast<int>(pix / (static_cast<long long>(ow) * oh));
+  int sy = static_cast<int>(floorf((static_cast<float>(y) + 0.5f) * (static_cast<float>(ih) / oh)));
+  int sx = static_cast<int>(floorf((static_cast<float>(x) + 0.5f) * (static_cast<float>(iw) / ow)));
+  sy = min(sy, ih - 1);
+  sx = min(sx, iw - 1);
+  out[t] = __ldg(in + ((static_cast<long long>(b) * ih + sy) * iw + sx) * cv + c);
+}
+
 }  // namespace
 }  // namespace ppb
 
@@ -167,6 +186,27 @@ int ppb_clip_boxes_f32(const float* boxes, float* out, long long total_boxes, fl
   PPB_REQUIRE(boxes != nullptr && out != nullptr, "ppb_clip_boxes_f32: null buffer");
   clip_boxes_kernel<<<static_cast<unsigned>((total_boxes + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const float4*>(boxes), reinterpret_cast<float4*>(out), total_boxes, width, height);
+  PPB_CUDA(cudaGetLastError());
+  count_launch();
+  return kOk;
+}
+
+int ppb_upsample_like_f32(const float* source, float* out, int batch, int src_h, int src_w, int dst_h, int dst_w,
+                          int channels, void* stream) {
+  PPB_REQUIRE(batch >= 0 && src_h > 0 && src_w > 0 && dst_h > 0 && dst_w > 0 && channels > 0,
+              "ppb_upsample_like_f32: bad shape");
+  if (batch == 0) return kOk;
+  PPB_REQUIRE(source != nullptr && out != nullptr, "ppb_upsample_like_f32: null buffer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool v4 = channels % 4 == 0 && (reinterpret_cast<uintptr_t>(source) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+  const int cv = v4 ? channels / 4 : channels;
+  const long long total = static_cast<long long>(batch) * dst_h * dst_w * cv;
+  const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
+  if (v4)
+    upsample_like_kernel<float4><<<blocks, 256, 0, st>>>(reinterpret_cast<const float4*>(source), reinterpret_cast<float4*>(out),
+                                                         batch, src_h, src_w, dst_h, dst_w, cv);
+  else
+    upsample_like_kernel<float><<<blocks, 256, 0, st>>>(source, out, batch, src_h, src_w, dst_h, dst_w, cv);
   PPB_CUDA(cudaGetLastError());
   count_launch();
   return kOk;

@@ -60,17 +60,12 @@ class Anchors(_Layer):
 
 class UpsampleLike(_Layer):
     """ Nearest-neighbour resize of `source` to the spatial size of `target` (_misc.py:96-115). On the hot path
-    this is fused into the PFPN add kernel; the layer form is an index gather on the tensor."""
+    this is fused into the PFPN add kernel; the layer form is its own kernel (ppb_upsample_like_f32)."""
 
     def call(self, inputs, **kwargs):
-        import torch
+        from .. import _kernels
         source, target = inputs
-        source = _cuda(source)
-        ih, iw = source.shape[1], source.shape[2]
-        oh, ow = target.shape[1], target.shape[2]
-        ys = torch.clamp(torch.floor((torch.arange(oh, device=source.device, dtype=torch.float32) + 0.5) * (ih / oh)).long(), max=ih - 1)
-        xs = torch.clamp(torch.floor((torch.arange(ow, device=source.device, dtype=torch.float32) + 0.5) * (iw / ow)).long(), max=iw - 1)
-        return source[:, ys][:, :, xs]
+        return _kernels.upsample_like(_cuda(source), int(target.shape[1]), int(target.shape[2]))
 
     def compute_output_shape(self, input_shape):
         return (input_shape[0][0],) + tuple(input_shape[1][1:3]) + (input_shape[0][-1],)
