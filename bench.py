@@ -661,8 +661,8 @@ def run_ours(args):
                          # ncu --set full capture (profiles/r01_full_heads_pair.txt, launch 0; B=32): 227.9 + 184.0 MB against
                          # 2 x 222k rows x 512 ch x 2 B = 455 MB of algorithmic input + output (the tail of the output
                          # is still in L2 when the kernel ends): no wasted re-reads
-                         "traffic": 411939840 if (B, H, W, C) == (32, 480, 640, 15) else None,
-                         "traffic_launch": "pyramid_regression3D_1 (CTA-pair + slab mode), profiles/r01_full_heads_pair.txt launch 0", "top_launch": top,
+                         "traffic": 411518976 if (B, H, W, C) == (32, 480, 640, 15) else None,
+                         "traffic_launch": "pyramid_regression3D_1 (CTA-pair + slab mode), dram read 228.2 MB + write 183.3 MB, profiles/r02_full_heads.txt launch 3", "top_launch": top,
                          "launches_per_step": n_conv, "conv_ms_per_step": conv_ms, "other_ms_per_step": other_ms,
                          "flops_per_image": flops_img, "peak_source": peak_src + " bf16_tflops (burst)",
                          "frac_of_burst": achieved / peak, "frac_of_sustained": achieved / peak_sus,

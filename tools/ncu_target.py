@@ -1,6 +1,6 @@
 """Short target for `ncu`: one CUDA-graph forward (78 conv launches) then one eager forward (78 more) at batch B.
 Conv launch order inside a forward: 0 conv1 | 1-52 ResNet bottlenecks | 53-55 laterals | 56 P4_mid 57 P3_mid
-58 P3_down 59 P3 60 P4_down 61 P4 62 P5 (see engine.cu build_plan) | 63-67 regression head | 68-72 cls head | 73-77 mask head.
+58 P3_down 59 P3 60 P4_down 61 P4 62 P5 (see engine.cu build_plan) | 63-67 cls head | 68-72 regression head | 73-77 mask head.
 Usage: python tools/ncu_target.py [B] [filter]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
