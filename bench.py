@@ -183,9 +183,14 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": ips, "unit": "images/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1000.0 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        # the same workload as our arm's line (each step here is a bounded sample of it: see cpu_baseline.sample)
         "config": {"workload": "PFPN ResNet-50 inference + 3D-box-corner decode + filter_detections (thr 0.05, NMS 0.5, "
-                               "max 300), 480x640, 15 classes",
-                   "note": "reference TF/Keras path unavailable on this box; this is the cited CPU restatement (oracle/)"},
+                               "max 300), batch %d per GPU, %dx%d, %d classes" % (args.batch, H, W, C),
+                   "global_batch": args.gpus * args.batch,
+                   "parallelism": "replicas x%d (no collective)" % args.gpus,
+                   "weights": "random-init (seed 1), he-normal heads, cls bias %.1f" % args.cls_bias,
+                   "note": "reference TF/Keras path unavailable on this box; this is the cited CPU restatement (oracle/) "
+                           "on rank 0's host cores"},
         "cpu_baseline": {"value": ips, "unit": "images/s", "cores": threads, "kind": "port",
                          "sample": "%d images per step, %d per oracle call (the faster of batch 1: %.2f and batch 4: %.2f "
                                    "images/s on this host; a bounded sample of the batch-32 step), forward+decode+filter, "
