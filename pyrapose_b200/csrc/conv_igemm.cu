@@ -557,6 +557,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   // zero-filled, its TMA stores clipped, and row_info() marks every row as outside the buffer.
   const int it_end = pair ? ((p.n_mtiles + 1) >> 1) * p.n_ntiles : total_tiles;
   auto tile_of = [&](int it) {
+    if (p.reverse) it = it_end - 1 - it;
     if (!pair) return it;
     const int mp = static_cast<int>(fastdiv(static_cast<uint32_t>(it), p.nt_mul, p.nt_sh));
     return ((mp << 1) + static_cast<int>(rank)) * p.n_ntiles + (it - mp * p.n_ntiles);
@@ -619,13 +620,21 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               tma_load_2d(sa, &tmap_a, 0, a_row, &full_bar[stage]);
             } else if (bres) {
               mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-              tma_load_2d(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage]);
+              if (p.l2_hint) tma_load_2d_hint(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage], kEvictFirst);
+              else tma_load_2d(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage]);
             } else {
               mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-              tma_load_2d(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage]);
-              for (int j = 0; j < taps_per_stage; ++j)
-                tma_load_2d(sa + a_bytes + j * b_tile_bytes, &tmap_b,
-                            p.b_col_base + ((tap + j) * p.cin_blocks + kb) * kConvBlockK, tc.n0, &full_bar[stage]);
+              if (p.l2_hint) tma_load_2d_hint(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage], kEvictFirst);
+              else tma_load_2d(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage]);
+              for (int j = 0; j < taps_per_stage; ++j) {
+                if (p.l2_hint)
+                  tma_load_2d_hint(sa + a_bytes + j * b_tile_bytes, &tmap_b,
+                                   p.b_col_base + ((tap + j) * p.cin_blocks + kb) * kConvBlockK, tc.n0, &full_bar[stage],
+                                   kEvictLast);
+                else
+                  tma_load_2d(sa + a_bytes + j * b_tile_bytes, &tmap_b,
+                              p.b_col_base + ((tap + j) * p.cin_blocks + kb) * kConvBlockK, tc.n0, &full_bar[stage]);
+              }
             }
             tr(kTrProducer, 2, tseq, kseq++);
             if (++stage == n_stages) {
@@ -714,7 +723,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           mbar_wait(&slot_empty_bar[s], ph ^ 1u, kFaultSlotEmpty);
           tr(kTrResidual, 7, tseq, c);
           mbar_arrive_expect_tx(&slot_full_bar[s], kChunkBytes);
-          tma_load_2d(ring + s * kChunkBytes, &tmap_res, tc.n0 + c * 64, tc.row0, &slot_full_bar[s]);
+          if (p.l2_hint) tma_load_2d_hint(ring + s * kChunkBytes, &tmap_res, tc.n0 + c * 64, tc.row0, &slot_full_bar[s], kEvictFirst);
+          else tma_load_2d(ring + s * kChunkBytes, &tmap_res, tc.n0 + c * 64, tc.row0, &slot_full_bar[s]);
           tr(kTrResidual, 8, tseq, c);
           if (++s == static_cast<uint32_t>(R)) {
             s = 0;

@@ -89,6 +89,10 @@ struct ConvParams {
   int a_cb;         // channel blocks per segment (C / 64)
   int a_seg[6];     // which activation part each segment reads
   int out_part_off, res_part_off;
+  int reverse;      // walk the tiles from the last to the first (engine: every other layer, PPB_SNAKE=1), so a layer
+                    // starts on the rows its producer wrote last, which are the ones still in L2
+  int l2_hint;      // activation / residual loads carry the evict-first L2 policy (read once, dead afterwards), weight
+                    // loads evict-last (PPB_L2HINT=1)
   unsigned nt_mul, nt_sh;  // division by n_ntiles (conv_fastdiv), filled by conv_launch
   int epi_groups;   // epilogue warp groups (2 or 3)     }
   int early_free;   // staged + residual: a ring slot is handed back as soon as ITS store has read it, not when the  }
