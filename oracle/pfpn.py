@@ -9,6 +9,8 @@ reference has no tests; this follows the model-building code line by line instea
   PFPN     : /root/reference/PyraPose/models/retinanet.py:180-214  (__create_sparceFPN)
   heads    : retinanet.py:9-54 (cls), 57-98 (mask), 101-131 (3D regression); pyramid concat :224-225
   inference: retinanet.py:302-335 (retinanet_bbox): Anchors + RegressBoxes3D
+The backbone restatement is cross-checked against an unrelated public implementation of the same Caffe ResNet-50
+(HuggingFace transformers ResNet, downsample_in_bottleneck=True, same weights): tests/test_oracle_resnet_crosscheck.py.
 Weights come in as a dict keyed "<keras layer name>/<param>" with HWIO kernels (pyrapose_b200.models.spec
 names); this file never creates weights.
 """
