@@ -24,10 +24,17 @@ from . import decode as odecode
 BN_EPS = 1e-5  # keras-resnet BatchNormalization(epsilon=1e-5)
 
 
+# Where the oracle's torch ops run. None = CPU (the default, and the only mode of the CPU test suite). A GPU test may
+# set it to a CUDA device to execute THE SAME fp32 graph through torch's library convolutions (TF32 off) at sizes the
+# CPU cannot afford — BASELINE config 2 at its full batch of 32 (tests/test_engine_gpu.py); still test infrastructure.
+DEVICE = [None]
+
+
 def _t(a):
     if isinstance(a, torch.Tensor):  # oracle/train.py passes leaf tensors so that autograd supplies gradients
         return a
-    return torch.from_numpy(np.ascontiguousarray(a))
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    return t.to(DEVICE[0]) if DEVICE[0] is not None else t
 
 
 # Rounding hook applied wherever the native engine stores an activation as bf16. Identity for the fp32 oracle;
@@ -96,8 +103,8 @@ def upsample_like(src, target):
     src index = min(floor((dst + 0.5) * in / out), in - 1)."""
     ih, iw = src.shape[2], src.shape[3]
     oh, ow = target.shape[2], target.shape[3]
-    ys = torch.clamp(torch.floor((torch.arange(oh, dtype=torch.float32) + 0.5) * (ih / oh)).long(), max=ih - 1)
-    xs = torch.clamp(torch.floor((torch.arange(ow, dtype=torch.float32) + 0.5) * (iw / ow)).long(), max=iw - 1)
+    ys = torch.clamp(torch.floor((torch.arange(oh, dtype=torch.float32) + 0.5) * (ih / oh)).long(), max=ih - 1).to(src.device)
+    xs = torch.clamp(torch.floor((torch.arange(ow, dtype=torch.float32) + 0.5) * (iw / ow)).long(), max=iw - 1).to(src.device)
     return src[:, :, ys][:, :, :, xs]
 
 
@@ -192,7 +199,7 @@ def forward_training(images_nhwc, w, num_classes, taps=None, num_threads=None):
         cls = torch.cat([classification_head(f, w, num_classes) for f in feats], dim=1)
         msk = mask_head(feats[0], w, num_classes)                                           # :296-297
         shapes = [(int(f.shape[2]), int(f.shape[3])) for f in feats]
-    return reg.numpy(), cls.numpy(), msk.numpy(), shapes
+    return reg.cpu().numpy(), cls.cpu().numpy(), msk.cpu().numpy(), shapes
 
 
 def forward_inference(images_nhwc, w, num_classes, anchor_params=None, taps=None, num_threads=None):
@@ -205,4 +212,4 @@ def forward_inference(images_nhwc, w, num_classes, anchor_params=None, taps=None
 
 
 def taps_to_nhwc(taps):
-    return {k: v.permute(0, 2, 3, 1).contiguous().numpy() for k, v in taps.items()}
+    return {k: v.permute(0, 2, 3, 1).contiguous().cpu().numpy() for k, v in taps.items()}

@@ -261,3 +261,43 @@ def test_production_arena_gives_identical_outputs_with_less_memory(cuda_device):
         assert np.array_equal(x, y)
     with pytest.raises(RuntimeError):
         e1.train_bind(1)
+
+
+def test_full_batch32_against_the_oracle_graph_run_by_cudnn(cuda_device):
+    """BASELINE config 2 at its real size — batch 32, 480x640, 15 classes — directly against the oracle: the SAME fp32
+    graph of oracle/pfpn.py, executed by torch's library convolutions on this GPU (TF32 off) because the CPU cannot
+    afford 32 images. First the device-executed oracle is tied to the CPU-executed one on image 0 (<= 1e-4), then
+    every image of the batch is compared with it at the bf16 tolerances of test_engine_matches_oracle."""
+    import torch
+    from oracle import pfpn
+    from pyrapose_b200 import models
+    from pyrapose_b200.models import spec
+    B, H, W, C = 32, 480, 640, 15
+    weights = spec.init_weights(C, seed=1, head_init="spread", randomize_bn=True)
+    train = models.backbone("resnet50").retinanet(C)
+    train.set_weights_dict(weights)
+    infer = models.convert_model(train, alias_arena=True)
+    img = make_images(1, B, H, W)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    cpu_b3, cpu_cls, cpu_mask = pfpn.forward_inference(img[:1], weights, C)
+    pfpn.DEVICE[0] = cuda_device
+    try:
+        refs = [pfpn.forward_inference(img[i:i + 8], weights, C) for i in range(0, B, 8)]
+    finally:
+        pfpn.DEVICE[0] = None
+    ref = [np.concatenate([r[k] for r in refs], axis=0) for k in range(3)]
+    for name, a, b in (("boxes3D", ref[0][:1], cpu_b3), ("cls", ref[1][:1], cpu_cls), ("mask", ref[2][:1], cpu_mask)):
+        assert rel_l2(a, b) <= 1e-4, ("the GPU-executed oracle left the CPU-executed one", name, rel_l2(a, b))
+    got = infer.predict_on_batch(img)
+    worst = {}
+    for i in range(B):
+        for name, g, r in zip(("boxes3D", "cls", "mask"), got, ref):
+            worst[name] = max(worst.get(name, 0.0), rel_l2(g[i], r[i]))
+    print("batch 32 vs the oracle graph on cuDNN, worst image: %s" % {k: "%.2e" % v for k, v in worst.items()})
+    assert worst["boxes3D"] < 1e-2 and worst["cls"] < 2e-2 and worst["mask"] < 2e-2
+    d = np.abs(got[1] - ref[1])
+    assert d.max() < 5e-2 and np.quantile(d[::7].ravel(), 0.999) < 2e-2
+    thr = 0.5
+    safe = np.abs(ref[1] - thr) > thr * 0.1
+    assert np.array_equal((got[1] > thr)[safe], (ref[1] > thr)[safe])
