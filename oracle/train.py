@@ -18,6 +18,11 @@ from . import pfpn
 L2_REG = 0.001
 
 
+def _dev(t):
+    """pfpn.DEVICE: None = CPU; a GPU test may run the same autograd graph through torch's library kernels."""
+    return t.to(pfpn.DEVICE[0]) if pfpn.DEVICE[0] is not None else t
+
+
 class _RoundBF16(torch.autograd.Function):
     """bf16 round-to-nearest-even of an activation; the gradient map coming back is rounded the same way (the native
     engine stores both as bf16)."""
@@ -109,7 +114,7 @@ def is_trainable(key):
 
 
 def forward_losses(images_nhwc, weights_t, targets, num_classes, emulate_bf16=False, pinned=None):
-    x = torch.from_numpy(np.ascontiguousarray(images_nhwc, dtype=np.float32)).permute(0, 3, 1, 2).contiguous()
+    x = _dev(torch.from_numpy(np.ascontiguousarray(images_nhwc, dtype=np.float32))).permute(0, 3, 1, 2).contiguous()
     net_w = weights_t
     saved = list(pfpn._Q)
     if emulate_bf16 or pinned is not None:
@@ -118,7 +123,7 @@ def forward_losses(images_nhwc, weights_t, targets, num_classes, emulate_bf16=Fa
         pfpn._Q[0] = lambda t, name: _RoundBF16.apply(t)
     if pinned is not None:
         def pin(name):
-            return torch.from_numpy(np.ascontiguousarray(pinned[name])).permute(0, 3, 1, 2).contiguous()
+            return _dev(torch.from_numpy(np.ascontiguousarray(pinned[name]))).permute(0, 3, 1, 2).contiguous()
         relu_names = set(n for n in pinned if n.endswith("_relu") or "_tower_t" in n)
         # ReLU points go to _PinRelu (pfpn._qrelu hands over the PRE-activation when _Q[1] is None), the rest to
         # _PinLinear
@@ -132,7 +137,7 @@ def forward_losses(images_nhwc, weights_t, targets, num_classes, emulate_bf16=Fa
         msk = pfpn.mask_head(feats[0], net_w, num_classes, 0)
     finally:
         pfpn._Q[0], pfpn._Q[1] = saved
-    y_reg, y_cls, y_mask = [torch.from_numpy(np.ascontiguousarray(t, dtype=np.float32)) for t in targets]
+    y_reg, y_cls, y_mask = [_dev(torch.from_numpy(np.ascontiguousarray(t, dtype=np.float32))) for t in targets]
     l_reg = olosses.orthogonal_l1(y_reg, reg)
     l_cls = olosses.focal(y_cls, cls)
     l_mask = olosses.focal(y_mask, msk)
@@ -154,7 +159,7 @@ def step(images_nhwc, weights, targets, num_classes, lr=1e-5, clipnorm=0.001, be
         torch.set_num_threads(num_threads)
     wt = {}
     for k, v in weights.items():
-        t = torch.from_numpy(np.ascontiguousarray(v, dtype=np.float32)).clone()
+        t = _dev(torch.from_numpy(np.ascontiguousarray(v, dtype=np.float32)).clone())
         if is_trainable(k):
             t.requires_grad_(True)
         wt[k] = t
@@ -171,12 +176,12 @@ def step(images_nhwc, weights, targets, num_classes, lr=1e-5, clipnorm=0.001, be
         g = grads[k] * scale
         m = (1.0 - beta_1) * g
         v = (1.0 - beta_2) * g * g
-        new_w[k] = (wt[k].detach() - lr_t * m / (torch.sqrt(v) + eps)).numpy()
+        new_w[k] = (wt[k].detach() - lr_t * m / (torch.sqrt(v) + eps)).cpu().numpy()
     return {
         "losses": {"3Dbox": l_reg.item(), "cls": l_cls.item(), "mask": l_mask.item(), "l2": l2.item(),
                    "total": total.item()},
-        "grads": {k: g.numpy() for k, g in grads.items()},
+        "grads": {k: g.cpu().numpy() for k, g in grads.items()},
         "grad_norm": norm,
         "weights": new_w,
-        "outputs": [o.detach().numpy() for o in outs],
+        "outputs": [o.detach().cpu().numpy() for o in outs],
     }
