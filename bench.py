@@ -127,6 +127,20 @@ class ClockSampler(object):
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def _build_info():
+    """Which build of libpyrapose_b200.so ran: source digest, compiler, flags (pyrapose_b200/_lib/build_info.json)."""
+    try:
+        from pyrapose_b200 import build as native_build
+        info = native_build.build_info()
+        if info is None:
+            return None
+        return {"sources_sha256": info["sources_sha256"][:16], "lib_sha256": info["lib_sha256"][:16],
+                "lib_unchanged_since_build": info["lib_sha256"] == info["lib_sha256_now"], "nvcc": info["nvcc"],
+                "arch_flags": info["arch_flags"], "built_utc": info["built_utc"], "translation_units": len(info["sources"])}
+    except Exception as e:
+        return {"error": repr(e)}
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -657,6 +671,7 @@ def run_ours(args):
                        "l2": "working set per step (activations ~%.1f GB) far exceeds the 126 MB L2; no flush needed"
                              % (eng.device_bytes() / 1e9)},
             "e2e": e2e,
+            "build": _build_info(),
             "sustained": sustained,
             "gpu_launches": int(launches),
             "clocks": clocks,

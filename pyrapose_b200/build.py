@@ -91,7 +91,27 @@ def build(force=False, verbose=False):
         raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))
     with open(stamp, "w") as f:
         f.write(digest)
+    # what was built, from what, with which compiler: travels with the .so (bench.py prints it as `build`)
+    import json
+    import time
+    ver = subprocess.run(["nvcc", "--version"], capture_output=True, text=True).stdout.strip().splitlines()
+    with open(os.path.join(LIBDIR, "build_info.json"), "w") as f:
+        json.dump({"sources_sha256": digest, "sources": [s for s, _ in sources], "nvcc": ver[-2:] if ver else None,
+                   "arch_flags": ARCH, "flags": COMMON, "exact_flags": ["-fmad=false"],
+                   "built_utc": time.strftime("%Y-%m-%dT%H:%M:%SZ", time.gmtime()),
+                   "lib_sha256": _digest([lib_path()])}, f, indent=1)
     return lib_path()
+
+
+def build_info():
+    """The record build() left beside the library (None when the library was not built by it)."""
+    import json
+    p = os.path.join(LIBDIR, "build_info.json")
+    if not os.path.exists(p):
+        return None
+    info = json.load(open(p))
+    info["lib_sha256_now"] = _digest([lib_path()]) if os.path.exists(lib_path()) else None
+    return info
 
 
 if __name__ == "__main__":
