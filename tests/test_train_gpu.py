@@ -238,3 +238,31 @@ def test_prediction_model_follows_training(cuda_device, tmp_path):
     assert np.array_equal(pred.predict_on_batch(img)[1], before[1])
     new = train.get_weights_dict()
     assert all(np.array_equal(new[k], weights[k]) for k in weights)
+
+
+def test_separate_engines_follow_training_too(cuda_device):
+    """Prediction models that do NOT share the training engine — the production arena (alias_arena=True) and the fp32
+    path — are refilled from the trained master weights when the model has stepped since they were loaded."""
+    from pyrapose_b200 import models, optimizers
+    from pyrapose_b200.models import spec
+    from pyrapose_b200.utils.anchors import anchor_targets_bbox, anchors_for_shape
+    weights = spec.init_weights(C, seed=9, head_init="spread", randomize_bn=True)
+    rng = np.random.default_rng(18)
+    img = rng.integers(0, 256, (B, H, W, 3)).astype(np.float32) - np.array([103.939, 116.779, 123.68], np.float32)
+    y = _targets(anchors_for_shape, anchor_targets_bbox)
+    train = models.backbone("resnet50").retinanet(num_classes=C)
+    train.set_weights_dict({k: v.copy() for k, v in weights.items()})
+    shared = models.convert_model(train)
+    prod = models.convert_model(train, alias_arena=True)
+    fp32 = models.convert_model(train, precision='fp32')
+    b_prod, b_fp32 = prod.predict_on_batch(img)[1].copy(), fp32.predict_on_batch(img)[1].copy()
+    train.compile(optimizer=optimizers.Adam(lr=1e-2, clipnorm=0.001))
+    for _ in range(2):
+        train.train_on_batch(img, y)
+    ref = shared.predict_on_batch(img)[1].copy()          # the engine the step updates in place
+    a_prod, a_fp32 = prod.predict_on_batch(img)[1], fp32.predict_on_batch(img)[1]
+    assert np.abs(a_prod - b_prod).max() > 1e-3 and np.abs(a_fp32 - b_fp32).max() > 1e-3
+    assert np.array_equal(a_prod, ref)                     # same bf16 weights, same kernels, other buffers
+    assert np.abs(a_fp32 - ref).max() < 5e-2               # fp32 path on the fp32 master weights vs the bf16 path
+    train.train_on_batch(img, y)                           # and again after a further step
+    assert np.array_equal(prod.predict_on_batch(img)[1], shared.predict_on_batch(img)[1])
