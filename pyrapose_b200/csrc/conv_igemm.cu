@@ -213,7 +213,10 @@ __device__ __forceinline__ void staged_chunk_row_masked(const ConvParams& p, con
 }
 
 // bf16 epilogue for NC (16 or 32) accumulator columns of one row, straight to global memory.
-template <int NC>
+// kExtra = false compiles the fp32-path parts and the fused second output out: the production path's epilogue is
+// bound by its own instruction stream, and the (uniform) tests for those options alone cost the direct-epilogue layers
+// 3-7 % (stage 4-5 branch2b / branch2a, the laterals) when they sat in the one copy.
+template <int NC, bool kExtra>
 __device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __restrict__ sbias, const RowInfo& ri, int m,
                                          int n0, uint32_t (&v)[NC], long long row2 = 0) {
   if (!ri.in_buf || n0 >= p.n_valid) return;
@@ -222,11 +225,11 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __res
     const uint4 z = make_uint4(0, 0, 0, 0);
 #pragma unroll
     for (int i = 0; i < NC / 8; ++i) reinterpret_cast<uint4*>(dst)[i] = z;
-    if (p.out2 != nullptr) {
+    if (kExtra && p.out2 != nullptr) {
 #pragma unroll
       for (int i = 0; i < NC / 8; ++i) reinterpret_cast<uint4*>(p.out2 + static_cast<size_t>(m) * p.out2_ld + n0)[i] = z;
     }
-    if (p.split) {
+    if (kExtra && p.split) {
       for (int part = 1; part < p.parts; ++part)
 #pragma unroll
         for (int i = 0; i < NC / 8; ++i) reinterpret_cast<uint4*>(dst + part * p.out_part_off)[i] = z;
@@ -257,7 +260,7 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __res
       f[i * 8 + 7] += bf16_hi(r.w);
     }
   }
-  if (p.split) {  // fp32 path: the residual's remaining parts, then the parts of the result
+  if (kExtra && p.split) {  // fp32 path: the residual's remaining parts, then the parts of the result
     if (p.residual != nullptr) {
       for (int part = 1; part < p.parts; ++part) {
         const uint4* rp = reinterpret_cast<const uint4*>(p.residual + static_cast<size_t>(m) * p.res_ld +
@@ -320,9 +323,9 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __res
       if (!(bf16_hi(r.w) > 0.0f)) f[i * 8 + 7] = 0.0f;
     }
   }
-  const uint4* r2p = p.out2 != nullptr
-                         ? reinterpret_cast<const uint4*>(p.res2 + static_cast<size_t>(row2) * p.res2_ld + n0) : nullptr;
-  uint4* d2p = p.out2 != nullptr ? reinterpret_cast<uint4*>(p.out2 + static_cast<size_t>(m) * p.out2_ld + n0) : nullptr;
+  const bool two = kExtra && p.out2 != nullptr;
+  const uint4* r2p = two ? reinterpret_cast<const uint4*>(p.res2 + static_cast<size_t>(row2) * p.res2_ld + n0) : nullptr;
+  uint4* d2p = two ? reinterpret_cast<uint4*>(p.out2 + static_cast<size_t>(m) * p.out2_ld + n0) : nullptr;
 #pragma unroll
   for (int i = 0; i < NC / 8; ++i) {
     uint4 o;
@@ -331,7 +334,7 @@ __device__ __forceinline__ void epi_bf16(const ConvParams& p, const float* __res
     o.z = pack_bf16x2(f[i * 8 + 4], f[i * 8 + 5]);
     o.w = pack_bf16x2(f[i * 8 + 6], f[i * 8 + 7]);
     reinterpret_cast<uint4*>(dst)[i] = o;
-    if (p.out2 != nullptr) {  // fused Add: the ROUNDED output + the second operand, rounded once more
+    if (two) {  // fused Add: the ROUNDED output + the second operand, rounded once more
       const uint4 r = __ldg(r2p + i);
       uint4 o2;
       o2.x = pack_bf16x2(bf16_lo(o.x) + bf16_lo(r.x), bf16_hi(o.x) + bf16_hi(r.x));
@@ -359,6 +362,7 @@ __device__ __forceinline__ long long fused_add_row(const ConvParams& p, const Co
 // decoding): bias, then sigmoid or box3D_transform_inv, into the fp32 staging tile `srow` (this row's [vals] slice).
 // The tile is written out afterwards in Keras' Reshape((-1, 16)) / Reshape((-1, C)) + Concatenate(axis=1) order
 // (retinanet.py:51, 129, 224-225), i.e. element (b, loc, n) at ((b*locs + loc)*vals + n).
+template <bool kExtra>
 __device__ __forceinline__ void epi_head16(const ConvParams& p, const float* __restrict__ sbias, int seg_idx,
                                            const RowInfo& ri, size_t loc, int n0, int tile_n0, const uint32_t* v,
                                            float* __restrict__ srow) {
@@ -375,9 +379,14 @@ __device__ __forceinline__ void epi_head16(const ConvParams& p, const float* __r
   if (p.epi == kEpiHeadSigmoid) {
     // ex2 + rcp on the SFU (relative error ~1e-6, far inside the 1e-2 score tolerance of the bf16 path): the
     // IEEE expf + division pair was a third of this epilogue's instructions with two warps per scheduler to hide them
+    if (kExtra && p.split) {  // fp32 path: IEEE forms. A separate uniform branch: as one select the compiler evaluated BOTH forms
+                    // for every score and the bf16 path's output convolution went from 0.112 to 0.137 ms
 #pragma unroll
-    for (int j = 0; j < 16; ++j)
-      f[j] = p.split ? 1.0f / (1.0f + expf(-f[j])) : __fdividef(1.0f, 1.0f + __expf(-f[j]));  // fp32 path: IEEE forms
+      for (int j = 0; j < 16; ++j) f[j] = 1.0f / (1.0f + expf(-f[j]));
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) f[j] = __fdividef(1.0f, 1.0f + __expf(-f[j]));
+    }
   } else if (p.epi == kEpiHeadDecode) {
     // box3D_transform_inv (PyraPose/backend/common.py:25-56) against the Anchors layer's boxes
     // (PyraPose/layers/_misc.py:52-69, backend/common.py:93-116): fp32 base anchor + fp32 shift.
@@ -433,7 +442,11 @@ __device__ __forceinline__ void add_side(uint32_t taddr_side, uint32_t (&v)[NC])
 // barrier passed), 13 = TMA store issued, 14 = accumulator released.
 enum TraceRole : int { kTrProducer = 0, kTrMma = 1, kTrResidual = 2, kTrEpilogue = 3 };
 
-template <bool kPair, int kGroups, bool kTrace = false>
+// kExtra: the instantiations that carry the fp32 path (ConvParams::split), the fused second output (out2), the L2
+// hints and the reversed tile walk. The production kernels are compiled without them: with everything in one copy the
+// kernel had grown from 4900 to 8200 instructions (130 KB of SASS) and the layers with the unrolled direct epilogue
+// (stage 4-5 branch2b, the pyramid's 3x3) ran 4-14 % slower than the same layers in r01.
+template <bool kPair, int kGroups, bool kTrace = false, bool kExtra = false>
 __global__ void __launch_bounds__((kCtrlWarps + 4 * kGroups) * 32, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
@@ -557,7 +570,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   // zero-filled, its TMA stores clipped, and row_info() marks every row as outside the buffer.
   const int it_end = pair ? ((p.n_mtiles + 1) >> 1) * p.n_ntiles : total_tiles;
   auto tile_of = [&](int it) {
-    if (p.reverse) it = it_end - 1 - it;
+    if (kExtra && p.reverse) it = it_end - 1 - it;
     if (!pair) return it;
     const int mp = static_cast<int>(fastdiv(static_cast<uint32_t>(it), p.nt_mul, p.nt_sh));
     return ((mp << 1) + static_cast<int>(rank)) * p.n_ntiles + (it - mp * p.n_ntiles);
@@ -593,7 +606,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
       // fp32-path layers: K-loop segment -> activation part (ConvParams::split)
       auto a_col = [&](int kb) {
-        if (p.split == 0) return kb * kConvBlockK;
+        if (!kExtra || p.split == 0) return kb * kConvBlockK;
         const int sgm = kb / p.a_cb;
         return (p.a_seg[sgm] * p.a_cb + kb - sgm * p.a_cb) * kConvBlockK;
       };
@@ -620,14 +633,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               tma_load_2d(sa, &tmap_a, 0, a_row, &full_bar[stage]);
             } else if (bres) {
               mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-              if (p.l2_hint) tma_load_2d_hint(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage], kEvictFirst);
+              if (kExtra && p.l2_hint) tma_load_2d_hint(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage], kEvictFirst);
               else tma_load_2d(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage]);
             } else {
               mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-              if (p.l2_hint) tma_load_2d_hint(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage], kEvictFirst);
+              if (kExtra && p.l2_hint) tma_load_2d_hint(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage], kEvictFirst);
               else tma_load_2d(sa, &tmap_a, a_col(kb), a_row, &full_bar[stage]);
               for (int j = 0; j < taps_per_stage; ++j) {
-                if (p.l2_hint)
+                if (kExtra && p.l2_hint)
                   tma_load_2d_hint(sa + a_bytes + j * b_tile_bytes, &tmap_b,
                                    p.b_col_base + ((tap + j) * p.cin_blocks + kb) * kConvBlockK, tc.n0, &full_bar[stage],
                                    kEvictLast);
@@ -662,7 +675,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kAccCols;
         int res_tap = 0, res_kb = 0;  // bres: (first tap, channel block) of k-iteration ki, in the producer's order
-        bool started[2] = {false, false};  // fp32 path: main / side accumulator already written in this tile
+        bool started_main = false, started_side = false;  // fp32 path: accumulator already written in this tile (two
+                                                          // scalars: indexed as an array they lived in local memory)
         for (int ki = 0; ki < k_iters; ++ki) {
           mbar_wait(&full_bar[stage], phase, kFaultFull);
           tr(kTrMma, 4, tseq, ki);
@@ -680,15 +694,19 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const uint32_t a_tap = a_addr + (p.slab3 == 0 ? 0u : (p.slab3 > 0 ? j : 2 - j) * 128u);
             const uint32_t b_tap = bres ? smem_u32(b_res) + ((res_tap + j) * p.cin_blocks + res_kb) * b_tile_bytes
                                         : b_addr + j * b_tile_bytes;
-            const int side = (p.split != 0 && res_kb >= p.a_cb) ? 1 : 0;  // segments 1.. -> the side accumulator
-            const uint32_t d_acc = d_tmem + side * kSideCol;
+            const bool side = kExtra && p.split != 0 && res_kb >= p.a_cb;  // segments 1.. -> the side accumulator
+            const uint32_t d_acc = side ? d_tmem + kSideCol : d_tmem;
+            const bool cont = (kExtra && p.split != 0) ? (side ? started_side : started_main) : ki != 0;
 #pragma unroll
             for (int k = 0; k < kConvBlockK / 16; ++k) {
-              const uint32_t accum = p.split != 0 ? ((started[side] || (j | k) != 0) ? 1u : 0u) : ((ki | j | k) != 0 ? 1u : 0u);
+              const uint32_t accum = (cont || (j | k) != 0) ? 1u : 0u;
               if (pair) tc_mma_bf16_2cta(d_acc, umma_desc_k128(a_tap + k * 32), umma_desc_k128(b_tap + k * 32), idesc, accum);
               else tc_mma_bf16(d_acc, umma_desc_k128(a_tap + k * 32), umma_desc_k128(b_tap + k * 32), idesc, accum);
             }
-            if (j == taps_per_stage - 1) started[side] = true;
+            if (j == taps_per_stage - 1) {
+              if (side) started_side = true;
+              else started_main = true;
+            }
           }
           if (pair) tc_commit2(&empty_bar[stage]);  // frees this stage in both CTAs
           else tc_commit(&empty_bar[stage]);
@@ -723,7 +741,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           mbar_wait(&slot_empty_bar[s], ph ^ 1u, kFaultSlotEmpty);
           tr(kTrResidual, 7, tseq, c);
           mbar_arrive_expect_tx(&slot_full_bar[s], kChunkBytes);
-          if (p.l2_hint) tma_load_2d_hint(ring + s * kChunkBytes, &tmap_res, tc.n0 + c * 64, tc.row0, &slot_full_bar[s], kEvictFirst);
+          if (kExtra && p.l2_hint) tma_load_2d_hint(ring + s * kChunkBytes, &tmap_res, tc.n0 + c * 64, tc.row0, &slot_full_bar[s], kEvictFirst);
           else tma_load_2d(ring + s * kChunkBytes, &tmap_res, tc.n0 + c * 64, tc.row0, &slot_full_bar[s]);
           tr(kTrResidual, 8, tseq, c);
           if (++s == static_cast<uint32_t>(R)) {
@@ -816,7 +834,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         if (tr_lead) tr(kTrEpilogue + g, 14, tseq, 0);
       } else if (p.epi == kEpiBf16) {
         // ---- direct bf16 epilogue: 32-column pieces alternate between the two groups
-        const long long row2 = p.out2 != nullptr ? fused_add_row(p, sg, ri, m) : 0;
+        const bool extra = kExtra && (p.split != 0 || p.out2 != nullptr);  // fp32 path / fused Add: the generic copy
+        const long long row2 = (kExtra && p.out2 != nullptr) ? fused_add_row(p, sg, ri, m) : 0;
         int piece = 0;
         for (int c0 = 0; c0 < p.block_n; c0 += 32, ++piece) {
           if (piece % kGroups != g) continue;
@@ -824,14 +843,22 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             uint32_t v[32];
             tmem_ld_32x32(taddr + c0, v);
             tmem_ld_wait();
-            if (p.split) add_side<32>(taddr + kSideCol + c0, v);
-            epi_bf16<32>(p, sbias, ri, m, tc.n0 + c0, v, row2);
+            if (!extra) {
+              epi_bf16<32, false>(p, sbias, ri, m, tc.n0 + c0, v);
+            } else if constexpr (kExtra) {
+              if (p.split) add_side<32>(taddr + kSideCol + c0, v);
+              epi_bf16<32, true>(p, sbias, ri, m, tc.n0 + c0, v, row2);
+            }
           } else {
             uint32_t v[16];
             tmem_ld_32x16(taddr + c0, v);
             tmem_ld_wait();
-            if (p.split) add_side<16>(taddr + kSideCol + c0, v);
-            epi_bf16<16>(p, sbias, ri, m, tc.n0 + c0, v, row2);
+            if (!extra) {
+              epi_bf16<16, false>(p, sbias, ri, m, tc.n0 + c0, v);
+            } else if constexpr (kExtra) {
+              if (p.split) add_side<16>(taddr + kSideCol + c0, v);
+              epi_bf16<16, true>(p, sbias, ri, m, tc.n0 + c0, v, row2);
+            }
           }
         }
         tc_fence_before();
@@ -851,15 +878,19 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             uint32_t v[32];
             tmem_ld_32x32(taddr + c0, v);
             tmem_ld_wait();
-            if (p.split) add_side<32>(taddr + kSideCol + c0, v);
-            epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0, tc.n0, v, srow);
-            epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0 + 16, tc.n0, v + 16, srow);
+            if constexpr (kExtra) {
+              if (p.split) add_side<32>(taddr + kSideCol + c0, v);
+            }
+            epi_head16<kExtra>(p, sbias, tc.seg, ri, loc, tc.n0 + c0, tc.n0, v, srow);
+            epi_head16<kExtra>(p, sbias, tc.seg, ri, loc, tc.n0 + c0 + 16, tc.n0, v + 16, srow);
           } else {
             uint32_t v[16];
             tmem_ld_32x16(taddr + c0, v);
             tmem_ld_wait();
-            if (p.split) add_side<16>(taddr + kSideCol + c0, v);
-            epi_head16(p, sbias, tc.seg, ri, loc, tc.n0 + c0, tc.n0, v, srow);
+            if constexpr (kExtra) {
+              if (p.split) add_side<16>(taddr + kSideCol + c0, v);
+            }
+            epi_head16<kExtra>(p, sbias, tc.seg, ri, loc, tc.n0 + c0, tc.n0, v, srow);
           }
         }
         tc_fence_before();
@@ -1041,7 +1072,8 @@ int conv_plan_smem(ConvParams& p) {
     const char* e = getenv("PPB_EPI_GROUPS");  // 2: never three groups; 3: default rule
     return e != nullptr ? atoi(e) : 3;
   }();
-  p.epi_groups = (groups_env >= 3 && p.epi == kEpiBf16 && p.staged && p.residual != nullptr && k_iters <= 8 && !p.pair)
+  p.epi_groups = (groups_env >= 3 && p.epi == kEpiBf16 && p.staged && p.residual != nullptr && k_iters <= 8 && !p.pair &&
+                  p.reverse == 0 && p.l2_hint == 0)  // the experiment switches live in the two-group kExtra kernels
                      ? 3 : 2;
   // (Three groups on every resident-weight layer, residual or not: res2*_branch2b 0.066 -> 0.079 ms. Not that either.)
   static const int early_env = [] {
@@ -1110,6 +1142,10 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
       attr_err = cudaFuncSetAttribute(conv_igemm_kernel<true, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     if (attr_err == cudaSuccess)
       attr_err = cudaFuncSetAttribute(conv_igemm_kernel<false, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(conv_igemm_kernel<false, 2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(conv_igemm_kernel<true, 2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     if (attr_err != cudaSuccess) return attr_err;
   }
   const int total = p.n_mtiles * p.n_ntiles;
@@ -1187,9 +1223,14 @@ cudaError_t conv_launch(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, co
     }
     if (ctas > 2 * max_clusters) cfg.gridDim = dim3(2 * max_clusters);
   }
+  // the fp32 path, the fused second output, the L2 hints and the reversed tile walk live in the kExtra instantiations
+  const bool extra = p.split != 0 || p.out2 != nullptr || p.l2_hint != 0 || p.reverse != 0;
+  if (extra && (p.trace != nullptr || p.epi_groups == 3)) return cudaErrorInvalidConfiguration;
   const cudaError_t err =
       // q = p + the division constants (its plan was checked equal to p's above)
-      p.trace != nullptr
+      extra ? (p.pair ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<true, 2, false, true>, tmap_a, tmap_b, tmap_out, tmap_res, q)
+                      : cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false, 2, false, true>, tmap_a, tmap_b, tmap_out, tmap_res, q))
+      : p.trace != nullptr
           ? (p.pair ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<true, 2, true>, tmap_a, tmap_b, tmap_out, tmap_res, q)
                     : (p.epi_groups == 3
                            ? cudaLaunchKernelEx(&cfg, conv_igemm_kernel<false, 3, true>, tmap_a, tmap_b, tmap_out, tmap_res, q)

@@ -246,7 +246,6 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
     if (rc == 0 && res != nullptr) rc = conv_encode_rows_tmap(&op.tr, res->ptr, res->rows(batch), res->C, res->ld);
     if (rc != 0) return fail(kErrCuda, "cuTensorMapEncodeTiled (output) failed for layer '%s' (%d)", l.name.c_str(), rc);
   }
-  if (conv_plan_smem(p) < 0) return fail(kErrInvalid, "layer '%s' does not fit the shared-memory plan", l.name.c_str());
   {  // experiments (measured in r02): tile walk direction alternating by layer, L2 eviction hints
     static const int snake = [] { const char* e = getenv("PPB_SNAKE"); return e ? atoi(e) : 0; }();
     static const int hint = [] { const char* e = getenv("PPB_L2HINT"); return e ? atoi(e) : 0; }();
@@ -255,6 +254,7 @@ int Engine::conv_op(const Tensor* x, int x_planes, const std::string& layer, con
     p.reverse = (snake != 0 && (n_conv & 1)) ? 1 : 0;
     p.l2_hint = (hint != 0 && !p.pair && !p.stem16) ? 1 : 0;
   }
+  if (conv_plan_smem(p) < 0) return fail(kErrInvalid, "layer '%s' does not fit the shared-memory plan", l.name.c_str());
   snprintf(op.name, sizeof(op.name), "%s", l.name.c_str());
   op.flops = 2.0 * batch * y->H * y->W * static_cast<double>(l.cout) * l.ksize * l.ksize * l.cin;
   ops.push_back(op);
