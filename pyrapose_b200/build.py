@@ -57,6 +57,11 @@ def _digest(paths):
     return h.hexdigest()
 
 
+def _file_sha(path):
+    with open(path, "rb") as f:
+        return hashlib.sha256(f.read()).hexdigest()
+
+
 def build(force=False, verbose=False):
     """Compile every CUDA source for sm_100a and link the shared library. Returns its path."""
     os.makedirs(LIBDIR, exist_ok=True)
@@ -99,7 +104,7 @@ def build(force=False, verbose=False):
         json.dump({"sources_sha256": digest, "sources": [s for s, _ in sources], "nvcc": ver[-2:] if ver else None,
                    "arch_flags": ARCH, "flags": COMMON, "exact_flags": ["-fmad=false"],
                    "built_utc": time.strftime("%Y-%m-%dT%H:%M:%SZ", time.gmtime()),
-                   "lib_sha256": _digest([lib_path()])}, f, indent=1)
+                   "lib_sha256": _file_sha(lib_path())}, f, indent=1)
     return lib_path()
 
 
@@ -110,7 +115,7 @@ def build_info():
     if not os.path.exists(p):
         return None
     info = json.load(open(p))
-    info["lib_sha256_now"] = _digest([lib_path()]) if os.path.exists(lib_path()) else None
+    info["lib_sha256_now"] = _file_sha(lib_path()) if os.path.exists(lib_path()) else None
     return info
 
 
