@@ -166,6 +166,22 @@ PPB_API int ppb_filter_detections(const float* boxes, const float* boxes3D, cons
                                   float nms_threshold, int max_detections, float* out_boxes, float* out_boxes3D,
                                   float* out_scores, int* out_labels, int* out_indices, void* workspace,
                                   size_t workspace_bytes, void* stream);
+/* ppb_filter_detections with NO allocation anywhere: no workspace argument, no cudaMalloc / cudaFree / allocating
+ * library call inside. No counterpart in the reference — added for callers that
+ * cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). The scratch is
+ * a file-scope `static __device__` array of ppb_filter_static_capacity_bytes() = 16 MiB inside the library (held by
+ * every GPU that loads it, until the process exits). Shapes whose ppb_filter_workspace_bytes(...) exceeds the capacity
+ * are rejected with PPB_ERR_INVALID and a message naming both sizes (one 480x640 image — 56 700 anchors — fits with up
+ * to 31 classes class-specific; batch 2 with 15; class-agnostic up to batch 17). Same inputs, outputs and results as
+ * ppb_filter_detections. All calls on a device share the one array, which keeps the previous call's contents (no part
+ * of it needs to start at zero): calls that overlap on the GPU — different streams without an ordering between them,
+ * or different host threads — race; serialise them. */
+PPB_API size_t ppb_filter_static_capacity_bytes(void);
+PPB_API int ppb_filter_detections_static(const float* boxes, const float* boxes3D, const float* classification,
+                                         int batch, int n, int num_classes, int class_specific, int nms,
+                                         float score_threshold, float nms_threshold, int max_detections,
+                                         float* out_boxes, float* out_boxes3D, float* out_scores, int* out_labels,
+                                         int* out_indices, void* stream);
 /* dst[b,d,:] = indices[b,d] >= 0 ? src[b, indices[b,d], :] : -1   (filter_detections.py:97,108 for `other`). */
 PPB_API int ppb_gather_rows_f32(const float* src, const int* indices, float* dst, int batch, int n,
                                 int max_detections, int row_elems, void* stream);

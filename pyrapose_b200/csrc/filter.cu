@@ -746,6 +746,13 @@ int launch_score_mask(const float* scores, int B, int N, int C, float thr, uint3
   return kOk;
 }
 
+// Built-in scratch of ppb_filter_detections_static (see there). 16 MiB: one 480x640 image (56 700 anchors) with up to
+// 31 classes class-specific, or two with 15 classes; class-agnostic up to batch 17 at that size.
+constexpr size_t kFilterStaticBytes = 16u << 20;
+constexpr int kFilterStaticMaxDevices = 64;
+static __device__ __align__(256) unsigned char g_filter_static_ws[kFilterStaticBytes];
+std::atomic<void*> g_filter_static_ptr[kFilterStaticMaxDevices];  // device address of the array, per device ordinal
+
 }  // namespace
 }  // namespace ppb
 
@@ -865,5 +872,49 @@ int ppb_vote_gather(const uint32_t* mask, const float* scores, const float* boxe
   count_launch();
   return kOk;
 }
+
+/* FilterDetections without any allocation by caller or library: the workspace of ppb_filter_detections is the
+ * file-scope device array g_filter_static_ws (kFilterStaticBytes; resident on every GPU that loads this library until
+ * the process exits). No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (graph capture, tight serving loops).
+ *
+ * In HOST code `g_filter_static_ws` is only the host-side shadow of the symbol, not a device address: the device
+ * address is looked up with cudaGetSymbolAddress once per device (with that device current) and cached.
+ * Nothing in the workspace has to start at zero: every buffer carved from it (mask, counts, keys, selections, class
+ * maxima, top-k scratch) is fully written by the kernel that produces it before the next one reads it, so the
+ * previous call's contents are harmless. All calls on a device share the one array: calls that overlap on the GPU
+ * (different streams, no ordering between them) race; callers serialise them. */
+int ppb_filter_detections_static(const float* boxes, const float* boxes3D, const float* classification, int batch,
+                                 int n, int num_classes, int class_specific, int nms, float score_threshold,
+                                 float nms_threshold, int max_detections, float* out_boxes, float* out_boxes3D,
+                                 float* out_scores, int* out_labels, int* out_indices, void* stream) {
+  PPB_REQUIRE(batch >= 0 && n > 0 && num_classes > 0,
+              "ppb_filter_detections_static: bad shape batch=%d n=%d classes=%d", batch, n, num_classes);
+  PPB_REQUIRE(max_detections > 0 && max_detections <= kMaxDetCap,
+              "ppb_filter_detections_static: max_detections must be in [1, %d], got %d", kMaxDetCap, max_detections);
+  if (batch == 0) return kOk;
+  const size_t need = ppb_filter_workspace_bytes(batch, n, num_classes, class_specific, max_detections);
+  PPB_REQUIRE(need <= kFilterStaticBytes,
+              "ppb_filter_detections_static: batch=%d n=%d classes=%d class_specific=%d max_detections=%d needs %zu "
+              "bytes of scratch, the built-in array holds %zu (use ppb_filter_detections with a caller workspace)",
+              batch, n, num_classes, class_specific, max_detections, need, kFilterStaticBytes);
+  int dev = -1;
+  PPB_CUDA(cudaGetDevice(&dev));
+  PPB_REQUIRE(dev >= 0 && dev < kFilterStaticMaxDevices, "ppb_filter_detections_static: device ordinal %d not supported",
+              dev);
+  void* ws = g_filter_static_ptr[dev].load(std::memory_order_acquire);
+  if (ws == nullptr) {  // set-up, once per device, with that device current
+    void* p = nullptr;
+    PPB_CUDA(cudaGetSymbolAddress(&p, g_filter_static_ws));
+    PPB_REQUIRE(p != nullptr, "ppb_filter_detections_static: cudaGetSymbolAddress returned a null address");
+    g_filter_static_ptr[dev].store(p, std::memory_order_release);
+    ws = p;
+  }
+  return ppb_filter_detections(boxes, boxes3D, classification, batch, n, num_classes, class_specific, nms,
+                               score_threshold, nms_threshold, max_detections, out_boxes, out_boxes3D, out_scores,
+                               out_labels, out_indices, ws, kFilterStaticBytes, stream);
+}
+
+size_t ppb_filter_static_capacity_bytes(void) { return kFilterStaticBytes; }
 
 }  // extern "C"
