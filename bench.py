@@ -315,6 +315,44 @@ def train_block(args, world, rank, dev, barrier):
         "losses": {k: losses[k] for k in ("3Dbox", "cls", "mask", "l2", "grad_norm")},
         "trainable_params": n_params,
     }
+    # end to end through model.fit_generator (the reference's loop, bin/train.py:381-390): every step a Sequence item =
+    # raw uint8 images in pinned host memory + the annotation lists, targets built on the device
+    # (anchor_targets_bbox_device), the next batch staged by a background thread while the GPU runs the current step,
+    # every batch's losses copied back and handed to a callback. Host wall clock, max over ranks.
+    import time
+    from pyrapose_b200.utils.anchors import anchor_targets_bbox_device, anchors_for_shape_device
+    raw = torch.from_numpy(np.random.default_rng(40 + rank).integers(0, 256, (TB, TH, TW, 3)).astype(np.uint8)).pin_memory()
+    anns = [pose_annotations((4 + rank) * 1000 + i, TC) for i in range(TB)]
+    shapes = [np.zeros((TH, TW, 3), np.uint8)] * TB
+    anchors_dev = anchors_for_shape_device((TH, TW, 3))
+
+    class Batches(object):
+        def __len__(self):
+            return steps
+
+        def __getitem__(self, i):
+            return raw, list(anchor_targets_bbox_device(anchors_dev, shapes, anns, TC))
+
+    seen = []
+
+    class Logs(object):
+        def on_batch_end(self, batch, logs):
+            seen.append(logs["loss"])
+
+    model.fit_generator(Batches(), steps_per_epoch=3, epochs=1, verbose=0)   # warm-up (rebinds for uint8 input)
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    model.fit_generator(Batches(), steps_per_epoch=steps, epochs=1, verbose=0, callbacks=[Logs()], shuffle=False)
+    torch.cuda.synchronize()
+    e2e_ms = _max_over_ranks(1e3 * (time.perf_counter() - t0) / steps, dev, world)
+    assert len(seen) == steps and np.isfinite(seen).all()
+    out["e2e"] = {"value": TB * world / (e2e_ms * 1e-3), "unit": "images/s", "ms_per_step": e2e_ms,
+                  "h2d_bytes_per_step": int(raw.numel()) + sum(a['bboxes'].shape[0] for a in anns) * 8 * (4 + 16)
+                  + TB * TH * TW,
+                  "d2h_bytes_per_step": 5 * 8,
+                  "api": "model.fit_generator(Sequence -> (uint8 host images, anchor_targets_bbox_device(annotation "
+                         "lists))), per-batch losses through on_batch_end"}
     del model, eng
     torch.cuda.empty_cache()
     if world > 1:

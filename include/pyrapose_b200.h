@@ -360,6 +360,11 @@ PPB_API int ppb_engine_train_grads(ppb_engine* engine, float** grads, long long*
 PPB_API int ppb_engine_train_apply(ppb_engine* engine, float lr, float beta1, float beta2, float epsilon,
                                    float clipnorm, float grad_scale, void* stream);
 PPB_API int ppb_engine_train_losses(ppb_engine* engine, double* out5_host, int* counts3_host, void* stream);
+/* The same read-back without a host synchronisation: the per-batch `logs` Keras hands to the callbacks of
+ * fit_generator (PyraPose/bin/train.py:381-390) arrive one step late, so the GPU never waits for the host. Copies the
+ * five loss doubles (3Dbox, cls, mask, l2, squared gradient norm) and optionally the three positive counts into
+ * PINNED host memory with cudaMemcpyAsync on `stream`; valid once work queued on `stream` up to here has completed. */
+PPB_API int ppb_engine_train_losses_async(ppb_engine* engine, double* out5_host, int* counts3_host, void* stream);
 /* Offsets (elements) of a layer's kernel [cout][k*k*cin] and bias [cout] inside the flat buffers; -1 if absent. */
 PPB_API int ppb_engine_train_param_info(const ppb_engine* engine, const char* layer, long long* kernel_offset,
                                         long long* bias_offset, int* trainable);

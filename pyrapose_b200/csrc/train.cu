@@ -1079,6 +1079,18 @@ int ppb_engine_train_losses(ppb_engine* h, double* out5_host, int* counts3_host,
   return kOk;
 }
 
+int ppb_engine_train_losses_async(ppb_engine* h, double* out5_host, int* counts3_host, void* stream) {
+  PPB_REQUIRE(h != nullptr && h->e.train, "ppb_engine_train_losses_async: training state not created");
+  PPB_REQUIRE(out5_host != nullptr, "ppb_engine_train_losses_async: null output");
+  Engine& e = h->e;
+  PPB_CUDA(cudaSetDevice(e.device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  PPB_CUDA(cudaMemcpyAsync(out5_host, e.train->loss, 5 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (counts3_host)
+    PPB_CUDA(cudaMemcpyAsync(counts3_host, e.train->counts, 3 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  return kOk;
+}
+
 int ppb_engine_train_param_info(const ppb_engine* h, const char* layer, long long* kernel_offset,
                                 long long* bias_offset, int* trainable) {
   PPB_REQUIRE(h != nullptr && h->e.train && layer != nullptr, "ppb_engine_train_param_info: training state not created");

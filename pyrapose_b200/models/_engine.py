@@ -288,6 +288,15 @@ class Engine(object):
         return {"3Dbox": out[0], "cls": out[1], "mask": out[2], "l2": out[3], "grad_norm": float(np.sqrt(out[4])),
                 "positives": (cnt[0], cnt[1], cnt[2])}
 
+    def train_losses_async(self, out5_pinned):
+        """No synchronisation: queues the copy of [3Dbox, cls, mask, l2, grad_norm^2] (float64) into the PINNED host
+        tensor `out5_pinned` on the current stream; the caller orders its read with an event."""
+        if not (out5_pinned.is_pinned() and out5_pinned.dtype == torch.float64 and out5_pinned.numel() >= 5):
+            raise ValueError("train_losses_async needs a pinned float64 host tensor of at least 5 elements")
+        with torch.cuda.device(self.device):
+            nat.check(self.lib.ppb_engine_train_losses_async(self._h, ctypes.c_void_p(out5_pinned.data_ptr()), None,
+                                                             nat.current_stream_ptr()))
+
     def train_param_info(self, layer):
         ko, bo = ctypes.c_longlong(), ctypes.c_longlong()
         tr = ctypes.c_int()

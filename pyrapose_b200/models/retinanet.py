@@ -516,6 +516,22 @@ class PFPNModel(object):
         self.last_step = l
         return [l["3Dbox"] + l["cls"] + l["mask"] + l["l2"], l["3Dbox"], l["cls"], l["mask"]]
 
+    def fit_generator(self, generator, steps_per_epoch=None, epochs=1, verbose=1, callbacks=None,
+                      validation_data=None, validation_steps=None, class_weight=None, max_queue_size=10, workers=1,
+                      use_multiprocessing=False, shuffle=True, initial_epoch=0):
+        """ The reference's training loop (PyraPose/bin/train.py:381-390) around train_on_batch: `generator` is a
+        keras.utils.Sequence-like object (`__len__`, `__getitem__` -> (inputs, [regression_3D, labels, mask]),
+        `on_epoch_end`) or a plain Python generator; arrays may be numpy or CUDA tensors (inject
+        `utils.anchors.anchor_targets_bbox_device` as the Generator's `compute_anchor_targets`,
+        preprocessing/generator.py:58-59, and the targets never leave the GPU). The next batch is staged by a
+        background thread while the GPU runs the current step, and per-batch losses reach the callbacks one launch
+        late (models/_fit.py). Returns a History (`.history['loss']`, `'3Dbox_loss'`, `'cls_loss'`, `'mask_loss'`)."""
+        from ._fit import fit_generator
+        return fit_generator(self, generator, steps_per_epoch=steps_per_epoch, epochs=epochs, verbose=verbose,
+                             callbacks=callbacks, validation_data=validation_data, validation_steps=validation_steps,
+                             class_weight=class_weight, max_queue_size=max_queue_size, workers=workers,
+                             use_multiprocessing=use_multiprocessing, shuffle=shuffle, initial_epoch=initial_epoch)
+
     def _p2p_exchange(self, eng, grads):
         """The engine's P2PExchange (created collectively on the first data-parallel step), or None for NCCL."""
         import torch
