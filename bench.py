@@ -326,9 +326,11 @@ def train_block(args, world, rank, dev, barrier):
     shapes = [np.zeros((TH, TW, 3), np.uint8)] * TB
     anchors_dev = anchors_for_shape_device((TH, TW, 3))
 
+    e2e_steps = max(steps, 20)   # one staged batch of pipeline fill is part of the timed call: amortised over >= 20
+
     class Batches(object):
         def __len__(self):
-            return steps
+            return e2e_steps
 
         def __getitem__(self, i):
             return raw, list(anchor_targets_bbox_device(anchors_dev, shapes, anns, TC))
@@ -343,11 +345,11 @@ def train_block(args, world, rank, dev, barrier):
     torch.cuda.synchronize()
     barrier()
     t0 = time.perf_counter()
-    model.fit_generator(Batches(), steps_per_epoch=steps, epochs=1, verbose=0, callbacks=[Logs()], shuffle=False)
+    model.fit_generator(Batches(), steps_per_epoch=e2e_steps, epochs=1, verbose=0, callbacks=[Logs()], shuffle=False)
     torch.cuda.synchronize()
-    e2e_ms = _max_over_ranks(1e3 * (time.perf_counter() - t0) / steps, dev, world)
-    assert len(seen) == steps and np.isfinite(seen).all()
-    out["e2e"] = {"value": TB * world / (e2e_ms * 1e-3), "unit": "images/s", "ms_per_step": e2e_ms,
+    e2e_ms = _max_over_ranks(1e3 * (time.perf_counter() - t0) / e2e_steps, dev, world)
+    assert len(seen) == e2e_steps and np.isfinite(seen).all()
+    out["e2e"] = {"value": TB * world / (e2e_ms * 1e-3), "unit": "images/s", "ms_per_step": e2e_ms, "steps": e2e_steps,
                   "h2d_bytes_per_step": int(raw.numel()) + sum(a['bboxes'].shape[0] for a in anns) * 8 * (4 + 16)
                   + TB * TH * TW,
                   "d2h_bytes_per_step": 5 * 8,

@@ -84,7 +84,10 @@ def fit_generator(model, generator, steps_per_epoch=None, epochs=1, verbose=1, c
     if dev is None:
         dev = torch.cuda.current_device()
     device = torch.device("cuda", dev) if isinstance(dev, int) else torch.device(dev)
-    stager = DeviceStager(device, n_slots=3)
+    # the staging stream and the pinned slots (cudaHostAlloc costs milliseconds per slot) are kept across calls
+    stager = model.__dict__.get("_stager")
+    if stager is None or stager.device != device:
+        stager = model.__dict__["_stager"] = DeviceStager(device, n_slots=3)
     depth = max(1, min(int(max_queue_size), 4))
     history = History()
     history.model = model
@@ -95,7 +98,10 @@ def fit_generator(model, generator, steps_per_epoch=None, epochs=1, verbose=1, c
     model.history = history
 
     main = torch.cuda.current_stream(device)
-    loss_slots = [dict(buf=torch.zeros(5, dtype=torch.float64).pin_memory(), ev=torch.cuda.Event()) for _ in range(2)]
+    loss_slots = model.__dict__.get("_loss_slots")
+    if loss_slots is None:
+        loss_slots = model.__dict__["_loss_slots"] = [
+            dict(buf=torch.zeros(5, dtype=torch.float64).pin_memory(), ev=torch.cuda.Event()) for _ in range(2)]
 
     def all_items():
         for _ in range(initial_epoch, int(epochs)):

@@ -155,6 +155,10 @@ class DeviceStager(object):
         if isinstance(a, torch.Tensor):
             if a.is_cuda:
                 return a
+            if a.is_pinned() and a.dtype in (torch.uint8, torch.float32) and a.is_contiguous():
+                # already page-locked: copied from where it lies; the generator must not overwrite it before the
+                # batch has been consumed (numpy arrays and pageable tensors are copied into the stager's own slots)
+                return a.to(self.device, non_blocking=True)
             a = a.numpy()
         a = np.asarray(a)
         if a.dtype != np.uint8:
