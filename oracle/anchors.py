@@ -2,7 +2,11 @@
 
 Follows /root/reference/PyraPose/utils/anchors.py (line numbers cited per function). Pinned: every
 function here is checked against the reference's own source executed in the build container
-(tests/golden/make_golden.py -> tests/golden/anchors_*.npz, tests/test_oracle_anchors.py).
+(tests/golden/make_golden.py -> tests/golden/anchors_*.npz, tests/test_oracle_anchors.py); anchor_targets_bbox as a
+WHOLE (states, one-hot labels, projected-corner regression targets, mask targets, padded batches) and the Anchors
+layer's float32 arithmetic are pinned by tests/golden/reference_text.npz (the reference's utils/anchors.py and
+layers/_misc.py imported and run, make_golden_shim.py; transforms3d's quat2mat restated, PIL is installed) in
+tests/test_oracle_reference_text.py, sha256 of the full arrays included.
 """
 import numpy as np
 

@@ -1,8 +1,11 @@
 """numpy restatement of the reference's per-anchor decode ops — TEST INFRASTRUCTURE ONLY.
 
-Follows /root/reference/PyraPose/backend/common.py (TensorFlow float32 elementwise graph ops;
-PARITY UNPINNED: TensorFlow cannot run here, the reference ships no vectors). float32 throughout,
+Follows /root/reference/PyraPose/backend/common.py (TensorFlow float32 elementwise graph ops). float32 throughout,
 each multiply/add rounded separately exactly as the unfused TF graph evaluates them.
+PINNED TO THE REFERENCE'S TEXT: tests/golden/reference_text.npz holds the outputs of the reference's own common.py
+and layers/_misc.py, imported and run over numpy stand-ins for the tensorflow / keras primitives
+(tests/golden/tf_shim.py, make_golden_shim.py); tests/test_oracle_reference_text.py compares bit for bit. What stays
+unpinned is TensorFlow's own kernels (they cannot run here), i.e. that TF evaluates these float32 ops unfused.
 """
 import numpy as np
 

@@ -10,7 +10,11 @@ TensorFlow ops it calls are restated from their published semantics (TF 2.1.1, n
                                         unspecified, synthetic scores are tie-free)
   tf.nn.top_k                           descending, ties -> lower index
   tf.pad(constant_values=-1)
-PARITY UNPINNED (no TensorFlow here, no reference vectors).
+PINNED TO THE REFERENCE'S TEXT for everything filter_detections.py itself decides (threshold, class loop,
+concatenation order, the gather / top_k / pad sequence, dtypes, `other`): tests/golden/reference_text.npz holds the
+outputs of the reference's own filter_detections / FilterDetections.call run over numpy stand-ins for the TF
+primitives (tests/golden/tf_shim.py), compared exactly in tests/test_oracle_reference_text.py. The primitives above
+remain restatements (TensorFlow cannot run here); NMS is cross-checked against torchvision.ops.nms.
 
 vote_filter follows /root/reference/PyraPose/utils/linemod_eval.py:307-334, 427-430.
 """

@@ -1,6 +1,9 @@
 """CPU restatement of the training objective of the hot path — TEST INFRASTRUCTURE ONLY.
 
-PARITY UNPINNED (Keras / TensorFlow are not installable here; the reference has no tests): these follow
+PINNED TO THE REFERENCE'S TEXT: the reference's own losses.py, imported and run over numpy stand-ins for the
+keras.backend calls it makes (tests/golden/tf_shim.py), gives the loss values in tests/golden/reference_text.npz;
+tests/test_oracle_reference_text.py compares to 2e-6 relative (float32 reduction order). Keras / TensorFlow themselves
+are not installable here, so keras.backend.binary_crossentropy is a restatement (below). These follow
   focal(alpha=0.25, gamma=2.0)          /root/reference/PyraPose/losses.py:22-68
   orthogonal_l1(weight=0.125, sigma=3)  /root/reference/PyraPose/losses.py:321-408
 line by line in torch (float32, CPU) so that autograd supplies the reference gradients the CUDA loss kernels
