@@ -1,7 +1,14 @@
 """fp32 CPU restatement (torch-CPU convolutions) of the reference's PFPN graph — TEST INFRASTRUCTURE ONLY.
 
-PARITY UNPINNED: TensorFlow 2.1.1 / Keras 2.3.1 / keras-resnet 0.1.0 are not installable here and the
-reference has no tests; this follows the model-building code line by line instead:
+WIRING PINNED TO THE REFERENCE'S TEXT, NUMERICS OF THE LIBRARIES UNPINNED. TensorFlow 2.1.1 / Keras 2.3.1 /
+keras-resnet 0.1.0 are not installable here and the reference has no tests. What IS done: the reference's own
+model-building code (models/__init__.py, models/resnet.py, models/retinanet.py, initializers.py, layers/_misc.py) is
+imported and run in the build container over a miniature Keras (tests/golden/keras_shim.py), loaded with the same
+weights through the Keras layer-name map, and its outputs are committed (tests/golden/reference_model.npz,
+make_golden_model.py); this file reproduces them — C3-C5, P3-P5, 3Dbox, cls, mask, boxes3D — to <= 2.5e-6 relative L2
+(tests/test_oracle_reference_model.py). That fixes the graph (who feeds whom, strides, paddings, activations, shared
+heads, Reshape / Concatenate order). The arithmetic of Conv2D / 'same' padding / MaxPooling2D / BatchNormalization and
+keras-resnet's ResNet50 are restatements on both sides. This follows the model-building code line by line:
   backbone : keras_resnet.models.ResNet50(include_top=False, freeze_bn=True) as called at
              /root/reference/PyraPose/models/resnet.py:87,110 (architecture restated from keras-resnet 0.1.0
              models/_2d.py::ResNet50 + blocks/_2d.py::bottleneck_2d: ZeroPad(3)+7x7/2 VALID, BN(eps=1e-5), ReLU,

@@ -280,7 +280,7 @@ def install(reference_root="/root/reference", compute_overlap_module=None):
     tf3d.quaternions = types.SimpleNamespace(quat2mat=quat2mat)
     put("transforms3d", tf3d)
     root = os.path.join(reference_root, "PyraPose")
-    for name, sub in (("PyraPose", ""), ("PyraPose.utils", "utils"), ("PyraPose.layers", "layers")):
+    for name, sub in (("PyraPose", ""), ("PyraPose.utils", "utils")):   # layers/, backend/, models/ import normally
         pkg = types.ModuleType(name)
         pkg.__path__ = [os.path.join(root, sub)]
         pkg.__spec__ = importlib.machinery.ModuleSpec(name, None, is_package=True)
