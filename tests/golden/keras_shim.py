@@ -406,6 +406,7 @@ def install(reference_root="/root/reference", compute_overlap_module=None):
         zeros=lambda: "zeros")
     utils = types.ModuleType("keras.utils")
     utils.get_file = lambda fname, origin=None, **kw: os.path.join("/nonexistent", fname)
+    utils.Sequence = object
     keras.utils = utils
     kr = _keras_resnet()
 
@@ -415,11 +416,6 @@ def install(reference_root="/root/reference", compute_overlap_module=None):
         sys.modules[name] = mod
 
     put("keras.utils", utils)
-    if "imgaug" not in sys.modules:          # utils/image.py imports the augmentation library at module level only
-        ia = types.ModuleType("imgaug")
-        ia.augmenters = types.ModuleType("imgaug.augmenters")
-        put("imgaug", ia)
-        put("imgaug.augmenters", ia.augmenters)
     put("keras_resnet", kr)
     put("keras_resnet.models", kr.models)
     put("keras_resnet.layers", kr.layers)

@@ -11,6 +11,8 @@ Executed reference code (nothing of it is copied into the repo; only inputs and 
                                     ClipBoxes.call :263-277
   PyraPose/layers/filter_detections.py   filter_detections :21-118, FilterDetections.call :153-191
   PyraPose/losses.py                focal :22-68, orthogonal_l1 :321-408
+  PyraPose/utils/image.py           preprocess_image :35-62, compute_resize_scale :281-305, resize_image :308-323
+  PyraPose/preprocessing/generator.py   Generator.compute_inputs :320-336
   PyraPose/utils/anchors.py         anchor_targets_bbox :72-287 (with compute_gt_annotations, box3D_transform,
                                     toPix_array, guess_shapes, anchors_for_shape), compute_overlap = the reference's
                                     Cython file compiled into oracle/_ref
@@ -177,6 +179,31 @@ def main():
         nonec[:, :, -1] = np.where(nonec[:, :, -1] == 1, 0, nonec[:, :, -1])
         nonec[:, :, :C] = 0
         out["loss_focal_no_positives"] = np.array([float(A(losses.focal()(t(nonec), t(p_cls))))])
+        # ---------------------------------------------------------------- input staging (utils/image.py, generator.py)
+        ref_image = importlib.import_module("PyraPose.utils.image")
+        ref_gen = importlib.import_module("PyraPose.preprocessing.generator")
+        shapes = [(375, 1242), (500, 333), (480, 640), (720, 1280)]
+        out["img_shapes"] = np.array(shapes)
+        out["img_seed"] = np.array([77])
+        rngi = np.random.default_rng(77)
+        staged, scales = [], []
+        for k, (h, w) in enumerate(shapes):
+            raw = rngi.integers(0, 256, (h, w, 3)).astype(np.uint8)
+            x = ref_image.preprocess_image(raw, mode='caffe')                    # image.py:35-62
+            assert x.dtype == np.float32
+            hashes["preprocess_%dx%d" % (h, w)] = sha(x)
+            y, scale = ref_image.resize_image(x, min_side=480, max_side=640)     # image.py:308-323
+            staged.append(y)
+            scales.append(scale)
+            out["img_resized_shape_%d" % k] = np.array(y.shape)
+            out["img_resized_sample_%d" % k] = y[::7, ::11].copy()
+        out["img_scales"] = np.array(scales, dtype=np.float64)
+        fake_self = types.SimpleNamespace(batch_size=len(staged))
+        batch = ref_gen.Generator.compute_inputs(fake_self, staged)              # generator.py:320-336
+        out["img_batch_shape"] = np.array(batch.shape)
+        out["img_batch_sample"] = batch[:, ::9, ::13].copy()
+        out["img_batch_nonzero_rows"] = np.array([[int(np.abs(b).sum(axis=(1, 2)).nonzero()[0].max()) + 1,
+                                                   int(np.abs(b).sum(axis=(0, 2)).nonzero()[0].max()) + 1] for b in batch])
     finally:
         tf_shim.uninstall(added)
     path = os.path.join(HERE, "reference_text.npz")

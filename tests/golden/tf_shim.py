@@ -237,6 +237,7 @@ def make_keras():
     layers.Layer = Layer
     keras.layers = layers
     keras.initializers = types.SimpleNamespace(Initializer=object)
+    keras.utils = types.SimpleNamespace(Sequence=object)
     return keras, K, layers
 
 
@@ -279,6 +280,11 @@ def install(reference_root="/root/reference", compute_overlap_module=None):
     tf3d = types.ModuleType("transforms3d")
     tf3d.quaternions = types.SimpleNamespace(quat2mat=quat2mat)
     put("transforms3d", tf3d)
+    if "imgaug" not in sys.modules:          # utils/image.py imports the augmentation library at module level only
+        ia = types.ModuleType("imgaug")
+        ia.augmenters = types.ModuleType("imgaug.augmenters")
+        put("imgaug", ia)
+        put("imgaug.augmenters", ia.augmenters)
     root = os.path.join(reference_root, "PyraPose")
     for name, sub in (("PyraPose", ""), ("PyraPose.utils", "utils")):   # layers/, backend/, models/ import normally
         pkg = types.ModuleType(name)

@@ -158,3 +158,31 @@ def test_losses_match_reference_text(gold):
     # float64 evaluation of the same restatement agrees too (the comparison is not a float32 accident)
     close(ol.focal(y_cls.double(), p_cls.double()), gold["loss_focal"], tol=2e-6)
     close(ol.orthogonal_l1(y_reg.double(), p_reg.double()), gold["loss_orth"], tol=2e-6)
+
+
+def _raw_images(gold):
+    rng = np.random.default_rng(int(gold["img_seed"][0]))
+    return [rng.integers(0, 256, (int(h), int(w), 3)).astype(np.uint8) for h, w in gold["img_shapes"]]
+
+
+def test_input_staging_host_mirror_equals_the_reference_functions(gold, sha):
+    """utils.image.preprocess_image / compute_resize_scale / compute_inputs (the host-side mirror; no GPU) against the
+    reference's own utils/image.py and Generator.compute_inputs. preprocess and the scale are exact; the resized
+    pixels come from cv2.resize on both sides (the reference's call) and are compared at 2 ulp of the pixel range,
+    since OpenCV dispatches SIMD code by CPU."""
+    cv2 = pytest.importorskip("cv2")
+    from pyrapose_b200.utils import image as ui
+    staged = []
+    for k, raw in enumerate(_raw_images(gold)):
+        x = ui.preprocess_image(raw)
+        assert x.dtype == np.float32 and _sha(x) == sha["preprocess_%dx%d" % raw.shape[:2]]
+        s = ui.compute_resize_scale(x.shape)
+        assert s == float(gold["img_scales"][k])
+        y = cv2.resize(x, None, fx=s, fy=s)
+        assert list(y.shape) == gold["img_resized_shape_%d" % k].tolist()
+        assert np.abs(y[::7, ::11] - gold["img_resized_sample_%d" % k]).max() <= 3.1e-5
+        staged.append(y)
+    batch = ui.compute_inputs(staged)
+    assert list(batch.shape) == gold["img_batch_shape"].tolist() and batch.dtype == np.float32
+    assert np.abs(batch[:, ::9, ::13] - gold["img_batch_sample"]).max() <= 3.1e-5
+    assert gold["img_batch_shape"].tolist() == [4, 640, 640, 3]

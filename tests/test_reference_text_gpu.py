@@ -126,3 +126,23 @@ def test_anchor_targets_bbox_equals_the_reference_text(cuda_device, gold, sha):
     reg_p, lab_p, _ = ua.anchor_targets_bbox(anchors, images_p, anns[:2], C)
     assert np.array_equal(reg_p[:, :, -1].astype(np.int8), gold["tgt_pad_states"])
     assert _sha(reg_p) == sha["targets_padded_regression_3D"] and _sha(lab_p) == sha["targets_padded_labels"]
+
+
+def test_stage_batch_equals_the_reference_functions(cuda_device, gold):
+    """Raw uint8 images -> ui.stage_batch (preprocess + bilinear resize + zero-padded batch in CUDA kernels) against
+    the reference's own preprocess_image + resize_image + Generator.compute_inputs (utils/image.py:35-62, 281-323;
+    preprocessing/generator.py:320-336). Scales, shapes and the zero padding exact; pixels within 2 ulp of the pixel
+    range (OpenCV's SIMD bilinear kernel may fuse multiply-adds; tests/test_image_gpu.py)."""
+    from pyrapose_b200.utils import image as ui
+    rng = np.random.default_rng(int(gold["img_seed"][0]))
+    raws = [rng.integers(0, 256, (int(h), int(w), 3)).astype(np.uint8) for h, w in gold["img_shapes"]]
+    got, scales = ui.stage_batch(raws)
+    got = got.cpu().numpy()
+    assert scales == [float(s) for s in gold["img_scales"]]
+    assert list(got.shape) == gold["img_batch_shape"].tolist()
+    d = np.abs(got[:, ::9, ::13] - gold["img_batch_sample"])
+    print("stage_batch vs the reference's staging functions: max |diff| %.2e, identical %.1f%%" % (d.max(), 100 * (d == 0).mean()))
+    assert d.max() <= 3.1e-5
+    for b, (rows, cols) in enumerate(gold["img_batch_nonzero_rows"]):
+        assert not got[b, rows:].any() and not got[b, :, cols:].any()
+        assert got[b, rows - 1].any() and got[b, :, cols - 1].any()
