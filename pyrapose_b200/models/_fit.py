@@ -17,7 +17,6 @@ What differs is WHEN things happen, so that the GPU never waits for the host:
 prefetch.py); `max_queue_size` bounds the staged batches (each holds its targets on the device: capped at 4)."""
 import time
 
-import numpy as np
 
 from ..utils.prefetch import BatchOrder, BatchPrefetcher, DeviceStager
 
