@@ -55,58 +55,88 @@ __device__ __forceinline__ long long head_row(const HeadGeom& g, int b, int loc)
   return g.row_begin[l] + (static_cast<long long>(b) * (g.h[l] + 2) + y + 1) * (g.w[l] + 2) + x + 1;
 }
 
-// One thread per (image, location, column pair): prob and grad are both contiguous over (anchor, class) inside a
-// location, so consecutive threads touch consecutive addresses.
+// One thread per (image, location, group of 8 columns): prob and grad are both contiguous over (anchor, class) inside
+// a location, so a thread reads 8 consecutive probabilities and writes one 16-byte piece of the gradient row; the
+// integer divisions are paid once per 8 columns and the (anchor, class) pair is advanced incrementally.
+// Measured per step (two launches, 190 MB; r02, ncu): one thread per column PAIR with five integer divisions and two
+// double additions per pair 0.244 ms; this form 0.141 ms; one warp per location with lanes over the columns (every
+// load one coalesced 128-byte request) 0.205 ms, the same with all loads of 256 columns issued up front 0.240 ms.
 __global__ void __launch_bounds__(256)
 focal_loss_grad_kernel(const float* __restrict__ prob, const float* __restrict__ y_true,
                        __nv_bfloat16* __restrict__ grad, int ld, const HeadGeom g, int batch, int A, int C, float alpha,
                        float gamma, const int* __restrict__ counts, int slot, double* __restrict__ loss) {
   const int vals = A * C;
-  const int pairs = (vals + 1) >> 1;
-  // 32-bit index arithmetic (the launcher rejects 2^31 or more column pairs): four 64-bit divisions per thread were a
-  // large share of this kernel
-  const unsigned total = static_cast<unsigned>(batch) * static_cast<unsigned>(g.locs) * static_cast<unsigned>(pairs);
+  const unsigned chunks = static_cast<unsigned>((vals + 7) >> 3);
+  // 32-bit index arithmetic (the launcher rejects 2^31 or more column groups)
+  const unsigned total = static_cast<unsigned>(batch) * static_cast<unsigned>(g.locs) * chunks;
   const float inv_norm = 1.0f / fmaxf(1.0f, static_cast<float>(__ldg(counts + slot)));
+  const bool g2 = gamma == 2.0f;
   double local = 0.0;
   for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
-    const unsigned bl = t / static_cast<unsigned>(pairs);
-    const int pr = static_cast<int>(t - bl * pairs);
+    const unsigned bl = t / chunks;                      // (image, location)
+    const int col0 = static_cast<int>(t - bl * chunks) << 3;
     const int b = static_cast<int>(bl / static_cast<unsigned>(g.locs));
     const int loc = static_cast<int>(bl - static_cast<unsigned>(b) * g.locs);
-    float gz[2] = {0.0f, 0.0f};
+    int a = col0 / C, c = col0 - a * C;
+    const long long n0 = static_cast<long long>(bl) * A;  // first anchor of the location
+    const float* yt = y_true + (n0 + a) * (C + 1);
+    const float* pp = prob + n0 * C + col0;               // prob[(n0 + a) * C + c] is contiguous over the columns
+    float state = __ldg(yt + C);
+    float gz[8];
+    float part = 0.0f;
 #pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const int col = pr * 2 + e;
-      if (col >= vals) continue;
-      const int a = col / C, c = col - a * C;
-      const long long n = (static_cast<long long>(b) * g.locs + loc) * A + a;
-      const float* yt = y_true + n * (C + 1);
-      const float state = __ldg(yt + C);
-      if (state == -1.0f) continue;  // "ignore" anchors are filtered out (losses.py:48-50)
-      const float label = __ldg(yt + c);
-      const float p = __ldg(prob + n * C + c);
-      const bool pos = label == 1.0f;
-      const float af = pos ? alpha : 1.0f - alpha;
-      const float q = pos ? 1.0f - p : p;          // focal_weight base (losses.py:55)
-      const float pc = fminf(fmaxf(p, 1e-7f), 1.0f - 1e-7f);  // keras.backend.binary_crossentropy clips to [eps, 1-eps]
-      const bool inside = p > 1e-7f && p < 1.0f - 1e-7f;       // gradient of the clip
-      // labels are one-hot in practice: one logarithm suffices; the general expression is kept for soft labels
-      float bce;
-      if (label == 1.0f) bce = -logf(pc);
-      else if (label == 0.0f) bce = -logf(1.0f - pc);
-      else bce = -(label * logf(pc) + (1.0f - label) * logf(1.0f - pc));
-      const bool g2 = gamma == 2.0f;
-      const float fw = af * (g2 ? q * q : powf(q, gamma));
-      local += static_cast<double>(fw * bce);
-      // d/dp: focal_weight' * bce + focal_weight * bce'
-      const float dq = pos ? -1.0f : 1.0f;
-      const float dfw = af * (g2 ? 2.0f * q : gamma * powf(q, gamma - 1.0f)) * dq;
-      const float dbce = inside ? -(label / pc - (1.0f - label) / (1.0f - pc)) : 0.0f;
-      const float dp = dfw * bce + fw * dbce;
-      gz[e] = dp * p * (1.0f - p) * inv_norm;  // through the sigmoid
+    for (int e = 0; e < 8; ++e) {
+      gz[e] = 0.0f;
+      if (col0 + e >= vals) continue;
+      if (state != -1.0f) {  // "ignore" anchors are filtered out (losses.py:48-50)
+        const float label = __ldg(yt + c);
+        const float p = __ldg(pp + e);
+        const bool pos = label == 1.0f;
+        const float af = pos ? alpha : 1.0f - alpha;
+        const float q = pos ? 1.0f - p : p;          // focal_weight base (losses.py:55)
+        const float pc = fminf(fmaxf(p, 1e-7f), 1.0f - 1e-7f);  // keras.backend.binary_crossentropy clips to [eps, 1-eps]
+        const bool inside = p > 1e-7f && p < 1.0f - 1e-7f;       // gradient of the clip
+        // labels are one-hot in practice: one logarithm and one division suffice; the general expression is kept for
+        // soft labels (for label 1 / 0 it reduces to exactly these values)
+        float bce, dbce;
+        // (the kernel is instruction-bound — ncu r02: 63 % issue slots busy, 18 % DRAM — so the one-hot cases use the
+        // SFU forms: __logf is accurate to ~2 ulp on [1e-7, 1), the quotient feeds a bf16 gradient)
+        if (label == 1.0f) {
+          bce = -__logf(pc);
+          dbce = -__fdividef(1.0f, pc);
+        } else if (label == 0.0f) {
+          bce = -__logf(1.0f - pc);
+          dbce = __fdividef(1.0f, 1.0f - pc);
+        } else {
+          bce = -(label * logf(pc) + (1.0f - label) * logf(1.0f - pc));
+          dbce = -(label / pc - (1.0f - label) / (1.0f - pc));
+        }
+        if (!inside) dbce = 0.0f;
+        const float fw = af * (g2 ? q * q : powf(q, gamma));
+        part += fw * bce;
+        // d/dp: focal_weight' * bce + focal_weight * bce'
+        const float dq = pos ? -1.0f : 1.0f;
+        const float dfw = af * (g2 ? 2.0f * q : gamma * powf(q, gamma - 1.0f)) * dq;
+        const float dp = dfw * bce + fw * dbce;
+        gz[e] = dp * p * (1.0f - p) * inv_norm;  // through the sigmoid
+      }
+      if (++c == C) {  // next anchor of the location
+        c = 0;
+        yt += C + 1;
+        if (col0 + e + 1 < vals) state = __ldg(yt + C);
+      }
     }
+    local += static_cast<double>(part);
     const long long row = head_row(g, b, loc);
-    *reinterpret_cast<uint32_t*>(grad + row * ld + pr * 2) = pack2(gz[0], gz[1]);
+    __nv_bfloat16* dst = grad + row * ld + col0;
+    if (col0 + 8 <= ld) {
+      *reinterpret_cast<uint4*>(dst) = make_uint4(pack2(gz[0], gz[1]), pack2(gz[2], gz[3]), pack2(gz[4], gz[5]),
+                                                  pack2(gz[6], gz[7]));
+    } else {
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        if (col0 + e < ld) dst[e] = __float2bfloat16(gz[e]);
+    }
   }
   block_accumulate(local * static_cast<double>(inv_norm), loss + slot);
 }
@@ -202,19 +232,27 @@ __global__ void __launch_bounds__(256)
 grad_combine_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, const uint4* __restrict__ c,
                     const uint4* __restrict__ d, int dH, int dW, const uint4* __restrict__ p, int pH, int pW,
                     int n_planes, const uint4* __restrict__ mask, uint4* __restrict__ out, int B, int H, int W, int C8) {
-  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  // 32-bit index arithmetic (the launcher rejects 2^32 or more vectors): the five 64-bit divisions of the first
+  // version cost more than the memory traffic on the small maps (1.6 TB/s over the seven launches of a step)
+  const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
   const int Hp = H + 2, Wp = W + 2;
-  const long long total = static_cast<long long>(B) * Hp * Wp * C8;
+  const unsigned total = static_cast<unsigned>(B) * Hp * Wp * C8;
   if (t >= total) return;
+  // all loads that do not depend on the pixel coordinates first
+  const uint4 va = a != nullptr ? __ldg(a + t) : make_uint4(0u, 0u, 0u, 0u);
+  const uint4 vb = b != nullptr ? __ldg(b + t) : make_uint4(0u, 0u, 0u, 0u);
+  const uint4 vc = c != nullptr ? __ldg(c + t) : make_uint4(0u, 0u, 0u, 0u);
+  const uint4 vm = mask != nullptr ? __ldg(mask + t) : make_uint4(0u, 0u, 0u, 0u);
   float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  if (a != nullptr) acc8(f, __ldg(a + t));
-  if (b != nullptr) acc8(f, __ldg(b + t));
-  if (c != nullptr) acc8(f, __ldg(c + t));
-  const int ch = static_cast<int>(t % C8);
-  const long long pix = t / C8;
-  const int wx = static_cast<int>(pix % Wp);
-  const int hy = static_cast<int>((pix / Wp) % Hp);
-  const int bi = static_cast<int>(pix / (static_cast<long long>(Wp) * Hp));
+  if (a != nullptr) acc8(f, va);
+  if (b != nullptr) acc8(f, vb);
+  if (c != nullptr) acc8(f, vc);
+  const unsigned pix = t / static_cast<unsigned>(C8);
+  const int ch = static_cast<int>(t - pix * C8);
+  const unsigned rowi = pix / static_cast<unsigned>(Wp);
+  const int wx = static_cast<int>(pix - rowi * Wp);
+  const int bi = static_cast<int>(rowi / static_cast<unsigned>(Hp));
+  const int hy = static_cast<int>(rowi - static_cast<unsigned>(bi) * Hp);
   const bool interior = hy >= 1 && hy <= H && wx >= 1 && wx <= W;
   if (interior && d != nullptr) {
     // adjoint of `up = nearest_resize(src HxW -> dH x dW)`: sum the gradient of every fine pixel that read (y, x)
@@ -239,7 +277,7 @@ grad_combine_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, co
     }
   }
   if (mask != nullptr) {
-    const uint4 m = __ldg(mask + t);
+    const uint4 m = vm;
     if (!(lo_f(m.x) > 0.f)) f[0] = 0.f;
     if (!(hi_f(m.x) > 0.f)) f[1] = 0.f;
     if (!(lo_f(m.y) > 0.f)) f[2] = 0.f;
@@ -257,7 +295,9 @@ grad_combine_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, co
   out[t] = o;
 }
 
-// Column sums of a bf16 matrix: block = 8 column vectors (64 columns) x 32 row lanes.
+// Column sums of a bf16 matrix: block = 8 column vectors (64 columns) x 32 row lanes; 3.9 TB/s over the 25 launches of a
+// step. Measured and rejected (r02): four independent loads per thread in flight (3.84 TB/s, no change) and a block of
+// 256 columns x 8 rows so that a warp reads 512 contiguous bytes of a row (3.25 TB/s, worse).
 __global__ void __launch_bounds__(256) bias_grad_kernel(const uint4* __restrict__ g, long long rows, int ld8, int cout,
                                                         float* __restrict__ dbias) {
   const int cv = threadIdx.x & 7;
@@ -299,14 +339,26 @@ grad_prepare_kernel(const ParamDesc* __restrict__ descs, const int* __restrict__
       gq[u] = i < end ? grads[d.offset + i] : 0.0f;
       wq[u] = (i < end && d.l2 > 0.0f) ? master[d.offset + i] : 0.0f;
     }
+    // output channel of the round's first element by ONE 32-bit division (a tensor has far fewer than 2^31 elements),
+    // advanced by subtraction for the other three (they lie blockDim.x apart); only BatchNorm-folded layers need it
+    unsigned co = 0, rem = 0;
+    if (d.scale != nullptr) {
+      co = static_cast<unsigned>(i0) / static_cast<unsigned>(k);
+      rem = static_cast<unsigned>(i0) - co * static_cast<unsigned>(k);
+    }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const long long i = i0 + static_cast<long long>(u) * blockDim.x;
       if (i >= end) continue;
       float gv = gq[u] * grad_scale;
-      // 32-bit division: a tensor has far fewer than 2^31 elements (the 64-bit one was a third of this loop)
-      const int co = static_cast<int>(static_cast<unsigned>(i) / static_cast<unsigned>(k));
-      if (d.scale != nullptr) gv *= __ldg(d.scale + co);  // chain rule through the folded BatchNorm scale
+      if (d.scale != nullptr) {
+        gv *= __ldg(d.scale + co);  // chain rule through the folded BatchNorm scale
+        rem += blockDim.x;
+        while (rem >= static_cast<unsigned>(k)) {
+          rem -= static_cast<unsigned>(k);
+          ++co;
+        }
+      }
       if (d.l2 > 0.0f) {
         const float w = wq[u];
         gv += 2.0f * d.l2 * w;
@@ -425,8 +477,8 @@ cudaError_t launch_count_positive(const float* y_true, long long rows, int width
 cudaError_t launch_focal_loss_grad(const float* prob, const float* y_true, __nv_bfloat16* grad, int ld, HeadGeom g,
                                    int batch, int A, int C, float alpha, float gamma, const int* counts, int slot,
                                    double* loss, cudaStream_t st) {
-  const long long total = static_cast<long long>(batch) * g.locs * ((A * C + 1) / 2);
-  if (total >= (1ll << 31)) return cudaErrorInvalidValue;
+  const long long total = static_cast<long long>(batch) * g.locs * ((A * C + 7) / 8);
+  if (total >= (1ll << 31) || ld % 8 != 0) return cudaErrorInvalidValue;
   const unsigned blocks = static_cast<unsigned>(min(static_cast<long long>(148 * 16), (total + 255) / 256));
   focal_loss_grad_kernel<<<blocks, 256, 0, st>>>(prob, y_true, grad, ld, g, batch, A, C, alpha, gamma, counts, slot,
                                                  loss);
@@ -448,6 +500,7 @@ cudaError_t launch_grad_combine(const __nv_bfloat16* a, const __nv_bfloat16* b, 
                                 int n_planes, const __nv_bfloat16* mask, __nv_bfloat16* out, int B, int H, int W, int C,
                                 cudaStream_t st) {
   const long long total = static_cast<long long>(B) * (H + 2) * (W + 2) * (C / 8);
+  if (total >= (1ll << 32) - 256) return cudaErrorInvalidValue;
   grad_combine_kernel<<<blocks_for(total), 256, 0, st>>>(
       reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b), reinterpret_cast<const uint4*>(c),
       reinterpret_cast<const uint4*>(d), dH, dW, reinterpret_cast<const uint4*>(p), pH, pW, n_planes,
