@@ -169,6 +169,12 @@ __device__ __forceinline__ void staged_chunk_row_masked(const ConvParams& p, con
                                                         const float* __restrict__ bsrc, uint8_t* rowp, int row,
                                                         bool interior, bool has_res,
                                                         const __nv_bfloat16* __restrict__ mask_row) {
+  // all eight 16-byte pieces of the mask row are requested before the first is used: left to the compiler the loads
+  // sat inside the loop, one global round trip per piece (the masked 1x1 dgrad layers ran at half the speed of the
+  // forward layers of the same shape)
+  uint4 mk[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) mk[j] = interior ? __ldg(reinterpret_cast<const uint4*>(mask_row + j * 8)) : make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     uint4* sp = reinterpret_cast<uint4*>(rowp + ((j ^ (row & 7)) << 4));
@@ -194,7 +200,7 @@ __device__ __forceinline__ void staged_chunk_row_masked(const ConvParams& p, con
 #pragma unroll
         for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.0f);
       }
-      const uint4 r = __ldg(reinterpret_cast<const uint4*>(mask_row + j * 8));
+      const uint4 r = mk[j];
       if (!(bf16_lo(r.x) > 0.0f)) f[0] = 0.0f;
       if (!(bf16_hi(r.x) > 0.0f)) f[1] = 0.0f;
       if (!(bf16_lo(r.y) > 0.0f)) f[2] = 0.0f;
@@ -774,6 +780,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const ConvSeg& sg = p.seg[tc.seg];
       const int m = tc.row0 + row;
       const RowInfo ri = row_info(sg, m);
+      if (staged && p.mask != nullptr && ri.interior) {
+        // dgrad through a ReLU: this thread's mask row (forward activations, long gone from L2) is read with plain
+        // loads after the accumulator arrives; ask for its lines now, while the tile's MMAs are still running (the
+        // groups split the tile's chunks between them, whichever group consumes a chunk later)
+        const __nv_bfloat16* mrow = p.mask + static_cast<size_t>(m) * p.mask_ld + tc.n0 + g * 64;
+        for (int c = g; c < n_chunks; c += kGroups, mrow += kGroups * 64) prefetch_l2(mrow);
+      }
       mbar_wait(&tmem_full_bar[acc], acc_phase, kFaultTmemFull);
       if (tr_lead) tr(kTrEpilogue + g, 9, tseq, 0);
       tc_fence_after();
