@@ -209,6 +209,48 @@ def test_filter_detections_full_size_sparse_and_dense(cuda_device):
     _check_filter(cuda_device, boxes, b3, cls)
 
 
+def _clustered_dets(seed, B, N, C, n_obj=6):
+    """Scores and boxes shaped like a TRAINED detector's (i.i.d. logits make an easy NMS load): a few objects
+    per image, every candidate near an object scores high for that object's class and regresses to nearly the same
+    box (mutual IoU 0.6-0.95), everything else sits at the background prior. Tie-free."""
+    rng = np.random.default_rng(seed)
+    ctr = rng.uniform(0, 640, (B, N, 2))
+    wh = rng.uniform(16, 120, (B, N, 2))
+    boxes = np.concatenate([ctr - wh / 2, ctr + wh / 2], axis=2)
+    logits = rng.normal(-7.0, 1.0, (B, N, C))
+    for b in range(B):
+        for _ in range(n_obj):
+            oc, ow = rng.uniform(100, 540, 2), rng.uniform(60, 160, 2)
+            cls = int(rng.integers(0, C))
+            near = np.nonzero(np.abs(ctr[b] - oc).max(axis=1) < ow.max() * 0.4)[0]
+            jit = rng.normal(0, 0.04, (near.size, 4)) * np.concatenate([ow, ow])
+            boxes[b, near] = np.concatenate([oc - ow / 2, oc + ow / 2]) + jit
+            logits[b, near, cls] = rng.normal(1.0, 1.0, near.size)
+    cls_p = (1.0 / (1.0 + np.exp(-logits))).astype(np.float32)
+    for b in range(B):
+        flat = cls_p[b].reshape(-1)
+        while np.unique(flat).size != flat.size:
+            _, first = np.unique(flat, return_index=True)
+            dup = np.ones(flat.size, bool)
+            dup[first] = False
+            flat[dup] = np.nextafter(flat[dup], np.float32(1.0)) + rng.uniform(0, 1e-6, dup.sum()).astype(np.float32)
+    b3 = rng.normal(0, 100, (B, N, 16)).astype(np.float32)
+    return boxes.astype(np.float32), b3, cls_p
+
+
+def test_filter_detections_clustered_candidates(cuda_device):
+    """Long suppression chains: hundreds of candidates per object that nearly coincide, so almost every candidate is
+    suppressed by an earlier one of its cluster (the greedy resolve has to walk deep into each 256-chunk)."""
+    boxes, b3, cls = _clustered_dets(9, 2, 20000, 6)
+    ref = _check_filter(cuda_device, boxes, b3, cls)
+    kept = int((ref[3] >= 0).sum())
+    cand = int((cls > 0.05).sum())
+    print("clustered set: %d candidates above 0.05, %d kept after NMS" % (cand, kept))
+    assert cand > 20 * kept > 0
+    _check_filter(cuda_device, boxes, b3, cls, class_specific_filter=False)
+    _check_filter(cuda_device, boxes, b3, cls, nms_threshold=0.3, max_detections=20)
+
+
 def test_filter_detections_edge_cases(cuda_device):
     from pyrapose_b200 import _kernels as K
     import torch

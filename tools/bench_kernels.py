@@ -118,6 +118,35 @@ for tag, mu in (("sparse 2%", -6.0), ("dense 13%", -4.6)):
           note="mask + per-class counts in one pass (memset + 1 launch)", peak=PEAK_READ,
           train=[(lambda x=x: _kernels.score_mask(x, 0.5)) for x in sc_set])
     del sc_set
+# ---- the same filter on scores shaped like a TRAINED detector's (i.i.d. logits are an easy NMS load): six objects per
+# image, every anchor whose centre lies near an object scores high for the object's class and regresses to nearly the
+# object's box, so each class list is a few clusters of nearly coincident boxes with long suppression chains
+def clustered(seed, n_obj=6):
+    gg = torch.Generator(device=dev).manual_seed(seed)
+    r = lambda *shape: torch.rand(*shape, generator=gg, device=dev)      # noqa: E731
+    rn = lambda *shape: torch.randn(*shape, generator=gg, device=dev)    # noqa: E731
+    ctr = (anchors_f32[:, :2] + anchors_f32[:, 2:]) * 0.5                 # (N, 2) anchor centres
+    logits = rn(B, N, C) - 7.0
+    hull_c = anchors_f32.unsqueeze(0).repeat(B, 1, 1).contiguous()
+    for b in range(B):
+        for _ in range(n_obj):
+            oc = r(2) * 440 + 100
+            ow = r(2) * 100 + 60
+            cls_id = int(torch.randint(0, C, (1,), generator=gg, device=dev))
+            near = ((ctr - oc).abs().amax(dim=1) < float(ow.max()) * 0.4).nonzero()[:, 0]
+            box = torch.cat([oc - ow / 2, oc + ow / 2])
+            hull_c[b, near] = box + rn(near.numel(), 4) * 0.04 * torch.cat([ow, ow])
+            logits[b, near, cls_id] = rn(near.numel()) + 1.0
+    return hull_c, torch.sigmoid(logits)
+
+
+hull_c, sc_c = clustered(5)
+boxes3d = _kernels.box3d_transform_inv(anchors_f32, deltas)
+cand = int((sc_c > 0.05).sum())
+kept = int((_kernels.filter_detections(hull_c, boxes3d, sc_c)[3] >= 0).sum())
+timed("filter_detections total [clustered]", lambda: _kernels.filter_detections(hull_c, boxes3d, sc_c), B * N * C * 4,
+      note="trained-detector-like scores: %d candidates above 0.05 in the batch, %d kept after NMS" % (cand, kept))
+del hull_c, sc_c
 # ---- IoU (config 3): B=64 images, K=100 GT boxes, float64
 B3, K = 64, 100
 anchors64 = ua.anchors_for_shape_device((480, 640, 3))
